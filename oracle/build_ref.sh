@@ -1,0 +1,45 @@
+#!/usr/bin/env bash
+# oracle/build_ref.sh — TEST INFRASTRUCTURE. Builds the REAL reference (unmodified pebblelib sources
+# where they lie under /root/reference + the FFTW 3.3.4 tarball the reference vendors) into
+# oracle/_ref/libpebbleref.so. Outputs only under oracle/_ref/ (git-ignored, travels with gpurun).
+# Nothing from /root/reference is copied into the tracked tree.
+set -euo pipefail
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF="${PEBBLE_REFERENCE:-/root/reference}"
+OUT="$HERE/_ref"
+if [ ! -d "$REF/pebblelib" ]; then
+    echo "build_ref: $REF not present (GPU box) — using prebuilt $OUT if any"; exit 0
+fi
+mkdir -p "$OUT/build"
+# 1. FFTW 3.3.4 (the version pebblelib/fftw.h:8 includes), static, PIC, runtime-dispatched SSE2/AVX.
+if [ ! -f "$OUT/fftw/lib/libfftw3.a" ]; then
+    tar xzf "$REF/External Library Source/fftw-3.3.4.tar.gz" -C "$OUT/build"
+    ( cd "$OUT/build/fftw-3.3.4" &&
+      ./configure --prefix="$OUT/fftw" --disable-fortran --enable-sse2 --enable-avx --with-pic \
+                  --disable-shared --enable-static > ../configure.log 2>&1 &&
+      make -j"$(nproc)" > ../make.log 2>&1 && make install > ../install.log 2>&1 )
+fi
+# 2. include layout so that `#include "../fftw-3.3.4/api/fftw3.h"` (fftw.h:8) resolves through -I.
+mkdir -p "$OUT/inc/pebblelib_inc" "$OUT/inc/fftw-3.3.4/api"
+cp "$OUT/fftw/include/fftw3.h" "$OUT/inc/fftw-3.3.4/api/fftw3.h"
+rm -rf "$OUT/build/fftw-3.3.4"
+# 3. the reference sources, compiled in place. -O2 without -march=native: the .so must run on the
+#    GPU box's host CPU too. -ffp-contract=off keeps x86-64 SSE2 double semantics (no FMA fusion).
+SRCS="cpx db windowfunction fft fftw fftcute fastfir downconvert nco mixer fir"
+OBJS=""
+CXXFLAGS="-O2 -fPIC -std=c++14 -w -ffp-contract=off -DUSE_FFTW -DPEBBLELIB_LIBRARY \
+  -I$HERE/qt_shim -I$OUT/inc/pebblelib_inc -I$REF/pebblelib"
+for s in $SRCS; do
+    src="$REF/pebblelib/$s.cpp"
+    if LC_ALL=C grep -q $'[\x80-\xff]' "$src"; then
+        # g++ 13 rejects the typographic quotes/dashes inside `#if 0` prose (db.cpp:70-96): compile a
+        # scratch copy with non-ASCII bytes replaced by '?'. Comment text only; no code is touched.
+        LC_ALL=C sed $'s/[\x80-\xff]/?/g' "$src" > "$OUT/build/$s.ascii.cpp"
+        src="$OUT/build/$s.ascii.cpp"
+    fi
+    g++ $CXXFLAGS -c "$src" -o "$OUT/build/$s.o"
+    OBJS="$OBJS $OUT/build/$s.o"
+done
+g++ $CXXFLAGS -c "$HERE/ref_shim.cpp" -o "$OUT/build/ref_shim.o"
+g++ -shared -o "$OUT/libpebbleref.so" $OBJS "$OUT/build/ref_shim.o" "$OUT/fftw/lib/libfftw3.a" -lm
+echo "build_ref: wrote $OUT/libpebbleref.so"

@@ -1,0 +1,99 @@
+// oracle/ref_shim.cpp — TEST INFRASTRUCTURE ONLY (never linked into the product library).
+//
+// extern "C" wrappers around the UNMODIFIED reference classes compiled from /root/reference/pebblelib
+// (see oracle/build_ref.sh). The resulting oracle/_ref/libpebbleref.so is the real reference, used
+//   * by tests/ to pin the C restatement (oracle/pebble_oracle.c) and to generate tests/golden/*,
+//   * by bench.py's cpu_baseline / --impl reference leg (kind "reference").
+// Nothing here re-implements arithmetic: every function forwards to the reference object.
+#include "cpx.h"
+#include "fft.h"
+#include "fastfir.h"
+#include "downconvert.h"
+#include "fir.h"
+#include "mixer.h"
+#include "windowfunction.h"
+#include <cstring>
+
+// pebblelib_global.h declares this extern; nothing on the hot path dereferences it.
+PebbleLibGlobal *pebbleLibGlobal = nullptr;
+
+extern "C" {
+
+// ---- CFastFIR (pebblelib/fastfir.h:50-77) -------------------------------------------------------
+void *ref_fastfir_create() { return new CFastFIR(); }
+void ref_fastfir_destroy(void *h) { delete (CFastFIR *)h; }
+void ref_fastfir_setup(void *h, double lo, double hi, double offset, double fs) {
+    ((CFastFIR *)h)->SetupParameters(lo, hi, offset, fs);
+}
+int ref_fastfir_process(void *h, int n, const double *in, double *out) {
+    return ((CFastFIR *)h)->ProcessData(n, (CPX *)in, (CPX *)out);
+}
+
+// ---- CDownConvert (pebblelib/downconvert.h:28-37) -------------------------------------------------
+void *ref_downconvert_create() { return new CDownConvert(); }
+void ref_downconvert_destroy(void *h) { delete (CDownConvert *)h; }
+double ref_downconvert_set_data_rate(void *h, double inRate, double maxBW) {
+    return ((CDownConvert *)h)->SetDataRate(inRate, maxBW);
+}
+double ref_downconvert_set_data_rate_simple(void *h, double inRate, double maxBW) {
+    return ((CDownConvert *)h)->SetDataRateSimple(inRate, maxBW);
+}
+void ref_downconvert_set_frequency(void *h, double f) { ((CDownConvert *)h)->SetFrequency(f); }
+void ref_downconvert_set_cw_offset(void *h, double f) { ((CDownConvert *)h)->SetCwOffset(f); }
+// NOTE: the reference clobbers `in` (downconvert.cpp:309-310,325); callers pass a scratch copy.
+int ref_downconvert_process(void *h, int n, double *in, double *out) {
+    return ((CDownConvert *)h)->ProcessData(n, (CPX *)in, (CPX *)out);
+}
+
+// ---- FFT (pebblelib/fft.h:29-62) via FFT::factory (USE_FFTW or USE_FFTCUTE at build time) ----------
+void *ref_fft_create() { return FFT::factory("oracle"); }
+void ref_fft_destroy(void *h) { delete (FFT *)h; }
+void ref_fft_params(void *h, unsigned size, double dbComp, double fs, int samplesPerBuffer, int windowType) {
+    ((FFT *)h)->fftParams(size, dbComp, fs, samplesPerBuffer, (WindowFunction::WINDOWTYPE)windowType);
+}
+int ref_fft_size(void *h) { return ((FFT *)h)->getFFTSize(); }
+void ref_fft_forward(void *h, const double *in, double *out, int n) {
+    ((FFT *)h)->fftForward((CPX *)in, (CPX *)out, n);
+}
+void ref_fft_inverse(void *h, const double *in, double *out, int n) {
+    ((FFT *)h)->fftInverse((CPX *)in, (CPX *)out, n);
+}
+int ref_fft_spectrum(void *h, const double *in, double *out_db, int n) {
+    return ((FFT *)h)->fftSpectrum((CPX *)in, out_db, n) ? 1 : 0;
+}
+
+// ---- WindowFunction (pebblelib/windowfunction.h) --------------------------------------------------
+double ref_window(int type, int n, double *w_out) {
+    WindowFunction w((WindowFunction::WINDOWTYPE)type, n);
+    if (w_out) memcpy(w_out, w.window, sizeof(double) * n);
+    return w.coherentGain;
+}
+
+// ---- CFir (pebblelib/fir.h:31-56) -----------------------------------------------------------------
+void *ref_cfir_create() { return new CFir(); }
+void ref_cfir_destroy(void *h) { delete (CFir *)h; }
+int ref_cfir_init_lp(void *h, int numTaps, double scale, double astop, double fpass, double fstop, double fs) {
+    return ((CFir *)h)->InitLPFilter(numTaps, scale, astop, fpass, fstop, fs);
+}
+int ref_cfir_init_hp(void *h, int numTaps, double scale, double astop, double fpass, double fstop, double fs) {
+    return ((CFir *)h)->InitHPFilter(numTaps, scale, astop, fpass, fstop, fs);
+}
+void ref_cfir_process_cpx(void *h, int n, const double *in, double *out) {
+    ((CFir *)h)->ProcessFilter(n, (CPX *)in, (CPX *)out);
+}
+void ref_cfir_process_real(void *h, int n, const double *in, double *out) {
+    ((CFir *)h)->ProcessFilter(n, (TYPEREAL *)in, (TYPEREAL *)out);
+}
+
+// ---- Mixer (pebblelib/mixer.h) --------------------------------------------------------------------
+void *ref_mixer_create(unsigned fs, unsigned nsamples) { return new Mixer(fs, nsamples); }
+void ref_mixer_destroy(void *h) { delete (Mixer *)h; }
+void ref_mixer_set_frequency(void *h, double f) { ((Mixer *)h)->setFrequency(f); }
+// Returns 1 if the reference returned `in` itself (f==0 pass-through), else 0; result copied to out.
+int ref_mixer_process(void *h, int n, const double *in, double *out) {
+    CPX *r = ((Mixer *)h)->processBlock((CPX *)in);
+    memcpy(out, r, sizeof(CPX) * n);
+    return r == (CPX *)in;
+}
+
+}  // extern "C"
