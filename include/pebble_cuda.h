@@ -1,0 +1,145 @@
+/*
+ * pebble_cuda.h — C ABI of libpebblecuda.so: PebbleSDR's receiver IQ hot path on B200 (sm_100a).
+ *
+ * This is the drop-in boundary. Every entry point replaces one method of a pebblelib /
+ * application operator; the reference interface it replaces is cited as file:line under the
+ * reference tree. Plain pointers and sizes only; no C++/torch types cross this boundary.
+ *
+ * Conventions
+ *   - CPX is std::complex<double> (pebblelib/cpx.h:96): buffers are interleaved re,im doubles, so a
+ *     `double*` of n complex samples holds 2n doubles.
+ *   - `*_process(h, n, in, out)` takes HOST pointers (the reference call shape); the library stages
+ *     through pinned memory on the handle's stream and returns when `out` is valid.
+ *   - `*_process_device(h, n, d_in, d_out, stream)` takes DEVICE pointers and enqueues on `stream`
+ *     (a cudaStream_t passed as void*; NULL = the legacy default stream) without synchronising.
+ *     The returned count is computed on the host (block arithmetic is deterministic).
+ *   - Return values: sample counts are >= 0. Errors are negative: PEBBLE_ERR_*; the text of the last
+ *     error on the calling thread is pebble_last_error(). There is NO CPU fallback: without a
+ *     usable CUDA device every create/process call fails with PEBBLE_ERR_CUDA.
+ *   - One handle = one stream of carried state, not thread-safe (the reference runs one DSP thread
+ *     per receiver). Setters take effect at the next process call.
+ */
+#ifndef PEBBLE_CUDA_H
+#define PEBBLE_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PEBBLE_ERR_ARG (-1)   /* bad argument (NULL handle, n not a multiple the chain requires, ...) */
+#define PEBBLE_ERR_CUDA (-2)  /* CUDA runtime/driver error, or no device */
+#define PEBBLE_ERR_STATE (-3) /* object not configured (e.g. process before SetDataRate) */
+
+/* ---- library / device ------------------------------------------------------------------------- */
+const char *pebble_last_error(void);
+int pebble_abi_version(void);
+int pebble_device_count(void);          /* >=0, or PEBBLE_ERR_CUDA */
+int pebble_set_device(int ordinal);     /* 0 or error; handles bind to the device current at create */
+int pebble_device_synchronize(void);
+/* Number of kernel launches this library has issued in this process (bench.py's gpu_launches). */
+uint64_t pebble_launch_count(void);
+
+/* ---- CFastFIR : overlap-save FFT band-pass ------------------------------------------------------
+ * Replaces pebblelib/fastfir.h:50-77 (class CFastFIR), implementation fastfir.cpp:77-334.
+ * pebble_fastfir_create()         <-> CFastFIR::CFastFIR()              fastfir.cpp:77-145 (2048/1025)
+ * pebble_fastfir_create_sized()   <-> same algorithm with CONV_FFT_SIZE/CONV_FIR_SIZE as parameters
+ *                                     (fastfir.cpp:65-66 are compile-time in the reference; BASELINE
+ *                                     config 5 needs 131072/65537). fir_size must be fft_size/2+1.
+ * pebble_fastfir_setup()          <-> CFastFIR::SetupParameters         fastfir.cpp:191-272
+ *      returns 0 = new filter installed, 1 = unchanged (fastfir.cpp:195-199),
+ *      2 = "Filter Parameter error": old filter kept, new parameters remembered (fastfir.cpp:208-216)
+ * pebble_fastfir_process()        <-> CFastFIR::ProcessData             fastfir.cpp:281-319
+ */
+typedef struct pebble_fastfir pebble_fastfir_t;
+pebble_fastfir_t *pebble_fastfir_create(void);
+pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size);
+void pebble_fastfir_destroy(pebble_fastfir_t *h);
+int pebble_fastfir_setup(pebble_fastfir_t *h, double f_lo, double f_hi, double offset, double sample_rate);
+int pebble_fastfir_process(pebble_fastfir_t *h, int n, const double *in, double *out);
+int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in, double *d_out, void *stream);
+/* Output count a process call with n inputs WOULD return, without running it. */
+int pebble_fastfir_out_count(const pebble_fastfir_t *h, int n);
+/* Carried state = the (fir_size-1)-sample overlap + the partially filled block (m_InBufInPos).
+ * Layout: int64 fill, then (fir_size-1 + fill) CPX. *_state_size returns bytes. */
+int64_t pebble_fastfir_state_size(const pebble_fastfir_t *h);
+int pebble_fastfir_get_state(pebble_fastfir_t *h, void *buf, int64_t bytes);
+int pebble_fastfir_set_state(pebble_fastfir_t *h, const void *buf, int64_t bytes);
+/* Filter spectrum as the reference holds it (natural FFTW bin order), fft_size CPX, host buffer. */
+int pebble_fastfir_get_filter(pebble_fastfir_t *h, double *coef_out);
+
+/* ---- CDownConvert : NCO mix + decimate-by-2 cascade ------------------------------------------------
+ * Replaces pebblelib/downconvert.h:28-37, implementation downconvert.cpp:64-535.
+ * pebble_downconvert_set_data_rate()        <-> CDownConvert::SetDataRate        downconvert.cpp:139-213
+ * pebble_downconvert_set_data_rate_simple() <-> CDownConvert::SetDataRateSimple  downconvert.cpp:220-244
+ * pebble_downconvert_set_frequency()        <-> CDownConvert::SetFrequency       downconvert.cpp:102-113
+ * pebble_downconvert_set_cw_offset()        <-> CDownConvert::SetCwOffset        downconvert.h:34
+ * pebble_downconvert_process()              <-> CDownConvert::ProcessData        downconvert.cpp:257-334
+ *      n must be a multiple of 2^stages. The reference mutates `in` (mix and decimate in place,
+ *      downconvert.cpp:309-310,325); this library leaves `in` untouched (documented deviation F6:
+ *      nothing downstream reads the clobbered buffer, receiver.cpp:908).
+ * The reference's MAX_DECSTAGES=10 leaves no NULL sentinel for a 10-stage chain (downconvert.h:23);
+ * this library allows up to 16 stages.
+ */
+typedef struct pebble_downconvert pebble_downconvert_t;
+pebble_downconvert_t *pebble_downconvert_create(void);
+void pebble_downconvert_destroy(pebble_downconvert_t *h);
+double pebble_downconvert_set_data_rate(pebble_downconvert_t *h, double in_rate, double max_bw);
+double pebble_downconvert_set_data_rate_simple(pebble_downconvert_t *h, double in_rate, double max_bw);
+void pebble_downconvert_set_frequency(pebble_downconvert_t *h, double nco_freq);
+void pebble_downconvert_set_cw_offset(pebble_downconvert_t *h, double offset);
+int pebble_downconvert_num_stages(const pebble_downconvert_t *h);
+/* Stage description for tests: writes up to max entries of the FIR length per stage
+ * (3 = CIC3, 11 = unrolled 11-tap half-band, 15..51 = generic half-band). Returns stage count. */
+int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, int max);
+int pebble_downconvert_process(pebble_downconvert_t *h, int n, const double *in, double *out);
+int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+                                      void *stream);
+int64_t pebble_downconvert_state_size(const pebble_downconvert_t *h);
+int pebble_downconvert_get_state(pebble_downconvert_t *h, void *buf, int64_t bytes);
+int pebble_downconvert_set_state(pebble_downconvert_t *h, const void *buf, int64_t bytes);
+
+/* ---- FFT / SignalSpectrum : windowed FFT, unfold, 2-tap averaged amplitude dB -------------------------
+ * Replaces pebblelib/fft.h:29-62 (class FFT + FFTfftw, fftw.cpp:17-81) and the FFT use of
+ * application/signalspectrum.cpp:54-113.
+ * pebble_fft_params()    <-> FFT::fftParams       fft.cpp:67-118  (size clamped to [2048,65535] there;
+ *                            here: power of two in [2048, 131072], other sizes -> PEBBLE_ERR_ARG)
+ * pebble_fft_forward()   <-> FFTfftw::fftForward  fftw.cpp:31-46  (window applied iff n==samples_per_buffer
+ *                            and window!=NONE, fft.cpp:129-157; zero-padded; natural bin order)
+ * pebble_fft_inverse()   <-> FFTfftw::fftInverse  fftw.cpp:49-67  (unnormalised)
+ * pebble_fft_spectrum()  <-> FFTfftw::fftSpectrum fftw.cpp:70-81 + FFT::calcPowerAverages fft.cpp:324-399
+ *                            returns the overload flag (1/0), writes fft_size doubles (amplitude dB).
+ * pebble_fft_spectrum_batch_device(): `frames` consecutive frames of n samples each; the 2-tap average
+ *                            state is carried frame to frame exactly as successive calls would.
+ * window_type uses WindowFunction::WINDOWTYPE numbering (windowfunction.h): see PEBBLE_WINDOW_*.
+ */
+enum {
+    PEBBLE_WINDOW_RECTANGULAR = 1, PEBBLE_WINDOW_HANNING = 2, PEBBLE_WINDOW_WELCH = 3,
+    PEBBLE_WINDOW_PARZEN = 4, PEBBLE_WINDOW_BARTLETT = 5, PEBBLE_WINDOW_HAMMING = 6,
+    PEBBLE_WINDOW_BLACKMAN2 = 7, PEBBLE_WINDOW_BLACKMAN3 = 8, PEBBLE_WINDOW_BLACKMAN4 = 9,
+    PEBBLE_WINDOW_EXPONENTIAL = 10, PEBBLE_WINDOW_RIEMANN = 11, PEBBLE_WINDOW_BLACKMANHARRIS = 12,
+    PEBBLE_WINDOW_BLACKMAN = 13, PEBBLE_WINDOW_NONE = 14
+};
+typedef struct pebble_fft pebble_fft_t;
+pebble_fft_t *pebble_fft_create(void);
+void pebble_fft_destroy(pebble_fft_t *h);
+int pebble_fft_params(pebble_fft_t *h, unsigned fft_size, double db_compensation, double sample_rate,
+                      int samples_per_buffer, int window_type);
+int pebble_fft_size(const pebble_fft_t *h);
+int pebble_fft_forward(pebble_fft_t *h, const double *in, double *out, int n);
+int pebble_fft_inverse(pebble_fft_t *h, const double *in, double *out, int n);
+int pebble_fft_spectrum(pebble_fft_t *h, const double *in, double *out_db, int n);
+int pebble_fft_spectrum_batch_device(pebble_fft_t *h, int frames, int n, const double *d_in, double *d_out_db,
+                                     int *d_overload_flags, void *stream);
+/* Window table + coherent gain exactly as WindowFunction::regenerate builds them (float-rounded
+ * constants, windowfunction.cpp:51-235). w_out may be NULL. */
+double pebble_window(int window_type, int n, double *w_out);
+/* averaging state (m_fftPower, m_fftAmplitude: 2*fft_size doubles) */
+int pebble_fft_get_state(pebble_fft_t *h, double *buf, int64_t count);
+int pebble_fft_set_state(pebble_fft_t *h, const double *buf, int64_t count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PEBBLE_CUDA_H */

@@ -1,0 +1,144 @@
+"""ctypes binding of oracle/_ref/libpebbleref.so — the UNMODIFIED reference pebblelib + FFTW 3.3.4
+compiled by oracle/build_ref.sh. TEST INFRASTRUCTURE ONLY (checker and CPU baseline)."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PATH = os.path.join(_HERE, "_ref", "libpebbleref.so")
+_vp, _d, _i = ctypes.c_void_p, ctypes.c_double, ctypes.c_int
+
+
+def available():
+    return os.path.exists(PATH)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = ctypes.CDLL(PATH)
+        sig = {
+            "ref_fastfir_create": (_vp, []), "ref_fastfir_destroy": (None, [_vp]),
+            "ref_fastfir_setup": (None, [_vp, _d, _d, _d, _d]), "ref_fastfir_process": (_i, [_vp, _i, _vp, _vp]),
+            "ref_downconvert_create": (_vp, []), "ref_downconvert_destroy": (None, [_vp]),
+            "ref_downconvert_set_data_rate": (_d, [_vp, _d, _d]),
+            "ref_downconvert_set_data_rate_simple": (_d, [_vp, _d, _d]),
+            "ref_downconvert_set_frequency": (None, [_vp, _d]), "ref_downconvert_set_cw_offset": (None, [_vp, _d]),
+            "ref_downconvert_process": (_i, [_vp, _i, _vp, _vp]),
+            "ref_fft_create": (_vp, []), "ref_fft_destroy": (None, [_vp]),
+            "ref_fft_params": (None, [_vp, ctypes.c_uint, _d, _d, _i, _i]), "ref_fft_size": (_i, [_vp]),
+            "ref_fft_forward": (None, [_vp, _vp, _vp, _i]), "ref_fft_inverse": (None, [_vp, _vp, _vp, _i]),
+            "ref_fft_spectrum": (_i, [_vp, _vp, _vp, _i]),
+            "ref_window": (_d, [_i, _i, _vp]),
+            "ref_cfir_create": (_vp, []), "ref_cfir_destroy": (None, [_vp]),
+            "ref_cfir_init_lp": (_i, [_vp, _i, _d, _d, _d, _d, _d]), "ref_cfir_init_hp": (_i, [_vp, _i, _d, _d, _d, _d, _d]),
+            "ref_cfir_process_cpx": (None, [_vp, _i, _vp, _vp]), "ref_cfir_process_real": (None, [_vp, _i, _vp, _vp]),
+            "ref_mixer_create": (_vp, [ctypes.c_uint, ctypes.c_uint]), "ref_mixer_destroy": (None, [_vp]),
+            "ref_mixer_set_frequency": (None, [_vp, _d]), "ref_mixer_process": (_i, [_vp, _i, _vp, _vp]),
+        }
+        for k, (r, a) in sig.items():
+            f = getattr(L, k)
+            f.restype, f.argtypes = r, a
+        _lib = L
+    return _lib
+
+
+class CFastFIR:
+    def __init__(self):
+        self.h = lib().ref_fastfir_create()
+
+    def SetupParameters(self, lo, hi, off, fs):
+        lib().ref_fastfir_setup(self.h, lo, hi, off, fs)
+
+    def ProcessData(self, n, inb, outb):
+        return lib().ref_fastfir_process(self.h, n, inb.ctypes.data, outb.ctypes.data)
+
+    def __del__(self):
+        lib().ref_fastfir_destroy(self.h)
+
+
+class CDownConvert:
+    def __init__(self):
+        self.h = lib().ref_downconvert_create()
+
+    def SetDataRate(self, r, bw):
+        return lib().ref_downconvert_set_data_rate(self.h, r, bw)
+
+    def SetDataRateSimple(self, r, bw):
+        return lib().ref_downconvert_set_data_rate_simple(self.h, r, bw)
+
+    def SetFrequency(self, f):
+        lib().ref_downconvert_set_frequency(self.h, f)
+
+    def SetCwOffset(self, f):
+        lib().ref_downconvert_set_cw_offset(self.h, f)
+
+    def ProcessData(self, n, inb, outb):
+        """The reference clobbers its input (downconvert.cpp:309-310): work on a scratch copy."""
+        scratch = np.array(inb[:n], dtype=np.complex128, copy=True)
+        return lib().ref_downconvert_process(self.h, n, scratch.ctypes.data, outb.ctypes.data)
+
+    def __del__(self):
+        lib().ref_downconvert_destroy(self.h)
+
+
+class FFT:
+    def __init__(self):
+        self.h = lib().ref_fft_create()
+
+    def fftParams(self, size, dbc, fs, spb, wtype):
+        lib().ref_fft_params(self.h, size, dbc, fs, spb, wtype)
+        self.size = lib().ref_fft_size(self.h)
+
+    def fftForward(self, inb, outb, n):
+        lib().ref_fft_forward(self.h, inb.ctypes.data, outb.ctypes.data, n)
+
+    def fftInverse(self, inb, outb, n):
+        lib().ref_fft_inverse(self.h, inb.ctypes.data, outb.ctypes.data, n)
+
+    def fftSpectrum(self, inb, out_db, n):
+        return bool(lib().ref_fft_spectrum(self.h, inb.ctypes.data, out_db.ctypes.data, n))
+
+    def __del__(self):
+        lib().ref_fft_destroy(self.h)
+
+
+class CFir:
+    def __init__(self):
+        self.h = lib().ref_cfir_create()
+
+    def InitLPFilter(self, ntaps, scale, astop, fpass, fstop, fs):
+        return lib().ref_cfir_init_lp(self.h, ntaps, scale, astop, fpass, fstop, fs)
+
+    def ProcessFilter(self, n, inb, outb):
+        lib().ref_cfir_process_cpx(self.h, n, inb.ctypes.data, outb.ctypes.data)
+
+    def __del__(self):
+        lib().ref_cfir_destroy(self.h)
+
+
+class Mixer:
+    def __init__(self, fs, n):
+        self.h = lib().ref_mixer_create(int(fs), int(n))
+        self.n = n
+
+    def setFrequency(self, f):
+        lib().ref_mixer_set_frequency(self.h, f)
+
+    def processBlock(self, inb):
+        out = np.empty(self.n, dtype=np.complex128)
+        lib().ref_mixer_process(self.h, self.n, inb.ctypes.data, out.ctypes.data)
+        return out
+
+    def __del__(self):
+        lib().ref_mixer_destroy(self.h)
+
+
+def window(wtype, n):
+    w = np.empty(n)
+    cg = lib().ref_window(wtype, n, w.ctypes.data)
+    return w, cg

@@ -1,0 +1,6 @@
+"""pebblesdr_b200 — PebbleSDR's receiver IQ hot path (DownConvert -> FastFIR -> demod, SignalSpectrum)
+as hand-written sm_100a CUDA kernels behind a C ABI (include/pebble_cuda.h). The Python classes in
+`ops` mirror the reference's operator surface (same names, arguments and return conventions) so the
+parity tests read like calls into pebblelib; all arithmetic happens in libpebblecuda.so on the GPU."""
+from ._lib import lib, PebbleError, LIB_PATH  # noqa: F401
+from .ops import CFastFIR, CDownConvert  # noqa: F401

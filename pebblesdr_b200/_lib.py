@@ -1,0 +1,73 @@
+"""ctypes binding of libpebblecuda.so (include/pebble_cuda.h). The library is the product; this file only
+declares signatures. There is no Python/CPU fallback: if the shared library is missing, import fails."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpebblecuda.so")
+
+c_int, c_dbl, c_vp, c_i64, c_u64 = ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.c_int64, ctypes.c_uint64
+
+# name -> (restype, argtypes); every symbol include/pebble_cuda.h declares
+SIGNATURES = {
+    "pebble_last_error": (ctypes.c_char_p, []),
+    "pebble_abi_version": (c_int, []),
+    "pebble_device_count": (c_int, []),
+    "pebble_set_device": (c_int, [c_int]),
+    "pebble_device_synchronize": (c_int, []),
+    "pebble_launch_count": (c_u64, []),
+    # CFastFIR
+    "pebble_fastfir_create": (c_vp, []),
+    "pebble_fastfir_create_sized": (c_vp, [c_int, c_int]),
+    "pebble_fastfir_destroy": (None, [c_vp]),
+    "pebble_fastfir_setup": (c_int, [c_vp, c_dbl, c_dbl, c_dbl, c_dbl]),
+    "pebble_fastfir_set_fused_scale": (c_int, [c_vp, c_dbl, c_dbl]),
+    "pebble_fastfir_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_fastfir_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    "pebble_fastfir_out_count": (c_int, [c_vp, c_int]),
+    "pebble_fastfir_state_size": (c_i64, [c_vp]),
+    "pebble_fastfir_get_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_fastfir_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_fastfir_get_filter": (c_int, [c_vp, c_vp]),
+    # CDownConvert
+    "pebble_downconvert_create": (c_vp, []),
+    "pebble_downconvert_destroy": (None, [c_vp]),
+    "pebble_downconvert_set_data_rate": (c_dbl, [c_vp, c_dbl, c_dbl]),
+    "pebble_downconvert_set_data_rate_simple": (c_dbl, [c_vp, c_dbl, c_dbl]),
+    "pebble_downconvert_set_frequency": (None, [c_vp, c_dbl]),
+    "pebble_downconvert_set_cw_offset": (None, [c_vp, c_dbl]),
+    "pebble_downconvert_num_stages": (c_int, [c_vp]),
+    "pebble_downconvert_stage_lengths": (c_int, [c_vp, c_vp, c_int]),
+    "pebble_downconvert_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_downconvert_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    "pebble_downconvert_state_size": (c_i64, [c_vp]),
+    "pebble_downconvert_get_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_downconvert_set_state": (c_int, [c_vp, c_vp, c_i64]),
+}
+
+
+def load(path=LIB_PATH):
+    if not os.path.exists(path):
+        raise ImportError(
+            "pebblesdr_b200: %s is missing. Build it with `python pebblesdr_b200/build.py` "
+            "(nvcc, sm_100a). There is no CPU fallback." % path)
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here == header/library mismatch: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = load()
+
+
+class PebbleError(RuntimeError):
+    pass
+
+
+def check(rc, what=""):
+    """Negative return codes are errors (PEBBLE_ERR_*)."""
+    if rc is None or (isinstance(rc, int) and rc < 0):
+        raise PebbleError("%s failed (%s): %s" % (what, rc, lib.pebble_last_error().decode()))
+    return rc

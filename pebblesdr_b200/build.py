@@ -1,0 +1,72 @@
+"""Builds pebblesdr_b200/libpebblecuda.so in-tree: nvcc (sm_100a) for the kernels + C ABI, g++ for the
+setup-time host code. Also builds the test-only artefacts under oracle/ (the C restatement and, when
+/root/reference is present, the real reference into oracle/_ref) — building the checker is not using it."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libpebblecuda.so")
+CU_SRCS = ["lib_common.cu", "downconvert.cu", "fastfir.cu", "spectrum.cu", "demod.cu", "receiver.cu"]
+CPP_SRCS = ["host_design.cpp", "host_window.cpp", "host_demod.cpp"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def _run(cmd):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + "\n")
+        raise RuntimeError("build failed: " + cmd[0])
+    return r.stdout
+
+
+def build_lib(force=False, verbose=False):
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers.append(os.path.join(ROOT, "include", "pebble_cuda.h"))
+    objs = []
+    for s in CU_SRCS + CPP_SRCS:
+        src = os.path.join(CSRC, s)
+        if not os.path.exists(src):
+            continue
+        obj = os.path.join(objdir, s + ".o")
+        objs.append(obj)
+        if force or _newer(obj, [src] + headers):
+            if s.endswith(".cu"):
+                out = _run(["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj])
+            else:
+                out = _run(["g++", "-O2", "-std=c++17", "-fPIC", "-c", src, "-o", obj])
+            if verbose:
+                print(out)
+    if force or _newer(LIB, objs):
+        _run(["nvcc", "-shared", "-o", LIB] + objs + ["-lquadmath"])
+    return LIB
+
+
+def build_oracle():
+    """C restatement (oracle/libpebbleoracle.so) and, in the build container, the real reference."""
+    odir = os.path.join(ROOT, "oracle")
+    src = os.path.join(odir, "pebble_oracle.c")
+    out = os.path.join(odir, "libpebbleoracle.so")
+    if os.path.exists(src) and _newer(out, [src]):
+        _run(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", out, src, "-lm"])
+    ref = os.path.join(odir, "_ref", "libpebbleref.so")
+    if os.path.isdir("/root/reference/pebblelib") and _newer(
+            ref, [os.path.join(odir, "ref_shim.cpp"), os.path.join(odir, "build_ref.sh")]):
+        _run(["bash", os.path.join(odir, "build_ref.sh")])
+
+
+if __name__ == "__main__":
+    print(build_lib(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    build_oracle()

@@ -1,0 +1,277 @@
+// downconvert.cu — CDownConvert on the GPU: kernel wrapper + C ABI (include/pebble_cuda.h).
+// Kernel body: dc_core.cuh (fused NCO mix + decimate-by-2 cascade, one segment per CTA).
+#include "lib_common.h"
+#include "cta_ctx.cuh"
+#include "dc_core.cuh"
+#include "host_design.h"
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#define DC_HDR_BYTES 128                                     // mbarriers
+#define DC_ST_BYTES (sizeof(DcStage) * PB_DC_MAX_STAGES)     // stage table copy
+
+__global__ void __launch_bounds__(256) dc_fused_kernel(const DcChain *__restrict__ ch, const DcCall call) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    CtaCtx ctx;
+    ctx.mbar = reinterpret_cast<uint64_t *>(smem_raw);
+    DcStage *st = reinterpret_cast<DcStage *>(smem_raw + DC_HDR_BYTES);
+    double *coef = reinterpret_cast<double *>(smem_raw + DC_HDR_BYTES + DC_ST_BYTES);
+    const int S = ch->nstages;
+    for (int i = threadIdx.x; i < S; i += blockDim.x) st[i] = ch->st[i];
+    for (int i = threadIdx.x; i < S * 52; i += blockDim.x) coef[i] = ch->coef[i];
+    const size_t coef_bytes = ((size_t)S * 52 * sizeof(double) + 127) & ~(size_t)127;
+    cpx *buffers = reinterpret_cast<cpx *>(smem_raw + DC_HDR_BYTES + DC_ST_BYTES + coef_bytes);
+    ctx.init();  // includes __syncthreads
+    dc_run_segment(ctx, ch, st, coef, call, buffers, (long long)blockIdx.x);
+}
+
+struct pebble_downconvert {
+    DcChain chain;          // host copy
+    DcChain *d_chain;       // device copy
+    bool dirty;             // host copy newer than device copy
+    cpx *d_state[2];
+    int cur;
+    uint64_t phase_hi, phase_lo;
+    long long stream_pos;
+    // reference members (downconvert.cpp:64-77)
+    double in_rate, max_bw, nco_freq, cw_offset, out_rate;
+    std::vector<int> lens;
+    int threads, chunk, front, group;
+    cudaStream_t stream;    // for the host-pointer entry point
+    pebble::Staging stg;
+};
+
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
+static void dc_update_osc(pebble_downconvert *h) {
+    // downconvert.cpp:108-110
+    double inc = 6.28318530717958647692528676656 * h->nco_freq / h->in_rate;
+    pebble_host::dc_set_osc(h->chain, cos(inc), sin(inc), h->threads);
+    h->dirty = true;
+}
+
+extern "C" {
+
+pebble_downconvert_t *pebble_downconvert_create(void) {
+    pebble_downconvert *h = new pebble_downconvert();
+    memset(&h->chain, 0, sizeof(h->chain));
+    h->d_chain = nullptr;
+    h->d_state[0] = h->d_state[1] = nullptr;
+    h->cur = 0;
+    h->phase_hi = h->phase_lo = 0;   // m_Osc1 = (1,0), downconvert.cpp:75-76
+    h->stream_pos = 0;
+    h->in_rate = 100000.0; h->max_bw = 10000.0; h->nco_freq = 0.0; h->cw_offset = 0.0; h->out_rate = 0.0;
+    h->threads = env_int("PEBBLE_DC_THREADS", 256);
+    h->chunk = env_int("PEBBLE_DC_CHUNK", 1024);
+    h->front = env_int("PEBBLE_DC_FRONT", 3);
+    h->group = env_int("PEBBLE_DC_GROUP", 8);
+    h->stream = nullptr;
+    const size_t sbytes = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX;
+    if (!pebble::cuda_ok(cudaMalloc(&h->d_chain, sizeof(DcChain)), "cudaMalloc(chain)") ||
+        !pebble::cuda_ok(cudaMalloc(&h->d_state[0], sbytes), "cudaMalloc(state)") ||
+        !pebble::cuda_ok(cudaMalloc(&h->d_state[1], sbytes), "cudaMalloc(state)") ||
+        !pebble::cuda_ok(cudaMemset(h->d_state[0], 0, sbytes), "cudaMemset") ||
+        !pebble::cuda_ok(cudaMemset(h->d_state[1], 0, sbytes), "cudaMemset") ||
+        !pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) {
+        pebble_downconvert_destroy(h);
+        return nullptr;
+    }
+    dc_update_osc(h);
+    return h;
+}
+
+void pebble_downconvert_destroy(pebble_downconvert_t *h) {
+    if (!h) return;
+    if (h->d_chain) cudaFree(h->d_chain);
+    if (h->d_state[0]) cudaFree(h->d_state[0]);
+    if (h->d_state[1]) cudaFree(h->d_state[1]);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    h->stg.release();
+    delete h;
+}
+
+static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, bool simple) {
+    if (!h) return 0.0;
+    // downconvert.cpp:143-146 / 224-227: rebuild only when a parameter changed
+    if (h->in_rate != in_rate || h->max_bw != max_bw) {
+        h->in_rate = in_rate;
+        h->max_bw = max_bw;
+        h->out_rate = pebble_host::dc_plan(in_rate, max_bw, simple, h->lens);
+        pebble_host::dc_fill_chain(h->chain, h->lens);
+        // DeleteFilters + new stages: the delay lines restart from zero (downconvert.cpp:150)
+        const size_t sbytes = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX;
+        cudaMemset(h->d_state[0], 0, sbytes);
+        cudaMemset(h->d_state[1], 0, sbytes);
+        // SetFrequency(m_NcoFreq) (downconvert.cpp:210): NOTE it negates the stored value again
+        h->nco_freq = -h->nco_freq + h->cw_offset;
+        dc_update_osc(h);
+    }
+    return h->out_rate;
+}
+double pebble_downconvert_set_data_rate(pebble_downconvert_t *h, double in_rate, double max_bw) {
+    return dc_set_rate(h, in_rate, max_bw, false);
+}
+double pebble_downconvert_set_data_rate_simple(pebble_downconvert_t *h, double in_rate, double max_bw) {
+    return dc_set_rate(h, in_rate, max_bw, true);
+}
+void pebble_downconvert_set_frequency(pebble_downconvert_t *h, double f) {
+    if (!h) return;
+    h->nco_freq = -f + h->cw_offset;  // downconvert.cpp:105-108; phase is NOT reset
+    dc_update_osc(h);
+}
+void pebble_downconvert_set_cw_offset(pebble_downconvert_t *h, double off) {
+    if (h) h->cw_offset = off;  // downconvert.h:34: takes effect at the next SetFrequency
+}
+int pebble_downconvert_num_stages(const pebble_downconvert_t *h) { return h ? h->chain.nstages : PEBBLE_ERR_ARG; }
+int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, int max) {
+    if (!h) return PEBBLE_ERR_ARG;
+    for (int i = 0; i < h->chain.nstages && i < max; ++i) lens[i] = h->chain.st[i].len;
+    return h->chain.nstages;
+}
+
+}  // extern "C"
+
+// Mix only (no decimation stages): out[i] = in[i] * Osc_i. Used for a 0-stage chain
+// (downconvert.cpp:323 loop never runs) and by the Mixer operator (mixer.cpp:48-81).
+__global__ void __launch_bounds__(256) dc_mix_kernel(const DcChain *__restrict__ ch, const cpx *__restrict__ in,
+                                                     cpx *__restrict__ out, long long n, uint64_t phase_hi,
+                                                     uint64_t phase_lo, long long stream_pos) {
+    // each thread: 8 consecutive-in-stride samples (i = base + tid + k*T), one exact seed
+    const int T = blockDim.x;
+    const long long base = (long long)blockIdx.x * T * 8;
+    const long long i0 = base + threadIdx.x;
+    if (i0 >= n) return;
+    const cpx seed = dc_phase_to_osc(dc_phase_at(phase_hi, phase_lo, ch->turn_hi, ch->turn_lo, (uint64_t)(i0 + 1)));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const long long i = i0 + (long long)k * T;
+        if (i < n) {
+            const long long g = stream_pos + i;
+            const double r = g >= PB_DC_RTAB ? ch->r_inf : ch->rtab[g];
+            cpx o = cpx_scale(cpx_mul(seed, ch->wtab[k]), r);
+            out[i] = cpx_mul(in[i], o);
+        }
+    }
+}
+
+extern "C" {
+
+int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+                                      void *stream_v) {
+    if (!h || n < 0 || (n && (!d_in || !d_out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    const int S = h->chain.nstages;
+    if (n & ((1 << S) - 1)) {
+        pebble::set_error("downconvert: n=%d is not a multiple of 2^%d", n, S);
+        return PEBBLE_ERR_ARG;
+    }
+    if (h->dirty) {
+        PB_CUDA(cudaMemcpyAsync(h->d_chain, &h->chain, sizeof(DcChain), cudaMemcpyHostToDevice, stream), PEBBLE_ERR_CUDA);
+        h->dirty = false;
+    }
+    if (S == 0) {
+        if (h->chain.wtab_stride != 256) { pebble::set_error("downconvert: mix kernel needs 256-thread table"); return PEBBLE_ERR_STATE; }
+        const int blocks = (int)((n + 2047) / 2048);
+        dc_mix_kernel<<<blocks, 256, 0, stream>>>(h->d_chain, (const cpx *)d_in, (cpx *)d_out, n, h->phase_hi,
+                                                  h->phase_lo, h->stream_pos);
+        pebble::count_launch();
+    } else {
+        int C = h->chunk;
+        const int g = 1 << S;
+        if (C < g) C = g;
+        if (C % g || C % h->threads || C / h->threads > PB_DC_MAX_WTAB || S > 11) {
+            pebble::set_error("downconvert: unsupported chain/chunk (S=%d C=%d T=%d)", S, C, h->threads);
+            return PEBBLE_ERR_STATE;
+        }
+        DcCall call;
+        call.in = (const cpx *)d_in;
+        call.out = (cpx *)d_out;
+        call.state_in = h->d_state[h->cur];
+        call.state_out = h->d_state[h->cur ^ 1];
+        call.n = n;
+        call.phase_hi = h->phase_hi;
+        call.phase_lo = h->phase_lo;
+        call.stream_pos = h->stream_pos;
+        call.chunk = C;
+        call.front = h->front;
+        call.group = h->group;
+        call.seg_len = n;
+        const DcSmem L = dc_smem_layout(call, S);
+        const size_t coef_bytes = ((size_t)S * 52 * sizeof(double) + 127) & ~(size_t)127;
+        const size_t smem = DC_HDR_BYTES + DC_ST_BYTES + coef_bytes + (size_t)L.total * sizeof(cpx);
+        static size_t smem_set = 0;
+        if (smem > smem_set) {
+            PB_CUDA(cudaFuncSetAttribute(dc_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                    PEBBLE_ERR_CUDA);
+            smem_set = smem;
+        }
+        int occ = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dc_fused_kernel, h->threads, smem);
+        if (occ < 1) occ = 1;
+        // segments: about two waves of resident CTAs, never shorter than 8x the pre-roll or 16 chunks
+        long long min_seg = (long long)h->chain.preroll * 8;
+        if (min_seg < 16LL * C) min_seg = 16LL * C;
+        long long target = (long long)pebble::num_sms() * occ * env_int("PEBBLE_DC_WAVES", 2);
+        long long seg = (n + target - 1) / target;
+        if (seg < min_seg) seg = min_seg;
+        seg = ((seg + C - 1) / C) * C;
+        call.seg_len = seg;
+        const int nseg = (int)((n + seg - 1) / seg);
+        dc_fused_kernel<<<nseg, h->threads, smem, stream>>>(h->d_chain, call);
+        pebble::count_launch();
+    }
+    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    h->cur ^= (S > 0);
+    pebble_host::phase_advance(h->phase_hi, h->phase_lo, h->chain.turn_hi, h->chain.turn_lo, (uint64_t)n);
+    h->stream_pos += n;
+    return n >> S;
+}
+
+int pebble_downconvert_process(pebble_downconvert_t *h, int n, const double *in, double *out) {
+    if (!h || n < 0 || (n && (!in || !out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    const int S = h->chain.nstages;
+    const size_t bi = (size_t)n * sizeof(cpx), bo = (size_t)(n >> S) * sizeof(cpx);
+    if (!h->stg.reserve(bi, bo)) return PEBBLE_ERR_CUDA;
+    memcpy(h->stg.h_in, in, bi);
+    PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
+    int k = pebble_downconvert_process_device(h, n, (const double *)h->stg.d_in, (double *)h->stg.d_out, h->stream);
+    if (k < 0) return k;
+    PB_CUDA(cudaMemcpyAsync(h->stg.h_out, h->stg.d_out, bo, cudaMemcpyDeviceToHost, h->stream), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamSynchronize(h->stream), PEBBLE_ERR_CUDA);
+    memcpy(out, h->stg.h_out, bo);
+    return k;
+}
+
+// state blob: uint64 phase_hi, phase_lo, int64 stream_pos, then nstages * PB_DC_PREFIX cpx
+int64_t pebble_downconvert_state_size(const pebble_downconvert_t *h) {
+    if (!h) return PEBBLE_ERR_ARG;
+    return 24 + (int64_t)sizeof(cpx) * PB_DC_PREFIX * h->chain.nstages;
+}
+int pebble_downconvert_get_state(pebble_downconvert_t *h, void *buf, int64_t bytes) {
+    if (!h || !buf || bytes < pebble_downconvert_state_size(h)) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    uint64_t hdr[3] = {h->phase_hi, h->phase_lo, (uint64_t)h->stream_pos};
+    memcpy(buf, hdr, 24);
+    PB_CUDA(cudaMemcpy((char *)buf + 24, h->d_state[h->cur], sizeof(cpx) * PB_DC_PREFIX * h->chain.nstages,
+                       cudaMemcpyDeviceToHost), PEBBLE_ERR_CUDA);
+    return 0;
+}
+int pebble_downconvert_set_state(pebble_downconvert_t *h, const void *buf, int64_t bytes) {
+    if (!h || !buf || bytes < pebble_downconvert_state_size(h)) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    uint64_t hdr[3];
+    memcpy(hdr, buf, 24);
+    h->phase_hi = hdr[0]; h->phase_lo = hdr[1]; h->stream_pos = (long long)hdr[2];
+    PB_CUDA(cudaMemcpy(h->d_state[h->cur], (const char *)buf + 24, sizeof(cpx) * PB_DC_PREFIX * h->chain.nstages,
+                       cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
+    return 0;
+}
+
+}  // extern "C"

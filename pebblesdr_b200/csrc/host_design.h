@@ -1,0 +1,34 @@
+// host_design.h — control-path (setup-time) computations done on the host in FP64, mirroring the
+// reference's setters: chain planning, oscillator constants, filter design, window tables.
+// These run once per parameter change (the reference runs them on the GUI thread under a mutex);
+// all per-sample work is on the GPU.
+#pragma once
+#include "dc_core.cuh"
+#include <vector>
+
+namespace pebble_host {
+
+// CDownConvert::SetDataRate / SetDataRateSimple (downconvert.cpp:139-244). Returns the output rate
+// and fills `lens` with the FIR length of every stage (3 = CIC3).
+double dc_plan(double in_rate, double max_bw, bool simple, std::vector<int> &lens);
+// Fill the stage table, coefficients and pre-roll of a DcChain from stage lengths.
+void dc_fill_chain(DcChain &ch, const std::vector<int> &lens);
+// Oscillator constants for cos/sin of the NCO increment as the reference rounds them
+// (downconvert.cpp:108-110). `threads` is the CTA size the step table is built for.
+void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads);
+// phase (0.128 turns) += k * turn
+void phase_advance(uint64_t &hi, uint64_t &lo, uint64_t thi, uint64_t tlo, uint64_t k);
+
+// CFastFIR::SetupParameters (fastfir.cpp:191-264) up to, not including, the forward FFT:
+// taps[0..fft_size) = zero-padded, frequency-shifted, 1/fft_size-scaled windowed-sinc.
+// Returns false for the reference's "Filter Parameter error" (fastfir.cpp:208-216).
+bool fastfir_design(int fft_size, int fir_size, double lo, double hi, double offset, double fs,
+                    std::vector<double> &taps_interleaved);
+
+// exp(-j 2 pi m / n), m < n, interleaved (computed in long double, rounded once).
+void twiddle_table(int n, std::vector<double> &tw_interleaved);
+
+// WindowFunction::regenerate (windowfunction.cpp:50-241). Returns coherentGain.
+double window_table(int type, int n, std::vector<double> &w);
+
+}  // namespace pebble_host

@@ -1,0 +1,80 @@
+#include "lib_common.h"
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+namespace pebble {
+static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+bool cuda_ok(cudaError_t e, const char *what) {
+    if (e == cudaSuccess) return true;
+    set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return false;
+}
+void count_launch(int n) { g_launches += (uint64_t)n; }
+int num_sms() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaDeviceProp p;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&p, dev) == cudaSuccess)
+            sms = p.multiProcessorCount;
+        else
+            sms = 148;
+    }
+    return sms;
+}
+bool Staging::reserve(size_t bi, size_t bo) {
+    if (bi > cap_in) {
+        if (h_in) cudaFreeHost(h_in);
+        if (d_in) cudaFree(d_in);
+        h_in = d_in = nullptr; cap_in = 0;
+        if (!cuda_ok(cudaMallocHost(&h_in, bi), "cudaMallocHost(in)")) return false;
+        if (!cuda_ok(cudaMalloc(&d_in, bi), "cudaMalloc(in)")) return false;
+        cap_in = bi;
+    }
+    if (bo > cap_out) {
+        if (h_out) cudaFreeHost(h_out);
+        if (d_out) cudaFree(d_out);
+        h_out = d_out = nullptr; cap_out = 0;
+        if (!cuda_ok(cudaMallocHost(&h_out, bo), "cudaMallocHost(out)")) return false;
+        if (!cuda_ok(cudaMalloc(&d_out, bo), "cudaMalloc(out)")) return false;
+        cap_out = bo;
+    }
+    return true;
+}
+void Staging::release() {
+    if (h_in) cudaFreeHost(h_in);
+    if (h_out) cudaFreeHost(h_out);
+    if (d_in) cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+    h_in = h_out = d_in = d_out = nullptr;
+    cap_in = cap_out = 0;
+}
+}  // namespace pebble
+
+extern "C" {
+const char *pebble_last_error(void) { return pebble::g_err; }
+int pebble_abi_version(void) { return 1; }
+int pebble_device_count(void) {
+    int n = 0;
+    PB_CUDA(cudaGetDeviceCount(&n), PEBBLE_ERR_CUDA);
+    return n;
+}
+int pebble_set_device(int ordinal) {
+    PB_CUDA(cudaSetDevice(ordinal), PEBBLE_ERR_CUDA);
+    return 0;
+}
+int pebble_device_synchronize(void) {
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    return 0;
+}
+uint64_t pebble_launch_count(void) { return pebble::g_launches.load(); }
+}
