@@ -11,7 +11,7 @@
 #define PB_D __device__ __forceinline__
 #else
 #define PB_HD inline
-struct double2 { double x, y; };
+struct alignas(16) double2 { double x, y; };  // same layout as CUDA's vector type
 static inline double2 make_double2(double x, double y) { double2 r; r.x = x; r.y = y; return r; }
 #endif
 
@@ -29,3 +29,4 @@ PB_HD cpx cpx_scale(cpx a, double s) { return make_double2(a.x * s, a.y * s); }
 template <bool INV> PB_HD cpx cpx_mulj(cpx a) {
     return INV ? make_double2(-a.y, a.x) : make_double2(a.y, -a.x);
 }
+static_assert(sizeof(cpx) == 16 && alignof(cpx) == 16, "cpx must match CUDA double2 in host-only translation units");
