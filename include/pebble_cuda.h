@@ -139,6 +139,74 @@ double pebble_window(int window_type, int n, double *w_out);
 int pebble_fft_get_state(pebble_fft_t *h, double *buf, int64_t count);
 int pebble_fft_set_state(pebble_fft_t *h, const double *buf, int64_t count);
 
+/* Library extension (no reference counterpart): scalar gains fused into the FastFIR kernel's load and
+ * store, used by the receiver chain for receiver.cpp:935-938 (gain restore) and AGC_OFF (agc.cpp:86-94). */
+int pebble_fastfir_set_fused_scale(pebble_fastfir_t *h, double in_scale, double out_scale);
+
+/* ---- CFir : Kaiser-windowed time-domain FIR (demod post filters) -------------------------------------
+ * Replaces pebblelib/fir.h:31-56. init_lp/init_hp <-> CFir::InitLPFilter / InitHPFilter (fir.cpp:246-337,
+ * 352-440; return the tap count), init_const <-> CFir::InitConstFir (fir.cpp:203-228),
+ * process <-> CFir::ProcessFilter(int, TYPECPX*, TYPECPX*) (fir.cpp:106-132; I taps on re, Q taps on im). */
+typedef struct pebble_cfir pebble_cfir_t;
+pebble_cfir_t *pebble_cfir_create(void);
+void pebble_cfir_destroy(pebble_cfir_t *h);
+int pebble_cfir_init_lp(pebble_cfir_t *h, int num_taps, double scale, double astop, double fpass, double fstop, double fs);
+int pebble_cfir_init_hp(pebble_cfir_t *h, int num_taps, double scale, double astop, double fpass, double fstop, double fs);
+int pebble_cfir_init_const(pebble_cfir_t *h, int num_taps, const double *icoef, const double *qcoef, double fs);
+int pebble_cfir_get_taps(pebble_cfir_t *h, double *out, int max);
+int pebble_cfir_process(pebble_cfir_t *h, int n, const double *in, double *out);
+int pebble_cfir_process_device(pebble_cfir_t *h, int n, const double *d_in, double *d_out, void *stream);
+
+/* ---- AGC ----------------------------------------------------------------------------------------------
+ * Replaces application/agc.h (class AGC : ProcessStep). mode: 0 AGC_OFF, 1 ACG_FAST, 2 AGC_MED, 3 AGC_SLOW,
+ * 4 AGC_LONG (agc.h:11). set_mode <-> AGC::setAgcMode (agc.cpp:52-82), set_threshold <-> AGC::setAgcThreshold
+ * (agc.cpp:43-50), process <-> AGC::processBlock (agc.cpp:84-207; n replaces the fixed numSamples). */
+typedef struct pebble_agc pebble_agc_t;
+pebble_agc_t *pebble_agc_create(unsigned sample_rate, unsigned buffer_size);
+void pebble_agc_destroy(pebble_agc_t *h);
+int pebble_agc_set_mode(pebble_agc_t *h, int mode, int threshold);
+int pebble_agc_set_threshold(pebble_agc_t *h, int g);
+int pebble_agc_process(pebble_agc_t *h, int n, const double *in, double *out);
+int pebble_agc_process_device(pebble_agc_t *h, int n, const double *d_in, double *d_out, void *stream);
+
+/* ---- Demod -------------------------------------------------------------------------------------------
+ * Replaces application/demod.h Demod::processBlock (demod.cpp:100-141). mode = DeviceInterface::DemodMode
+ * (device_interfaces.h:124-137): 0 dmAM (Demod_AM::processBlockFiltered, demod_am.cpp:40-64), 2 dmFMN
+ * (Demod_NFM::processBlockNCO, demod_nfm.cpp:225-257; variant 1 = processBlockFM2, :124-140),
+ * 5..12 DSB/LSB/USB/CW/DIG/NONE = pass-through (the reference returns `in`; here out is a copy and
+ * pebble_demod_is_passthrough() reports it). 1 dmSAM, 3 dmFMM, 4 dmFMS: PEBBLE_ERR_STATE (out of scope). */
+typedef struct pebble_demod pebble_demod_t;
+pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples);
+void pebble_demod_destroy(pebble_demod_t *h);
+int pebble_demod_set_mode(pebble_demod_t *h, int mode);
+int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant);
+int pebble_demod_set_bandwidth(pebble_demod_t *h, double bandwidth);
+int pebble_demod_is_passthrough(const pebble_demod_t *h);
+int pebble_demod_process(pebble_demod_t *h, int n, const double *in, double *out);
+int pebble_demod_process_device(pebble_demod_t *h, int n, const double *d_in, double *d_out, void *stream);
+
+/* ---- Receiver chain : the non-WFM branch of Receiver::processIQData ------------------------------------
+ * Replaces application/receiver.cpp:903-996: m_downConvert1.ProcessData -> m_sampleBuf re-framing to
+ * framesPerBuffer (:922-931) -> scaleCPX gain restore (:935-938) -> m_bpFilter->process (:950) ->
+ * m_agc->processBlock (:983) -> m_demod->processBlock (:987). Returns the number of demodulated samples
+ * written (a multiple of framesPerBuffer; 0 while a frame is still filling). SignalSpectrum, squelch,
+ * noise filter, modem plugins and the audio resampler are not part of this entry point. */
+typedef struct pebble_receiver pebble_receiver_t;
+pebble_receiver_t *pebble_receiver_create(double sample_rate, int frames_per_buffer);
+void pebble_receiver_destroy(pebble_receiver_t *h);
+double pebble_receiver_set_data_rate(pebble_receiver_t *h, double max_bw);
+void pebble_receiver_set_mixer(pebble_receiver_t *h, double freq);
+int pebble_receiver_set_filter(pebble_receiver_t *h, double lo, double hi);
+int pebble_receiver_set_demod_mode(pebble_receiver_t *h, int mode);
+int pebble_receiver_set_demod_bandwidth(pebble_receiver_t *h, double bandwidth);
+int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold);
+int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages);
+int pebble_receiver_out_count(const pebble_receiver_t *h, int n);
+int pebble_receiver_process(pebble_receiver_t *h, int n, const double *in, double *out);
+int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_in, double *d_out, void *stream);
+/* in/out are page-locked HOST buffers; copies and kernels are enqueued on `stream` without synchronising */
+int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const double *in, double *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

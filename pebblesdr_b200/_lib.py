@@ -43,6 +43,57 @@ SIGNATURES = {
     "pebble_downconvert_state_size": (c_i64, [c_vp]),
     "pebble_downconvert_get_state": (c_int, [c_vp, c_vp, c_i64]),
     "pebble_downconvert_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    # FFT / SignalSpectrum
+    "pebble_fft_create": (c_vp, []),
+    "pebble_fft_destroy": (None, [c_vp]),
+    "pebble_fft_params": (c_int, [c_vp, ctypes.c_uint, c_dbl, c_dbl, c_int, c_int]),
+    "pebble_fft_size": (c_int, [c_vp]),
+    "pebble_fft_forward": (c_int, [c_vp, c_vp, c_vp, c_int]),
+    "pebble_fft_inverse": (c_int, [c_vp, c_vp, c_vp, c_int]),
+    "pebble_fft_spectrum": (c_int, [c_vp, c_vp, c_vp, c_int]),
+    "pebble_fft_spectrum_batch_device": (c_int, [c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "pebble_window": (c_dbl, [c_int, c_int, c_vp]),
+    "pebble_fft_get_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_fft_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    # CFir
+    "pebble_cfir_create": (c_vp, []),
+    "pebble_cfir_destroy": (None, [c_vp]),
+    "pebble_cfir_init_lp": (c_int, [c_vp, c_int, c_dbl, c_dbl, c_dbl, c_dbl, c_dbl]),
+    "pebble_cfir_init_hp": (c_int, [c_vp, c_int, c_dbl, c_dbl, c_dbl, c_dbl, c_dbl]),
+    "pebble_cfir_init_const": (c_int, [c_vp, c_int, c_vp, c_vp, c_dbl]),
+    "pebble_cfir_get_taps": (c_int, [c_vp, c_vp, c_int]),
+    "pebble_cfir_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_cfir_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    # AGC
+    "pebble_agc_create": (c_vp, [ctypes.c_uint, ctypes.c_uint]),
+    "pebble_agc_destroy": (None, [c_vp]),
+    "pebble_agc_set_mode": (c_int, [c_vp, c_int, c_int]),
+    "pebble_agc_set_threshold": (c_int, [c_vp, c_int]),
+    "pebble_agc_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_agc_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    # Demod
+    "pebble_demod_create": (c_vp, [ctypes.c_uint, ctypes.c_uint]),
+    "pebble_demod_destroy": (None, [c_vp]),
+    "pebble_demod_set_mode": (c_int, [c_vp, c_int]),
+    "pebble_demod_set_nfm_variant": (c_int, [c_vp, c_int]),
+    "pebble_demod_set_bandwidth": (c_int, [c_vp, c_dbl]),
+    "pebble_demod_is_passthrough": (c_int, [c_vp]),
+    "pebble_demod_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_demod_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    # Receiver chain
+    "pebble_receiver_create": (c_vp, [c_dbl, c_int]),
+    "pebble_receiver_destroy": (None, [c_vp]),
+    "pebble_receiver_set_data_rate": (c_dbl, [c_vp, c_dbl]),
+    "pebble_receiver_set_mixer": (None, [c_vp, c_dbl]),
+    "pebble_receiver_set_filter": (c_int, [c_vp, c_dbl, c_dbl]),
+    "pebble_receiver_set_demod_mode": (c_int, [c_vp, c_int]),
+    "pebble_receiver_set_demod_bandwidth": (c_int, [c_vp, c_dbl]),
+    "pebble_receiver_set_agc": (c_int, [c_vp, c_int, c_int]),
+    "pebble_receiver_set_gain_stages": (c_int, [c_vp, c_int]),
+    "pebble_receiver_out_count": (c_int, [c_vp, c_int]),
+    "pebble_receiver_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_receiver_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    "pebble_receiver_process_pinned": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
 }
 
 

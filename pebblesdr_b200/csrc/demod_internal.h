@@ -1,0 +1,28 @@
+// demod_internal.h — handle layouts shared between demod.cu and receiver.cu (library-internal).
+#pragma once
+#include "lib_common.h"
+#include "common.cuh"
+#include "host_design.h"
+
+struct pebble_cfir {
+    int ntaps = 0;
+    double fs = 0.0;
+    double hI[75], hQ[75];
+    double *d_hI = nullptr, *d_hQ = nullptr;
+    cpx *d_hist[2] = {nullptr, nullptr};
+    int cur = 0;
+    cudaStream_t stream = nullptr;
+    pebble::Staging stg;
+};
+int cfir_alloc(pebble_cfir *f);
+void cfir_release(pebble_cfir *f);
+int cfir_upload(pebble_cfir *f);   // after hI/hQ/ntaps changed: uploads taps and zeroes the history
+int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStream_t st);
+
+struct pebble_agc;
+struct pebble_demod;
+// device-pointer forms used by the fused receiver chain
+int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough);
+int agc_run_device(pebble_agc *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st);
+double agc_manual_gain(const pebble_agc *h);
+int agc_is_off(const pebble_agc *h);

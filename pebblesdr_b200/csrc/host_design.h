@@ -32,3 +32,19 @@ void twiddle_table(int n, std::vector<double> &tw_interleaved);
 double window_table(int type, int n, std::vector<double> &w);
 
 }  // namespace pebble_host
+
+namespace pebble_host {
+// CFir::InitLPFilter / InitHPFilter (fir.cpp:246-337, 352-440): Kaiser-windowed sinc, taps clamped to
+// [3,75] (LP) / [3,74]|1 (HP). Returns the tap count and fills coef[0..ntaps).
+int cfir_design_lp(int num_taps, double scale, double astop, double fpass, double fstop, double fs, double *coef);
+int cfir_design_hp(int num_taps, double scale, double astop, double fpass, double fstop, double fs, double *coef);
+
+// AGC::setParameters (application/agc.cpp:237-309) for the non-OFF modes.
+struct AgcParams {
+    int use_hang;
+    double knee, gain_slope, fixed_gain;
+    double attack_rise, attack_fall, decay_rise, decay_fall;
+    int hang_time, delay_samples, window_samples;
+};
+void agc_params(double sample_rate, bool use_hang, int threshold, int slope_factor, int decay_ms, AgcParams &p);
+}  // namespace pebble_host

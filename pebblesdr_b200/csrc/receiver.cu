@@ -1,0 +1,199 @@
+// receiver.cu — the non-WFM branch of Receiver::processIQData (application/receiver.cpp:903-996) as one
+// device-resident chain: CDownConvert -> re-framing to framesPerBuffer -> gain restore -> BandPassFilter
+// (CFastFIR) -> AGC -> Demod. Every step is the same GPU operator the stand-alone C ABI exposes; the
+// chain only owns the intermediate device buffers and fuses the two scalar gains into the FastFIR kernel.
+#include "lib_common.h"
+#include "common.cuh"
+#include "demod_internal.h"
+#include <cmath>
+#include <cstring>
+
+struct pebble_receiver {
+    double sample_rate = 0, demod_rate = 0;
+    int fpb = 2048;                // framesPerBuffer (settings.cpp:57)
+    pebble_downconvert_t *dc = nullptr;
+    pebble_fastfir_t *bp = nullptr;
+    pebble_agc *agc = nullptr;
+    pebble_demod *demod = nullptr;
+    int gain_stages = -1;          // -1: use the CDownConvert stage count
+    cpx *d_frames = nullptr; size_t frames_cap = 0;   // m_sampleBuf: decimated samples waiting for a full frame
+    int fill = 0;                                      // m_sampleBufLen
+    cpx *d_bp = nullptr, *d_agc = nullptr; size_t work_cap = 0;
+    void *d_pin_in = nullptr, *d_pin_out = nullptr; size_t pin_in_cap = 0, pin_out_cap = 0;
+    cudaStream_t stream = nullptr;
+    pebble::Staging stg;
+};
+
+static int rx_reserve(pebble_receiver *h, size_t dec_total) {
+    if (dec_total > h->frames_cap) {
+        cpx *nb = nullptr;
+        PB_CUDA(cudaMalloc(&nb, sizeof(cpx) * dec_total), PEBBLE_ERR_CUDA);
+        if (h->d_frames) {
+            PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+            PB_CUDA(cudaMemcpy(nb, h->d_frames, sizeof(cpx) * (size_t)h->fill, cudaMemcpyDeviceToDevice), PEBBLE_ERR_CUDA);
+            cudaFree(h->d_frames);
+        }
+        h->d_frames = nb;
+        h->frames_cap = dec_total;
+    }
+    if (dec_total > h->work_cap) {
+        PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+        cudaFree(h->d_bp); cudaFree(h->d_agc);
+        h->d_bp = h->d_agc = nullptr; h->work_cap = 0;
+        PB_CUDA(cudaMalloc(&h->d_bp, sizeof(cpx) * dec_total), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaMalloc(&h->d_agc, sizeof(cpx) * dec_total), PEBBLE_ERR_CUDA);
+        h->work_cap = dec_total;
+    }
+    return 0;
+}
+
+extern "C" {
+
+pebble_receiver_t *pebble_receiver_create(double sample_rate, int frames_per_buffer) {
+    if (frames_per_buffer <= 0 || frames_per_buffer % 1024) {
+        pebble::set_error("receiver: framesPerBuffer must be a positive multiple of 1024");
+        return nullptr;
+    }
+    pebble_receiver *h = new pebble_receiver();
+    h->sample_rate = sample_rate; h->fpb = frames_per_buffer;
+    h->dc = pebble_downconvert_create();
+    h->bp = pebble_fastfir_create();
+    if (!h->dc || !h->bp || !pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) {
+        pebble_receiver_destroy(h);
+        return nullptr;
+    }
+    h->demod_rate = sample_rate;
+    return h;
+}
+void pebble_receiver_destroy(pebble_receiver_t *h) {
+    if (!h) return;
+    if (h->dc) pebble_downconvert_destroy(h->dc);
+    if (h->bp) pebble_fastfir_destroy(h->bp);
+    if (h->agc) pebble_agc_destroy(h->agc);
+    if (h->demod) pebble_demod_destroy(h->demod);
+    cudaFree(h->d_frames); cudaFree(h->d_bp); cudaFree(h->d_agc); cudaFree(h->d_pin_in); cudaFree(h->d_pin_out);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    h->stg.release();
+    delete h;
+}
+// m_downConvert1.SetDataRate(sampleRate, maxBW) -> demod sample rate; (re)creates AGC and Demod at that rate
+double pebble_receiver_set_data_rate(pebble_receiver_t *h, double max_bw) {
+    if (!h) return 0.0;
+    h->demod_rate = pebble_downconvert_set_data_rate(h->dc, h->sample_rate, max_bw);
+    if (h->agc) pebble_agc_destroy(h->agc);
+    if (h->demod) pebble_demod_destroy(h->demod);
+    h->agc = pebble_agc_create((unsigned)h->demod_rate, (unsigned)h->fpb);
+    h->demod = pebble_demod_create((unsigned)h->demod_rate, (unsigned)h->fpb);
+    h->fill = 0;
+    return (h->agc && h->demod) ? h->demod_rate : 0.0;
+}
+void pebble_receiver_set_mixer(pebble_receiver_t *h, double freq) { if (h) pebble_downconvert_set_frequency(h->dc, freq); }
+int pebble_receiver_set_filter(pebble_receiver_t *h, double lo, double hi) {  // BandPassFilter::setBandPass, bandpassfilter.cpp:35-45
+    if (!h) return PEBBLE_ERR_ARG;
+    return pebble_fastfir_setup(h->bp, lo, hi, 0, h->demod_rate);
+}
+int pebble_receiver_set_demod_mode(pebble_receiver_t *h, int mode) {
+    if (!h || !h->demod) return PEBBLE_ERR_STATE;
+    return pebble_demod_set_mode(h->demod, mode);
+}
+int pebble_receiver_set_demod_bandwidth(pebble_receiver_t *h, double bw) {
+    if (!h || !h->demod) return PEBBLE_ERR_STATE;
+    return pebble_demod_set_bandwidth(h->demod, bw);
+}
+int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold) {
+    if (!h || !h->agc) return PEBBLE_ERR_STATE;
+    return pebble_agc_set_mode(h->agc, mode, threshold);
+}
+int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages) {
+    if (!h) return PEBBLE_ERR_ARG;
+    h->gain_stages = stages;
+    return 0;
+}
+int pebble_receiver_out_count(const pebble_receiver_t *h, int n) {
+    if (!h || n < 0) return PEBBLE_ERR_ARG;
+    const int S = pebble_downconvert_num_stages(h->dc);
+    return (int)((((long long)h->fill + (n >> S)) / h->fpb) * h->fpb);
+}
+
+int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_in, double *d_out, void *stream_v) {
+    if (!h || n < 0 || (n && !d_in)) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
+    if (!h->agc || !h->demod) { pebble::set_error("receiver: set_data_rate not called"); return PEBBLE_ERR_STATE; }
+    if (n == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream_v;
+    const int S = pebble_downconvert_num_stages(h->dc);
+    const int ndec = n >> S;
+    int r = rx_reserve(h, (size_t)h->fill + (size_t)ndec);
+    if (r < 0) return r;
+    // receiver.cpp:908 + 922-924: decimated samples are appended to m_sampleBuf
+    r = pebble_downconvert_process_device(h->dc, n, d_in, (double *)(h->d_frames + h->fill), st);
+    if (r < 0) return r;
+    const int total = h->fill + ndec;
+    const int nframes = total / h->fpb;
+    const int nproc = nframes * h->fpb;
+    if (nframes == 0) { h->fill = total; return 0; }  // receiver.cpp:927-928
+    if (!d_out) { pebble::set_error("receiver: NULL output"); return PEBBLE_ERR_ARG; }
+    // receiver.cpp:935-938: restore decimation gain, 2 dB per stage
+    const int gs = h->gain_stages >= 0 ? h->gain_stages : S;
+    const double gain = pow(10, (gs * 2) / 20.0);
+    const bool fuse_agc = agc_is_off(h->agc);
+    pebble_fastfir_set_fused_scale(h->bp, gain, fuse_agc ? agc_manual_gain(h->agc) : 1.0);
+    r = pebble_fastfir_process_device(h->bp, nproc, (const double *)h->d_frames, (double *)h->d_bp, st);  // receiver.cpp:950
+    if (r < 0) return r;
+    if (r != nproc) { pebble::set_error("receiver: FastFIR returned %d of %d", r, nproc); return PEBBLE_ERR_STATE; }
+    const cpx *next = h->d_bp;
+    if (!fuse_agc) {  // receiver.cpp:983
+        r = agc_run_device(h->agc, nproc, next, h->d_agc, st);
+        if (r < 0) return r;
+        next = h->d_agc;
+    }
+    r = demod_run_device(h->demod, nproc, next, (cpx *)d_out, st, nullptr);  // receiver.cpp:987
+    if (r < 0) return r;
+    // keep the incomplete frame for the next call
+    const int rem = total - nproc;
+    if (rem > 0)
+        PB_CUDA(cudaMemcpyAsync(h->d_frames, h->d_frames + nproc, sizeof(cpx) * (size_t)rem, cudaMemcpyDeviceToDevice, st), PEBBLE_ERR_CUDA);
+    h->fill = rem;
+    return nproc;
+}
+
+int pebble_receiver_process(pebble_receiver_t *h, int n, const double *in, double *out) {
+    if (!h || n < 0 || (n && !in)) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    const int k = pebble_receiver_out_count(h, n);
+    const size_t bi = sizeof(cpx) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
+    if (!h->stg.reserve(bi, bo)) return PEBBLE_ERR_CUDA;
+    memcpy(h->stg.h_in, in, bi);
+    PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
+    int r = pebble_receiver_process_device(h, n, (const double *)h->stg.d_in, (double *)h->stg.d_out, h->stream);
+    if (r < 0) return r;
+    if (r > 0) PB_CUDA(cudaMemcpyAsync(h->stg.h_out, h->stg.d_out, sizeof(cpx) * (size_t)r, cudaMemcpyDeviceToHost, h->stream), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamSynchronize(h->stream), PEBBLE_ERR_CUDA);
+    if (r > 0 && out) memcpy(out, h->stg.h_out, sizeof(cpx) * (size_t)r);
+    return r;
+}
+// Pinned-buffer form for end-to-end timing: `in`/`out` must be page-locked host memory (no extra memcpy).
+int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const double *in, double *out, void *stream_v) {
+    if (!h || n <= 0 || !in) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream_v;
+    const int k = pebble_receiver_out_count(h, n);
+    const size_t bi = sizeof(cpx) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
+    if (bi > h->pin_in_cap) {
+        PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+        cudaFree(h->d_pin_in); h->d_pin_in = nullptr; h->pin_in_cap = 0;
+        PB_CUDA(cudaMalloc(&h->d_pin_in, bi), PEBBLE_ERR_CUDA);
+        h->pin_in_cap = bi;
+    }
+    if (bo > h->pin_out_cap) {
+        PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+        cudaFree(h->d_pin_out); h->d_pin_out = nullptr; h->pin_out_cap = 0;
+        PB_CUDA(cudaMalloc(&h->d_pin_out, bo), PEBBLE_ERR_CUDA);
+        h->pin_out_cap = bo;
+    }
+    PB_CUDA(cudaMemcpyAsync(h->d_pin_in, in, bi, cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
+    int r = pebble_receiver_process_device(h, n, (const double *)h->d_pin_in, (double *)h->d_pin_out, st);
+    if (r < 0) return r;
+    if (r > 0 && out) PB_CUDA(cudaMemcpyAsync(out, h->d_pin_out, sizeof(cpx) * (size_t)r, cudaMemcpyDeviceToHost, st), PEBBLE_ERR_CUDA);
+    return r;
+}
+
+}  // extern "C"

@@ -1,0 +1,319 @@
+// spectrum.cu — the FFT operator (pebblelib/fft.h:29-62, fftw.cpp:17-81) and the SignalSpectrum hot
+// path (application/signalspectrum.cpp:63-113 -> FFT::fftSpectrum) on the GPU.
+// One CTA per frame: window x input (+ overload flag) -> shared memory -> in-place FP64 FFT -> unfold
+// (fftshift) -> |X|/coherentGain/maxBinPower -> 2-tap average with the previous frame's UNAVERAGED value
+// (finding F14) -> 20*log10 -> clip [-120, 0]. In a batch a CTA walks a run of consecutive frames and
+// keeps the previous frame's amplitudes in registers; the first frame of a run recomputes its
+// predecessor (one extra FFT per run) instead of exchanging data with the neighbouring CTA.
+#include "lib_common.h"
+#include "fft_kernels.cuh"
+#include "host_design.h"
+#include <cstring>
+#include <vector>
+
+template <int N>
+__device__ __forceinline__ bool spec_load_frame(cpx *a, const cpx *__restrict__ in, int n, const double *__restrict__ win,
+                                                bool windowed, double over_limit) {
+    constexpr int SH = FftPlan<N>::SH;
+    int over = 0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+        cpx v = cpx_make(0.0, 0.0);
+        if (i < n) {
+            v = in[i];
+            if (windowed) {
+                // fft.cpp:136-142: overload test on the raw sample, then in[i] * windowCpx[i] (= (w, 0))
+                if (fabs(v.x) > over_limit || fabs(v.y) > over_limit) over = 1;
+                v = cpx_scale(v, win[i]);
+            }
+        }
+        a[fft_swz<SH>(i)] = v;
+    }
+    return __syncthreads_or(over) != 0;  // also the barrier that completes a[]
+}
+
+// amplitude (already / coherentGain / maxBinPower) of unfolded bin j
+template <int N> __device__ __forceinline__ double spec_asd(const cpx *a, int j, double cg, double maxbin) {
+    const int f = (j + N / 2) & (N - 1);  // m_unfoldInOrder, fft.cpp:183-225
+    const cpx X = a[fft_swz<FftPlan<N>::SH>(FftPlan<N>::freq2pos(f))];
+    double asd = sqrt(X.x * X.x + X.y * X.y) / cg;  // DB::amplitude / coherentGain, fft.cpp:350
+    return asd / maxbin;                           // fft.cpp:358
+}
+
+template <int N>
+__global__ void __launch_bounds__(FftPlan<N>::THREADS)
+spectrum_kernel(const cpx *__restrict__ in, int frames, int n, const double *__restrict__ win, int windowed,
+                double cg, double maxbin, double over_limit, const double *__restrict__ prev_in,
+                double *__restrict__ prev_out, const int *__restrict__ flag_in, int *__restrict__ flag_out,
+                double *__restrict__ out_db, int *__restrict__ out_flags, int run, const cpx *__restrict__ tw) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cpx *a = reinterpret_cast<cpx *>(smem_raw);
+    constexpr int T = FftPlan<N>::THREADS;
+    constexpr int PER = N / T;
+    double prev[PER];
+    const int f0 = blockIdx.x * run;
+    int f1 = f0 + run;
+    if (f1 > frames) f1 = frames;
+    const int carried_flag = *flag_in;
+    if (f0 == 0) {
+#pragma unroll
+        for (int k = 0; k < PER; ++k) prev[k] = prev_in[threadIdx.x + k * T];
+    } else {
+        // pre-roll: unaveraged amplitudes of frame f0-1
+        spec_load_frame<N>(a, in + (long long)(f0 - 1) * n, n, win, windowed != 0, over_limit);
+        fft_forward_smem<N>(a, tw);
+#pragma unroll
+        for (int k = 0; k < PER; ++k) prev[k] = spec_asd<N>(a, threadIdx.x + k * T, cg, maxbin);
+        __syncthreads();
+    }
+    for (int f = f0; f < f1; ++f) {
+        const bool over = spec_load_frame<N>(a, in + (long long)f * n, n, win, windowed != 0, over_limit);
+        fft_forward_smem<N>(a, tw);
+        double *o = out_db + (long long)f * N;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const int j = threadIdx.x + k * T;
+            const double asd = spec_asd<N>(a, j, cg, maxbin);
+            const double bin = (asd + prev[k]) / 2;   // fft.cpp:380 (m_isAveraged is always true, fft.cpp:103)
+            prev[k] = asd;                            // fft.cpp:388: keep the UNAVERAGED value
+            double db = bin == 0 ? -120.0 : 20 * log10(bin);  // DB::amplitudeTodB, db.h:44-48
+            db = fmax(-120.0, fmin(0.0, db));                 // DB::clip, db.h:24-26
+            o[j] = db;
+        }
+        if (threadIdx.x == 0) {
+            const int fl = windowed ? (over ? 1 : 0) : carried_flag;
+            if (out_flags) out_flags[f] = fl;
+            if (f == frames - 1) *flag_out = fl;
+        }
+        __syncthreads();
+    }
+    if (f1 == frames && f0 < f1) {
+#pragma unroll
+        for (int k = 0; k < PER; ++k) prev_out[threadIdx.x + k * T] = prev[k];
+    }
+}
+
+// plain transforms with natural (FFTW) bin order at the interface
+template <int N, bool INV>
+__global__ void __launch_bounds__(FftPlan<N>::THREADS)
+fft_c2c_kernel(const cpx *__restrict__ in, int n, const double *__restrict__ win, int windowed, double over_limit,
+               cpx *__restrict__ out, const int *__restrict__ flag_in, int *__restrict__ flag_out,
+               const cpx *__restrict__ tw) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cpx *a = reinterpret_cast<cpx *>(smem_raw);
+    constexpr int SH = FftPlan<N>::SH;
+    if (!INV) {
+        const bool over = spec_load_frame<N>(a, in, n, win, windowed != 0, over_limit);
+        if (threadIdx.x == 0) *flag_out = windowed ? (over ? 1 : 0) : *flag_in;
+        fft_forward_smem<N>(a, tw);
+        for (int f = threadIdx.x; f < N; f += blockDim.x) out[f] = a[fft_swz<SH>(FftPlan<N>::freq2pos(f))];
+    } else {
+        // fftw.cpp:55-60: bins beyond numSamples are zero
+        for (int f = threadIdx.x; f < N; f += blockDim.x)
+            a[fft_swz<SH>(FftPlan<N>::freq2pos(f))] = f < n ? in[f] : cpx_make(0.0, 0.0);
+        __syncthreads();
+        fft_inverse_smem<N>(a, tw);
+        for (int i = threadIdx.x; i < N; i += blockDim.x) out[i] = a[fft_swz<SH>(i)];
+    }
+}
+
+struct pebble_fft {
+    int N = 0, spb = 0, wtype = 14;
+    double cg = 1.0, maxbin = 1.0, fs = 0.0;
+    bool params_set = false;
+    cpx *d_tw = nullptr;
+    double *d_win = nullptr;
+    double *d_prev[2] = {nullptr, nullptr};   // unaveraged amplitudes of the last frame (m_fftAmplitude)
+    int *d_flag[2] = {nullptr, nullptr};      // m_isOverload
+    int cur = 0;
+    cudaStream_t stream = nullptr;
+    pebble::Staging stg;
+    int *h_flag = nullptr;                    // pinned
+};
+
+static void fft_free(pebble_fft *h) {
+    cudaFree(h->d_tw); cudaFree(h->d_win); cudaFree(h->d_prev[0]); cudaFree(h->d_prev[1]);
+    cudaFree(h->d_flag[0]); cudaFree(h->d_flag[1]);
+    h->d_tw = nullptr; h->d_win = nullptr; h->d_prev[0] = h->d_prev[1] = nullptr; h->d_flag[0] = h->d_flag[1] = nullptr;
+}
+
+template <int N> static cudaError_t spec_launch(pebble_fft *h, int frames, int n, const cpx *in, double *out, int *flags,
+                                                cudaStream_t st) {
+    const size_t smem = sizeof(cpx) * N;
+    cudaError_t e = cudaFuncSetAttribute(spectrum_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spectrum_kernel<N>, FftPlan<N>::THREADS, smem);
+    if (occ < 1) occ = 1;
+    // runs of consecutive frames per CTA: >= 8 frames (pre-roll <= 12.5 %) once there is enough work
+    int target = pebble::num_sms() * occ * 2;
+    int run = (frames + target - 1) / target;
+    if (run < 8) run = 8;
+    if (run > frames) run = frames;
+    const int grid = (frames + run - 1) / run;
+    const bool windowed = h->wtype != PEBBLE_WINDOW_NONE && n == h->spb;
+    spectrum_kernel<N><<<grid, FftPlan<N>::THREADS, smem, st>>>(in, frames, n, h->d_win, windowed ? 1 : 0, h->cg, h->maxbin, 0.9,
+                                                               h->d_prev[h->cur], h->d_prev[h->cur ^ 1], h->d_flag[h->cur],
+                                                               h->d_flag[h->cur ^ 1], out, flags, run, h->d_tw);
+    pebble::count_launch();
+    return cudaGetLastError();
+}
+template <int N, bool INV> static cudaError_t c2c_launch(pebble_fft *h, int n, const cpx *in, cpx *out, cudaStream_t st) {
+    const size_t smem = sizeof(cpx) * N;
+    cudaError_t e = cudaFuncSetAttribute(fft_c2c_kernel<N, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const bool windowed = !INV && h->wtype != PEBBLE_WINDOW_NONE && n == h->spb;
+    fft_c2c_kernel<N, INV><<<1, FftPlan<N>::THREADS, smem, st>>>(in, n, h->d_win, windowed ? 1 : 0, 0.9, out, h->d_flag[h->cur],
+                                                                h->d_flag[h->cur ^ 1], h->d_tw);
+    pebble::count_launch();
+    return cudaGetLastError();
+}
+
+#define FFT_DISPATCH(h, X) ((h)->N == 2048 ? X(2048) : (h)->N == 4096 ? X(4096) : X(8192))
+
+extern "C" {
+
+pebble_fft_t *pebble_fft_create(void) {
+    pebble_fft *h = new pebble_fft();
+    if (!pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !pebble::cuda_ok(cudaMallocHost(&h->h_flag, sizeof(int)), "cudaMallocHost")) {
+        delete h;
+        return nullptr;
+    }
+    return h;
+}
+void pebble_fft_destroy(pebble_fft_t *h) {
+    if (!h) return;
+    fft_free(h);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->h_flag) cudaFreeHost(h->h_flag);
+    h->stg.release();
+    delete h;
+}
+
+int pebble_fft_params(pebble_fft_t *h, unsigned fft_size, double db_comp, double fs, int spb, int wtype) {
+    (void)db_comp;  // unused by the reference too (fft.cpp:70)
+    if (!h) return PEBBLE_ERR_ARG;
+    if (fft_size == 0) return 0;  // fft.cpp:72-73: silently ignored
+    // fft.cpp:74-79 clamps to [2048, 65535]; this build implements the power-of-two sizes below
+    if (fft_size < 2048) fft_size = 2048;
+    if (fft_size != 2048 && fft_size != 4096 && fft_size != 8192) {
+        pebble::set_error("fft: size %u not supported (2048, 4096, 8192)", fft_size);
+        return PEBBLE_ERR_ARG;
+    }
+    if (spb <= 0 || spb > (int)fft_size || wtype == PEBBLE_WINDOW_BLACKMAN || wtype < 1 || wtype > 14) {
+        pebble::set_error("fft: bad samples_per_buffer/window (BLACKMAN reads uninitialised memory in the reference)");
+        return PEBBLE_ERR_ARG;
+    }
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    fft_free(h);
+    h->N = (int)fft_size; h->spb = spb; h->wtype = wtype; h->fs = fs;
+    h->maxbin = 1.0 * spb;  // m_maxBinPower = m_ampMax * m_samplesPerBuffer, fft.cpp:84
+    std::vector<double> tw, win;
+    pebble_host::twiddle_table(h->N, tw);
+    // WindowFunction(NONE) leaves coherentGain uninitialised in the reference; 1.0 is used here
+    h->cg = wtype == PEBBLE_WINDOW_NONE ? 1.0 : pebble_host::window_table(wtype, spb, win);
+    if (win.empty()) win.assign((size_t)spb, 1.0);
+    const size_t nb = sizeof(cpx) * (size_t)h->N;
+    PB_CUDA(cudaMalloc(&h->d_tw, nb), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMalloc(&h->d_win, sizeof(double) * (size_t)spb), PEBBLE_ERR_CUDA);
+    for (int b = 0; b < 2; ++b) {
+        PB_CUDA(cudaMalloc(&h->d_prev[b], sizeof(double) * (size_t)h->N), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaMemset(h->d_prev[b], 0, sizeof(double) * (size_t)h->N), PEBBLE_ERR_CUDA);  // reference: new double[] (uninitialised)
+        PB_CUDA(cudaMalloc(&h->d_flag[b], sizeof(int)), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaMemset(h->d_flag[b], 0, sizeof(int)), PEBBLE_ERR_CUDA);  // m_isOverload = false, fft.cpp:26
+    }
+    PB_CUDA(cudaMemcpy(h->d_tw, tw.data(), nb, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpy(h->d_win, win.data(), sizeof(double) * (size_t)spb, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
+    h->cur = 0;
+    h->params_set = true;
+    return 0;
+}
+int pebble_fft_size(const pebble_fft_t *h) { return h ? h->N : PEBBLE_ERR_ARG; }
+
+int pebble_fft_spectrum_batch_device(pebble_fft_t *h, int frames, int n, const double *d_in, double *d_out, int *d_flags,
+                                     void *stream_v) {
+    if (!h || frames < 0 || n <= 0 || !d_in || !d_out) { pebble::set_error("fft: bad argument"); return PEBBLE_ERR_ARG; }
+    if (!h->params_set) { pebble::set_error("fft: fftParams not called"); return PEBBLE_ERR_STATE; }  // fftw.cpp:72-73
+    if (n > h->N) { pebble::set_error("fft: numSamples %d > fftSize %d", n, h->N); return PEBBLE_ERR_ARG; }
+    if (frames == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream_v;
+#define X(NN) spec_launch<NN>(h, frames, n, (const cpx *)d_in, d_out, d_flags, st)
+    cudaError_t e = FFT_DISPATCH(h, X);
+#undef X
+    PB_CUDA(e, PEBBLE_ERR_CUDA);
+    h->cur ^= 1;
+    return frames;
+}
+
+int pebble_fft_spectrum(pebble_fft_t *h, const double *in, double *out_db, int n) {
+    if (!h || !in || !out_db || n <= 0) { pebble::set_error("fft: bad argument"); return PEBBLE_ERR_ARG; }
+    if (!h->params_set) return 0;  // fftw.cpp:72-73 returns false
+    if (n > h->N) { pebble::set_error("fft: numSamples %d > fftSize %d", n, h->N); return PEBBLE_ERR_ARG; }
+    const size_t bi = sizeof(cpx) * (size_t)n, bo = sizeof(double) * (size_t)h->N;
+    if (!h->stg.reserve(bi, bo)) return PEBBLE_ERR_CUDA;
+    memcpy(h->stg.h_in, in, bi);
+    PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
+    int r = pebble_fft_spectrum_batch_device(h, 1, n, (const double *)h->stg.d_in, (double *)h->stg.d_out, nullptr, h->stream);
+    if (r < 0) return r;
+    PB_CUDA(cudaMemcpyAsync(h->stg.h_out, h->stg.d_out, bo, cudaMemcpyDeviceToHost, h->stream), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpyAsync(h->h_flag, h->d_flag[h->cur], sizeof(int), cudaMemcpyDeviceToHost, h->stream), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamSynchronize(h->stream), PEBBLE_ERR_CUDA);
+    memcpy(out_db, h->stg.h_out, bo);
+    return *h->h_flag ? 1 : 0;
+}
+
+static int fft_c2c_host(pebble_fft_t *h, const double *in, double *out, int n, bool inverse) {
+    if (!h || !in || !out || n <= 0) {
+        pebble::set_error("fft: in==NULL/out==NULL internal-buffer forms are not part of this ABI");
+        return PEBBLE_ERR_ARG;
+    }
+    if (!h->params_set) return 0;  // fftw.cpp:33-34: silent return
+    if (n > h->N) { pebble::set_error("fft: numSamples %d > fftSize %d", n, h->N); return PEBBLE_ERR_ARG; }
+    const size_t bi = sizeof(cpx) * (size_t)n, bo = sizeof(cpx) * (size_t)h->N;
+    if (!h->stg.reserve(bi, bo)) return PEBBLE_ERR_CUDA;
+    memcpy(h->stg.h_in, in, bi);
+    PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
+    cudaError_t e;
+    if (inverse) {
+#define X(NN) c2c_launch<NN, true>(h, n, (const cpx *)h->stg.d_in, (cpx *)h->stg.d_out, h->stream)
+        e = FFT_DISPATCH(h, X);
+#undef X
+    } else {
+#define X(NN) c2c_launch<NN, false>(h, n, (const cpx *)h->stg.d_in, (cpx *)h->stg.d_out, h->stream)
+        e = FFT_DISPATCH(h, X);
+#undef X
+        h->cur ^= 1;  // the forward kernel wrote the flag into the other slot; amplitudes follow it
+        cudaMemcpyAsync(h->d_prev[h->cur], h->d_prev[h->cur ^ 1], sizeof(double) * (size_t)h->N, cudaMemcpyDeviceToDevice, h->stream);
+    }
+    PB_CUDA(e, PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpyAsync(h->stg.h_out, h->stg.d_out, bo, cudaMemcpyDeviceToHost, h->stream), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamSynchronize(h->stream), PEBBLE_ERR_CUDA);
+    memcpy(out, h->stg.h_out, bo);
+    return h->N;
+}
+int pebble_fft_forward(pebble_fft_t *h, const double *in, double *out, int n) { return fft_c2c_host(h, in, out, n, false); }
+int pebble_fft_inverse(pebble_fft_t *h, const double *in, double *out, int n) { return fft_c2c_host(h, in, out, n, true); }
+
+double pebble_window(int wtype, int n, double *w_out) {
+    std::vector<double> w;
+    double cg = pebble_host::window_table(wtype, n, w);
+    if (w_out && !w.empty()) memcpy(w_out, w.data(), sizeof(double) * (size_t)n);
+    return cg;
+}
+
+// state: m_fftPower[N] then m_fftAmplitude[N] (fft.cpp:387-388); power is derived: psd = asd^2 * maxBinPower
+int pebble_fft_get_state(pebble_fft_t *h, double *buf, int64_t count) {
+    if (!h || !buf || !h->params_set || count < 2 * (int64_t)h->N) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpy(buf + h->N, h->d_prev[h->cur], sizeof(double) * (size_t)h->N, cudaMemcpyDeviceToHost), PEBBLE_ERR_CUDA);
+    for (int i = 0; i < h->N; ++i) buf[i] = buf[h->N + i] * buf[h->N + i] * h->maxbin;
+    return 0;
+}
+int pebble_fft_set_state(pebble_fft_t *h, const double *buf, int64_t count) {
+    if (!h || !buf || !h->params_set || count < 2 * (int64_t)h->N) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpy(h->d_prev[h->cur], buf + h->N, sizeof(double) * (size_t)h->N, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
+    return 0;
+}
+
+}  // extern "C"

@@ -142,3 +142,195 @@ class CDownConvert(_Handle):
 
     def SetState(self, buf):
         check(lib.pebble_downconvert_set_state(self._h, buf.ctypes.data, buf.size), "SetState")
+
+
+def _np_ptr(a, count, dtype, writable=False):
+    if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags.c_contiguous or a.size < count:
+        raise PebbleError("expected a C-contiguous numpy %s array with >= %d elements" % (np.dtype(dtype), count))
+    if writable and not a.flags.writeable:
+        raise PebbleError("output array is read-only")
+    return a.ctypes.data
+
+
+class WindowFunction:
+    """pebblelib/windowfunction.h: WINDOWTYPE numbering and table builder."""
+    RECTANGULAR, HANNING, WELCH, PARZEN, BARTLETT, HAMMING, BLACKMAN2, BLACKMAN3, BLACKMAN4, EXPONENTIAL, RIEMANN, \
+        BLACKMANHARRIS, BLACKMAN, NONE = range(1, 15)
+
+    def __init__(self, _type, _numSamples):
+        self.window = np.zeros(_numSamples)
+        self.coherentGain = lib.pebble_window(_type, _numSamples, self.window.ctypes.data)
+
+
+class FFT(_Handle):
+    """pebblelib/fft.h:29-62 — fftParams / fftForward / fftInverse / fftSpectrum."""
+    _destroy = staticmethod(lib.pebble_fft_destroy)
+
+    def __init__(self):
+        super().__init__(lib.pebble_fft_create(), "FFT")
+
+    def fftParams(self, _fftSize, _dBCompensation, _sampleRate, _samplesPerBuffer, _windowType):
+        check(lib.pebble_fft_params(self._h, _fftSize, _dBCompensation, _sampleRate, _samplesPerBuffer, _windowType),
+              "fftParams")
+
+    def getFFTSize(self):
+        return check(lib.pebble_fft_size(self._h))
+
+    def fftForward(self, inb, outb, numSamples):
+        check(lib.pebble_fft_forward(self._h, _host_ptr(inb, numSamples), _host_ptr(outb, self.getFFTSize(), True),
+                                     numSamples), "fftForward")
+
+    def fftInverse(self, inb, outb, numSamples):
+        check(lib.pebble_fft_inverse(self._h, _host_ptr(inb, numSamples), _host_ptr(outb, self.getFFTSize(), True),
+                                     numSamples), "fftInverse")
+
+    def fftSpectrum(self, inb, out, numSamples):
+        """Returns the overload flag like the reference (fftw.cpp:70-81)."""
+        return bool(check(lib.pebble_fft_spectrum(self._h, _host_ptr(inb, numSamples),
+                                                  _np_ptr(out, self.getFFTSize(), np.float64, True), numSamples),
+                          "fftSpectrum"))
+
+    def fftSpectrumBatch(self, frames, numSamples, d_in, d_out_db, d_flags=None):
+        """Device-resident batch: `frames` consecutive frames (torch CUDA tensors)."""
+        return check(lib.pebble_fft_spectrum_batch_device(
+            self._h, frames, numSamples, _dev_ptr(d_in, frames * numSamples), d_out_db.data_ptr(),
+            d_flags.data_ptr() if d_flags is not None else None, _stream_ptr()), "fftSpectrumBatch")
+
+    def GetState(self):
+        buf = np.zeros(2 * self.getFFTSize())
+        check(lib.pebble_fft_get_state(self._h, buf.ctypes.data, buf.size))
+        return buf
+
+    def SetState(self, buf):
+        check(lib.pebble_fft_set_state(self._h, buf.ctypes.data, buf.size))
+
+
+class CFir(_Handle):
+    """pebblelib/fir.h:31-56."""
+    _destroy = staticmethod(lib.pebble_cfir_destroy)
+
+    def __init__(self):
+        super().__init__(lib.pebble_cfir_create(), "CFir")
+
+    def InitLPFilter(self, NumTaps, Scale, Astop, Fpass, Fstop, Fsamprate):
+        return check(lib.pebble_cfir_init_lp(self._h, NumTaps, Scale, Astop, Fpass, Fstop, Fsamprate), "InitLPFilter")
+
+    def InitHPFilter(self, NumTaps, Scale, Astop, Fpass, Fstop, Fsamprate):
+        return check(lib.pebble_cfir_init_hp(self._h, NumTaps, Scale, Astop, Fpass, Fstop, Fsamprate), "InitHPFilter")
+
+    def GetTaps(self):
+        a = np.zeros(75)
+        n = check(lib.pebble_cfir_get_taps(self._h, a.ctypes.data, 75))
+        return a[:n].copy()
+
+    def ProcessFilter(self, InLength, InBuf, OutBuf):
+        if _is_cuda_tensor(InBuf):
+            check(lib.pebble_cfir_process_device(self._h, InLength, _dev_ptr(InBuf, InLength), _dev_ptr(OutBuf, InLength),
+                                                 _stream_ptr()), "ProcessFilter")
+        else:
+            check(lib.pebble_cfir_process(self._h, InLength, _host_ptr(InBuf, InLength), _host_ptr(OutBuf, InLength, True)),
+                  "ProcessFilter")
+
+
+class AGC(_Handle):
+    """application/agc.h."""
+    AGC_OFF, ACG_FAST, AGC_MED, AGC_SLOW, AGC_LONG = range(5)
+    _destroy = staticmethod(lib.pebble_agc_destroy)
+
+    def __init__(self, _sampleRate, _bufferSize):
+        super().__init__(lib.pebble_agc_create(int(_sampleRate), int(_bufferSize)), "AGC")
+        self.numSamples = int(_bufferSize)
+
+    def setAgcMode(self, m, threshold):
+        check(lib.pebble_agc_set_mode(self._h, m, threshold), "setAgcMode")
+
+    def setAgcThreshold(self, g):
+        check(lib.pebble_agc_set_threshold(self._h, g), "setAgcThreshold")
+
+    def processBlock(self, pInData, n=None):
+        n = self.numSamples if n is None else n
+        out = np.empty(n, dtype=np.complex128)
+        check(lib.pebble_agc_process(self._h, n, _host_ptr(pInData, n), out.ctypes.data), "processBlock")
+        return out
+
+
+class Demod(_Handle):
+    """application/demod.h — Demod::processBlock mode dispatch."""
+    dmAM, dmSAM, dmFMN, dmFMM, dmFMS, dmDSB, dmLSB, dmUSB, dmCWL, dmCWU, dmDIGL, dmDIGU, dmNONE = range(13)
+    _destroy = staticmethod(lib.pebble_demod_destroy)
+
+    def __init__(self, _sampleRate, _bufferSize):
+        super().__init__(lib.pebble_demod_create(int(_sampleRate), int(_bufferSize)), "Demod")
+
+    def setDemodMode(self, _mode, _sourceSampleRate=0, _audioSampleRate=0):
+        check(lib.pebble_demod_set_mode(self._h, _mode), "setDemodMode")
+
+    def setNfmVariant(self, variant):
+        check(lib.pebble_demod_set_nfm_variant(self._h, variant))
+
+    def setBandwidth(self, bandwidth):
+        check(lib.pebble_demod_set_bandwidth(self._h, bandwidth), "setBandwidth")
+
+    def processBlock(self, inb, bufSize):
+        """Like the reference, pass-through modes return the INPUT array itself (demod.cpp:127-138)."""
+        if lib.pebble_demod_is_passthrough(self._h) == 1:
+            return inb
+        out = np.empty(bufSize, dtype=np.complex128)
+        check(lib.pebble_demod_process(self._h, bufSize, _host_ptr(inb, bufSize), out.ctypes.data), "processBlock")
+        return out
+
+
+class Receiver(_Handle):
+    """The non-WFM branch of Receiver::processIQData (application/receiver.cpp:903-996) as one chain."""
+    _destroy = staticmethod(lib.pebble_receiver_destroy)
+
+    def __init__(self, sampleRate, framesPerBuffer=2048):
+        super().__init__(lib.pebble_receiver_create(float(sampleRate), int(framesPerBuffer)), "Receiver")
+        self.framesPerBuffer = framesPerBuffer
+
+    def setDataRate(self, maxBW):
+        r = lib.pebble_receiver_set_data_rate(self._h, maxBW)
+        if r <= 0:
+            raise PebbleError("setDataRate: " + lib.pebble_last_error().decode())
+        return r
+
+    def setMixer(self, freq):
+        lib.pebble_receiver_set_mixer(self._h, freq)
+
+    def setFilter(self, lo, hi):
+        return check(lib.pebble_receiver_set_filter(self._h, lo, hi), "setFilter")
+
+    def setDemodMode(self, mode):
+        check(lib.pebble_receiver_set_demod_mode(self._h, mode), "setDemodMode")
+
+    def setDemodBandwidth(self, bw):
+        check(lib.pebble_receiver_set_demod_bandwidth(self._h, bw), "setDemodBandwidth")
+
+    def setAgc(self, mode, threshold):
+        check(lib.pebble_receiver_set_agc(self._h, mode, threshold), "setAgc")
+
+    def setGainStages(self, stages):
+        check(lib.pebble_receiver_set_gain_stages(self._h, stages))
+
+    def outCount(self, n):
+        return check(lib.pebble_receiver_out_count(self._h, n))
+
+    def processIQData(self, inb, numSamples, out=None):
+        """Host arrays (numpy) or device tensors (torch). Returns (count, out)."""
+        k = self.outCount(numSamples)
+        if _is_cuda_tensor(inb):
+            if out is None:
+                out = torch.empty(max(k, 1), dtype=torch.complex128, device=inb.device)
+            r = check(lib.pebble_receiver_process_device(self._h, numSamples, _dev_ptr(inb, numSamples),
+                                                         _dev_ptr(out, k), _stream_ptr()), "processIQData")
+            return r, out
+        if out is None:
+            out = np.empty(max(k, 1), dtype=np.complex128)
+        r = check(lib.pebble_receiver_process(self._h, numSamples, _host_ptr(inb, numSamples), _host_ptr(out, k, True)),
+                  "processIQData")
+        return r, out
+
+    def processPinned(self, pinned_in, numSamples, pinned_out):
+        """pinned_in/out: torch CPU tensors in page-locked memory; enqueues H2D, chain, D2H on the current stream."""
+        return check(lib.pebble_receiver_process_pinned(self._h, numSamples, pinned_in.data_ptr(), pinned_out.data_ptr(),
+                                                        _stream_ptr()), "processPinned")

@@ -1,0 +1,154 @@
+"""GPU parity: CFir, AGC, Demod (AM / NBFM / pass-through) and the receiver chain vs the reference CFir and the
+C oracle restatement of the application-side steps. Tolerances: rel-RMS <= 1e-10 for double paths,
+<= 1e-4 for the float-state NBFM PLL; counts exact."""
+import numpy as np
+import pytest
+
+from conftest import rel_rms, iq_noise_tones
+
+pytestmark = pytest.mark.gpu
+RATE = 78125
+
+
+def _am_signal(n, rate, seed=1, fc=1500.0):
+    rng = np.random.default_rng(seed)
+    t = np.arange(n) / rate
+    env = 0.3 * (1 + 0.5 * np.cos(2 * np.pi * 1000.0 * t))
+    x = env * np.exp(2j * np.pi * fc * t) + 0.003 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))
+    return np.ascontiguousarray(x)
+
+
+def _fm_signal(n, rate, seed=2):
+    rng = np.random.default_rng(seed)
+    t = np.arange(n) / rate
+    ph = 2 * np.pi * 5000.0 / (2 * np.pi * 1000.0) * np.sin(2 * np.pi * 1000.0 * t)
+    x = 0.5 * np.exp(1j * ph) + 0.002 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))
+    return np.ascontiguousarray(x)
+
+
+def test_cfir_design_and_filter_vs_reference():
+    import pebblesdr_b200 as pb
+    from oracle import ref, port
+    g, r, o = pb.CFir(), ref.CFir(), port.CFir()
+    for args in [(0, 1.0, 50.0, 3000.0, 4800.0, 78125.0), (0, 1.0, 50.0, 16000.0, 28800.0, 78125.0), (21, 2.0, 40.0, 500.0, 900.0, 8000.0)]:
+        ng, nr, no = g.InitLPFilter(*args), r.InitLPFilter(*args), o.InitLPFilter(*args)
+        assert ng == nr == no
+        assert np.array_equal(g.GetTaps(), o.GetTaps())
+        x = iq_noise_tones(5000, 4, args[5], [(300.0, 0.5)])
+        yg, yr = [], []
+        for a, b in ((0, 1), (1, 2048), (2048, 5000)):     # odd splits: carried delay line
+            og, orr = np.zeros(b - a, complex), np.zeros(b - a, complex)
+            g.ProcessFilter(b - a, x[a:b].copy(), og)
+            r.ProcessFilter(b - a, x[a:b].copy(), orr)
+            yg.append(og)
+            yr.append(orr)
+        assert rel_rms(np.concatenate(yg), np.concatenate(yr)) <= 1e-10
+    assert g.InitHPFilter(0, 1.0, 50.0, 900.0, 500.0, 8000.0) == o.InitHPFilter(0, 1.0, 50.0, 900.0, 500.0, 8000.0)
+    assert np.array_equal(g.GetTaps(), o.GetTaps())
+
+
+def test_am_demod_vs_oracle():
+    import pebblesdr_b200 as pb
+    from oracle import port
+    n = 2048 * 12
+    x = _am_signal(n, RATE)
+    g, o = pb.Demod(RATE, 2048), port.Demod(RATE)
+    g.setDemodMode(pb.Demod.dmAM)
+    g.setBandwidth(10000.0)
+    o.setBandwidth(10000.0)
+    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    yo = np.concatenate([o.am(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    assert rel_rms(yg, yo) <= 1e-10
+    # one big block == many small ones (scan carries across tiles and calls)
+    g2 = pb.Demod(RATE, 2048)
+    g2.setBandwidth(10000.0)
+    y2 = g2.processBlock(x, n)
+    assert rel_rms(y2, yo) <= 1e-10
+    # recovered audio is the 1 kHz tone
+    spec = np.abs(np.fft.rfft(yo[8192:8192 + 8192].real))
+    assert abs(np.argmax(spec[5:]) + 5 - round(1000.0 / RATE * 8192)) <= 1
+
+
+def test_nbfm_pll_and_fm2_vs_oracle():
+    import pebblesdr_b200 as pb
+    from oracle import port
+    n = 2048 * 6
+    x = _fm_signal(n, RATE)
+    g, o = pb.Demod(RATE, 2048), port.Demod(RATE)
+    g.setDemodMode(pb.Demod.dmFMN)
+    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    yo = np.concatenate([o.nfm_pll(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    assert np.all(yg.imag == 0.0) or rel_rms(yg.imag, yo.imag) <= 1e-4   # PLL output is real-only before the LP
+    assert rel_rms(yg, yo) <= 1e-4                                         # float PLL state (finding F10)
+    g.setNfmVariant(1)
+    o2 = port.Demod(RATE)
+    yg2 = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    yo2 = np.concatenate([o2.fm2(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    assert rel_rms(yg2, yo2) <= 1e-10
+
+
+def test_ssb_passthrough_returns_input():
+    import pebblesdr_b200 as pb
+    g = pb.Demod(RATE, 2048)
+    x = _am_signal(2048, RATE)
+    for mode in (pb.Demod.dmUSB, pb.Demod.dmLSB, pb.Demod.dmCWU, pb.Demod.dmDIGL, pb.Demod.dmNONE):
+        g.setDemodMode(mode)
+        assert g.processBlock(x, 2048) is x            # demod.cpp:127-138 returns `in`
+    g.setDemodMode(pb.Demod.dmSAM)
+    with pytest.raises(pb.PebbleError):
+        g.processBlock(x, 2048)
+
+
+@pytest.mark.parametrize("mode,thr", [(0, 20), (0, 37), (1, 20), (3, 40)])
+def test_agc_vs_oracle(mode, thr):
+    import pebblesdr_b200 as pb
+    from oracle import port
+    n = 2048 * 4
+    x = _am_signal(n, RATE, seed=7)
+    x[3000:3400] *= 20.0                                  # a burst to exercise attack/decay and the peak rescan
+    g, o = pb.AGC(RATE, 2048), port.AGC(RATE)
+    g.setAgcMode(mode, thr)
+    o.setAgcMode(mode, thr)
+    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy()) for i in range(0, n, 2048)])
+    yo = np.concatenate([o.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    assert rel_rms(yg, yo) <= 1e-10
+
+
+@pytest.mark.parametrize("demod,lo,hi", [(7, 300.0, 3000.0), (0, -5000.0, 5000.0)])
+def test_receiver_chain_config2(demod, lo, hi):
+    # BASELINE config 2: 10 MSPS -> /128 -> FastFIR -> USB (identity) / AM, AGC_OFF threshold 20, 32768-sample calls
+    import pebblesdr_b200 as pb
+    from oracle import port
+    n = 32768 * 24
+    t = np.arange(n)
+    x = iq_noise_tones(n, 2345, 10e6, [(-2e6, 0.5)], noise=0.01)
+    x += 0.3 * (1 + 0.5 * np.cos(2 * np.pi * 1e3 / 10e6 * t)) * np.exp(2j * np.pi * (1.2e6 + 1500.0) / 10e6 * t)
+    g = pb.Receiver(10e6, 2048)
+    o = port.Receiver(10e6, 2048, 15000.0)
+    assert g.setDataRate(15000.0) == o.demod_rate == 78125.0
+    g.setMixer(1.2e6)
+    g.setFilter(lo, hi)
+    g.setDemodMode(demod)
+    g.setAgc(0, 20)
+    o.config(1.2e6, lo, hi, demod, 0, 20)
+    if demod == 0:
+        g.setDemodBandwidth(10000.0)
+        o.setAmBandwidth(10000.0)
+    yg, yo = [], []
+    for i in range(0, n, 32768):
+        k, out = g.processIQData(x[i:i + 32768].copy(), 32768)
+        yg.append(out[:k].copy())
+        yo.append(o.processIQData(x[i:i + 32768], 32768))
+        assert k == len(yo[-1])                            # frame boundaries exact (receiver.cpp:927-931)
+    yg, yo = np.concatenate(yg), np.concatenate(yo)
+    assert len(yg) == (n >> 7) // 2048 * 2048
+    assert rel_rms(yg, yo) <= 1e-10
+    # device-resident single call over the whole capture gives the same stream
+    import torch
+    g2 = pb.Receiver(10e6, 2048)
+    g2.setDataRate(15000.0); g2.setMixer(1.2e6); g2.setFilter(lo, hi); g2.setDemodMode(demod); g2.setAgc(0, 20)
+    if demod == 0:
+        g2.setDemodBandwidth(10000.0)
+    k, out = g2.processIQData(torch.from_numpy(x).cuda(), n)
+    assert k == len(yo)
+    assert rel_rms(out[:k].cpu().numpy(), yo) <= 1e-10
