@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric on BASELINE config 2 (configs[1]):
+
+    complex MS/s through the full receiver chain CDownConvert (NCO mix + halfband decimators, 10 MSPS -> /128 ->
+    78 125 S/s) -> CFastFIR -> AGC_OFF -> demod, 1 channel, synthetic IQ; with the fraction of the HBM roofline.
+
+A "step" is one pass of the chain over one batch of 2^LOG2N input samples (default 2^26 CPX = 1 GiB, larger than
+the 126 MB L2, so no L2 flush is needed between steps). One JSON line on stdout (rank 0).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            this repo's CUDA path through the C ABI
+  python bench.py --impl reference ...                           the reference's own CPU chain on the host cores
+
+Multi-GPU: a single receiver stream does not shard (DESIGN.md "replicas only"): --gpus N runs N independent
+receivers, one process per GPU (torchrun), no data-path collective; value = all ranks' samples / max-over-ranks time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "complex MS/s through DownConvert->FastFIR->demod chain"
+UNIT = "MS/s"
+RATE, MAX_BW, MIXER = 10e6, 15000.0, 1.2e6
+MODES = {"am": (0, -5000.0, 5000.0), "usb": (7, 300.0, 3000.0)}
+ALG_BYTES_PER_SAMPLE_DC = 16.0 + 16.0 / 128.0      # 16 B read + 16/128 B written
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--log2n", type=int, default=26, help="input samples per step = 2^log2n")
+    ap.add_argument("--mode", default="am", choices=sorted(MODES))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work per baseline leg")
+    return ap.parse_args()
+
+
+def workload_config(args, extra=None):
+    demod, lo, hi = MODES[args.mode]
+    cfg = {
+        "workload": "BASELINE config 2: full receiver chain, 1 channel, 10 MSPS synthetic IQ: CDownConvert "
+                    "SetDataRate(10e6,15000) [CIC3,HB11x4,HB15,HB27 => /128, 78125 S/s], SetFrequency(1.2e6) -> "
+                    "re-frame 2048 -> gain restore -> CFastFIR(%g,%g) -> AGC_OFF(20) -> %s demod" %
+                    (lo, hi, "AM (Demod_AM::processBlockFiltered)" if demod == 0 else "USB (pass-through)"),
+        "cpx": "std::complex<double>, 16 B/sample",
+        "samples_per_step": 1 << args.log2n,
+        "l2": "inputs (%d MiB/step) larger than the 126 MB L2; no flush" % ((16 << args.log2n) >> 20),
+        "parallelism": "replicas only (1 receiver per GPU)" if args.gpus > 1 else "1 GPU",
+    }
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# synthetic input: AM carrier (1 kHz tone, m=0.5, amp 0.3) at +1.2 MHz (+1.5 kHz so the
+# demodulated carrier sits inside both the USB and the AM pass-band), Gaussian noise 0.01, interferer at -2 MHz 0.5
+# ---------------------------------------------------------------------------------------------------------------
+def synth_numpy(n, seed=2345):
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    t = np.arange(n, dtype=np.float64)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.01
+    x += 0.5 * np.exp(2j * np.pi * (-2e6 / RATE) * t)
+    x += 0.3 * (1 + 0.5 * np.cos(2 * np.pi * (1e3 / RATE) * t)) * np.exp(2j * np.pi * ((MIXER + 1500.0) / RATE) * t)
+    return np.ascontiguousarray(x.astype(np.complex128))
+
+
+def synth_torch(n, device, seed=2345):
+    import math
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    x = torch.empty(n, dtype=torch.complex128, device=device)
+    xr = torch.view_as_real(x)
+    blk = 1 << 22
+    for i in range(0, n, blk):
+        m = min(blk, n - i)
+        t = torch.arange(i, i + m, dtype=torch.float64, device=device)
+        xr[i:i + m] = torch.randn(m, 2, generator=g, dtype=torch.float64, device=device) * 0.01
+        am = 0.3 * (1 + 0.5 * torch.cos(2 * math.pi * (1e3 / RATE) * t))
+        ph1 = 2 * math.pi * torch.remainder(((MIXER + 1500.0) / RATE) * t, 1.0)
+        ph2 = 2 * math.pi * torch.remainder((-2e6 / RATE) * t, 1.0)
+        xr[i:i + m, 0] += am * torch.cos(ph1) + 0.5 * torch.cos(ph2)
+        xr[i:i + m, 1] += am * torch.sin(ph1) + 0.5 * torch.sin(ph2)
+    return x
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region (B200_PROFILING.md recipe)
+# ---------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [c.strip() for c in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU baseline: the reference's own chain on the host cores, bounded sample (oracle/cpu_chain.py)
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_chain_kwargs(args):
+    demod, lo, hi = MODES[args.mode]
+    return dict(rate=RATE, fpb=2048, max_bw=MAX_BW, mixer=MIXER, lo=lo, hi=hi, demod_mode=demod, agc_threshold=20,
+                am_bandwidth=10000.0)
+
+
+def cpu_sample_size(args, threads, steps):
+    """Calibrate one thread on 2^21 samples, then size the per-thread sample so that `steps` timed steps total
+    about args.cpu_seconds of wall clock (multiple of 32768 samples, at least 2^20)."""
+    from oracle import cpu_chain
+    kw = cpu_chain_kwargs(args)
+    x = synth_numpy(1 << 21)
+    c = cpu_chain.CpuChain(**kw)
+    c.run(x[:1 << 18].copy())
+    t0 = time.perf_counter()
+    c.run(x)
+    per_sample = (time.perf_counter() - t0) / (1 << 21)
+    per_step = args.cpu_seconds / max(steps, 1)
+    n = int(per_step / per_sample / 1.5)            # threads sharing caches/DRAM run slower than one alone
+    n = max(1 << 20, min(n, 1 << 28)) // 32768 * 32768
+    return n, 1.0 / per_sample / 1e6
+
+
+def run_cpu_baseline(args, steps, warmup):
+    from oracle import cpu_chain
+    threads = cpu_chain.host_threads()
+    n, one_thread_msps = cpu_sample_size(args, threads, steps + warmup)
+    times, total = cpu_chain.timed_throughput(synth_numpy, n, threads, steps=steps, warmup=warmup,
+                                              chain_kwargs=cpu_chain_kwargs(args))
+    n = total // threads
+    dt = sum(times) / len(times)
+    return {
+        "value": total / dt / 1e6, "unit": UNIT, "cores": threads, "kind": cpu_chain.kind(),
+        "one_thread": one_thread_msps,
+        "sample": "%d independent receivers (one per host thread), each %d samples of the bench workload per step "
+                  "(passes over a 2^22-sample buffer, 32768-sample calls), %d timed steps; CDownConvert+CFastFIR = %s, AGC_OFF/demod = C restatement" %
+                  (threads, n, steps, "unmodified reference pebblelib+FFTW 3.3.4 (oracle/_ref)"
+                   if cpu_chain.kind() == "reference" else "C restatement (oracle/pebble_oracle.c)"),
+    }, times, total
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    base, times, total = run_cpu_baseline(args, max(args.steps, 1), max(args.warmup, 0))
+    ms = 1e3 * sum(times) / len(times)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, {"samples_per_step": total, "l2": "n/a (host)",
+                                         "parallelism": "%d host threads, one receiver each" % base["cores"]}),
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# this repo's arm: libpebblecuda.so through the C ABI (pebblesdr_b200.Receiver = ctypes over include/pebble_cuda.h)
+# ---------------------------------------------------------------------------------------------------------------
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy, this pool)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def ncu_traffic(n):
+    """dram__bytes_read.sum + dram__bytes_write.sum of dc_fused_kernel from the committed ncu capture, if it was
+    taken at this launch size (profiles/traffic.json, written by tools/ncu_summary.py)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        e = t.get("dc_fused_kernel", {})
+        if int(e.get("samples_per_launch", -1)) == n:
+            return float(e["dram_bytes"])
+    except Exception:
+        pass
+    return None
+
+
+def make_receiver(pb, args):
+    demod, lo, hi = MODES[args.mode]
+    rx = pb.Receiver(RATE, 2048)
+    out_rate = rx.setDataRate(MAX_BW)
+    assert out_rate == 78125.0, out_rate
+    rx.setMixer(MIXER)
+    rx.setFilter(lo, hi)
+    rx.setDemodMode(demod)
+    rx.setAgc(0, 20)
+    if demod == 0:
+        rx.setDemodBandwidth(10000.0)
+    return rx
+
+
+def main_ours(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this arm has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import pebblesdr_b200 as pb
+    from pebblesdr_b200 import lib
+
+    n = 1 << args.log2n
+    K, W = args.steps, args.warmup
+    x = synth_torch(n, dev, seed=2345 + rank)
+    rx = make_receiver(pb, args)
+    nout = rx.outCount(n)
+    out = torch.zeros(max(nout, 1), dtype=torch.complex128, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident: `value` -------------------------------------------------------------------------
+    for _ in range(W):
+        rx.processIQData(x, n, out)
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.3)
+    rx.setProfiling(True)
+    l0 = lib.pebble_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    produced = 0
+    for _ in range(K):
+        k, _o = rx.processIQData(x, n, out)
+        produced += k
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = lib.pebble_launch_count() - l0
+    prof, calls = rx.getProfile()
+    rx.setProfiling(False)
+    clk = clocks.stop() if rank == 0 else None
+    checksum = float(torch.view_as_real(out[:nout]).abs().sum().item())   # result is finite and non-trivial
+    assert produced == K * nout and checksum > 0 and checksum == checksum, (produced, nout, checksum)
+
+    # ---- end to end through the host-buffer C-ABI call: `e2e` -----------------------------------------------
+    pin_in = torch.empty(n, dtype=torch.complex128, pin_memory=True)
+    pin_in.copy_(x)
+    pin_out = torch.zeros(max(nout, 1), dtype=torch.complex128, pin_memory=True)
+    rx2 = make_receiver(pb, args)
+    for _ in range(min(W, 3)):
+        rx2.processPinned(pin_in, n, pin_out)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    f0.record()
+    for _ in range(K):
+        rx2.processPinned(pin_in, n, pin_out)
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    assert float(torch.view_as_real(pin_out[:nout]).abs().sum()) > 0
+
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        dc_ms = prof["downconvert"] / max(calls, 1)
+        achieved = ALG_BYTES_PER_SAMPLE_DC * n / (dc_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": world * n * K / (ms_total * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args),
+            "e2e": {"value": world * n * K / (ms_e2e * 1e-3) / 1e6, "unit": UNIT,
+                    "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e / K,
+                    "call": "pebble_receiver_process_pinned (host buffers, H2D + chain + D2H per step)"},
+            "roofline": {"bound": "hbm", "kernel": "dc_fused_kernel (CDownConvert: NCO mix + 7-stage decimator)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic(n), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": ALG_BYTES_PER_SAMPLE_DC * n, "kernel_ms": dc_ms,
+                         "chain_frac": ALG_BYTES_PER_SAMPLE_DC * n * K / (ms_total * 1e-3) / 1e9 / peak,
+                         "step_ms_by_operator": {k: v / max(calls, 1) for k, v in prof.items()}},
+            "gpu_launches": int(launches), "clocks": clk,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            base, _, _ = run_cpu_baseline(args, steps=3, warmup=1)
+            line["cpu_baseline"] = base
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(main_reference(a) if a.impl == "reference" else main_ours(a))

@@ -202,6 +202,11 @@ int pebble_receiver_set_demod_bandwidth(pebble_receiver_t *h, double bandwidth);
 int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold);
 int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages);
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n);
+/* Library extension (the reference's Perform timer call sites, receiver.cpp:788,805,827, are commented out):
+ * per-step DEVICE time via CUDA events recorded on the caller's stream. get_profile sums the calls made since
+ * profiling was enabled (ms[0] CDownConvert, ms[1] CFastFIR, ms[2] AGC, ms[3] Demod), then resets. */
+int pebble_receiver_set_profiling(pebble_receiver_t *h, int on);
+int pebble_receiver_get_profile(pebble_receiver_t *h, double *ms4, int64_t *calls);
 int pebble_receiver_process(pebble_receiver_t *h, int n, const double *in, double *out);
 int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_in, double *d_out, void *stream);
 /* in/out are page-locked HOST buffers; copies and kernels are enqueued on `stream` without synchronising */

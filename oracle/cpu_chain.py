@@ -1,0 +1,135 @@
+"""oracle/cpu_chain.py — TEST INFRASTRUCTURE ONLY (checker and timed CPU baseline; never the product path).
+
+The reference's CPU receiver chain for BASELINE config 2, ordered as Receiver::processIQData's non-WFM branch
+(application/receiver.cpp:903-996):
+
+    CDownConvert::ProcessData (:908) -> m_sampleBuf re-framing to framesPerBuffer (:922-931) -> gain restore
+    10^(2*stages/20) (:935-938) -> BandPassFilter/CFastFIR::ProcessData (:950) -> AGC_OFF gain (agc.cpp:86-94)
+    -> Demod (USB: return in, demod.cpp:127-138; AM: Demod_AM::processBlockFiltered, demod_am.cpp:40-64)
+
+kind "reference": CDownConvert and CFastFIR are the REAL reference objects from oracle/_ref/libpebbleref.so
+(unmodified pebblelib + FFTW 3.3.4); together they are >99 % of the CPU time (the mixer and first decimator stages
+run at the full input rate). AGC_OFF and Demod_AM inherit QObject and cannot be compiled without Qt, so those two
+steps (which run at 1/128 of the input rate) come from the C restatement oracle/pebble_oracle.c.
+kind "port": everything from oracle/pebble_oracle.c (used when oracle/_ref is absent).
+"""
+import os
+import threading
+import time
+
+import numpy as np
+
+from . import port, ref
+
+CALL = 32768  # samples per CDownConvert call (multiple of 128; generic HB buffers cap it, downconvert.cpp:60,345)
+
+
+def kind():
+    return "reference" if ref.available() else "port"
+
+
+class CpuChain:
+    def __init__(self, rate=10e6, fpb=2048, max_bw=15000.0, mixer=1.2e6, lo=-5000.0, hi=5000.0, demod_mode=0,
+                 agc_threshold=20, am_bandwidth=10000.0, use_ref=None):
+        self.use_ref = ref.available() if use_ref is None else use_ref
+        self.fpb = fpb
+        self.demod_mode = demod_mode
+        if self.use_ref:
+            self.dc = ref.CDownConvert()
+            self.ff = ref.CFastFIR()
+            self._dc_process = ref.lib().ref_downconvert_process
+            self._ff_process = ref.lib().ref_fastfir_process
+        else:
+            self.dc = port.CDownConvert()
+            self.ff = port.CFastFIR()
+            self._dc_process = port.lib().orc_downconvert_process
+            self._ff_process = port.lib().orc_fastfir_process
+        self.demod_rate = self.dc.SetDataRate(rate, max_bw)
+        self.dc.SetFrequency(mixer)
+        self.ff.SetupParameters(lo, hi, 0.0, self.demod_rate)
+        self.stages = int(round(np.log2(rate / self.demod_rate)))
+        self.gain = 10.0 ** ((self.stages * 2) / 20.0)             # receiver.cpp:935-938
+        agc = port.AGC(self.demod_rate)
+        agc.setAgcMode(0, agc_threshold)
+        self.agc_gain = port.lib().orc_agc_manual_gain(agc.h)      # agc.cpp:86-94
+        self.demod = port.Demod(self.demod_rate)
+        if demod_mode == 0:
+            self.demod.setBandwidth(am_bandwidth)
+        self.sample_buf = np.zeros(CALL + 2 * fpb, dtype=np.complex128)   # m_sampleBuf
+        self.fill = 0
+        self._dec = np.zeros(CALL, dtype=np.complex128)
+        self._bp = np.zeros(fpb, dtype=np.complex128)
+
+    def process(self, scratch, n, out):
+        """scratch: n input samples (CLOBBERED, like the reference, downconvert.cpp:309-310). n a multiple of 128
+        and <= CALL. Appends demodulated samples to out (list) and returns their count."""
+        k = self._dc_process(self.dc.h, n, scratch.ctypes.data, self._dec.ctypes.data)
+        self.sample_buf[self.fill:self.fill + k] = self._dec[:k]
+        self.fill += k
+        produced = 0
+        while self.fill >= self.fpb:
+            frame = self.sample_buf[:self.fpb] * self.gain
+            self._ff_process(self.ff.h, self.fpb, frame.ctypes.data, self._bp.ctypes.data)
+            y = self._bp * self.agc_gain
+            if self.demod_mode == 0:
+                y = self.demod.am(np.ascontiguousarray(y), self.fpb)
+            out.append(y.copy())
+            produced += self.fpb
+            rem = self.fill - self.fpb
+            self.sample_buf[:rem] = self.sample_buf[self.fpb:self.fill]
+            self.fill = rem
+        return produced
+
+    def run(self, buf):
+        """Whole buffer (clobbered) in CALL-sized calls; returns the concatenated demodulated stream."""
+        out = []
+        for i in range(0, len(buf), CALL):
+            n = min(CALL, len(buf) - i)
+            self.process(buf[i:i + n], n, out)
+        return np.concatenate(out) if out else np.zeros(0, dtype=np.complex128)
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+BUF_CAP = 1 << 22   # samples per thread-private input buffer (64 MiB); longer steps re-fill it (untimed) and go again
+
+
+def timed_throughput(make_input, samples_per_thread, threads, steps=1, warmup=0, chain_kwargs=None):
+    """One independent receiver (own CpuChain, own input buffer) per thread — how N reference receivers would run on
+    N cores; the reference itself is single-threaded per receiver. A step pushes `samples_per_thread` samples
+    through every receiver as passes over a BUF_CAP-sample buffer; because CDownConvert clobbers its input, the
+    buffer is re-filled before each pass and that copy is NOT timed (the device plugin hands the chain a fresh
+    buffer). Step time = max over threads of the time spent inside the chain, all threads running concurrently.
+    Returns (list of per-step seconds, samples per step over all threads). ctypes releases the GIL inside the C calls."""
+    chain_kwargs = chain_kwargs or {}
+    per_pass = min(BUF_CAP, samples_per_thread) // CALL * CALL
+    passes = max(1, samples_per_thread // per_pass)
+    src = make_input(per_pass)
+    chains = [CpuChain(**chain_kwargs) for _ in range(threads)]
+    bufs = [np.empty_like(src) for _ in range(threads)]
+    times = []
+    for step in range(warmup + steps):
+        busy = [0.0] * threads
+        start = threading.Barrier(threads)
+
+        def work(i):
+            start.wait()
+            for _ in range(passes):
+                np.copyto(bufs[i], src)
+                t0 = time.perf_counter()
+                chains[i].run(bufs[i])
+                busy[i] += time.perf_counter() - t0
+
+        ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        if step >= warmup:
+            times.append(max(busy))
+    return times, per_pass * passes * threads

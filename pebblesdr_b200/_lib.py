@@ -91,6 +91,8 @@ SIGNATURES = {
     "pebble_receiver_set_agc": (c_int, [c_vp, c_int, c_int]),
     "pebble_receiver_set_gain_stages": (c_int, [c_vp, c_int]),
     "pebble_receiver_out_count": (c_int, [c_vp, c_int]),
+    "pebble_receiver_set_profiling": (c_int, [c_vp, c_int]),
+    "pebble_receiver_get_profile": (c_int, [c_vp, c_vp, c_vp]),
     "pebble_receiver_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "pebble_receiver_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
     "pebble_receiver_process_pinned": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),

@@ -7,6 +7,7 @@
 #include "demod_internal.h"
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 struct pebble_receiver {
     double sample_rate = 0, demod_rate = 0;
@@ -22,7 +23,22 @@ struct pebble_receiver {
     void *d_pin_in = nullptr, *d_pin_out = nullptr; size_t pin_in_cap = 0, pin_out_cap = 0;
     cudaStream_t stream = nullptr;
     pebble::Staging stg;
+    // optional per-step device timing (bench.py's roofline leg): 5 events per process call, recorded on the
+    // caller's stream: [before dc, after dc, after fastfir, after agc, after demod]
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev;
+    size_t ev_used = 0;
 };
+
+static void rx_mark(pebble_receiver *h, cudaStream_t st) {
+    if (!h->profiling) return;
+    if (h->ev_used == h->ev.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        h->ev.push_back(e);
+    }
+    cudaEventRecord(h->ev[h->ev_used++], st);
+}
 
 static int rx_reserve(pebble_receiver *h, size_t dec_total) {
     if (dec_total > h->frames_cap) {
@@ -73,6 +89,7 @@ void pebble_receiver_destroy(pebble_receiver_t *h) {
     if (h->demod) pebble_demod_destroy(h->demod);
     cudaFree(h->d_frames); cudaFree(h->d_bp); cudaFree(h->d_agc); cudaFree(h->d_pin_in); cudaFree(h->d_pin_out);
     if (h->stream) cudaStreamDestroy(h->stream);
+    for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     h->stg.release();
     delete h;
 }
@@ -109,6 +126,29 @@ int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages) {
     h->gain_stages = stages;
     return 0;
 }
+int pebble_receiver_set_profiling(pebble_receiver_t *h, int on) {
+    if (!h) return PEBBLE_ERR_ARG;
+    h->profiling = on != 0;
+    h->ev_used = 0;
+    return 0;
+}
+// Sums the device time of each step over the calls made since profiling was (re)enabled, then resets.
+// ms[0] CDownConvert, ms[1] CFastFIR (+fused gains), ms[2] AGC (0 when fused), ms[3] Demod. Synchronises.
+int pebble_receiver_get_profile(pebble_receiver_t *h, double *ms, int64_t *calls) {
+    if (!h || !ms) return PEBBLE_ERR_ARG;
+    ms[0] = ms[1] = ms[2] = ms[3] = 0.0;
+    const size_t nc = h->ev_used / 5;
+    if (nc) PB_CUDA(cudaEventSynchronize(h->ev[nc * 5 - 1]), PEBBLE_ERR_CUDA);
+    for (size_t c = 0; c < nc; ++c)
+        for (int k = 0; k < 4; ++k) {
+            float t = 0.f;
+            PB_CUDA(cudaEventElapsedTime(&t, h->ev[c * 5 + k], h->ev[c * 5 + k + 1]), PEBBLE_ERR_CUDA);
+            ms[k] += t;
+        }
+    if (calls) *calls = (int64_t)nc;
+    h->ev_used = 0;
+    return 0;
+}
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n) {
     if (!h || n < 0) return PEBBLE_ERR_ARG;
     const int S = pebble_downconvert_num_stages(h->dc);
@@ -125,12 +165,18 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
     int r = rx_reserve(h, (size_t)h->fill + (size_t)ndec);
     if (r < 0) return r;
     // receiver.cpp:908 + 922-924: decimated samples are appended to m_sampleBuf
+    rx_mark(h, st);
     r = pebble_downconvert_process_device(h->dc, n, d_in, (double *)(h->d_frames + h->fill), st);
     if (r < 0) return r;
+    rx_mark(h, st);
     const int total = h->fill + ndec;
     const int nframes = total / h->fpb;
     const int nproc = nframes * h->fpb;
-    if (nframes == 0) { h->fill = total; return 0; }  // receiver.cpp:927-928
+    if (nframes == 0) {  // receiver.cpp:927-928
+        h->fill = total;
+        rx_mark(h, st); rx_mark(h, st); rx_mark(h, st);
+        return 0;
+    }
     if (!d_out) { pebble::set_error("receiver: NULL output"); return PEBBLE_ERR_ARG; }
     // receiver.cpp:935-938: restore decimation gain, 2 dB per stage
     const int gs = h->gain_stages >= 0 ? h->gain_stages : S;
@@ -140,14 +186,17 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
     r = pebble_fastfir_process_device(h->bp, nproc, (const double *)h->d_frames, (double *)h->d_bp, st);  // receiver.cpp:950
     if (r < 0) return r;
     if (r != nproc) { pebble::set_error("receiver: FastFIR returned %d of %d", r, nproc); return PEBBLE_ERR_STATE; }
+    rx_mark(h, st);
     const cpx *next = h->d_bp;
     if (!fuse_agc) {  // receiver.cpp:983
         r = agc_run_device(h->agc, nproc, next, h->d_agc, st);
         if (r < 0) return r;
         next = h->d_agc;
     }
+    rx_mark(h, st);
     r = demod_run_device(h->demod, nproc, next, (cpx *)d_out, st, nullptr);  // receiver.cpp:987
     if (r < 0) return r;
+    rx_mark(h, st);
     // keep the incomplete frame for the next call
     const int rem = total - nproc;
     if (rem > 0)

@@ -315,6 +315,16 @@ class Receiver(_Handle):
     def outCount(self, n):
         return check(lib.pebble_receiver_out_count(self._h, n))
 
+    def setProfiling(self, on):
+        check(lib.pebble_receiver_set_profiling(self._h, int(bool(on))))
+
+    def getProfile(self):
+        """({"downconvert": ms, "fastfir": ms, "agc": ms, "demod": ms}, calls) summed since setProfiling(True)."""
+        ms = (ctypes.c_double * 4)()
+        calls = ctypes.c_int64(0)
+        check(lib.pebble_receiver_get_profile(self._h, ms, ctypes.byref(calls)), "getProfile")
+        return dict(zip(("downconvert", "fastfir", "agc", "demod"), list(ms))), calls.value
+
     def processIQData(self, inb, numSamples, out=None):
         """Host arrays (numpy) or device tensors (torch). Returns (count, out)."""
         k = self.outCount(numSamples)
