@@ -1,31 +1,13 @@
 // downconvert.cu — CDownConvert on the GPU: kernel wrapper + C ABI (include/pebble_cuda.h).
-// Kernel body: dc_core.cuh (fused NCO mix + decimate-by-2 cascade, one segment per CTA).
+// Kernel body: dc_fused.cuh (fused NCO mix + decimate-by-2 cascade, one segment per CTA).
 #include "lib_common.h"
-#include "cta_ctx.cuh"
-#include "dc_core.cuh"
+#include "dc_fused.cuh"
 #include "host_design.h"
+#include "hb_coefs.h"
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
-
-#define DC_HDR_BYTES 128                                     // mbarriers
-#define DC_ST_BYTES (sizeof(DcStage) * PB_DC_MAX_STAGES)     // stage table copy
-
-__global__ void __launch_bounds__(256) dc_fused_kernel(const DcChain *__restrict__ ch, const DcCall call) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    CtaCtx ctx;
-    ctx.mbar = reinterpret_cast<uint64_t *>(smem_raw);
-    DcStage *st = reinterpret_cast<DcStage *>(smem_raw + DC_HDR_BYTES);
-    double *coef = reinterpret_cast<double *>(smem_raw + DC_HDR_BYTES + DC_ST_BYTES);
-    const int S = ch->nstages;
-    for (int i = threadIdx.x; i < S; i += blockDim.x) st[i] = ch->st[i];
-    for (int i = threadIdx.x; i < S * 52; i += blockDim.x) coef[i] = ch->coef[i];
-    const size_t coef_bytes = ((size_t)S * 52 * sizeof(double) + 127) & ~(size_t)127;
-    cpx *buffers = reinterpret_cast<cpx *>(smem_raw + DC_HDR_BYTES + DC_ST_BYTES + coef_bytes);
-    ctx.init();  // includes __syncthreads
-    dc_run_segment(ctx, ch, st, coef, call, buffers, (long long)blockIdx.x);
-}
 
 struct pebble_downconvert {
     DcChain chain;          // host copy
@@ -39,9 +21,32 @@ struct pebble_downconvert {
     double in_rate, max_bw, nco_freq, cw_offset, out_rate;
     std::vector<int> lens;
     int threads, chunk, front, group;
+    size_t smem_set = 0;
+    const void *fn_set = nullptr;
     cudaStream_t stream;    // for the host-pointer entry point
     pebble::Staging stg;
 };
+
+// The specialised kernel when the three front stages are one of the instantiated combinations (every chain
+// SetDataRate plans for an input rate >= ~300x the output bandwidth starts with one of these), else the generic one.
+template <int C> static const void *dc_pick_fast(int l0, int l1, int l2) {
+    if (l0 == 3 && l1 == 11 && l2 == 11) return (const void *)dc_fast_kernel<C, 3, 11, 11>;
+    if (l0 == 3 && l1 == 3 && l2 == 11) return (const void *)dc_fast_kernel<C, 3, 3, 11>;
+    if (l0 == 3 && l1 == 3 && l2 == 3) return (const void *)dc_fast_kernel<C, 3, 3, 3>;
+    if (l0 == 11 && l1 == 11 && l2 == 11) return (const void *)dc_fast_kernel<C, 11, 11, 11>;
+    if (l0 == 11 && l1 == 11 && l2 == 15) return (const void *)dc_fast_kernel<C, 11, 11, 15>;
+    return nullptr;
+}
+static const void *dc_pick_kernel(int C, int front, const DcChain &ch) {
+    const void *fn = nullptr;
+    if (ch.nstages >= 3 && front == 3 && !getenv("PEBBLE_DC_GENERIC")) {
+        if (C == 1024) fn = dc_pick_fast<1024>(ch.st[0].len, ch.st[1].len, ch.st[2].len);
+        if (C == 2048) fn = dc_pick_fast<2048>(ch.st[0].len, ch.st[1].len, ch.st[2].len);
+    }
+    if (fn) return fn;
+    return C == 512 ? (const void *)dc_fused_kernel<512> : C == 1024 ? (const void *)dc_fused_kernel<1024>
+         : C == 2048 ? (const void *)dc_fused_kernel<2048> : (const void *)dc_fused_kernel<4096>;
+}
 
 static int env_int(const char *name, int dflt) {
     const char *v = getenv(name);
@@ -51,7 +56,7 @@ static int env_int(const char *name, int dflt) {
 static void dc_update_osc(pebble_downconvert *h) {
     // downconvert.cpp:108-110
     double inc = 6.28318530717958647692528676656 * h->nco_freq / h->in_rate;
-    pebble_host::dc_set_osc(h->chain, cos(inc), sin(inc), h->threads);
+    pebble_host::dc_set_osc(h->chain, cos(inc), sin(inc), PB_DC_THREADS, h->chunk);
     h->dirty = true;
 }
 
@@ -66,10 +71,13 @@ pebble_downconvert_t *pebble_downconvert_create(void) {
     h->phase_hi = h->phase_lo = 0;   // m_Osc1 = (1,0), downconvert.cpp:75-76
     h->stream_pos = 0;
     h->in_rate = 100000.0; h->max_bw = 10000.0; h->nco_freq = 0.0; h->cw_offset = 0.0; h->out_rate = 0.0;
-    h->threads = env_int("PEBBLE_DC_THREADS", 256);
+    h->threads = PB_DC_THREADS;
     h->chunk = env_int("PEBBLE_DC_CHUNK", 1024);
+    if (h->chunk != 512 && h->chunk != 1024 && h->chunk != 2048 && h->chunk != 4096) h->chunk = 1024;
     h->front = env_int("PEBBLE_DC_FRONT", 3);
-    h->group = env_int("PEBBLE_DC_GROUP", 8);
+    h->group = env_int("PEBBLE_DC_GROUP", 4);
+    if (h->front < 1) h->front = 1;
+    if (h->group < 1) h->group = 1;
     h->stream = nullptr;
     const size_t sbytes = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX;
     if (!pebble::cuda_ok(cudaMalloc(&h->d_chain, sizeof(DcChain)), "cudaMalloc(chain)") ||
@@ -77,7 +85,8 @@ pebble_downconvert_t *pebble_downconvert_create(void) {
         !pebble::cuda_ok(cudaMalloc(&h->d_state[1], sbytes), "cudaMalloc(state)") ||
         !pebble::cuda_ok(cudaMemset(h->d_state[0], 0, sbytes), "cudaMemset") ||
         !pebble::cuda_ok(cudaMemset(h->d_state[1], 0, sbytes), "cudaMemset") ||
-        !pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) {
+        !pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !pebble::cuda_ok(cudaMemcpyToSymbol(c_hb, pebble_hb::kHalfBandTaps, sizeof(double) * 341), "cudaMemcpyToSymbol(c_hb)")) {
         pebble_downconvert_destroy(h);
         return nullptr;
     }
@@ -182,11 +191,9 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
                                                   h->phase_lo, h->stream_pos);
         pebble::count_launch();
     } else {
-        int C = h->chunk;
-        const int g = 1 << S;
-        if (C < g) C = g;
-        if (C % g || C % h->threads || C / h->threads > PB_DC_MAX_WTAB || S > 11) {
-            pebble::set_error("downconvert: unsupported chain/chunk (S=%d C=%d T=%d)", S, C, h->threads);
+        const int C = h->chunk;
+        if (S > 12 || (C >> S) < 1) {
+            pebble::set_error("downconvert: unsupported chain (S=%d, chunk=%d)", S, C);
             return PEBBLE_ERR_STATE;
         }
         DcCall call;
@@ -198,32 +205,30 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         call.phase_hi = h->phase_hi;
         call.phase_lo = h->phase_lo;
         call.stream_pos = h->stream_pos;
-        call.chunk = C;
-        call.front = h->front;
+        call.front = h->front < S ? h->front : S;
         call.group = h->group;
-        call.seg_len = n;
-        const DcSmem L = dc_smem_layout(call, S);
-        const size_t coef_bytes = ((size_t)S * 52 * sizeof(double) + 127) & ~(size_t)127;
-        const size_t smem = DC_HDR_BYTES + DC_ST_BYTES + coef_bytes + (size_t)L.total * sizeof(cpx);
-        static size_t smem_set = 0;
-        if (smem > smem_set) {
-            PB_CUDA(cudaFuncSetAttribute(dc_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                    PEBBLE_ERR_CUDA);
-            smem_set = smem;
+        const size_t smem = (size_t)dc_smem_cpx(h->chain, C, call.front, call.group) * sizeof(cpx);
+        const void *fn = dc_pick_kernel(C, call.front, h->chain);
+        if (smem > h->smem_set || fn != h->fn_set) {
+            PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
+            h->smem_set = smem;
+            h->fn_set = fn;
         }
         int occ = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dc_fused_kernel, h->threads, smem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, PB_DC_THREADS, smem);
         if (occ < 1) occ = 1;
-        // segments: about two waves of resident CTAs, never shorter than 8x the pre-roll or 16 chunks
+        // segments: one wave of resident CTAs (PEBBLE_DC_WAVES to change), never shorter than 8x the pre-roll or
+        // 16 chunks, and a whole number of chunks
         long long min_seg = (long long)h->chain.preroll * 8;
         if (min_seg < 16LL * C) min_seg = 16LL * C;
-        long long target = (long long)pebble::num_sms() * occ * env_int("PEBBLE_DC_WAVES", 2);
+        long long target = (long long)pebble::num_sms() * occ * env_int("PEBBLE_DC_WAVES", 1);
         long long seg = (n + target - 1) / target;
         if (seg < min_seg) seg = min_seg;
         seg = ((seg + C - 1) / C) * C;
         call.seg_len = seg;
         const int nseg = (int)((n + seg - 1) / seg);
-        dc_fused_kernel<<<nseg, h->threads, smem, stream>>>(h->d_chain, call);
+        void *args[2] = {(void *)&h->d_chain, (void *)&call};
+        PB_CUDA(cudaLaunchKernel(fn, dim3(nseg), dim3(PB_DC_THREADS), args, smem, stream), PEBBLE_ERR_CUDA);
         pebble::count_launch();
     }
     PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);

@@ -70,7 +70,7 @@ void dc_fill_chain(DcChain &ch, const std::vector<int> &lens) {
     ch.preroll = (int)(((mem + g - 1) / g) * g);
 }
 
-void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads) {
+void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads, int chunk) {
     // effective rotation per sample of the recursive oscillator = angle of the ROUNDED (cos, sin)
     __float128 th = atan2q((__float128)osc_sin, (__float128)osc_cos);
     const __float128 two_pi = 8 * atanq((__float128)1.0);
@@ -87,6 +87,16 @@ void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads) {
         ch.wtab[k].x = (double)cosq(a);
         ch.wtab[k].y = (double)sinq(a);
     }
+    for (int k = 0; k < PB_DC_MAX_PAIRS; ++k) {
+        __float128 a = th * (__float128)((long long)k * 2 * threads);
+        ch.wpair[k].x = (double)cosq(a);
+        ch.wpair[k].y = (double)sinq(a);
+    }
+    ch.w1.x = (double)cosq(th);
+    ch.w1.y = (double)sinq(th);
+    ch.chunk = chunk;
+    ch.wchunk.x = (double)cosq(th * (__float128)chunk);
+    ch.wchunk.y = (double)sinq(th * (__float128)chunk);
     // amplitude recurrence r_{i+1} = r_i * (1.95 - r_i^2), r_0 = 1 (downconvert.cpp:281-287)
     double r = 1.0;
     for (int i = 0; i < PB_DC_RTAB; ++i) {
@@ -94,6 +104,7 @@ void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads) {
         r = r * (1.95 - r * r);
     }
     ch.r_inf = r;
+    ch.inv_r_inf = 1.0 / r;
 }
 
 void phase_advance(uint64_t &hi, uint64_t &lo, uint64_t thi, uint64_t tlo, uint64_t k) {

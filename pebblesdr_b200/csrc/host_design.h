@@ -3,7 +3,7 @@
 // These run once per parameter change (the reference runs them on the GUI thread under a mutex);
 // all per-sample work is on the GPU.
 #pragma once
-#include "dc_core.cuh"
+#include "dc_types.h"
 #include <vector>
 
 namespace pebble_host {
@@ -14,8 +14,8 @@ double dc_plan(double in_rate, double max_bw, bool simple, std::vector<int> &len
 // Fill the stage table, coefficients and pre-roll of a DcChain from stage lengths.
 void dc_fill_chain(DcChain &ch, const std::vector<int> &lens);
 // Oscillator constants for cos/sin of the NCO increment as the reference rounds them
-// (downconvert.cpp:108-110). `threads` is the CTA size the step table is built for.
-void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads);
+// (downconvert.cpp:108-110). `threads` is the CTA size and `chunk` the chunk length the step tables are built for.
+void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads, int chunk);
 // phase (0.128 turns) += k * turn
 void phase_advance(uint64_t &hi, uint64_t &lo, uint64_t thi, uint64_t tlo, uint64_t k);
 
