@@ -1,7 +1,7 @@
 // downconvert.cu — CDownConvert on the GPU: kernel wrapper + C ABI (include/pebble_cuda.h).
 // Kernel body: dc_fused.cuh (fused NCO mix + decimate-by-2 cascade, one segment per CTA).
 #include "lib_common.h"
-#include "dc_fused.cuh"
+#include "dc_cic.cuh"
 #include "host_design.h"
 #include "hb_coefs.h"
 #include <cmath>
@@ -29,6 +29,12 @@ struct pebble_downconvert {
 
 // The specialised kernel when the three front stages are one of the instantiated combinations (every chain
 // SetDataRate plans for an input rate >= ~300x the output bandwidth starts with one of these), else the generic one.
+template <int C, int MINB> static const void *dc_pick_cic(int l1, int l2) {
+    if (l1 == 11 && l2 == 11) return (const void *)dc_cic_kernel<C, 11, 11, MINB>;
+    if (l1 == 3 && l2 == 11) return (const void *)dc_cic_kernel<C, 3, 11, MINB>;
+    if (l1 == 3 && l2 == 3) return (const void *)dc_cic_kernel<C, 3, 3, MINB>;
+    return nullptr;
+}
 template <int C> static const void *dc_pick_fast(int l0, int l1, int l2) {
     if (l0 == 3 && l1 == 11 && l2 == 11) return (const void *)dc_fast_kernel<C, 3, 11, 11>;
     if (l0 == 3 && l1 == 3 && l2 == 11) return (const void *)dc_fast_kernel<C, 3, 3, 11>;
@@ -37,8 +43,15 @@ template <int C> static const void *dc_pick_fast(int l0, int l1, int l2) {
     if (l0 == 11 && l1 == 11 && l2 == 15) return (const void *)dc_fast_kernel<C, 11, 11, 15>;
     return nullptr;
 }
-static const void *dc_pick_kernel(int C, int front, const DcChain &ch) {
+static const void *dc_pick_kernel(int C, int front, const DcChain &ch, bool *cic) {
     const void *fn = nullptr;
+    *cic = false;
+    if (ch.nstages >= 3 && front == 3 && ch.st[0].len == 3 && !getenv("PEBBLE_DC_NOCIC") && !getenv("PEBBLE_DC_GENERIC")) {
+        const bool m4 = getenv("PEBBLE_DC_MINB") && atoi(getenv("PEBBLE_DC_MINB")) == 4;
+        if (C == 1024) fn = m4 ? dc_pick_cic<1024, 4>(ch.st[1].len, ch.st[2].len) : dc_pick_cic<1024, 3>(ch.st[1].len, ch.st[2].len);
+        if (C == 2048) fn = dc_pick_cic<2048, 2>(ch.st[1].len, ch.st[2].len);
+        if (fn) { *cic = true; return fn; }
+    }
     if (ch.nstages >= 3 && front == 3 && !getenv("PEBBLE_DC_GENERIC")) {
         if (C == 1024) fn = dc_pick_fast<1024>(ch.st[0].len, ch.st[1].len, ch.st[2].len);
         if (C == 2048) fn = dc_pick_fast<2048>(ch.st[0].len, ch.st[1].len, ch.st[2].len);
@@ -72,8 +85,7 @@ pebble_downconvert_t *pebble_downconvert_create(void) {
     h->stream_pos = 0;
     h->in_rate = 100000.0; h->max_bw = 10000.0; h->nco_freq = 0.0; h->cw_offset = 0.0; h->out_rate = 0.0;
     h->threads = PB_DC_THREADS;
-    h->chunk = env_int("PEBBLE_DC_CHUNK", 1024);
-    if (h->chunk != 512 && h->chunk != 1024 && h->chunk != 2048 && h->chunk != 4096) h->chunk = 1024;
+    h->chunk = 1024;
     h->front = env_int("PEBBLE_DC_FRONT", 3);
     h->group = env_int("PEBBLE_DC_GROUP", 4);
     if (h->front < 1) h->front = 1;
@@ -112,6 +124,13 @@ static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, 
         h->max_bw = max_bw;
         h->out_rate = pebble_host::dc_plan(in_rate, max_bw, simple, h->lens);
         pebble_host::dc_fill_chain(h->chain, h->lens);
+        // chunk length: the CIC3-fused kernel amortises its per-chunk barriers best at 2048 (measured);
+        // the others at 1024. PEBBLE_DC_CHUNK overrides.
+        h->chunk = (h->chain.nstages >= 3 && h->chain.st[0].len == 3) ? 2048 : 1024;
+        {
+            const int c = env_int("PEBBLE_DC_CHUNK", 0);
+            if (c == 512 || c == 1024 || c == 2048 || c == 4096) h->chunk = c;
+        }
         // DeleteFilters + new stages: the delay lines restart from zero (downconvert.cpp:150)
         const size_t sbytes = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX;
         cudaMemset(h->d_state[0], 0, sbytes);
@@ -207,8 +226,11 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         call.stream_pos = h->stream_pos;
         call.front = h->front < S ? h->front : S;
         call.group = h->group;
-        const size_t smem = (size_t)dc_smem_cpx(h->chain, C, call.front, call.group) * sizeof(cpx);
-        const void *fn = dc_pick_kernel(C, call.front, h->chain);
+        bool cic = false;
+        const void *fn = dc_pick_kernel(C, call.front, h->chain, &cic);
+        // the CIC3-fused kernel keeps the full-rate stage in registers: no stage-0 arrays
+        const size_t smem = (size_t)(dc_smem_cpx(h->chain, C, call.front, call.group) -
+                                     (cic ? 2 * dc_stage_arr(h->chain.st[0], C) : 0)) * sizeof(cpx);
         if (smem > h->smem_set || fn != h->fn_set) {
             PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
             h->smem_set = smem;
