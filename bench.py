@@ -341,7 +341,7 @@ def main_ours(args):
             "e2e": {"value": world * n * K / (ms_e2e * 1e-3) / 1e6, "unit": UNIT,
                     "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e / K,
                     "call": "pebble_receiver_process_pinned (host buffers, H2D + chain + D2H per step)"},
-            "roofline": {"bound": "hbm", "kernel": "dc_fused_kernel (CDownConvert: NCO mix + 7-stage decimator)",
+            "roofline": {"bound": "hbm", "kernel": "dc_cic_kernel (CDownConvert: NCO mix + CIC3 fused in registers + 6 half-band stages)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(n), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": ALG_BYTES_PER_SAMPLE_DC * n, "kernel_ms": dc_ms,

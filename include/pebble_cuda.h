@@ -90,6 +90,10 @@ double pebble_downconvert_set_data_rate_simple(pebble_downconvert_t *h, double i
 void pebble_downconvert_set_frequency(pebble_downconvert_t *h, double nco_freq);
 void pebble_downconvert_set_cw_offset(pebble_downconvert_t *h, double offset);
 int pebble_downconvert_num_stages(const pebble_downconvert_t *h);
+/* Host-only planner, no device needed: the stage list CDownConvert::SetDataRate (simple = 0, downconvert.cpp:139-213)
+ * or SetDataRateSimple (simple = 1, :220-244) builds for (in_rate, max_bw). Writes up to `max` FIR lengths
+ * (3 = CIC3), stores the output rate in *out_rate (may be NULL) and returns the stage count. */
+int pebble_downconvert_plan(double in_rate, double max_bw, int simple, int *lens, int max, double *out_rate);
 /* Stage description for tests: writes up to max entries of the FIR length per stage
  * (3 = CIC3, 11 = unrolled 11-tap half-band, 15..51 = generic half-band). Returns stage count. */
 int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, int max);

@@ -37,6 +37,7 @@ SIGNATURES = {
     "pebble_downconvert_set_frequency": (None, [c_vp, c_dbl]),
     "pebble_downconvert_set_cw_offset": (None, [c_vp, c_dbl]),
     "pebble_downconvert_num_stages": (c_int, [c_vp]),
+    "pebble_downconvert_plan": (c_int, [c_dbl, c_dbl, c_int, c_vp, c_int, c_vp]),
     "pebble_downconvert_stage_lengths": (c_int, [c_vp, c_vp, c_int]),
     "pebble_downconvert_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "pebble_downconvert_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),

@@ -155,6 +155,13 @@ void pebble_downconvert_set_frequency(pebble_downconvert_t *h, double f) {
 void pebble_downconvert_set_cw_offset(pebble_downconvert_t *h, double off) {
     if (h) h->cw_offset = off;  // downconvert.h:34: takes effect at the next SetFrequency
 }
+int pebble_downconvert_plan(double in_rate, double max_bw, int simple, int *lens, int max, double *out_rate) {
+    std::vector<int> v;
+    const double r = pebble_host::dc_plan(in_rate, max_bw, simple != 0, v);
+    if (out_rate) *out_rate = r;
+    for (int i = 0; i < (int)v.size() && i < max && lens; ++i) lens[i] = v[i];
+    return (int)v.size();
+}
 int pebble_downconvert_num_stages(const pebble_downconvert_t *h) { return h ? h->chain.nstages : PEBBLE_ERR_ARG; }
 int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, int max) {
     if (!h) return PEBBLE_ERR_ARG;

@@ -1,0 +1,126 @@
+"""CPU tests (no GPU): pin the oracle.
+
+1. tests/golden/*.npz were produced by the REAL reference (unmodified pebblelib + FFTW 3.3.4 compiled from
+   /root/reference, tests/golden/make_golden.py). The C restatement (oracle/pebble_oracle.c) must reproduce every
+   fixture. This runs everywhere (the GPU box has no /root/reference).
+2. Where the real reference library exists (oracle/_ref/libpebbleref.so, built here and shipped with gpurun) it must
+   reproduce the fixtures too, and the restatement is compared with it live on larger inputs.
+
+Tolerances: relative RMS <= 1e-10 (the restatement's FFT is a textbook radix-2, the reference's is FFTW: results
+differ at 1e-15); spectrum dB <= 1e-6 on un-clipped bins; counts, rates, flags and tap counts exact."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import rel_rms
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+import make_golden  # noqa: E402
+from oracle import port, ref  # noqa: E402
+
+TOL = 1e-10
+
+
+def _check(name, got, want):
+    kind = make_golden.CASES[name]["kind"]
+    for key in want.files:
+        g, w = np.asarray(got[key]), want[key]
+        assert g.shape == w.shape, (name, key, g.shape, w.shape)
+        if key in ("counts", "flags", "ntaps", "rate"):
+            assert np.array_equal(g, w), (name, key, g, w)
+        elif kind == "spectrum":
+            clipped = (w <= -120.0) | (w >= 0.0)
+            assert np.array_equal(g[clipped], w[clipped])
+            assert np.max(np.abs(g[~clipped] - w[~clipped])) <= 1e-6
+        elif key == "cg":
+            assert abs(g[0] - w[0]) <= 1e-12 * abs(w[0])
+        else:
+            assert rel_rms(g, w) <= TOL, (name, key, rel_rms(g, w))
+
+
+@pytest.mark.parametrize("name", sorted(make_golden.CASES))
+def test_c_oracle_reproduces_reference_golden(name):
+    want = np.load(os.path.join(HERE, "golden", name + ".npz"))
+    _check(name, make_golden.run_case(make_golden.CASES[name], port), want)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libpebbleref.so not built (needs /root/reference)")
+@pytest.mark.parametrize("name", sorted(make_golden.CASES))
+def test_reference_library_reproduces_golden(name):
+    want = np.load(os.path.join(HERE, "golden", name + ".npz"))
+    _check(name, make_golden.run_case(make_golden.CASES[name], ref), want)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libpebbleref.so not built (needs /root/reference)")
+@pytest.mark.parametrize("rate,freq,calls", [(10e6, 1.2e6, [32768] * 6), (2e6, -3.5e5, [4096, 8192, 32, 20480]),
+                                             (500e3, 1e4, [2048] * 5)])
+def test_c_oracle_downconvert_vs_reference_live(rate, freq, calls):
+    from golden.signals import iq
+    n = sum(calls)
+    x = iq(n, 77, rate, [(freq + 800.0, 0.4), (-0.3 * rate, 0.5)], 0.02)
+    a, b = port.CDownConvert(), ref.CDownConvert()
+    assert a.SetDataRate(rate, 15000.0) == b.SetDataRate(rate, 15000.0)
+    a.SetFrequency(freq)
+    b.SetFrequency(freq)
+    S = a.NumStages()
+    pos = 0
+    for c in calls:
+        oa, ob = np.zeros(c >> S, complex), np.zeros(c >> S, complex)
+        assert a.ProcessData(c, x[pos:pos + c].copy(), oa) == b.ProcessData(c, x[pos:pos + c].copy(), ob) == c >> S
+        assert rel_rms(oa, ob) <= 1e-12
+        pos += c
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libpebbleref.so not built (needs /root/reference)")
+def test_c_oracle_fastfir_vs_reference_live_split_points():
+    # same stream as 1 x N, N x 2048 and ragged calls: identical counts and samples (fastfir.cpp:299-313)
+    from golden.signals import iq
+    n = 2048 * 9
+    x = iq(n, 78, 2e6, [(1e3, 0.5), (5e4, 0.5)], 0.1)
+    outs = []
+    for impl in (port, ref):
+        for calls in ([n], [2048] * 9, [5, 1019, 3072, 1, 2047, n - 6144]):
+            f = impl.CFastFIR()
+            f.SetupParameters(-3000.0, 3000.0, 0.0, 2e6)
+            got, pos = [], 0
+            for c in calls:
+                o = np.zeros(c + 2048, complex)
+                k = f.ProcessData(c, x[pos:pos + c].copy(), o)
+                got.append(o[:k].copy())
+                pos += c
+            outs.append(np.concatenate(got))
+    assert all(len(o) == n for o in outs)            # m_InBufInPos starts at 1024: 2048*9 in -> 2048*9 out
+    for o in outs[1:]:
+        assert rel_rms(o, outs[0]) <= TOL
+
+
+def test_known_answer_minus10dbfs_tone():
+    # the reference's only worked numeric example (fft.cpp:302-319): a -10 dBFS tone peaks at -10 dB
+    n = 8192
+    f = port.FFT()
+    f.fftParams(n, 0, 2e6, n, 12)
+    k = np.arange(n)
+    x = np.ascontiguousarray(10 ** (-10 / 20) * np.exp(2j * np.pi * (512 / n) * k)).astype(np.complex128)
+    db = np.zeros(n)
+    f.fftSpectrum(x, db, n)
+    f.fftSpectrum(x, db, n)                          # second frame: the 2-tap average has settled
+    assert abs(db.max() - (-10.0)) < 0.05
+    assert int(np.argmax(db)) == n // 2 + 512        # unfolded: DC at n/2 (fft.cpp:183-225)
+
+
+def test_cpu_chain_matches_receiver_restatement():
+    # bench.py's CPU baseline chain (reference CDownConvert+CFastFIR when available) == oracle receiver restatement
+    from bench import synth_numpy
+    from oracle import cpu_chain
+    n = 32768 * 12
+    x = synth_numpy(n)
+    o = port.Receiver(10e6, 2048, 15000.0)
+    o.config(1.2e6, -5000.0, 5000.0, 0, 0, 20)
+    o.setAmBandwidth(10000.0)
+    want = np.concatenate([o.processIQData(x[i:i + 32768], 32768) for i in range(0, n, 32768)])
+    got = cpu_chain.CpuChain().run(x.copy())
+    assert len(got) == len(want) == (n >> 7) // 2048 * 2048
+    assert rel_rms(got, want) <= TOL
