@@ -216,6 +216,41 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
 /* in/out are page-locked HOST buffers; copies and kernels are enqueued on `stream` without synchronising */
 int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const double *in, double *out, void *stream);
 
+/* ---- Batched forms (library extensions for BASELINE config 4; no single reference counterpart) -------------------------
+ * nch CDownConvert objects with the same (InRate, MaxBW) and one NCO each, run in one launch over ONE input stream:
+ * set_channels <-> nch x CDownConvert::CDownConvert + SetDataRate, set_channel_frequency <-> SetFrequency of object
+ * `ch`, process_channels_device <-> ProcessData of every object on the same input; outputs are [channel][n >> S] rows
+ * `out_stride` CPX apart. Needs a chain that starts with CIC3 (in_rate >= ~667 x max_bw), else PEBBLE_ERR_STATE. */
+int pebble_downconvert_set_channels(pebble_downconvert_t *h, int nch);
+int pebble_downconvert_set_channel_frequency(pebble_downconvert_t *h, int ch, double nco_freq);
+int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+                                               long long out_stride, void *stream);
+/* `streams` independent CFastFIR objects sharing one filter: stream s reads row s of d_in (rows in_stride CPX apart). */
+int pebble_fastfir_set_streams(pebble_fastfir_t *h, int streams);
+int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double *d_in, long long in_stride, double *d_out,
+                                        long long out_stride, void *stream);
+
+/* ---- Channelizer: nch receiver chains (receiver.cpp:903-996) over one wideband capture, BASELINE config 4 ----------------
+ * Every channel = CDownConvert(own mixer frequency) -> gain restore -> CFastFIR(lo,hi) -> AGC_OFF(threshold) -> Demod(mode),
+ * framesPerBuffer 2048. Channel-major device output: row `ch` holds that channel's demodulated samples. Channels shard
+ * across GPUs by giving each rank its own channelizer over its channel range (no data-path collective). */
+typedef struct pebble_channelizer pebble_channelizer_t;
+pebble_channelizer_t *pebble_channelizer_create(int nchannels, double in_rate, double max_bw);
+void pebble_channelizer_destroy(pebble_channelizer_t *h);
+double pebble_channelizer_out_rate(const pebble_channelizer_t *h);
+int pebble_channelizer_num_stages(const pebble_channelizer_t *h);
+int pebble_channelizer_num_channels(const pebble_channelizer_t *h);
+int pebble_channelizer_set_frequency(pebble_channelizer_t *h, int ch, double freq);
+int pebble_channelizer_set_filter(pebble_channelizer_t *h, double lo, double hi);
+int pebble_channelizer_set_demod_mode(pebble_channelizer_t *h, int ch, int mode);   /* 0 dmAM, 2 dmFMN (PLL), >= 5 pass-through */
+int pebble_channelizer_set_am_bandwidth(pebble_channelizer_t *h, double bandwidth);
+int pebble_channelizer_set_agc_threshold(pebble_channelizer_t *h, int threshold);
+int pebble_channelizer_out_count(const pebble_channelizer_t *h, int n);
+int pebble_channelizer_downconvert_device(pebble_channelizer_t *h, int n, const double *d_in, double *d_out,
+                                          long long out_stride, void *stream);
+int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const double *d_in, double *d_out, long long out_stride,
+                                      void *stream);
+
 #ifdef __cplusplus
 }
 #endif

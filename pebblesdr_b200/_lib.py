@@ -81,6 +81,25 @@ SIGNATURES = {
     "pebble_demod_is_passthrough": (c_int, [c_vp]),
     "pebble_demod_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "pebble_demod_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    # batched forms + channelizer
+    "pebble_downconvert_set_channels": (c_int, [c_vp, c_int]),
+    "pebble_downconvert_set_channel_frequency": (c_int, [c_vp, c_int, c_dbl]),
+    "pebble_downconvert_process_channels_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_fastfir_set_streams": (c_int, [c_vp, c_int]),
+    "pebble_fastfir_process_batch_device": (c_int, [c_vp, c_int, c_vp, ctypes.c_longlong, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_channelizer_create": (c_vp, [c_int, c_dbl, c_dbl]),
+    "pebble_channelizer_destroy": (None, [c_vp]),
+    "pebble_channelizer_out_rate": (c_dbl, [c_vp]),
+    "pebble_channelizer_num_stages": (c_int, [c_vp]),
+    "pebble_channelizer_num_channels": (c_int, [c_vp]),
+    "pebble_channelizer_set_frequency": (c_int, [c_vp, c_int, c_dbl]),
+    "pebble_channelizer_set_filter": (c_int, [c_vp, c_dbl, c_dbl]),
+    "pebble_channelizer_set_demod_mode": (c_int, [c_vp, c_int, c_int]),
+    "pebble_channelizer_set_am_bandwidth": (c_int, [c_vp, c_dbl]),
+    "pebble_channelizer_set_agc_threshold": (c_int, [c_vp, c_int]),
+    "pebble_channelizer_out_count": (c_int, [c_vp, c_int]),
+    "pebble_channelizer_downconvert_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_channelizer_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
     # Receiver chain
     "pebble_receiver_create": (c_vp, [c_dbl, c_int]),
     "pebble_receiver_destroy": (None, [c_vp]),

@@ -92,7 +92,11 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
     }
     __syncthreads();
 
-    const long long seg = blockIdx.x;
+    const int chn = call.nch > 1 ? (int)(blockIdx.x % (unsigned)call.nch) : 0;
+    const long long seg = call.nch > 1 ? blockIdx.x / (unsigned)call.nch : blockIdx.x;
+    const cpx *state_in = call.state_in + (long long)chn * call.state_stride;
+    cpx *state_out = call.state_out + (long long)chn * call.state_stride;
+    cpx *gout = call.out + chn * call.out_stride;
     const long long seg_begin = seg * call.seg_len;
     long long seg_end = seg_begin + call.seg_len;
     if (seg_end > call.n) seg_end = call.n;
@@ -104,12 +108,12 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
     for (int s = 1; s < S; ++s) {
         const int hist = 2 * bhh[s];
         for (int i = tid; i < hist; i += T)
-            smem[((i & 1) ? bod[s] : bev[s]) + dc_slot(i >> 1)] = seg == 0 ? call.state_in[s * PB_DC_PREFIX + i] : cpx_make(0.0, 0.0);
+            smem[((i & 1) ? bod[s] : bev[s]) + dc_slot(i >> 1)] = seg == 0 ? state_in[s * PB_DC_PREFIX + i] : cpx_make(0.0, 0.0);
     }
     // stage 0 (CIC3) state = the last mixed pair (downconvert.cpp:528-531): B of that pair, used by thread 0 of chunk 0
     cpx b_state = cpx_make(0.0, 0.0);
     if (seg == 0) {
-        const cpx e = call.state_in[0], o = call.state_in[1];
+        const cpx e = state_in[0], o = state_in[1];
         b_state = cpx_make(fma(.375, o.x, .125 * e.x), fma(.375, o.y, .125 * e.y));
     }
 
@@ -118,7 +122,11 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
     // chunks that must take the guarded path because the oscillator amplitude is still converging
     const long long tr = PB_DC_RTAB - (call.stream_pos + start);
     const int n_transient = tr > 0 ? (int)((tr + C - 1) / C) : 0;
-    const cpx w1 = ch->w1, w2 = cpx_mul(w1, w1), wchunk = ch->wchunk;
+    const cpx w1 = call.chan ? call.chan[chn].w1 : ch->w1, w2 = cpx_mul(w1, w1);
+    const cpx wchunk = call.chan ? call.chan[chn].wchunk : ch->wchunk;
+    const uint64_t turn_hi = call.chan ? call.chan[chn].turn_hi : ch->turn_hi, turn_lo = call.chan ? call.chan[chn].turn_lo : ch->turn_lo;
+    const uint64_t phase_hi = call.chan ? call.chan[chn].phase_hi : call.phase_hi;
+    const uint64_t phase_lo = call.chan ? call.chan[chn].phase_lo : call.phase_lo;
     const double rinf = ch->r_inf;
     int sl[K];   // slot of this thread's q-th CIC3 output inside stage 1's arrays (even q -> EV1, odd q -> OD1)
 #pragma unroll
@@ -169,7 +177,7 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
             }
         }
         if ((ci & 31) == 0) {
-            seed = cpx_scale(dc_phase_to_osc(dc_phase_at(call.phase_hi, call.phase_lo, ch->turn_hi, ch->turn_lo,
+            seed = cpx_scale(dc_phase_to_osc(dc_phase_at(phase_hi, phase_lo, turn_hi, turn_lo,
                                                          (uint64_t)(pos + NS * tid + 1))), rinf);
         } else {
             seed = cpx_mul(seed, wchunk);
@@ -185,8 +193,8 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
 #pragma unroll
                 for (int q = 0; q < K; ++q) smem[sl[q]] = y[q];
                 if (last_seg && ci == nchunks - 1 && NS * tid + NS == len) {   // CIC3 delay line for the next call
-                    call.state_out[0] = ml0;
-                    call.state_out[1] = ml1;
+                    state_out[0] = ml0;
+                    state_out[1] = ml1;
                 }
             }
         }
@@ -206,7 +214,7 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
             const int nout = len >> 3;
             if (4 * tid < nout) {
                 if (S > 3) dc_tile4<L2>(e_t + EV2, e_t + OD2, tid, nout, SmemSink{smem + bev[3], smem + bod[3], bhh[3] + (accF >> 1)});
-                else dc_tile4<L2>(e_t + EV2, e_t + OD2, tid, nout, GlobalSink{call.out, pos >> 3, first_out});
+                else dc_tile4<L2>(e_t + EV2, e_t + OD2, tid, nout, GlobalSink{gout, pos >> 3, first_out});
             }
             dc_carry2(smem + EV1, smem + OD1, HH1, len >> 1);
         }
@@ -223,7 +231,7 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
                     if (4 * tid < nout) {
                         if (s == S - 1)
                             dc_tile4_rt(blen[s], e_t + bev[s], e_t + bod[s], tid, nout,
-                                        GlobalSink{call.out, group_pos >> (s + 1), first_out});
+                                        GlobalSink{gout, group_pos >> (s + 1), first_out});
                         else
                             dc_tile4_rt(blen[s], e_t + bev[s], e_t + bod[s], tid, nout,
                                         SmemSink{smem + bev[s + 1], smem + bod[s + 1], bhh[s + 1]});
@@ -246,7 +254,7 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_cic_kernel(const DcCha
         for (int s = 1; s < S; ++s) {
             const int hist = 2 * bhh[s];
             for (int i = tid; i < hist; i += T)
-                call.state_out[s * PB_DC_PREFIX + i] = smem[((i & 1) ? bod[s] : bev[s]) + dc_slot(i >> 1)];
+                state_out[s * PB_DC_PREFIX + i] = smem[((i & 1) ? bod[s] : bev[s]) + dc_slot(i >> 1)];
         }
     }
 }

@@ -42,6 +42,13 @@ struct DcChain {
     double rtab[PB_DC_RTAB];     // r_i for stream sample i < PB_DC_RTAB (exact recurrence)
 };
 
+// Per-channel oscillator of the batched (multi-channel) form: all channels share the stage chain of one DcChain,
+// each has its own NCO. phase = oscillator phase before sample 0 of the call.
+struct DcChan {
+    uint64_t turn_hi, turn_lo, phase_hi, phase_lo;
+    cpx w1, wchunk;
+};
+
 // Per-call arguments of the fused kernel.
 struct DcCall {
     const cpx *in;       // n input samples
@@ -54,6 +61,12 @@ struct DcCall {
     long long stream_pos;         // samples mixed since the oscillator was created (for rtab)
     int front;           // F: stages 0..F-1 run every chunk
     int group;           // G: stages F..S-1 run every G chunks on the accumulated samples
+    // batched form (dc_cic_kernel only): blockIdx.x = segment * nch + channel, so that the CTAs resident at the
+    // same time read the SAME input segments (served by L2) for different channels
+    const DcChan *chan;       // nullptr: single channel, oscillator from DcChain + phase_hi/lo above
+    int nch;                  // channels (>= 1)
+    int state_stride;         // cpx between two channels' carried state
+    long long out_stride;     // cpx between two channels' outputs
 };
 
 // 128-bit phase: (hi,lo) + k*(thi,tlo), returns the top 64 bits.

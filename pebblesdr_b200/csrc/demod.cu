@@ -12,253 +12,7 @@
 #include <cstring>
 #include <vector>
 
-#define PB_FIR_MAX 75
-#define PB_SCAN_THREADS 256
-#define PB_SCAN_PER 8
-#define PB_SCAN_TILE (PB_SCAN_THREADS * PB_SCAN_PER)
-
-// ---- CFir ---------------------------------------------------------------------------------------
-// virtual stream = hist (ntaps-1 samples) ++ in; out[i] = sum_k h[k] * xv[i + ntaps-1 - k]
-__global__ void cfir_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, const double *__restrict__ hI,
-                            const double *__restrict__ hQ, int ntaps, cpx *__restrict__ out) {
-    __shared__ double sI[PB_FIR_MAX], sQ[PB_FIR_MAX];
-    for (int k = threadIdx.x; k < ntaps; k += blockDim.x) { sI[k] = hI[k]; sQ[k] = hQ[k]; }
-    __syncthreads();
-    const int h = ntaps - 1;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        double re = 0.0, im = 0.0;
-        for (int k = 0; k < ntaps; ++k) {
-            const int v = i + h - k;  // index into the virtual stream
-            const cpx x = v < h ? hist[v] : in[v - h];
-            re += sI[k] * x.x;
-            im += sQ[k] * x.y;
-        }
-        out[i] = cpx_make(re, im);
-    }
-}
-__global__ void cfir_state_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, int h,
-                                  cpx *__restrict__ new_hist) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < h) {
-        const int v = n + i;  // last h samples of hist ++ in
-        new_hist[i] = v < h ? hist[v] : in[v - h];
-    }
-}
-
-// ---- affine scan helpers (d <- A*d + B composition) ---------------------------------------------------
-struct Aff { double a, b; };
-__device__ __forceinline__ Aff aff_then(Aff first, Aff second) {  // apply `first`, then `second`
-    Aff r;
-    r.a = first.a * second.a;
-    r.b = second.a * first.b + second.b;
-    return r;
-}
-// Exclusive scan of per-thread maps over the CTA (in thread order). Returns the composition of all
-// lower-numbered threads' maps; *total (valid in every thread) = composition of all threads' maps.
-__device__ __forceinline__ Aff block_aff_exclusive(Aff mine, Aff *total) {
-    __shared__ Aff warp_tot[PB_SCAN_THREADS / 32];
-    __shared__ Aff warp_pre[PB_SCAN_THREADS / 32 + 1];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    Aff inc = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        Aff o;
-        o.a = __shfl_up_sync(0xffffffffu, inc.a, d);
-        o.b = __shfl_up_sync(0xffffffffu, inc.b, d);
-        if (lane >= d) inc = aff_then(o, inc);
-    }
-    if (lane == 31) warp_tot[w] = inc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        Aff run; run.a = 1.0; run.b = 0.0;
-        for (int i = 0; i < PB_SCAN_THREADS / 32; ++i) { warp_pre[i] = run; run = aff_then(run, warp_tot[i]); }
-        warp_pre[PB_SCAN_THREADS / 32] = run;
-    }
-    __syncthreads();
-    Aff ex;
-    ex.a = __shfl_up_sync(0xffffffffu, inc.a, 1);
-    ex.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
-    if (lane == 0) { ex.a = 1.0; ex.b = 0.0; }
-    *total = warp_pre[PB_SCAN_THREADS / 32];
-    return aff_then(warp_pre[w], ex);
-}
-
-// ---- Demod_AM::processBlockFiltered, demod_am.cpp:40-59 ------------------------------------------------
-// d_n = alpha*d_{n-1} + |x_n| ; y_n = d_n - d_{n-1} ; out = (y, y)
-// pass 1: per-tile aggregate map; pass 2: serial carry over tiles; pass 3: apply.
-__global__ void __launch_bounds__(PB_SCAN_THREADS) am_tile_kernel(const cpx *__restrict__ in, int n, double alpha,
-                                                                  Aff *__restrict__ tile_map) {
-    const int base = blockIdx.x * PB_SCAN_TILE + threadIdx.x * PB_SCAN_PER;
-    Aff m; m.a = 1.0; m.b = 0.0;
-#pragma unroll
-    for (int k = 0; k < PB_SCAN_PER; ++k) {
-        if (base + k < n) {
-            const cpx x = in[base + k];
-            m.b = alpha * m.b + sqrt(x.x * x.x + x.y * x.y);  // DB::amplitude, db.h:28-30
-            m.a *= alpha;
-        }
-    }
-    Aff tot;
-    block_aff_exclusive(m, &tot);
-    if (threadIdx.x == 0) tile_map[blockIdx.x] = tot;
-}
-__global__ void am_carry_kernel(const Aff *__restrict__ tile_map, int ntiles, const double *__restrict__ d_last_in,
-                                double *__restrict__ carry) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        double d = *d_last_in;
-        for (int t = 0; t < ntiles; ++t) {
-            carry[t] = d;
-            d = tile_map[t].a * d + tile_map[t].b;
-        }
-    }
-}
-__global__ void __launch_bounds__(PB_SCAN_THREADS) am_apply_kernel(const cpx *__restrict__ in, int n, double alpha,
-                                                                   const double *__restrict__ carry,
-                                                                   cpx *__restrict__ out, double *__restrict__ d_last_out) {
-    const int base = blockIdx.x * PB_SCAN_TILE + threadIdx.x * PB_SCAN_PER;
-    double mag[PB_SCAN_PER];
-    Aff m; m.a = 1.0; m.b = 0.0;
-#pragma unroll
-    for (int k = 0; k < PB_SCAN_PER; ++k) {
-        mag[k] = 0.0;
-        if (base + k < n) {
-            const cpx x = in[base + k];
-            mag[k] = sqrt(x.x * x.x + x.y * x.y);
-            m.b = alpha * m.b + mag[k];
-            m.a *= alpha;
-        }
-    }
-    Aff tot;
-    const Aff ex = block_aff_exclusive(m, &tot);
-    double d = ex.a * carry[blockIdx.x] + ex.b;  // m_amDcLast entering this thread's first sample
-#pragma unroll
-    for (int k = 0; k < PB_SCAN_PER; ++k) {
-        if (base + k < n) {
-            const double dn = (alpha * d) + mag[k];  // demod_am.cpp:52
-            const double y = dn - d;                 // demod_am.cpp:53
-            d = dn;
-            out[base + k] = cpx_make(y, y);
-            if (base + k == n - 1) *d_last_out = d;
-        }
-    }
-}
-
-// ---- AGC_OFF / gain: out = g * in (agc.cpp:86-94, receiver.cpp:935-938) ---------------------------------
-__global__ void scale_kernel(const cpx *__restrict__ in, int n, double g, cpx *__restrict__ out) {
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = cpx_scale(in[i], g);
-}
-
-// ---- Demod_NFM::processBlockFM2, demod_nfm.cpp:124-140 (phase difference) --------------------------------
-__device__ __forceinline__ double phase_cpx(cpx c) {  // CpxUtil::phaseCpx, cpx.cpp:5-21
-    double tmp = atan(c.y / ((c.x == 0) ? 1e-200 : c.x));
-    if (c.x < 0 && c.y < 0) tmp -= 3.14159265358979323846;
-    else if (c.x < 0 && c.y >= 0) tmp += 3.14159265358979323846;
-    return tmp;
-}
-__global__ void fm2_kernel(const cpx *__restrict__ in, int n, const cpx *__restrict__ last_in, cpx *__restrict__ out,
-                           cpx *__restrict__ last_out) {
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const cpx prev = i ? in[i - 1] : *last_in;
-        const cpx prod = cpx_mulc(in[i], prev);
-        const double v = phase_cpx(prod) * .0005;
-        out[i] = cpx_make(v, v);
-        if (i == n - 1) *last_out = in[i];
-    }
-}
-
-// ---- Demod_NFM::processBlockNCO, demod_nfm.cpp:225-257 (PLL; state and constants are `float`) ----------
-struct PllConst { float alpha, beta, dc_alpha, lo, hi, out_gain; };
-struct PllState { float phase, freq, dc; };
-// one thread per stream; stream s occupies in[s*stride .. s*stride + n)
-__global__ void pll_kernel(const cpx *__restrict__ in, int n, long long stride, int nstreams, PllConst c,
-                           PllState *__restrict__ st, cpx *__restrict__ out) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= nstreams) return;
-    PllState v = st[s];
-    const cpx *x = in + (long long)s * stride;
-    cpx *y = out + (long long)s * stride;
-    for (int i = 0; i < n; ++i) {
-        // sin/cos of a float resolve to the float overloads in the reference build
-        const double ncoSin = (double)sinf(v.phase);
-        const double ncoCos = (double)cosf(v.phase);
-        const cpx xi = x[i];
-        const double tr = ncoCos * xi.x - ncoSin * xi.y;
-        const double ti = ncoCos * xi.y + ncoSin * xi.x;
-        const double phzerror = -atan2(ti, tr);
-        v.freq = (float)((double)v.freq + ((double)c.beta * phzerror));
-        if (v.freq > c.hi) v.freq = c.hi;
-        else if (v.freq < c.lo) v.freq = c.lo;
-        v.phase = (float)((double)v.phase + ((double)v.freq + (double)c.alpha * phzerror));
-        v.dc = (float)((1.0 - (double)c.dc_alpha) * (double)v.dc + (double)c.dc_alpha * (double)v.freq);
-        const float o = (v.freq - v.dc) * c.out_gain;
-        y[i] = cpx_make((double)o, 0.0);  // CPX = float: imaginary part is zero
-    }
-    v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
-    st[s] = v;
-}
-
-// ---- AGC::processBlock, agc.cpp:84-207 (modes other than OFF) --------------------------------------------
-#define PB_AGC_BUF 2048  // MAX_DELAY_BUF, agc.h:27
-struct AgcState {
-    int sig_ptr, mag_pos, hang_timer, pad;
-    double peak, attack_avg, decay_avg;
-};
-__global__ void agc_kernel(const cpx *__restrict__ in, int n, long long stride, int nstreams, pebble_host::AgcParams p,
-                           AgcState *__restrict__ st, cpx *__restrict__ sig_buf, double *__restrict__ mag_buf,
-                           cpx *__restrict__ out) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= nstreams) return;
-    AgcState v = st[s];
-    cpx *sig = sig_buf + (long long)s * PB_AGC_BUF;
-    double *mb = mag_buf + (long long)s * PB_AGC_BUF;
-    const cpx *x = in + (long long)s * stride;
-    cpx *y = out + (long long)s * stride;
-    const double min_const = (double)1e-8f;   // MIN_CONSTANT is a float constant, agc.h:58
-    const double outscale = (double)0.7f;     // AGC_OUTSCALE, agc.h:49
-    for (int i = 0; i < n; ++i) {
-        const cpx xin = x[i];
-        const cpx delayed = sig[v.sig_ptr];
-        sig[v.sig_ptr++] = xin;
-        if (v.sig_ptr >= p.delay_samples) v.sig_ptr = 0;
-        double mag = fabs(xin.x);
-        const double mim = fabs(xin.y);
-        if (mim > mag) mag = mim;
-        mag = log10(mag + min_const);  // - log10(MAX_AMPLITUDE) == 0
-        double tmp = mb[v.mag_pos];
-        mb[v.mag_pos++] = mag;
-        if (v.mag_pos >= p.window_samples) v.mag_pos = 0;
-        if (mag > v.peak) {
-            v.peak = mag;
-        } else if (tmp == v.peak) {
-            v.peak = -8.0;
-            for (int k = 0; k < p.window_samples; ++k) {
-                tmp = mb[k];
-                if (tmp > v.peak) v.peak = tmp;
-            }
-        }
-        if (v.peak > v.attack_avg) v.attack_avg = (1.0 - p.attack_rise) * v.attack_avg + p.attack_rise * v.peak;
-        else v.attack_avg = (1.0 - p.attack_fall) * v.attack_avg + p.attack_fall * v.peak;
-        if (p.use_hang) {
-            if (v.peak > v.decay_avg) {
-                v.decay_avg = (1.0 - p.decay_rise) * v.decay_avg + p.decay_rise * v.peak;
-                v.hang_timer = 0;
-            } else if (v.hang_timer < p.hang_time) {
-                v.hang_timer++;
-            } else {
-                v.decay_avg = (1.0 - p.decay_fall) * v.decay_avg + p.decay_fall * v.peak;
-            }
-        } else {
-            if (v.peak > v.decay_avg) v.decay_avg = (1.0 - p.decay_rise) * v.decay_avg + p.decay_rise * v.peak;
-            else v.decay_avg = (1.0 - p.decay_fall) * v.decay_avg + p.decay_fall * v.peak;
-        }
-        mag = v.attack_avg > v.decay_avg ? v.attack_avg : v.decay_avg;
-        double gain;
-        if (mag <= p.knee) gain = p.fixed_gain;
-        else gain = outscale * pow(10.0, mag * (p.gain_slope - 1.0));
-        y[i] = cpx_make(delayed.x * gain, delayed.y * gain);
-    }
-    st[s] = v;
-}
+#include "demod_kernels.cuh"
 
 // =====================================================================================================
 // host side

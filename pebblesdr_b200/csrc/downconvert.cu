@@ -22,6 +22,13 @@ struct pebble_downconvert {
     std::vector<int> lens;
     int threads, chunk, front, group;
     size_t smem_set = 0;
+    // batched (multi-channel) form: nch NCOs sharing this object's stage chain
+    int nch = 0;
+    std::vector<DcChan> chans;      // host copy (phase = before sample 0 of the next call)
+    std::vector<double> chan_freq;  // m_NcoFreq per channel (already negated, downconvert.cpp:105-108)
+    DcChan *d_chans = nullptr;
+    cpx *d_cstate[2] = {nullptr, nullptr};
+    int ccur = 0;
     const void *fn_set = nullptr;
     cudaStream_t stream;    // for the host-pointer entry point
     pebble::Staging stg;
@@ -112,8 +119,18 @@ void pebble_downconvert_destroy(pebble_downconvert_t *h) {
     if (h->d_state[0]) cudaFree(h->d_state[0]);
     if (h->d_state[1]) cudaFree(h->d_state[1]);
     if (h->stream) cudaStreamDestroy(h->stream);
+    cudaFree(h->d_chans); cudaFree(h->d_cstate[0]); cudaFree(h->d_cstate[1]);
     h->stg.release();
     delete h;
+}
+
+static void dc_chan_set_freq(pebble_downconvert *h, int k) {
+    // same rounding path as SetFrequency: inc -> cos/sin doubles -> effective angle of the recursive oscillator
+    const double inc = 6.28318530717958647692528676656 * h->chan_freq[k] / h->in_rate;
+    static thread_local DcChain tmp;
+    pebble_host::dc_set_osc(tmp, cos(inc), sin(inc), PB_DC_THREADS, h->chunk);
+    DcChan &c = h->chans[k];
+    c.turn_hi = tmp.turn_hi; c.turn_lo = tmp.turn_lo; c.w1 = tmp.w1; c.wchunk = tmp.wchunk;
 }
 
 static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, bool simple) {
@@ -138,6 +155,12 @@ static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, 
         // SetFrequency(m_NcoFreq) (downconvert.cpp:210): NOTE it negates the stored value again
         h->nco_freq = -h->nco_freq + h->cw_offset;
         dc_update_osc(h);
+        for (int k = 0; k < h->nch; ++k) dc_chan_set_freq(h, k);
+        if (h->nch) {
+            const size_t cb = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX * (size_t)h->nch;
+            cudaMemset(h->d_cstate[0], 0, cb);
+            cudaMemset(h->d_cstate[1], 0, cb);
+        }
     }
     return h->out_rate;
 }
@@ -233,6 +256,10 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         call.stream_pos = h->stream_pos;
         call.front = h->front < S ? h->front : S;
         call.group = h->group;
+        call.chan = nullptr;
+        call.nch = 1;
+        call.state_stride = 0;
+        call.out_stride = 0;
         bool cic = false;
         const void *fn = dc_pick_kernel(C, call.front, h->chain, &cic);
         // the CIC3-fused kernel keeps the full-rate stage in registers: no stage-0 arrays
@@ -306,6 +333,100 @@ int pebble_downconvert_set_state(pebble_downconvert_t *h, const void *buf, int64
     PB_CUDA(cudaMemcpy(h->d_state[h->cur], (const char *)buf + 24, sizeof(cpx) * PB_DC_PREFIX * h->chain.nstages,
                        cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
     return 0;
+}
+
+
+// ---- batched form: nch channels = nch CDownConvert objects with the same (InRate, MaxBW) and their own NCO ---------
+int pebble_downconvert_set_channels(pebble_downconvert_t *h, int nch) {
+    if (!h || nch < 1) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    cudaFree(h->d_chans); cudaFree(h->d_cstate[0]); cudaFree(h->d_cstate[1]);
+    h->d_chans = nullptr; h->d_cstate[0] = h->d_cstate[1] = nullptr; h->nch = 0;
+    const size_t cb = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX * (size_t)nch;
+    PB_CUDA(cudaMalloc(&h->d_chans, sizeof(DcChan) * (size_t)nch), PEBBLE_ERR_CUDA);
+    for (int b = 0; b < 2; ++b) {
+        PB_CUDA(cudaMalloc(&h->d_cstate[b], cb), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaMemset(h->d_cstate[b], 0, cb), PEBBLE_ERR_CUDA);
+    }
+    h->nch = nch; h->ccur = 0;
+    h->chans.assign(nch, DcChan());
+    h->chan_freq.assign(nch, 0.0);
+    for (int k = 0; k < nch; ++k) {
+        h->chans[k].phase_hi = h->chans[k].phase_lo = 0;   // m_Osc1 = (1,0)
+        dc_chan_set_freq(h, k);
+    }
+    h->stream_pos = 0;
+    return 0;
+}
+int pebble_downconvert_set_channel_frequency(pebble_downconvert_t *h, int ch, double f) {
+    if (!h || ch < 0 || ch >= h->nch) return PEBBLE_ERR_ARG;
+    h->chan_freq[ch] = -f + h->cw_offset;   // downconvert.cpp:105-108; the phase is NOT reset
+    dc_chan_set_freq(h, ch);
+    return 0;
+}
+int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+                                               long long out_stride, void *stream_v) {
+    if (!h || n < 0 || (n && (!d_in || !d_out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
+    if (h->nch < 1) { pebble::set_error("downconvert: set_channels not called"); return PEBBLE_ERR_STATE; }
+    if (n == 0) return 0;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    const int S = h->chain.nstages, C = h->chunk;
+    if (n & ((1 << S) - 1)) { pebble::set_error("downconvert: n=%d is not a multiple of 2^%d", n, S); return PEBBLE_ERR_ARG; }
+    if (out_stride < (n >> S)) { pebble::set_error("downconvert: out_stride smaller than the output count"); return PEBBLE_ERR_ARG; }
+    bool cic = false;
+    const int front = h->front < S ? h->front : S;
+    const void *fn = dc_pick_kernel(C, front, h->chain, &cic);
+    if (!cic) {
+        pebble::set_error("downconvert: the batched form needs a chain that starts with CIC3 (input rate >= ~667x max_bw)");
+        return PEBBLE_ERR_STATE;
+    }
+    if (h->dirty) {
+        PB_CUDA(cudaMemcpyAsync(h->d_chain, &h->chain, sizeof(DcChain), cudaMemcpyHostToDevice, stream), PEBBLE_ERR_CUDA);
+        h->dirty = false;
+    }
+    PB_CUDA(cudaMemcpyAsync(h->d_chans, h->chans.data(), sizeof(DcChan) * (size_t)h->nch, cudaMemcpyHostToDevice, stream),
+            PEBBLE_ERR_CUDA);
+    DcCall call;
+    call.in = (const cpx *)d_in;
+    call.out = (cpx *)d_out;
+    call.state_in = h->d_cstate[h->ccur];
+    call.state_out = h->d_cstate[h->ccur ^ 1];
+    call.n = n;
+    call.phase_hi = call.phase_lo = 0;
+    call.stream_pos = h->stream_pos;
+    call.front = front;
+    call.group = h->group;
+    call.chan = h->d_chans;
+    call.nch = h->nch;
+    call.state_stride = PB_DC_MAX_STAGES * PB_DC_PREFIX;
+    call.out_stride = out_stride;
+    const size_t smem = (size_t)(dc_smem_cpx(h->chain, C, front, call.group) - 2 * dc_stage_arr(h->chain.st[0], C)) * sizeof(cpx);
+    if (smem > h->smem_set || fn != h->fn_set) {
+        PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
+        h->smem_set = smem;
+        h->fn_set = fn;
+    }
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, PB_DC_THREADS, smem);
+    if (occ < 1) occ = 1;
+    // segments: at least 8x the pre-roll; enough (segment, channel) CTAs for ~4 waves when there are few channels
+    long long min_seg = (long long)h->chain.preroll * 8;
+    if (min_seg < 16LL * C) min_seg = 16LL * C;
+    long long want = ((long long)pebble::num_sms() * occ * 4 + h->nch - 1) / h->nch;
+    if (want < 1) want = 1;
+    long long seg = (n + want - 1) / want;
+    if (seg < min_seg) seg = min_seg;
+    seg = ((seg + C - 1) / C) * C;
+    call.seg_len = seg;
+    const long long nseg = (n + seg - 1) / seg;
+    void *args[2] = {(void *)&h->d_chain, (void *)&call};
+    PB_CUDA(cudaLaunchKernel(fn, dim3((unsigned)(nseg * h->nch)), dim3(PB_DC_THREADS), args, smem, stream), PEBBLE_ERR_CUDA);
+    pebble::count_launch();
+    h->ccur ^= 1;
+    for (int k = 0; k < h->nch; ++k)
+        pebble_host::phase_advance(h->chans[k].phase_hi, h->chans[k].phase_lo, h->chans[k].turn_hi, h->chans[k].turn_lo, (uint64_t)n);
+    h->stream_pos += n;
+    return n >> S;
 }
 
 }  // extern "C"

@@ -18,11 +18,15 @@ template <int N>
 __global__ void __launch_bounds__(FftPlan<N>::THREADS)
 fastfir_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
                const cpx *__restrict__ hpos, const cpx *__restrict__ tw, int nblocks, double in_scale,
-               double out_scale) {
+               double out_scale, long long in_stride, long long out_stride, int state_stride) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx *a = reinterpret_cast<cpx *>(smem_raw);
     constexpr int L = N / 2;
     constexpr int SH = FftPlan<N>::SH;
+    // batched form: blockIdx.y = independent stream (own overlap state, own rows of in/out), same filter
+    state += (long long)blockIdx.y * state_stride;
+    in += blockIdx.y * in_stride;
+    out += blockIdx.y * out_stride;
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const long long v0 = (long long)blk * L;
         for (int i = threadIdx.x; i < N; i += blockDim.x)
@@ -54,7 +58,11 @@ fastfir_filter_kernel(const cpx *__restrict__ taps, cpx *__restrict__ hpos, cons
 
 // new_state[i] = V[start + i], V = state ++ in
 __global__ void fastfir_state_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in,
-                                     cpx *__restrict__ new_state, long long start, int count) {
+                                     cpx *__restrict__ new_state, long long start, int count, long long in_stride,
+                                     int state_stride) {
+    state += (long long)blockIdx.y * state_stride;
+    new_state += (long long)blockIdx.y * state_stride;
+    in += blockIdx.y * in_stride;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) new_state[i] = vs_load(state, s0, in, start + i);
 }
@@ -65,6 +73,7 @@ struct pebble_fastfir {
     double lo, hi, offset, fs;
     cpx *d_tw, *d_hpos, *d_taps, *d_state[2];
     int cur, fill;
+    int streams;          // independent streams sharing this filter (batched form); state is streams x N cpx
     bool have_filter;
     double in_scale, out_scale;
     cudaStream_t stream;
@@ -80,7 +89,8 @@ template <int N> static cudaError_t ff_launch_filter(pebble_fastfir *h, cudaStre
     return cudaGetLastError();
 }
 template <int N>
-static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out, int nblocks, cudaStream_t st) {
+static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out, int nblocks, cudaStream_t st,
+                                     int streams = 1, long long in_stride = 0, long long out_stride = 0) {
     const size_t smem = sizeof(cpx) * N;
     cudaError_t e = cudaFuncSetAttribute(fastfir_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -88,9 +98,12 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fastfir_kernel<N>, FftPlan<N>::THREADS, smem);
     if (occ < 1) occ = 1;
     int grid = pebble::num_sms() * occ * 4;
+    if (streams > 1) grid = (grid + streams - 1) / streams;
     if (grid > nblocks) grid = nblocks;
-    fastfir_kernel<N><<<grid, FftPlan<N>::THREADS, smem, st>>>(h->d_state[h->cur], h->L + h->fill, in, out, h->d_hpos,
-                                                              h->d_tw, nblocks, h->in_scale, h->out_scale);
+    if (grid < 1) grid = 1;
+    fastfir_kernel<N><<<dim3(grid, streams), FftPlan<N>::THREADS, smem, st>>>(
+        h->d_state[h->cur], h->L + h->fill, in, out, h->d_hpos, h->d_tw, nblocks, h->in_scale, h->out_scale, in_stride,
+        out_stride, streams > 1 ? h->N : 0);
     pebble::count_launch();
     return cudaGetLastError();
 }
@@ -109,7 +122,7 @@ pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size) {
     h->N = fft_size; h->fir = fir_size; h->L = fft_size / 2;
     h->lo = -1.0; h->hi = 1.0; h->offset = 1.0; h->fs = 1.0;   // fastfir.cpp:140-143
     h->d_tw = h->d_hpos = h->d_taps = nullptr; h->d_state[0] = h->d_state[1] = nullptr;
-    h->cur = 0; h->fill = 0; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
+    h->cur = 0; h->fill = 0; h->streams = 1; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
     const size_t nb = sizeof(cpx) * (size_t)fft_size;
     std::vector<double> tw;
     pebble_host::twiddle_table(fft_size, tw);
@@ -160,8 +173,50 @@ int pebble_fastfir_out_count(const pebble_fastfir_t *h, int n) {
     return (int)((((long long)h->fill + n) / h->L) * h->L);
 }
 
+int pebble_fastfir_set_streams(pebble_fastfir_t *h, int streams) {
+    if (!h || streams < 1) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    const size_t nb = sizeof(cpx) * (size_t)h->N * (size_t)streams;
+    for (int b = 0; b < 2; ++b) {
+        cudaFree(h->d_state[b]); h->d_state[b] = nullptr;
+        PB_CUDA(cudaMalloc(&h->d_state[b], nb), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaMemset(h->d_state[b], 0, nb), PEBBLE_ERR_CUDA);
+    }
+    h->streams = streams; h->cur = 0; h->fill = 0;
+    return 0;
+}
+
+int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double *d_in, long long in_stride,
+                                        double *d_out, long long out_stride, void *stream_v) {
+    if (!h || n < 0 || (n && !d_in)) { pebble::set_error("fastfir: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream_v;
+    const long long total = (long long)h->fill + n;
+    const int nblocks = (int)(total / h->L);
+    if (nblocks > 0) {
+        if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
+        cudaError_t e = FF_DISPATCH(h,
+            ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, h->streams, in_stride, out_stride),
+            ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, h->streams, in_stride, out_stride),
+            ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, h->streams, in_stride, out_stride));
+        PB_CUDA(e, PEBBLE_ERR_CUDA);
+    }
+    const int new_fill = (int)(total % h->L);
+    const int count = h->L + new_fill;
+    const long long vlen = (long long)h->L + total;
+    fastfir_state_kernel<<<dim3((count + 255) / 256, h->streams), 256, 0, st>>>(
+        h->d_state[h->cur], h->L + h->fill, (const cpx *)d_in, h->d_state[h->cur ^ 1], vlen - count, count, in_stride,
+        h->streams > 1 ? h->N : 0);
+    pebble::count_launch();
+    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    h->cur ^= 1;
+    h->fill = new_fill;
+    return nblocks * h->L;
+}
+
 int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in, double *d_out, void *stream_v) {
     if (!h || n < 0 || (n && !d_in)) { pebble::set_error("fastfir: bad argument"); return PEBBLE_ERR_ARG; }
+    if (h->streams != 1) { pebble::set_error("fastfir: handle is batched, use process_batch_device"); return PEBBLE_ERR_STATE; }
     if (n == 0) return 0;  // fastfir.cpp:287-288
     cudaStream_t st = (cudaStream_t)stream_v;
     const long long total = (long long)h->fill + n;
@@ -178,7 +233,7 @@ int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in
     const int count = h->L + new_fill;
     const long long vlen = (long long)h->L + total;  // length of state ++ in
     fastfir_state_kernel<<<(count + 255) / 256, 256, 0, st>>>(h->d_state[h->cur], h->L + h->fill, (const cpx *)d_in,
-                                                             h->d_state[h->cur ^ 1], vlen - count, count);
+                                                             h->d_state[h->cur ^ 1], vlen - count, count, 0, 0);
     pebble::count_launch();
     PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
     h->cur ^= 1;

@@ -344,3 +344,44 @@ class Receiver(_Handle):
         """pinned_in/out: torch CPU tensors in page-locked memory; enqueues H2D, chain, D2H on the current stream."""
         return check(lib.pebble_receiver_process_pinned(self._h, numSamples, pinned_in.data_ptr(), pinned_out.data_ptr(),
                                                         _stream_ptr()), "processPinned")
+
+
+class Channelizer(_Handle):
+    """nch receiver chains (receiver.cpp:903-996) over one wideband capture — BASELINE config 4. Device tensors only."""
+    _destroy = staticmethod(lib.pebble_channelizer_destroy)
+
+    def __init__(self, nchannels, sampleRate, maxBW):
+        super().__init__(lib.pebble_channelizer_create(int(nchannels), float(sampleRate), float(maxBW)), "Channelizer")
+        self.nchannels = int(nchannels)
+        self.outRate = lib.pebble_channelizer_out_rate(self._h)
+        self.numStages = check(lib.pebble_channelizer_num_stages(self._h))
+
+    def setFrequency(self, ch, freq):
+        check(lib.pebble_channelizer_set_frequency(self._h, ch, freq), "setFrequency")
+
+    def setFilter(self, lo, hi):
+        return check(lib.pebble_channelizer_set_filter(self._h, lo, hi), "setFilter")
+
+    def setDemodMode(self, ch, mode):
+        check(lib.pebble_channelizer_set_demod_mode(self._h, ch, mode), "setDemodMode")
+
+    def setAmBandwidth(self, bw):
+        check(lib.pebble_channelizer_set_am_bandwidth(self._h, bw), "setAmBandwidth")
+
+    def setAgcThreshold(self, thr):
+        check(lib.pebble_channelizer_set_agc_threshold(self._h, thr))
+
+    def outCount(self, n):
+        return check(lib.pebble_channelizer_out_count(self._h, n))
+
+    def downConvert(self, d_in, n, d_out):
+        """d_out: [nchannels, >= n >> S] complex128 CUDA tensor (rows contiguous)."""
+        assert d_out.dim() == 2 and d_out.shape[0] == self.nchannels and d_out.stride(1) == 1
+        return check(lib.pebble_channelizer_downconvert_device(self._h, n, _dev_ptr(d_in, n), d_out.data_ptr(),
+                                                               d_out.stride(0), _stream_ptr()), "downConvert")
+
+    def process(self, d_in, n, d_out):
+        """d_out: [nchannels, >= n >> S] complex128 CUDA tensor. Returns demodulated samples per channel."""
+        assert d_out.dim() == 2 and d_out.shape[0] == self.nchannels and d_out.stride(1) == 1
+        return check(lib.pebble_channelizer_process_device(self._h, n, _dev_ptr(d_in, n), d_out.data_ptr(),
+                                                           d_out.stride(0), _stream_ptr()), "process")
