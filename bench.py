@@ -37,11 +37,18 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--log2n", type=int, default=26, help="input samples per step = 2^log2n")
+    ap.add_argument("--log2n", type=int, default=None, help="input samples per step = 2^log2n (26 chain, 24 channelizer)")
+    ap.add_argument("--workload", default="chain", choices=["chain", "channelizer"],
+                    help="chain = BASELINE config 2 (default, the metric's configuration); channelizer = config 4")
+    ap.add_argument("--channels", type=int, default=1024, help="channelizer workload: total channels")
     ap.add_argument("--mode", default="am", choices=sorted(MODES))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work per baseline leg")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.log2n_set = a.log2n is not None
+    if a.log2n is None:
+        a.log2n = 26
+    return a
 
 
 def workload_config(args, extra=None):
@@ -360,4 +367,9 @@ def main_ours(args):
 
 if __name__ == "__main__":
     a = parse()
-    sys.exit(main_reference(a) if a.impl == "reference" else main_ours(a))
+    if a.impl == "reference":
+        sys.exit(main_reference(a))
+    if a.workload == "channelizer":
+        import bench_channelizer
+        sys.exit(bench_channelizer.main(a, sys.modules[__name__]))
+    sys.exit(main_ours(a))

@@ -39,13 +39,20 @@ static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__rest
         st[c].pll = v;
     } else if (mode == CH_AM) {           // Demod_AM::processBlockFiltered, demod_am.cpp:40-59
         double d = st[c].am_dc_last;
-        for (int i = 0; i < n; ++i) {
-            const cpx xi = x[i];
-            const double mag = sqrt(xi.x * xi.x + xi.y * xi.y);   // DB::amplitude, db.h:28-30
-            const double dn = (am_alpha * d) + mag;               // demod_am.cpp:52
-            const double v = dn - d;                              // demod_am.cpp:53
-            d = dn;
-            y[i] = cpx_make(v, v);
+        for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {           // register-blocked like pll_run
+            cpx xs[PB_SERIAL_BLK];
+#pragma unroll
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) xs[j] = i0 + j < n ? x[i0 + j] : cpx_make(0.0, 0.0);
+#pragma unroll
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+                if (i0 + j < n) {
+                    const double mag = sqrt(xs[j].x * xs[j].x + xs[j].y * xs[j].y);   // DB::amplitude, db.h:28-30
+                    const double dn = (am_alpha * d) + mag;                           // demod_am.cpp:52
+                    const double v = dn - d;                                          // demod_am.cpp:53
+                    d = dn;
+                    y[i0 + j] = cpx_make(v, v);
+                }
+            }
         }
         st[c].am_dc_last = d;
     } else {                              // USB/LSB/...: Demod::processBlock returns `in` (demod.cpp:127-138)
@@ -247,7 +254,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
     r = pebble_fastfir_process_batch_device(h->bp, nd, (const double *)h->d_dec, row, (double *)h->d_bp, row, st);   // :950
     if (r < 0) return r;
     if (r != nd) { pebble::set_error("channelizer: FastFIR returned %d of %d", r, nd); return PEBBLE_ERR_STATE; }
-    chan_demod_kernel<<<(h->nch + 63) / 64, 64, 0, st>>>(h->d_bp, h->d_tmp, nd, row, h->nch, h->d_modes, h->pll,
+    chan_demod_kernel<<<(h->nch + 31) / 32, 32, 0, st>>>(h->d_bp, h->d_tmp, nd, row, h->nch, h->d_modes, h->pll,
                                                         (double)0.9999f, h->d_state);                                 // :987
     int gx = (nd + 255) / 256;
     if (gx > 64) gx = 64;

@@ -162,22 +162,42 @@ static __global__ void fm2_kernel(const cpx *__restrict__ in, int n, const cpx *
 struct PllConst { float alpha, beta, dc_alpha, lo, hi, out_gain; };
 struct PllState { float phase, freq, dc; };
 // The PLL recurrence over one stream (demod_nfm.cpp:225-257); state and constants are `float` like the reference's.
+__device__ __forceinline__ void pll_step(const cpx xi, cpx &yo, const PllConst &c, PllState &v) {
+    // sin/cos of a float resolve to the float overloads in the reference build
+    const double ncoSin = (double)sinf(v.phase);
+    const double ncoCos = (double)cosf(v.phase);
+    const double tr = ncoCos * xi.x - ncoSin * xi.y;
+    const double ti = ncoCos * xi.y + ncoSin * xi.x;
+    const double phzerror = -atan2(ti, tr);
+    v.freq = (float)((double)v.freq + ((double)c.beta * phzerror));
+    if (v.freq > c.hi) v.freq = c.hi;
+    else if (v.freq < c.lo) v.freq = c.lo;
+    v.phase = (float)((double)v.phase + ((double)v.freq + (double)c.alpha * phzerror));
+    v.dc = (float)((1.0 - (double)c.dc_alpha) * (double)v.dc + (double)c.dc_alpha * (double)v.freq);
+    const float o = (v.freq - v.dc) * c.out_gain;
+    yo = cpx_make((double)o, 0.0);  // CPX = float: imaginary part is zero
+}
+// The serial recurrence walks its stream in register blocks of PB_SERIAL_BLK samples: the loads of a block are
+// independent and issued back to back, so the (uncoalesced, one-row-per-thread) memory latency is paid once per block
+// instead of once per sample.
+#define PB_SERIAL_BLK 16
 __device__ __forceinline__ void pll_run(const cpx *__restrict__ x, cpx *__restrict__ y, int n, const PllConst c, PllState &v) {
-    for (int i = 0; i < n; ++i) {
-        // sin/cos of a float resolve to the float overloads in the reference build
-        const double ncoSin = (double)sinf(v.phase);
-        const double ncoCos = (double)cosf(v.phase);
-        const cpx xi = x[i];
-        const double tr = ncoCos * xi.x - ncoSin * xi.y;
-        const double ti = ncoCos * xi.y + ncoSin * xi.x;
-        const double phzerror = -atan2(ti, tr);
-        v.freq = (float)((double)v.freq + ((double)c.beta * phzerror));
-        if (v.freq > c.hi) v.freq = c.hi;
-        else if (v.freq < c.lo) v.freq = c.lo;
-        v.phase = (float)((double)v.phase + ((double)v.freq + (double)c.alpha * phzerror));
-        v.dc = (float)((1.0 - (double)c.dc_alpha) * (double)v.dc + (double)c.dc_alpha * (double)v.freq);
-        const float o = (v.freq - v.dc) * c.out_gain;
-        y[i] = cpx_make((double)o, 0.0);  // CPX = float: imaginary part is zero
+    int i = 0;
+    for (; i + PB_SERIAL_BLK <= n; i += PB_SERIAL_BLK) {
+        cpx xs[PB_SERIAL_BLK];
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) xs[j] = x[i + j];
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+            cpx yo;
+            pll_step(xs[j], yo, c, v);
+            y[i + j] = yo;
+        }
+    }
+    for (; i < n; ++i) {
+        cpx yo;
+        pll_step(x[i], yo, c, v);
+        y[i] = yo;
     }
     v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
 }
