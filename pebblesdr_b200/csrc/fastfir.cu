@@ -6,6 +6,7 @@
 #include "lib_common.h"
 #include "fft_kernels.cuh"
 #include "host_design.h"
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -43,6 +44,195 @@ fastfir_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in
     }
 }
 
+// ---- N = 2048 (the reference's CONV_FFT_SIZE, fastfir.cpp:65): register-fused pass schedule --------------------------
+// The generic kernel above makes 16 shared-memory accesses per point (load, 3 forward passes, multiply, 3 inverse
+// passes, store) and ncu showed its L1/LSU data pipe 92 % busy: for 16-byte FP64 samples shared-memory bandwidth, not
+// HBM or FP64, is the first wall. This schedule factors 2048 = 8 x 16 x 16 and makes 8 accesses per point:
+//   F0   global -> registers -> radix-8 (stride 256) -> twiddle -> smem         (input never staged untransformed)
+//   F1   smem -> radix-16 (stride 16 inside each 256-block) -> twiddle (smem table) -> smem
+//   MID  smem -> radix-16 (contiguous) -> multiply by H (CpxMpy, fastfir.cpp:306,324-334) -> inverse radix-16 -> smem
+//   I1   smem -> conj twiddle -> inverse radix-16 -> smem
+//   I0   smem -> conj twiddle -> inverse radix-8 -> registers -> global         (upper L samples only, fastfir.cpp:308-311)
+// Register budget <= 128 so that four CTAs (16 warps) share an SM: the F0/I0 twiddles are rebuilt from w, w^2, w^4 per
+// butterfly (4 complex multiplies), the F1/I1 twiddles come from a 4 KB shared table laid out [power][butterfly].
+// Slot p = 256 q0 + 16 q1 + q2 holds bin q0 + 8 q1 + 128 q2; H is pre-permuted to that order and transposed to
+// [k][thread] so the MID loads are coalesced (ff2048_permute_kernel).
+__device__ __forceinline__ int ff_swz(int p) { return p ^ ((p >> 4) & 7); }
+PB_HD int ff2048_pos2freq(int p) { return (p >> 8) + 8 * ((p >> 4) & 15) + 128 * (p & 15); }
+
+__global__ void ff2048_permute_kernel(const cpx *__restrict__ hpos, cpx *__restrict__ ht) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // idx = k * 128 + t  <->  slot 16 t + k
+    if (idx < 2048) ht[idx] = hpos[FftPlan<2048>::freq2pos(ff2048_pos2freq(16 * (idx & 127) + (idx >> 7)))];
+}
+
+template <bool INV> __device__ __forceinline__ void ff_tw8(cpx (&u)[8], cpx w1, cpx w2, cpx w4) {
+    const cpx w3 = cpx_mul(w1, w2), w5 = cpx_mul(w1, w4), w6 = cpx_mul(w2, w4), w7 = cpx_mul(w3, w4);
+    if (INV) {
+        u[1] = cpx_mulc(u[1], w1); u[2] = cpx_mulc(u[2], w2); u[3] = cpx_mulc(u[3], w3); u[4] = cpx_mulc(u[4], w4);
+        u[5] = cpx_mulc(u[5], w5); u[6] = cpx_mulc(u[6], w6); u[7] = cpx_mulc(u[7], w7);
+    } else {
+        u[1] = cpx_mul(u[1], w1); u[2] = cpx_mul(u[2], w2); u[3] = cpx_mul(u[3], w3); u[4] = cpx_mul(u[4], w4);
+        u[5] = cpx_mul(u[5], w5); u[6] = cpx_mul(u[6], w6); u[7] = cpx_mul(u[7], w7);
+    }
+}
+
+// The three middle phases, shared by the 2048 (T = 128 threads) and 4096 (T = 256) kernels: every thread owns one
+// radix-16 butterfly per phase. a: T*16 slots; t1[16 q + i] = exp(-j 2 pi i q / 256); ht[T k + t] = H of slot 16 t + k.
+template <int T>
+__device__ __forceinline__ void ff_mid_phases(cpx *a, const cpx *t1, const cpx *__restrict__ ht, int t) {
+    const int i1 = t & 15, base1 = (t >> 4) * 256 + i1;
+    cpx v[16];
+    // ---- F1
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = a[ff_swz(base1 + 16 * k)];
+    dft16<false>(v);
+#pragma unroll
+    for (int q = 1; q < 16; ++q) v[q] = cpx_mul(v[q], t1[16 * q + i1]);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[ff_swz(base1 + 16 * k)] = v[k];
+    __syncthreads();
+    // ---- MID: forward radix-16, times H (CpxMpy, fastfir.cpp:306,324-334), inverse radix-16 on 16 contiguous slots
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = a[ff_swz(16 * t + k)];
+    dft16<false>(v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = cpx_mul(ht[T * k + t], v[k]);
+    dft16<true>(v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[ff_swz(16 * t + k)] = v[k];
+    __syncthreads();
+    // ---- I1
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = a[ff_swz(base1 + 16 * k)];
+#pragma unroll
+    for (int q = 1; q < 16; ++q) v[q] = cpx_mulc(v[q], t1[16 * q + i1]);
+    dft16<true>(v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[ff_swz(base1 + 16 * k)] = v[k];
+    __syncthreads();
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB)
+fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
+                   const cpx *__restrict__ ht, const cpx *__restrict__ tw, int blk_first, int nblocks, double in_scale,
+                   double out_scale, long long in_stride, long long out_stride, int state_stride) {
+    constexpr int L = 1024;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cpx *a = reinterpret_cast<cpx *>(smem_raw);
+    cpx *t1 = a + 2048;
+    state += (long long)blockIdx.y * state_stride;
+    in += blockIdx.y * in_stride;
+    out += blockIdx.y * out_stride;
+    const int t = threadIdx.x;
+    for (int idx = t; idx < 256; idx += 128) t1[idx] = tw[8 * (idx & 15) * (idx >> 4)];
+    const cpx wa1 = tw[t], wa2 = tw[2 * t], wa4 = tw[4 * t];
+    const cpx wb1 = tw[t + 128], wb2 = tw[2 * t + 256], wb4 = tw[4 * t + 512];
+    __syncthreads();
+    for (int blk = blk_first + blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const long long v0 = (long long)blk * L;
+        // ---- F0
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const int i = t + 128 * g;
+            cpx u[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) u[k] = cpx_scale(vs_load(state, s0, in, v0 + i + 256 * k), in_scale);
+            dft8<false>(u);
+            ff_tw8<false>(u, g ? wb1 : wa1, g ? wb2 : wa2, g ? wb4 : wa4);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[ff_swz(i + 256 * k)] = u[k];
+        }
+        __syncthreads();
+        ff_mid_phases<128>(a, t1, ht, t);
+        // ---- I0 -> global
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const int i = t + 128 * g;
+            cpx u[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) u[k] = a[ff_swz(i + 256 * k)];
+            ff_tw8<true>(u, g ? wb1 : wa1, g ? wb2 : wa2, g ? wb4 : wa4);
+            dft8<true>(u);
+#pragma unroll
+            for (int k = 4; k < 8; ++k) out[v0 + i + 256 * (k - 4)] = cpx_scale(u[k], out_scale);
+        }
+        __syncthreads();
+    }
+}
+
+// ---- Triple block: the same linear convolution from 4096-point transforms ---------------------------------------------
+// Overlap-save with N = 2048 and 1025 taps transforms 2 points per output sample; FP64 issue and shared-memory wavefronts
+// (ncu: 53 % and 78 % of peak in the kernel above) both scale with the points transformed. A 4096-point transform with
+// the SAME 1025 taps yields 3072 valid samples (4096 - 1024), i.e. 1.33 points per output, and 4096 = 16^3 needs no more
+// passes than 2048 = 8*16*16. The circular convolution of length 4096 holds the linear convolution of 3 consecutive
+// reference blocks exactly (3072 + 1025 - 1 = 4096), so outputs equal the reference's up to FP64 rounding; the
+// reference's 1/2048 normalisation folded into the taps (fastfir.cpp:243) becomes 1/4096 by an exact factor 0.5 in H.
+// Big block b produces outputs [3072 b, 3072 b + 3072) from virtual-stream samples [3072 b, 3072 b + 4096).
+// tw4[m] = exp(-j 2 pi m / 4096); ht4[256 k + t] = 0.5 * FFT4096(taps)[bin of slot 16 t + k].
+__global__ void ff4096_permute_kernel(const cpx *__restrict__ hpos4, cpx *__restrict__ ht4) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // idx = 256 k + t  <->  slot 16 t + k (FftPlan<4096> order)
+    if (idx < 4096) ht4[idx] = cpx_scale(hpos4[16 * (idx & 255) + (idx >> 8)], 0.5);
+}
+
+__global__ void __launch_bounds__(256, 2)
+fastfir4096x3_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
+                     const cpx *__restrict__ ht4, const cpx *__restrict__ tw4, int nbig, double in_scale, double out_scale,
+                     long long in_stride, long long out_stride, int state_stride) {
+    constexpr int LB = 3072;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cpx *a = reinterpret_cast<cpx *>(smem_raw);
+    cpx *t1 = a + 4096;
+    state += (long long)blockIdx.y * state_stride;
+    in += blockIdx.y * in_stride;
+    out += blockIdx.y * out_stride;
+    const int t = threadIdx.x;
+    t1[t] = tw4[16 * (t & 15) * (t >> 4)];
+    const cpx w1 = tw4[t], w2 = tw4[2 * t], w4 = tw4[4 * t], w8 = tw4[8 * t];
+    __syncthreads();
+    for (int blk = blockIdx.x; blk < nbig; blk += gridDim.x) {
+        const long long v0 = (long long)blk * LB;
+        {
+            cpx v[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = cpx_scale(vs_load(state, s0, in, v0 + t + 256 * k), in_scale);
+            dft16<false>(v);
+            {
+                const cpx w3 = cpx_mul(w1, w2), w5 = cpx_mul(w1, w4), w6 = cpx_mul(w2, w4), w7 = cpx_mul(w3, w4);
+                v[1] = cpx_mul(v[1], w1); v[2] = cpx_mul(v[2], w2); v[3] = cpx_mul(v[3], w3); v[4] = cpx_mul(v[4], w4);
+                v[5] = cpx_mul(v[5], w5); v[6] = cpx_mul(v[6], w6); v[7] = cpx_mul(v[7], w7); v[8] = cpx_mul(v[8], w8);
+                v[9] = cpx_mul(v[9], cpx_mul(w1, w8)); v[10] = cpx_mul(v[10], cpx_mul(w2, w8));
+                v[11] = cpx_mul(v[11], cpx_mul(w3, w8)); v[12] = cpx_mul(v[12], cpx_mul(w4, w8));
+                v[13] = cpx_mul(v[13], cpx_mul(w5, w8)); v[14] = cpx_mul(v[14], cpx_mul(w6, w8));
+                v[15] = cpx_mul(v[15], cpx_mul(w7, w8));
+            }
+#pragma unroll
+            for (int k = 0; k < 16; ++k) a[ff_swz(t + 256 * k)] = v[k];
+        }
+        __syncthreads();
+        ff_mid_phases<256>(a, t1, ht4, t);
+        {
+            cpx v[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = a[ff_swz(t + 256 * k)];
+            {
+                const cpx w3 = cpx_mul(w1, w2), w5 = cpx_mul(w1, w4), w6 = cpx_mul(w2, w4), w7 = cpx_mul(w3, w4);
+                v[1] = cpx_mulc(v[1], w1); v[2] = cpx_mulc(v[2], w2); v[3] = cpx_mulc(v[3], w3); v[4] = cpx_mulc(v[4], w4);
+                v[5] = cpx_mulc(v[5], w5); v[6] = cpx_mulc(v[6], w6); v[7] = cpx_mulc(v[7], w7); v[8] = cpx_mulc(v[8], w8);
+                v[9] = cpx_mulc(v[9], cpx_mul(w1, w8)); v[10] = cpx_mulc(v[10], cpx_mul(w2, w8));
+                v[11] = cpx_mulc(v[11], cpx_mul(w3, w8)); v[12] = cpx_mulc(v[12], cpx_mul(w4, w8));
+                v[13] = cpx_mulc(v[13], cpx_mul(w5, w8)); v[14] = cpx_mulc(v[14], cpx_mul(w6, w8));
+                v[15] = cpx_mulc(v[15], cpx_mul(w7, w8));
+            }
+            dft16<true>(v);
+            // samples 1024 .. 4095 of the inverse transform are the valid ones
+#pragma unroll
+            for (int k = 4; k < 16; ++k) out[v0 + t + 256 * (k - 4)] = cpx_scale(v[k], out_scale);
+        }
+        __syncthreads();
+    }
+}
+
 // Forward FFT of the zero-padded taps, stored in slot order (what fastfir_kernel multiplies by).
 template <int N>
 __global__ void __launch_bounds__(FftPlan<N>::THREADS)
@@ -71,7 +261,8 @@ struct pebble_fastfir {
     int N, fir, L;
     // reference members (fastfir.cpp:140-143): "unset" sentinels so the first setup always runs
     double lo, hi, offset, fs;
-    cpx *d_tw, *d_hpos, *d_taps, *d_state[2];
+    cpx *d_tw, *d_hpos, *d_ht, *d_taps, *d_state[2];   // d_ht: H in the fused 2048 kernel's order
+    cpx *d_tw4, *d_hpos4, *d_ht4;                      // N == 2048 only: 4096-point twiddles and H for the triple-block kernel
     int cur, fill;
     int streams;          // independent streams sharing this filter (batched form); state is streams x N cpx
     bool have_filter;
@@ -86,6 +277,17 @@ template <int N> static cudaError_t ff_launch_filter(pebble_fastfir *h, cudaStre
     if (e != cudaSuccess) return e;
     fastfir_filter_kernel<N><<<1, FftPlan<N>::THREADS, smem, st>>>(h->d_taps, h->d_hpos, h->d_tw);
     pebble::count_launch();
+    if (N == 2048) {
+        ff2048_permute_kernel<<<8, 256, 0, st>>>(h->d_hpos, h->d_ht);
+        pebble::count_launch();
+        // the triple-block kernel's H: 4096-point transform of the same taps (d_taps is zero beyond N)
+        const size_t smem4 = sizeof(cpx) * 4096;
+        e = cudaFuncSetAttribute(fastfir_filter_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
+        if (e != cudaSuccess) return e;
+        fastfir_filter_kernel<4096><<<1, FftPlan<4096>::THREADS, smem4, st>>>(h->d_taps, h->d_hpos4, h->d_tw4);
+        ff4096_permute_kernel<<<16, 256, 0, st>>>(h->d_hpos4, h->d_ht4);
+        pebble::count_launch(); pebble::count_launch();
+    }
     return cudaGetLastError();
 }
 template <int N>
@@ -101,6 +303,53 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
     if (streams > 1) grid = (grid + streams - 1) / streams;
     if (grid > nblocks) grid = nblocks;
     if (grid < 1) grid = 1;
+    if (N == 2048 && !getenv("PEBBLE_FF_GENERIC")) {
+        const size_t smem2 = sizeof(cpx) * (2048 + 256), smem4 = sizeof(cpx) * (4096 + 256);
+        static int occ2 = 0, occ4 = 0, waves = 2;
+        static bool triple = true;
+        static void (*kern)(const cpx *, int, const cpx *, cpx *, const cpx *, const cpx *, int, int, double, double,
+                            long long, long long, int) = nullptr;
+        if (!occ2) {
+            const char *mb = getenv("PEBBLE_FF_MINB");   // registers per thread: 4 -> 128, 3 -> 168, 2 -> 255
+            const int minb = mb ? atoi(mb) : 4;
+            kern = minb <= 2 ? fastfir2048_kernel<2> : minb == 3 ? fastfir2048_kernel<3> : fastfir2048_kernel<4>;
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+            if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(fastfir4096x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
+            if (e != cudaSuccess) return e;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, fastfir4096x3_kernel, 256, smem4);
+            if (occ4 < 1) occ4 = 1;
+            const char *wv = getenv("PEBBLE_FF_WAVES");
+            if (wv) waves = atoi(wv) > 0 ? atoi(wv) : 1;
+            triple = !getenv("PEBBLE_FF_NO3");
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, kern, 128, smem2);
+            if (occ2 < 1) occ2 = 1;
+        }
+        const int state_stride = streams > 1 ? h->N : 0;
+        const int nbig = triple ? nblocks / 3 : 0;
+        if (nbig > 0) {
+            grid = pebble::num_sms() * occ4 * waves;
+            if (streams > 1) grid = (grid + streams - 1) / streams;
+            if (grid > nbig) grid = nbig;
+            fastfir4096x3_kernel<<<dim3(grid, streams), 256, smem4, st>>>(
+                h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht4, h->d_tw4, nbig, h->in_scale, h->out_scale, in_stride,
+                out_stride, state_stride);
+            pebble::count_launch();
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
+        }
+        const int rest = nblocks - 3 * nbig;
+        if (rest > 0) {
+            grid = pebble::num_sms() * occ2 * waves;
+            if (streams > 1) grid = (grid + streams - 1) / streams;
+            if (grid > rest) grid = rest;
+            kern<<<dim3(grid, streams), 128, smem2, st>>>(
+                h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht, h->d_tw, 3 * nbig, nblocks, h->in_scale, h->out_scale,
+                in_stride, out_stride, state_stride);
+            pebble::count_launch();
+        }
+        return cudaGetLastError();
+    }
     fastfir_kernel<N><<<dim3(grid, streams), FftPlan<N>::THREADS, smem, st>>>(
         h->d_state[h->cur], h->L + h->fill, in, out, h->d_hpos, h->d_tw, nblocks, h->in_scale, h->out_scale, in_stride,
         out_stride, streams > 1 ? h->N : 0);
@@ -121,19 +370,27 @@ pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size) {
     pebble_fastfir *h = new pebble_fastfir();
     h->N = fft_size; h->fir = fir_size; h->L = fft_size / 2;
     h->lo = -1.0; h->hi = 1.0; h->offset = 1.0; h->fs = 1.0;   // fastfir.cpp:140-143
-    h->d_tw = h->d_hpos = h->d_taps = nullptr; h->d_state[0] = h->d_state[1] = nullptr;
+    h->d_tw = h->d_hpos = h->d_ht = h->d_taps = nullptr; h->d_tw4 = h->d_hpos4 = h->d_ht4 = nullptr; h->d_state[0] = h->d_state[1] = nullptr;
     h->cur = 0; h->fill = 0; h->streams = 1; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
     const size_t nb = sizeof(cpx) * (size_t)fft_size;
     std::vector<double> tw;
     pebble_host::twiddle_table(fft_size, tw);
     bool ok = pebble::cuda_ok(cudaMalloc(&h->d_tw, nb), "cudaMalloc") && pebble::cuda_ok(cudaMalloc(&h->d_hpos, nb), "cudaMalloc") &&
-              pebble::cuda_ok(cudaMalloc(&h->d_taps, nb), "cudaMalloc") && pebble::cuda_ok(cudaMalloc(&h->d_state[0], nb), "cudaMalloc") &&
+              pebble::cuda_ok(cudaMalloc(&h->d_ht, nb), "cudaMalloc") && pebble::cuda_ok(cudaMemset(h->d_ht, 0, nb), "cudaMemset") &&
+              pebble::cuda_ok(cudaMalloc(&h->d_taps, 2 * nb), "cudaMalloc") && pebble::cuda_ok(cudaMemset(h->d_taps, 0, 2 * nb), "cudaMemset") && pebble::cuda_ok(cudaMalloc(&h->d_state[0], nb), "cudaMalloc") &&
               pebble::cuda_ok(cudaMalloc(&h->d_state[1], nb), "cudaMalloc") &&
               pebble::cuda_ok(cudaMemcpy(h->d_tw, tw.data(), nb, cudaMemcpyHostToDevice), "cudaMemcpy(tw)") &&
               pebble::cuda_ok(cudaMemset(h->d_state[0], 0, nb), "cudaMemset") && pebble::cuda_ok(cudaMemset(h->d_state[1], 0, nb), "cudaMemset") &&
               // until SetupParameters runs the reference multiplies by an uninitialised buffer; we use zeros
               pebble::cuda_ok(cudaMemset(h->d_hpos, 0, nb), "cudaMemset") &&
               pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    if (ok && fft_size == 2048) {
+        std::vector<double> tw4;
+        pebble_host::twiddle_table(4096, tw4);
+        ok = pebble::cuda_ok(cudaMalloc(&h->d_tw4, 2 * nb), "cudaMalloc") && pebble::cuda_ok(cudaMalloc(&h->d_hpos4, 2 * nb), "cudaMalloc") &&
+             pebble::cuda_ok(cudaMalloc(&h->d_ht4, 2 * nb), "cudaMalloc") && pebble::cuda_ok(cudaMemset(h->d_ht4, 0, 2 * nb), "cudaMemset") &&
+             pebble::cuda_ok(cudaMemcpy(h->d_tw4, tw4.data(), 2 * nb, cudaMemcpyHostToDevice), "cudaMemcpy(tw4)");
+    }
     if (!ok) { pebble_fastfir_destroy(h); return nullptr; }
     return h;
 }
@@ -141,7 +398,7 @@ pebble_fastfir_t *pebble_fastfir_create(void) { return pebble_fastfir_create_siz
 
 void pebble_fastfir_destroy(pebble_fastfir_t *h) {
     if (!h) return;
-    cudaFree(h->d_tw); cudaFree(h->d_hpos); cudaFree(h->d_taps); cudaFree(h->d_state[0]); cudaFree(h->d_state[1]);
+    cudaFree(h->d_tw); cudaFree(h->d_hpos); cudaFree(h->d_ht); cudaFree(h->d_tw4); cudaFree(h->d_hpos4); cudaFree(h->d_ht4); cudaFree(h->d_taps); cudaFree(h->d_state[0]); cudaFree(h->d_state[1]);
     if (h->stream) cudaStreamDestroy(h->stream);
     h->stg.release();
     delete h;

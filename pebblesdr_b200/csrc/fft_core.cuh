@@ -93,6 +93,27 @@ template <bool INV> struct DftR<16, INV> { static PB_HD void run(cpx (&v)[16]) {
 
 template <int SH> PB_HD int fft_swz(int i) { return i ^ ((i >> SH) & 7); }
 
+// Twiddle powers w^1..w^(R-1) of one butterfly from FOUR table reads (w^1, w^2, w^4, w^8) and R-5 complex
+// multiplies (depth <= 3), instead of R-1 scattered 16-byte gathers: the gathers kept the L1/LSU data pipe (which the
+// shared-memory passes already saturate) and the long-scoreboard busy; FP64 had room (ncu: 23 % of the pipe).
+// tw[m] = exp(-j 2 pi m / N); `step` = i * (N / M). Powers beyond R-1 are not formed.
+template <int R> PB_HD void fft_twiddle_powers(const cpx *tw, int step, int nmask, cpx (&w)[16]) {
+    w[1] = tw[step & nmask];
+    w[2] = tw[(2 * step) & nmask];
+    w[3] = cpx_mul(w[1], w[2]);
+    if (R > 4) {
+        w[4] = tw[(4 * step) & nmask];
+        w[5] = cpx_mul(w[1], w[4]);
+        w[6] = cpx_mul(w[2], w[4]);
+        w[7] = cpx_mul(w[3], w[4]);
+    }
+    if (R > 8) {
+        w[8] = tw[(8 * step) & nmask];
+#pragma unroll
+        for (int q = 9; q < 16; ++q) w[q] = cpx_mul(w[q - 8], w[8]);
+    }
+}
+
 // One radix-R butterfly of the in-place pass whose current sub-transform length is M (stride M/R).
 // tw[m] = exp(-j 2 pi m / N), m < N. Forward: DFT then twiddle; inverse: conj twiddle then DFT.
 template <int N, int R, int M, bool INV, int SH>
@@ -101,16 +122,18 @@ PB_HD void fft_butterfly(cpx *a, const cpx *tw, int bf) {
     const int b = bf / S, i = bf - b * S;
     const int base = b * M + i;
     cpx v[R];
+    cpx w[16];
 #pragma unroll
     for (int k = 0; k < R; ++k) v[k] = a[fft_swz<SH>(base + k * S)];
+    if (S > 1) fft_twiddle_powers<R>(tw, i * (N / M), N - 1, w);
     if (INV && S > 1) {
 #pragma unroll
-        for (int q = 1; q < R; ++q) v[q] = cpx_mulc(v[q], tw[i * q * (N / M)]);
+        for (int q = 1; q < R; ++q) v[q] = cpx_mulc(v[q], w[q]);
     }
     DftR<R, INV>::run(v);
     if (!INV && S > 1) {
 #pragma unroll
-        for (int q = 1; q < R; ++q) v[q] = cpx_mul(v[q], tw[i * q * (N / M)]);
+        for (int q = 1; q < R; ++q) v[q] = cpx_mul(v[q], w[q]);
     }
 #pragma unroll
     for (int k = 0; k < R; ++k) a[fft_swz<SH>(base + k * S)] = v[k];

@@ -1,7 +1,8 @@
 """Summarise an ncu capture for profiles/: headline raw metrics of one kernel + profiles/traffic.json (bench.py reads
-the measured DRAM bytes per launch from it). usage: ncu_summary.py <rep.ncu-rep> <kernel key> <samples_per_launch> <out.txt>"""
+the measured DRAM bytes per launch from it). usage: ncu_summary.py <rep.ncu-rep> <kernel key> <samples_per_launch> <out.txt> [algorithmic bytes per sample = 16.125]"""
 import csv, json, os, subprocess, sys
 rep, key, spl, out = sys.argv[1], sys.argv[2], int(sys.argv[3]), sys.argv[4]
+ALG = float(sys.argv[5]) if len(sys.argv) > 5 else 16.125
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
@@ -31,7 +32,7 @@ def to_bytes(v, u):
     return float(v.replace(",", "")) * m[u]
 ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
 traffic = to_bytes(r[ir], units[ir]) + to_bytes(r[iw], units[iw])
-lines.append("dram bytes per launch (read+write): %.0f ; algorithmic: %.0f ; ratio %.3f" % (traffic, 16.125 * spl, traffic / (16.125 * spl)))
+lines.append("dram bytes per launch (read+write): %.0f ; algorithmic: %.0f ; ratio %.3f" % (traffic, ALG * spl, traffic / (ALG * spl)))
 open(out, "w").write("\n".join(lines) + "\n")
 tj = os.path.join(ROOT, "profiles", "traffic.json")
 t = json.load(open(tj)) if os.path.exists(tj) else {}
