@@ -53,9 +53,13 @@ int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStre
     if (n <= 0) return 0;
     if (f->ntaps <= 0) { pebble::set_error("cfir: filter not initialised"); return PEBBLE_ERR_STATE; }
     if (d_in == d_out) { pebble::set_error("cfir: in-place device call not supported"); return PEBBLE_ERR_ARG; }
-    cfir_kernel<<<grid_for(n), 256, 0, st>>>(f->d_hist[f->cur], d_in, n, f->d_hI, f->d_hQ, f->ntaps, d_out);
-    cfir_state_kernel<<<1, 128, 0, st>>>(f->d_hist[f->cur], d_in, n, f->ntaps - 1, f->d_hist[f->cur ^ 1]);
-    pebble::count_launch(2);
+    FirTaps taps;
+    memset(&taps, 0, sizeof(taps));
+    memcpy(taps.hI, f->hI, sizeof(double) * f->ntaps);
+    memcpy(taps.hQ, f->hQ, sizeof(double) * f->ntaps);
+    cfir_kernel<<<grid_for(n, PB_FIR_TILE), PB_FIR_THREADS, 0, st>>>(f->d_hist[f->cur], d_in, n, taps, f->ntaps, d_out,
+                                                                    f->d_hist[f->cur ^ 1]);
+    pebble::count_launch();
     PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
     f->cur ^= 1;
     return n;
@@ -275,9 +279,11 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         const double alpha = (double)0.9999f;  // DC_ALPHA is a float literal, demod_am.cpp:36
         const int tiles = (n + PB_SCAN_TILE - 1) / PB_SCAN_TILE;
         am_tile_kernel<<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, h->d_tiles);
-        am_carry_kernel<<<1, 32, 0, st>>>(h->d_tiles, tiles, h->d_am_last[h->am_cur], h->d_carry);
-        am_apply_kernel<<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, h->d_carry, h->d_tmp, h->d_am_last[h->am_cur ^ 1]);
-        pebble::count_launch(3);
+        const bool direct = tiles <= PB_AM_DIRECT;
+        if (!direct) am_carry_kernel<<<1, PB_SCAN_THREADS, 0, st>>>(h->d_tiles, tiles, h->d_am_last[h->am_cur], h->d_carry);
+        am_apply_kernel<<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, direct ? nullptr : h->d_carry, h->d_tiles,
+                                                          h->d_am_last[h->am_cur], h->d_tmp, h->d_am_last[h->am_cur ^ 1]);
+        pebble::count_launch(direct ? 2 : 3);
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
         h->am_cur ^= 1;
         return cfir_run_device(&h->am_lp, n, h->d_tmp, d_out, st);  // demod_am.cpp:62

@@ -10,30 +10,65 @@
 #define PB_SCAN_TILE (PB_SCAN_THREADS * PB_SCAN_PER)
 
 // ---- CFir ---------------------------------------------------------------------------------------
-// virtual stream = hist (ntaps-1 samples) ++ in; out[i] = sum_k h[k] * xv[i + ntaps-1 - k]
-static __global__ void cfir_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, const double *__restrict__ hI,
-                            const double *__restrict__ hQ, int ntaps, cpx *__restrict__ out) {
-    __shared__ double sI[PB_FIR_MAX], sQ[PB_FIR_MAX];
-    for (int k = threadIdx.x; k < ntaps; k += blockDim.x) { sI[k] = hI[k]; sQ[k] = hQ[k]; }
-    __syncthreads();
+// virtual stream = hist (ntaps-1 samples) ++ in; out[i] = sum_k h[k] * xv[i + ntaps-1 - k]   (fir.cpp:85-130)
+// One CTA filters a tile of PB_FIR_TILE outputs: the tile's window (tile + ntaps-1 samples) is staged in shared memory
+// once (one pad slot per 8 so that threads 8 outputs apart read distinct banks), every thread produces PB_FIR_R
+// CONSECUTIVE outputs from a register window that slides by one sample per tap (one 16-byte shared load per tap for
+// 8 outputs); the taps are kernel parameters, read from the constant bank.
+// The accumulation order over k is the reference's. CTA 0 also stores the carried history (ping-pong buffer).
+#define PB_FIR_R 8
+#define PB_FIR_THREADS 128
+#define PB_FIR_TILE (PB_FIR_R * PB_FIR_THREADS)
+struct FirTaps { double hI[PB_FIR_MAX], hQ[PB_FIR_MAX]; };
+__device__ __forceinline__ int fir_slot(int p) { return p + (p >> 3); }
+
+static __global__ void __launch_bounds__(PB_FIR_THREADS)
+cfir_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, const __grid_constant__ FirTaps taps, int ntaps,
+            cpx *__restrict__ out, cpx *__restrict__ new_hist) {
+    __shared__ cpx win[PB_FIR_TILE + PB_FIR_MAX + (PB_FIR_TILE + PB_FIR_MAX) / 8 + 1];
     const int h = ntaps - 1;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        double re = 0.0, im = 0.0;
-        for (int k = 0; k < ntaps; ++k) {
-            const int v = i + h - k;  // index into the virtual stream
-            const cpx x = v < h ? hist[v] : in[v - h];
-            re += sI[k] * x.x;
-            im += sQ[k] * x.y;
+    if (blockIdx.x == 0 && new_hist) {
+        for (int i = threadIdx.x; i < h; i += PB_FIR_THREADS) {
+            const int v = n + i;  // last h samples of hist ++ in
+            new_hist[i] = v < h ? hist[v] : in[v - h];
         }
-        out[i] = cpx_make(re, im);
     }
-}
-static __global__ void cfir_state_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, int h,
-                                  cpx *__restrict__ new_hist) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < h) {
-        const int v = n + i;  // last h samples of hist ++ in
-        new_hist[i] = v < h ? hist[v] : in[v - h];
+    const int ntiles = (n + PB_FIR_TILE - 1) / PB_FIR_TILE;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int t0 = tile * PB_FIR_TILE;
+        const int valid = min(PB_FIR_TILE, n - t0);
+        __syncthreads();
+        for (int p = threadIdx.x; p < valid + h; p += PB_FIR_THREADS) {
+            const int v = t0 + p;
+            win[fir_slot(p)] = v < h ? hist[v] : in[v - h];
+        }
+        __syncthreads();
+        const int i0 = threadIdx.x * PB_FIR_R;
+        if (i0 >= valid) continue;
+        double re[PB_FIR_R], im[PB_FIR_R];
+        cpx w[PB_FIR_R];
+#pragma unroll
+        for (int j = 0; j < PB_FIR_R; ++j) { re[j] = 0.0; im[j] = 0.0; w[j] = win[fir_slot(i0 + h + j)]; }
+        // taps in groups of PB_FIR_R: after PB_FIR_R one-sample shifts the register window is back in place, so the
+        // group body is unrolled with static register names while the loop over groups stays rolled (a full unroll of
+        // 75 taps x 16 FMAs is ~25 KB of code and runs out of instruction cache)
+        for (int k0 = 0; k0 < ntaps; k0 += PB_FIR_R) {
+#pragma unroll
+            for (int kk = 0; kk < PB_FIR_R; ++kk) {
+                const int k = k0 + kk;
+                if (k < ntaps) {
+                    const double cI = taps.hI[k], cQ = taps.hQ[k];
+#pragma unroll
+                    for (int j = 0; j < PB_FIR_R; ++j) { re[j] += cI * w[j].x; im[j] += cQ * w[j].y; }
+#pragma unroll
+                    for (int j = PB_FIR_R - 1; j > 0; --j) w[j] = w[j - 1];
+                    if (k + 1 < ntaps) w[0] = win[fir_slot(i0 + h - k - 1)];
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < PB_FIR_R; ++j)
+            if (i0 + j < valid) out[t0 + i0 + j] = cpx_make(re[j], im[j]);
     }
 }
 
@@ -94,18 +129,29 @@ static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_tile_kernel(const c
     block_aff_exclusive(m, &tot);
     if (threadIdx.x == 0) tile_map[blockIdx.x] = tot;
 }
-static __global__ void am_carry_kernel(const Aff *__restrict__ tile_map, int ntiles, const double *__restrict__ d_last_in,
-                                double *__restrict__ carry) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        double d = *d_last_in;
-        for (int t = 0; t < ntiles; ++t) {
-            carry[t] = d;
-            d = tile_map[t].a * d + tile_map[t].b;
-        }
+// Parallel carry (streams of more than PB_AM_DIRECT tiles): one CTA composes the tile maps chunk by chunk.
+static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_carry_kernel(const Aff *__restrict__ tile_map, int ntiles,
+                                                                   const double *__restrict__ d_last_in,
+                                                                   double *__restrict__ carry) {
+    const int per = (ntiles + PB_SCAN_THREADS - 1) / PB_SCAN_THREADS;
+    const int j0 = threadIdx.x * per, j1 = min(ntiles, j0 + per);
+    Aff m; m.a = 1.0; m.b = 0.0;
+    for (int j = j0; j < j1; ++j) m = aff_then(m, tile_map[j]);
+    Aff tot;
+    const Aff ex = block_aff_exclusive(m, &tot);
+    double d = ex.a * (*d_last_in) + ex.b;
+    for (int j = j0; j < j1; ++j) {
+        carry[j] = d;
+        d = tile_map[j].a * d + tile_map[j].b;
     }
 }
+// carry == nullptr: the CTA folds the maps of all earlier tiles itself (at most PB_AM_DIRECT of them), which
+// removes the carry launch from the short streams the receiver tail sees (2^19 samples = 256 tiles).
+#define PB_AM_DIRECT 512
 static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_apply_kernel(const cpx *__restrict__ in, int n, double alpha,
                                                                    const double *__restrict__ carry,
+                                                                   const Aff *__restrict__ tile_map,
+                                                                   const double *__restrict__ d_last_in,
                                                                    cpx *__restrict__ out, double *__restrict__ d_last_out) {
     const int base = blockIdx.x * PB_SCAN_TILE + threadIdx.x * PB_SCAN_PER;
     double mag[PB_SCAN_PER];
@@ -120,9 +166,21 @@ static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_apply_kernel(const 
             m.a *= alpha;
         }
     }
+    double d_tile;  // m_amDcLast entering this tile
+    if (carry) {
+        d_tile = carry[blockIdx.x];
+    } else {
+        const int nt = blockIdx.x, per = (nt + PB_SCAN_THREADS - 1) / PB_SCAN_THREADS;
+        const int j0 = threadIdx.x * per, j1 = min(nt, j0 + per);
+        Aff pm; pm.a = 1.0; pm.b = 0.0;
+        for (int j = j0; j < j1; ++j) pm = aff_then(pm, tile_map[j]);
+        Aff ptot;
+        block_aff_exclusive(pm, &ptot);
+        d_tile = ptot.a * (*d_last_in) + ptot.b;
+    }
     Aff tot;
     const Aff ex = block_aff_exclusive(m, &tot);
-    double d = ex.a * carry[blockIdx.x] + ex.b;  // m_amDcLast entering this thread's first sample
+    double d = ex.a * d_tile + ex.b;  // m_amDcLast entering this thread's first sample
 #pragma unroll
     for (int k = 0; k < PB_SCAN_PER; ++k) {
         if (base + k < n) {

@@ -39,11 +39,21 @@ __device__ __forceinline__ void vs_prefetch_l2(const cpx *__restrict__ state, in
     }
 }
 
+// Carried state of the NEXT call, new_state[i] = V[start + i] (V = state ++ in): written by CTA 0 of the last kernel a
+// process call launches (inputs only, so it does not depend on the filtering), instead of by a launch of its own.
+struct FfCarry { cpx *new_state; long long start; int count; };
+__device__ __forceinline__ void ff_carry_state(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, FfCarry c,
+                                               int state_stride) {
+    if (blockIdx.x != 0 || c.count <= 0) return;
+    cpx *ns = c.new_state + (long long)blockIdx.y * state_stride;
+    for (int i = threadIdx.x; i < c.count; i += blockDim.x) ns[i] = vs_load(state, s0, in, c.start + i);
+}
+
 template <int N>
 __global__ void __launch_bounds__(FftPlan<N>::THREADS)
 fastfir_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
                const cpx *__restrict__ hpos, const cpx *__restrict__ tw, int nblocks, double in_scale,
-               double out_scale, long long in_stride, long long out_stride, int state_stride) {
+               double out_scale, long long in_stride, long long out_stride, int state_stride, FfCarry carry) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx *a = reinterpret_cast<cpx *>(smem_raw);
     constexpr int L = N / 2;
@@ -52,6 +62,7 @@ fastfir_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in
     state += (long long)blockIdx.y * state_stride;
     in += blockIdx.y * in_stride;
     out += blockIdx.y * out_stride;
+    ff_carry_state(state, s0, in, carry, state_stride);
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const long long v0 = (long long)blk * L;
         for (int i = threadIdx.x; i < N; i += blockDim.x)
@@ -84,9 +95,10 @@ fastfir_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in
 __device__ __forceinline__ int ff_swz(int p) { return p ^ ((p >> 4) & 7); }
 PB_HD int ff2048_pos2freq(int p) { return (p >> 8) + 8 * ((p >> 4) & 15) + 128 * (p & 15); }
 
-__global__ void ff2048_permute_kernel(const cpx *__restrict__ hpos, cpx *__restrict__ ht) {
+// `scale` = in_scale * out_scale of the handle: the fused kernels are linear, so the two gains ride on H.
+__global__ void ff2048_permute_kernel(const cpx *__restrict__ hpos, cpx *__restrict__ ht, double scale) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // idx = k * 128 + t  <->  slot 16 t + k
-    if (idx < 2048) ht[idx] = hpos[FftPlan<2048>::freq2pos(ff2048_pos2freq(16 * (idx & 127) + (idx >> 7)))];
+    if (idx < 2048) ht[idx] = cpx_scale(hpos[FftPlan<2048>::freq2pos(ff2048_pos2freq(16 * (idx & 127) + (idx >> 7)))], scale);
 }
 
 template <bool INV> __device__ __forceinline__ void ff_tw8(cpx (&u)[8], cpx w1, cpx w2, cpx w4) {
@@ -119,8 +131,8 @@ template <bool INV> __device__ __forceinline__ void ff_tw16(cpx (&v)[16], cpx w1
 // All three phases of thread t stay inside the 256-slot block t/16, which is written and read by the SAME half warp
 // (F1 butterflies of block j are threads 16 j .. 16 j + 15, the MID groups of those threads are slots 256 j .. 256 j + 255),
 // so the phases are separated by __syncwarp() only: the CTA-wide barriers are the ones around F0 and I0.
-template <int T>
-__device__ __forceinline__ void ff_mid_phases(cpx *a, const cpx *t1, const cpx *__restrict__ ht, int t) {
+template <int T, bool NAMED>
+__device__ __forceinline__ void ff_mid_phases(cpx *a, const cpx *t1, const cpx *__restrict__ ht, int t, int bar) {
     const int i1 = t & 15, base1 = (t >> 4) * 256 + i1;
     cpx v[16];
     // ---- F1
@@ -148,14 +160,15 @@ __device__ __forceinline__ void ff_mid_phases(cpx *a, const cpx *t1, const cpx *
     dft16<true>(v);
 #pragma unroll
     for (int k = 0; k < 16; ++k) a[ff_swz(base1 + 16 * k)] = v[k];
-    __syncthreads();
+    if (NAMED) asm volatile("bar.sync %0, %1;" ::"r"(bar), "n"(T) : "memory");
+    else __syncthreads();
 }
 
 template <int MINB>
 __global__ void __launch_bounds__(128, MINB)
 fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
-                   const cpx *__restrict__ ht, const cpx *__restrict__ tw, int blk_first, int nblocks, double in_scale,
-                   double out_scale, long long in_stride, long long out_stride, int state_stride) {
+                   const cpx *__restrict__ ht, const cpx *__restrict__ tw, int blk_first, int nblocks, long long in_stride,
+                   long long out_stride, int state_stride, FfCarry carry) {
     constexpr int L = 1024;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx *a = reinterpret_cast<cpx *>(smem_raw);
@@ -164,6 +177,7 @@ fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict_
     in += blockIdx.y * in_stride;
     out += blockIdx.y * out_stride;
     const int t = threadIdx.x;
+    ff_carry_state(state, s0, in, carry, state_stride);
     if (t < 64) t1[t] = tw[8 * ((t & 15) << (t >> 4))];   // t = 16 b + i -> exp(-j 2 pi i 2^b / 256)
     const cpx wa1 = tw[t], wa2 = tw[2 * t], wa4 = tw[4 * t];
     const cpx wb1 = tw[t + 128], wb2 = tw[2 * t + 256], wb4 = tw[4 * t + 512];
@@ -176,14 +190,14 @@ fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict_
             const int i = t + 128 * g;
             cpx u[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) u[k] = cpx_scale(vs_load_stream(state, s0, in, v0 + i + 256 * k), in_scale);
+            for (int k = 0; k < 8; ++k) u[k] = vs_load_stream(state, s0, in, v0 + i + 256 * k);
             dft8<false>(u);
             ff_tw8<false>(u, g ? wb1 : wa1, g ? wb2 : wa2, g ? wb4 : wa4);
 #pragma unroll
             for (int k = 0; k < 8; ++k) a[ff_swz(i + 256 * k)] = u[k];
         }
         __syncthreads();
-        ff_mid_phases<128>(a, t1, ht, t);
+        ff_mid_phases<128, false>(a, t1, ht, t, 0);
         // ---- I0 -> global
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
@@ -194,9 +208,9 @@ fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict_
             ff_tw8<true>(u, g ? wb1 : wa1, g ? wb2 : wa2, g ? wb4 : wa4);
             dft8<true>(u);
 #pragma unroll
-            for (int k = 4; k < 8; ++k) ff_st_stream(out + v0 + i + 256 * (k - 4), cpx_scale(u[k], out_scale));
+            for (int k = 4; k < 8; ++k) ff_st_stream(out + v0 + i + 256 * (k - 4), u[k]);
         }
-        __syncthreads();
+        // no barrier here: the next F0 of thread t overwrites exactly the slots i + 256 k that only thread t read in I0
     }
 }
 
@@ -209,51 +223,62 @@ fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict_
 // reference's 1/2048 normalisation folded into the taps (fastfir.cpp:243) becomes 1/4096 by an exact factor 0.5 in H.
 // Big block b produces outputs [3072 b, 3072 b + 3072) from virtual-stream samples [3072 b, 3072 b + 4096).
 // tw4[m] = exp(-j 2 pi m / 4096); ht4[256 k + t] = 0.5 * FFT4096(taps)[bin of slot 16 t + k].
-__global__ void ff4096_permute_kernel(const cpx *__restrict__ hpos4, cpx *__restrict__ ht4) {
+__global__ void ff4096_permute_kernel(const cpx *__restrict__ hpos4, cpx *__restrict__ ht4, double scale) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // idx = 256 k + t  <->  slot 16 t + k (FftPlan<4096> order)
-    if (idx < 4096) ht4[idx] = cpx_scale(hpos4[16 * (idx & 255) + (idx >> 8)], 0.5);
+    if (idx < 4096) ht4[idx] = cpx_scale(hpos4[16 * (idx & 255) + (idx >> 8)], 0.5 * scale);
 }
 
-__global__ void __launch_bounds__(256, 2)
+// One CTA per SM, 512 threads = two independent groups of 256, each transforming its own big block in its own 64 KB of
+// shared memory; H (64 KB) and the twiddle tables are loaded into shared memory ONCE per CTA and shared by both groups.
+// ncu on the two-CTAs-per-SM form with H read through L1: 31 % L1 hit rate (the register spills of 2 x 256 threads and
+// the streaming samples evict H), long-scoreboard the top stall. Here the MID phase has no global access at all, no
+// twiddle lives in a register across phases (no spills), and the groups synchronise on their own named barrier.
+#define PB_FF4_SMEM_CPX (4096 + 2 * 4096 + 64 + 4 * 256)
+__global__ void __launch_bounds__(512, 1)
 fastfir4096x3_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
-                     const cpx *__restrict__ ht4, const cpx *__restrict__ tw4, int nbig, double in_scale, double out_scale,
-                     long long in_stride, long long out_stride, int state_stride) {
+                     const cpx *__restrict__ ht4, const cpx *__restrict__ tw4, int nbig, long long in_stride,
+                     long long out_stride, int state_stride, FfCarry carry) {
     constexpr int LB = 3072;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    cpx *a = reinterpret_cast<cpx *>(smem_raw);
-    cpx *t1 = a + 4096;
+    cpx *hs = reinterpret_cast<cpx *>(smem_raw);      // hs[256 k + t] = H of slot 16 t + k
+    const int g = threadIdx.x >> 8, t = threadIdx.x & 255;
+    cpx *a = hs + 4096 + 4096 * g;
+    cpx *t1 = hs + 3 * 4096;                            // t1[16 b + i] = exp(-j 2 pi i 2^b / 256)
+    cpx *f0 = t1 + 64;                                  // f0[256 b + t] = exp(-j 2 pi t 2^b / 4096)
     state += (long long)blockIdx.y * state_stride;
     in += blockIdx.y * in_stride;
     out += blockIdx.y * out_stride;
-    const int t = threadIdx.x;
-    if (t < 64) t1[t] = tw4[16 * ((t & 15) << (t >> 4))];   // t = 16 b + i -> exp(-j 2 pi i 2^b / 256)
-    const cpx w1 = tw4[t], w2 = tw4[2 * t], w4 = tw4[4 * t], w8 = tw4[8 * t];
+    ff_carry_state(state, s0, in, carry, state_stride);
+    for (int i = threadIdx.x; i < 4096; i += 512) hs[i] = ht4[i];
+    if (threadIdx.x < 64) t1[threadIdx.x] = tw4[16 * ((threadIdx.x & 15) << (threadIdx.x >> 4))];
+    for (int i = threadIdx.x; i < 1024; i += 512) f0[i] = tw4[(i & 255) << (i >> 8)];
     __syncthreads();
-    for (int blk = blockIdx.x; blk < nbig; blk += gridDim.x) {
+    const int step = 2 * gridDim.x;
+    for (int blk = 2 * blockIdx.x + g; blk < nbig; blk += step) {
         const long long v0 = (long long)blk * LB;
         {
             cpx v[16];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) v[k] = cpx_scale(vs_load_stream(state, s0, in, v0 + t + 256 * k), in_scale);
-            if (blk + (int)gridDim.x < nbig) vs_prefetch_l2<256>(state, s0, in, v0 + (long long)gridDim.x * LB + 1024, LB, t);
+            for (int k = 0; k < 16; ++k) v[k] = vs_load_stream(state, s0, in, v0 + t + 256 * k);
+            if (blk + step < nbig) vs_prefetch_l2<256>(state, s0, in, v0 + (long long)step * LB + 1024, LB, t);
             dft16<false>(v);
-            ff_tw16<false>(v, w1, w2, w4, w8);
+            ff_tw16<false>(v, f0[t], f0[256 + t], f0[512 + t], f0[768 + t]);
 #pragma unroll
             for (int k = 0; k < 16; ++k) a[ff_swz(t + 256 * k)] = v[k];
         }
-        __syncthreads();
-        ff_mid_phases<256>(a, t1, ht4, t);
+        asm volatile("bar.sync %0, 256;" ::"r"(g + 1) : "memory");
+        ff_mid_phases<256, true>(a, t1, hs, t, g + 1);
         {
             cpx v[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) v[k] = a[ff_swz(t + 256 * k)];
-            ff_tw16<true>(v, w1, w2, w4, w8);
+            ff_tw16<true>(v, f0[t], f0[256 + t], f0[512 + t], f0[768 + t]);
             dft16<true>(v);
             // samples 1024 .. 4095 of the inverse transform are the valid ones
 #pragma unroll
-            for (int k = 4; k < 16; ++k) ff_st_stream(out + v0 + t + 256 * (k - 4), cpx_scale(v[k], out_scale));
+            for (int k = 4; k < 16; ++k) ff_st_stream(out + v0 + t + 256 * (k - 4), v[k]);
         }
-        __syncthreads();
+        // no barrier here: the next F0 of thread t overwrites exactly the slots t + 256 k that only thread t read in I0
     }
 }
 
@@ -286,6 +311,7 @@ struct pebble_fastfir {
     // reference members (fastfir.cpp:140-143): "unset" sentinels so the first setup always runs
     double lo, hi, offset, fs;
     cpx *d_tw, *d_hpos, *d_ht, *d_taps, *d_state[2];   // d_ht: H in the fused 2048 kernel's order
+    bool h_scale_valid; double h_scale;               // gain currently folded into d_ht / d_ht4
     cpx *d_tw4, *d_hpos4, *d_ht4;                      // N == 2048 only: 4096-point twiddles and H for the triple-block kernel
     int cur, fill;
     int streams;          // independent streams sharing this filter (batched form); state is streams x N cpx
@@ -302,21 +328,20 @@ template <int N> static cudaError_t ff_launch_filter(pebble_fastfir *h, cudaStre
     fastfir_filter_kernel<N><<<1, FftPlan<N>::THREADS, smem, st>>>(h->d_taps, h->d_hpos, h->d_tw);
     pebble::count_launch();
     if (N == 2048) {
-        ff2048_permute_kernel<<<8, 256, 0, st>>>(h->d_hpos, h->d_ht);
-        pebble::count_launch();
         // the triple-block kernel's H: 4096-point transform of the same taps (d_taps is zero beyond N)
         const size_t smem4 = sizeof(cpx) * 4096;
         e = cudaFuncSetAttribute(fastfir_filter_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
         if (e != cudaSuccess) return e;
         fastfir_filter_kernel<4096><<<1, FftPlan<4096>::THREADS, smem4, st>>>(h->d_taps, h->d_hpos4, h->d_tw4);
-        ff4096_permute_kernel<<<16, 256, 0, st>>>(h->d_hpos4, h->d_ht4);
-        pebble::count_launch(); pebble::count_launch();
+        pebble::count_launch();
+        h->h_scale_valid = false;   // d_ht / d_ht4 are rebuilt (with the fused gains) by the next process call
     }
     return cudaGetLastError();
 }
 template <int N>
-static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out, int nblocks, cudaStream_t st,
+static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out, int nblocks, cudaStream_t st, FfCarry carry,
                                      int streams = 1, long long in_stride = 0, long long out_stride = 0) {
+    const FfCarry none = {nullptr, 0, 0};
     const size_t smem = sizeof(cpx) * N;
     cudaError_t e = cudaFuncSetAttribute(fastfir_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -328,11 +353,11 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
     if (grid > nblocks) grid = nblocks;
     if (grid < 1) grid = 1;
     if (N == 2048 && !getenv("PEBBLE_FF_GENERIC")) {
-        const size_t smem2 = sizeof(cpx) * (2048 + 64), smem4 = sizeof(cpx) * (4096 + 64);
-        static int occ2 = 0, occ4 = 0, waves = 2;
+        const size_t smem2 = sizeof(cpx) * (2048 + 64), smem4 = sizeof(cpx) * PB_FF4_SMEM_CPX;
+        static int occ2 = 0, waves = 2;
         static bool triple = true;
-        static void (*kern)(const cpx *, int, const cpx *, cpx *, const cpx *, const cpx *, int, int, double, double,
-                            long long, long long, int) = nullptr;
+        static void (*kern)(const cpx *, int, const cpx *, cpx *, const cpx *, const cpx *, int, int, long long, long long,
+                            int, FfCarry) = nullptr;
         if (!occ2) {
             const char *mb = getenv("PEBBLE_FF_MINB");   // registers per thread: 4 -> 128, 3 -> 168, 2 -> 255
             const int minb = mb ? atoi(mb) : 4;
@@ -341,42 +366,54 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
             if (e != cudaSuccess) return e;
             e = cudaFuncSetAttribute(fastfir4096x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
             if (e != cudaSuccess) return e;
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, fastfir4096x3_kernel, 256, smem4);
-            if (occ4 < 1) occ4 = 1;
             const char *wv = getenv("PEBBLE_FF_WAVES");
             if (wv) waves = atoi(wv) > 0 ? atoi(wv) : 1;
             triple = !getenv("PEBBLE_FF_NO3");
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, kern, 128, smem2);
             if (occ2 < 1) occ2 = 1;
         }
+        // the fused kernels carry in_scale * out_scale on H; rebuild the permuted copies when the filter or the gain changed
+        const double hs = h->in_scale * h->out_scale;
+        if (!h->h_scale_valid || hs != h->h_scale) {
+            ff2048_permute_kernel<<<8, 256, 0, st>>>(h->d_hpos, h->d_ht, hs);
+            ff4096_permute_kernel<<<16, 256, 0, st>>>(h->d_hpos4, h->d_ht4, hs);
+            pebble::count_launch(); pebble::count_launch();
+            h->h_scale = hs; h->h_scale_valid = true;
+        }
         const int state_stride = streams > 1 ? h->N : 0;
-        const int nbig = triple ? nblocks / 3 : 0;
+        // The triple-block kernel wins on throughput (fewer points transformed per output) but one big block is a long
+        // dependent chain and every CTA first loads 64 KB of H: take it only when each 256-thread group gets at least
+        // `big_min` big blocks, otherwise the call is latency-bound and ONE launch of the 2048 kernel is faster
+        // (the receiver tail: 512 reference blocks per step, 29 us as big + rest vs ~10 us).
+        static int big_min = getenv("PEBBLE_FF_BIGMIN") ? atoi(getenv("PEBBLE_FF_BIGMIN")) : 4;
+        const int ctas_big = streams > 1 ? (pebble::num_sms() + streams - 1) / streams : pebble::num_sms();
+        const int nbig = (triple && nblocks / 3 >= 2 * ctas_big * big_min) ? nblocks / 3 : 0;
+        const int rest = nblocks - 3 * nbig;
         if (nbig > 0) {
-            grid = pebble::num_sms() * occ4 * waves;
+            grid = pebble::num_sms();                       // one 512-thread CTA per SM, two big blocks in flight each
             if (streams > 1) grid = (grid + streams - 1) / streams;
-            if (grid > nbig) grid = nbig;
-            fastfir4096x3_kernel<<<dim3(grid, streams), 256, smem4, st>>>(
-                h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht4, h->d_tw4, nbig, h->in_scale, h->out_scale, in_stride,
-                out_stride, state_stride);
+            if (grid > (nbig + 1) / 2) grid = (nbig + 1) / 2;
+            fastfir4096x3_kernel<<<dim3(grid, streams), 512, smem4, st>>>(
+                h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht4, h->d_tw4, nbig, in_stride, out_stride, state_stride,
+                rest > 0 ? none : carry);
             pebble::count_launch();
             e = cudaGetLastError();
             if (e != cudaSuccess) return e;
         }
-        const int rest = nblocks - 3 * nbig;
         if (rest > 0) {
             grid = pebble::num_sms() * occ2 * waves;
             if (streams > 1) grid = (grid + streams - 1) / streams;
             if (grid > rest) grid = rest;
             kern<<<dim3(grid, streams), 128, smem2, st>>>(
-                h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht, h->d_tw, 3 * nbig, nblocks, h->in_scale, h->out_scale,
-                in_stride, out_stride, state_stride);
+                h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht, h->d_tw, 3 * nbig, nblocks, in_stride, out_stride,
+                state_stride, carry);
             pebble::count_launch();
         }
         return cudaGetLastError();
     }
     fastfir_kernel<N><<<dim3(grid, streams), FftPlan<N>::THREADS, smem, st>>>(
         h->d_state[h->cur], h->L + h->fill, in, out, h->d_hpos, h->d_tw, nblocks, h->in_scale, h->out_scale, in_stride,
-        out_stride, streams > 1 ? h->N : 0);
+        out_stride, streams > 1 ? h->N : 0, carry);
     pebble::count_launch();
     return cudaGetLastError();
 }
@@ -394,7 +431,7 @@ pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size) {
     pebble_fastfir *h = new pebble_fastfir();
     h->N = fft_size; h->fir = fir_size; h->L = fft_size / 2;
     h->lo = -1.0; h->hi = 1.0; h->offset = 1.0; h->fs = 1.0;   // fastfir.cpp:140-143
-    h->d_tw = h->d_hpos = h->d_ht = h->d_taps = nullptr; h->d_tw4 = h->d_hpos4 = h->d_ht4 = nullptr; h->d_state[0] = h->d_state[1] = nullptr;
+    h->d_tw = h->d_hpos = h->d_ht = h->d_taps = nullptr; h->d_tw4 = h->d_hpos4 = h->d_ht4 = nullptr; h->h_scale_valid = false; h->h_scale = 1.0; h->d_state[0] = h->d_state[1] = nullptr;
     h->cur = 0; h->fill = 0; h->streams = 1; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
     const size_t nb = sizeof(cpx) * (size_t)fft_size;
     std::vector<double> tw;
@@ -474,22 +511,25 @@ int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double
     cudaStream_t st = (cudaStream_t)stream_v;
     const long long total = (long long)h->fill + n;
     const int nblocks = (int)(total / h->L);
+    // carry: the last L samples before the first unprocessed one, plus the unprocessed remainder
+    const int new_fill = (int)(total % h->L);
+    const int count = h->L + new_fill;
+    const long long vlen = (long long)h->L + total;  // length of state ++ in
+    const FfCarry carry = {h->d_state[h->cur ^ 1], vlen - count, count};
     if (nblocks > 0) {
         if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
         cudaError_t e = FF_DISPATCH(h,
-            ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, h->streams, in_stride, out_stride),
-            ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, h->streams, in_stride, out_stride),
-            ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, h->streams, in_stride, out_stride));
+            ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride),
+            ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride),
+            ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride));
         PB_CUDA(e, PEBBLE_ERR_CUDA);
+    } else {
+        fastfir_state_kernel<<<dim3((count + 255) / 256, h->streams), 256, 0, st>>>(
+            h->d_state[h->cur], h->L + h->fill, (const cpx *)d_in, carry.new_state, carry.start, count, in_stride,
+            h->streams > 1 ? h->N : 0);
+        pebble::count_launch();
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
     }
-    const int new_fill = (int)(total % h->L);
-    const int count = h->L + new_fill;
-    const long long vlen = (long long)h->L + total;
-    fastfir_state_kernel<<<dim3((count + 255) / 256, h->streams), 256, 0, st>>>(
-        h->d_state[h->cur], h->L + h->fill, (const cpx *)d_in, h->d_state[h->cur ^ 1], vlen - count, count, in_stride,
-        h->streams > 1 ? h->N : 0);
-    pebble::count_launch();
-    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
     h->cur ^= 1;
     h->fill = new_fill;
     return nblocks * h->L;
@@ -502,21 +542,23 @@ int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in
     cudaStream_t st = (cudaStream_t)stream_v;
     const long long total = (long long)h->fill + n;
     const int nblocks = (int)(total / h->L);
-    if (nblocks > 0) {
-        if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
-        cudaError_t e = FF_DISPATCH(h, ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st),
-                                    ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st),
-                                    ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st));
-        PB_CUDA(e, PEBBLE_ERR_CUDA);
-    }
     // carry: the last L samples before the first unprocessed one, plus the unprocessed remainder
     const int new_fill = (int)(total % h->L);
     const int count = h->L + new_fill;
     const long long vlen = (long long)h->L + total;  // length of state ++ in
-    fastfir_state_kernel<<<(count + 255) / 256, 256, 0, st>>>(h->d_state[h->cur], h->L + h->fill, (const cpx *)d_in,
-                                                             h->d_state[h->cur ^ 1], vlen - count, count, 0, 0);
-    pebble::count_launch();
-    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    const FfCarry carry = {h->d_state[h->cur ^ 1], vlen - count, count};
+    if (nblocks > 0) {
+        if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
+        cudaError_t e = FF_DISPATCH(h, ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),
+                                    ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),
+                                    ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry));
+        PB_CUDA(e, PEBBLE_ERR_CUDA);
+    } else {
+        fastfir_state_kernel<<<(count + 255) / 256, 256, 0, st>>>(h->d_state[h->cur], h->L + h->fill, (const cpx *)d_in,
+                                                                 carry.new_state, carry.start, count, 0, 0);
+        pebble::count_launch();
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    }
     h->cur ^= 1;
     h->fill = new_fill;
     return nblocks * h->L;

@@ -60,7 +60,10 @@ def test_filter_spectrum_matches_reference_design():
     assert rel_rms(h[:1025] , out[:1025]) <= 1e-9
 
 
-@pytest.mark.parametrize("sizes", [[2048] * 16, [1000, 24, 1024, 3000, 1, 1, 2046, 5000, 777], [1023, 1, 1024, 4096]])
+@pytest.mark.parametrize("sizes", [[2048] * 16, [1000, 24, 1024, 3000, 1, 1, 2046, 5000, 777], [1023, 1, 1024, 4096],
+                                   # 6+ reference blocks per call: the triple-block (4096-point) kernel with 0, 1 and 2
+                                   # left-over reference blocks, mixed with calls that only take the 2048-point kernel
+                                   [6144, 7168, 8192, 5120, 9216, 10240], [7000, 6500, 8100, 1, 13000, 40000]])
 def test_split_stream_counts_and_samples(sizes):
     # fastfir.cpp:299-313 block boundaries: first block after 1024 inputs; any split gives the same stream
     n = sum(sizes)
@@ -123,3 +126,18 @@ def test_device_resident_large_linearity():
     err = (outs[2] - (outs[0] + 2.0 * outs[1])).abs().max().item()
     ref = outs[2].abs().max().item()
     assert err <= 1e-12 * max(ref, 1.0)
+
+
+def test_fused_gain_rides_on_filter_spectrum():
+    # the receiver folds the decimation gain (receiver.cpp:935-938) and the fixed AGC gain into the FastFIR call; the
+    # fused kernels carry the product on H and must pick up a change between two calls of the same stream
+    g, r = _pair()
+    n = 1 << 15
+    x = iq_noise_tones(2 * n, 5, 2e6, [(1.5e3, 0.4)])
+    yr, _ = _feed(r, x, [n, n])
+    g.SetFusedScale(2.5, 0.5)
+    y0, _ = _feed(g, x[:n], [n])
+    g.SetFusedScale(4.0, 3.0)
+    y1, _ = _feed(g, x[n:], [n])
+    assert rel_rms(y0, 1.25 * yr[:n]) <= TOL
+    assert rel_rms(y1, 12.0 * yr[n:]) <= TOL
