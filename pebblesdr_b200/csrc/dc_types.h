@@ -67,6 +67,11 @@ struct DcCall {
     int nch;                  // channels (>= 1)
     int state_stride;         // cpx between two channels' carried state
     long long out_stride;     // cpx between two channels' outputs
+    // single-channel oscillator constants as kernel parameters (constant bank, no registers held across the chunk
+    // loop): used by dc_pipe_kernel; copies of DcChain::w1 / wchunk / r_inf / turn
+    cpx w1, wchunk;
+    double r_inf;
+    uint64_t turn_hi, turn_lo;
 };
 
 // 128-bit phase: (hi,lo) + k*(thi,tlo), returns the top 64 bits.

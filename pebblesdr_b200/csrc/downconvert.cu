@@ -1,7 +1,7 @@
 // downconvert.cu — CDownConvert on the GPU: kernel wrapper + C ABI (include/pebble_cuda.h).
 // Kernel body: dc_fused.cuh (fused NCO mix + decimate-by-2 cascade, one segment per CTA).
 #include "lib_common.h"
-#include "dc_cic.cuh"
+#include "dc_pipe.cuh"
 #include "host_design.h"
 #include "hb_coefs.h"
 #include <cmath>
@@ -66,6 +66,18 @@ static const void *dc_pick_kernel(int C, int front, const DcChain &ch, bool *cic
     if (fn) return fn;
     return C == 512 ? (const void *)dc_fused_kernel<512> : C == 1024 ? (const void *)dc_fused_kernel<1024>
          : C == 2048 ? (const void *)dc_fused_kernel<2048> : (const void *)dc_fused_kernel<4096>;
+}
+
+// The fully compile-time, chunk-pipelined kernel (dc_pipe.cuh) for the 7-stage chains it is instantiated for.
+static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem) {
+    if (getenv("PEBBLE_DC_NOPIPE") || getenv("PEBBLE_DC_NOCIC") || getenv("PEBBLE_DC_GENERIC")) return nullptr;
+    if (ch.nstages != 7 || ch.st[0].len != 3) return nullptr;
+    const int l[6] = {ch.st[1].len, ch.st[2].len, ch.st[3].len, ch.st[4].len, ch.st[5].len, ch.st[6].len};
+    if (l[0] == 11 && l[1] == 11 && l[2] == 11 && l[3] == 11 && l[4] == 15 && l[5] == 27) {   // 10 MSPS / 15 kHz: BASELINE config 2
+        if (C == 2048) { *smem = sizeof(cpx) * DcPipe<2048, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<2048, 11, 11, 11, 11, 15, 27>; }
+        if (C == 1024) { *smem = sizeof(cpx) * DcPipe<1024, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 11, 11, 11, 11, 15, 27>; }
+    }
+    return nullptr;
 }
 
 static int env_int(const char *name, int dflt) {
@@ -144,6 +156,11 @@ static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, 
         // chunk length: the CIC3-fused kernel amortises its per-chunk barriers best at 2048 (measured);
         // the others at 1024. PEBBLE_DC_CHUNK overrides.
         h->chunk = (h->chain.nstages >= 3 && h->chain.st[0].len == 3) ? 2048 : 1024;
+        {
+            // the chunk-pipelined kernel (one barrier per chunk) runs best at 1024: 0.267 ms vs 0.291 ms per 2^26 samples
+            size_t unused = 0;
+            if (dc_pick_pipe(1024, h->chain, &unused)) h->chunk = 1024;
+        }
         {
             const int c = env_int("PEBBLE_DC_CHUNK", 0);
             if (c == 512 || c == 1024 || c == 2048 || c == 4096) h->chunk = c;
@@ -260,11 +277,15 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         call.nch = 1;
         call.state_stride = 0;
         call.out_stride = 0;
+        call.w1 = h->chain.w1; call.wchunk = h->chain.wchunk; call.r_inf = h->chain.r_inf;
+        call.turn_hi = h->chain.turn_hi; call.turn_lo = h->chain.turn_lo;
         bool cic = false;
         const void *fn = dc_pick_kernel(C, call.front, h->chain, &cic);
         // the CIC3-fused kernel keeps the full-rate stage in registers: no stage-0 arrays
-        const size_t smem = (size_t)(dc_smem_cpx(h->chain, C, call.front, call.group) -
-                                     (cic ? 2 * dc_stage_arr(h->chain.st[0], C) : 0)) * sizeof(cpx);
+        size_t smem = (size_t)(dc_smem_cpx(h->chain, C, call.front, call.group) -
+                               (cic ? 2 * dc_stage_arr(h->chain.st[0], C) : 0)) * sizeof(cpx);
+        size_t smem_pipe = 0;
+        if (const void *pf = dc_pick_pipe(C, h->chain, &smem_pipe)) { fn = pf; smem = smem_pipe; }
         if (smem > h->smem_set || fn != h->fn_set) {
             PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
             h->smem_set = smem;
@@ -400,6 +421,7 @@ int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, c
     call.nch = h->nch;
     call.state_stride = PB_DC_MAX_STAGES * PB_DC_PREFIX;
     call.out_stride = out_stride;
+    call.w1 = call.wchunk = cpx_make(0.0, 0.0); call.r_inf = 0.0; call.turn_hi = call.turn_lo = 0;   // per channel: DcChan
     const size_t smem = (size_t)(dc_smem_cpx(h->chain, C, front, call.group) - 2 * dc_stage_arr(h->chain.st[0], C)) * sizeof(cpx);
     if (smem > h->smem_set || fn != h->fn_set) {
         PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
