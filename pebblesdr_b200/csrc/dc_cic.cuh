@@ -27,20 +27,15 @@ template <int K, bool FULL>
 __device__ __forceinline__ void dc_mix_cic(const cpx (&x0)[K], const cpx (&x1)[K], cpx xh0, cpx xh1, cpx seed, cpx w1, cpx w2,
                                            const DcChain *__restrict__ ch, long long g0 /* stream index of x0[0] */,
                                            bool halo_from_state, cpx b_state, cpx (&y)[K], cpx &m_last0, cpx &m_last1) {
-    cpx o[2 * K];
-    o[0] = seed;
-    o[1] = cpx_mul(seed, w1);
-#pragma unroll
-    for (int i = 2; i < 2 * K; ++i) o[i] = cpx_mul(o[i - 2], w2);
+    // oscillator of the even / odd sample of the current pair, stepped by w^2 per pair (two short dependent chains
+    // instead of 2K values held at once: the register budget is what bounds the chunk length)
+    cpx oe = seed, oo = cpx_mul(seed, w1);
     cpx oh0 = cpx_mulc(seed, w2), oh1 = cpx_mulc(seed, w1);   // oscillator two and one samples BEFORE x0[0]
-    if (!FULL) {
-        if (g0 < PB_DC_RTAB) {   // amplitude still converging (first PB_DC_RTAB samples of a stream, finding F5)
-            const double ir = ch->inv_r_inf, rinf = ch->r_inf;
-#pragma unroll
-            for (int i = 0; i < 2 * K; ++i) o[i] = cpx_scale(o[i], (g0 + i < PB_DC_RTAB ? ch->rtab[g0 + i] : rinf) * ir);
-            oh0 = cpx_scale(oh0, (g0 >= 2 ? ch->rtab[g0 - 2] : rinf) * ir);
-            oh1 = cpx_scale(oh1, (g0 >= 1 ? ch->rtab[g0 - 1] : rinf) * ir);
-        }
+    const bool transient = !FULL && g0 < PB_DC_RTAB;   // amplitude still converging (first PB_DC_RTAB samples, finding F5)
+    const double ir = transient ? ch->inv_r_inf : 1.0, rinf = transient ? ch->r_inf : 1.0;
+    if (transient) {
+        oh0 = cpx_scale(oh0, (g0 >= 2 ? ch->rtab[g0 - 2] : rinf) * ir);
+        oh1 = cpx_scale(oh1, (g0 >= 1 ? ch->rtab[g0 - 1] : rinf) * ir);
     }
     cpx bprev;
     {
@@ -51,7 +46,13 @@ __device__ __forceinline__ void dc_mix_cic(const cpx (&x0)[K], const cpx (&x1)[K
     cpx b = cpx_make(0.0, 0.0);
 #pragma unroll
     for (int q = 0; q < K; ++q) {
-        const cpx m0 = cpx_mul(x0[q], o[2 * q]), m1 = cpx_mul(x1[q], o[2 * q + 1]);
+        cpx ce = oe, co = oo;
+        if (transient) {
+            ce = cpx_scale(oe, (g0 + 2 * q < PB_DC_RTAB ? ch->rtab[g0 + 2 * q] : rinf) * ir);
+            co = cpx_scale(oo, (g0 + 2 * q + 1 < PB_DC_RTAB ? ch->rtab[g0 + 2 * q + 1] : rinf) * ir);
+        }
+        const cpx m0 = cpx_mul(x0[q], ce), m1 = cpx_mul(x1[q], co);
+        if (q + 1 < K) { oe = cpx_mul(oe, w2); oo = cpx_mul(oo, w2); }
         const cpx a = cpx_make(fma(.375, m0.x, .125 * m1.x), fma(.375, m0.y, .125 * m1.y));
         const cpx bn = cpx_make(fma(.375, m1.x, .125 * m0.x), fma(.375, m1.y, .125 * m0.y));
         if (q == 0) y[0] = a;                       // completed below once the neighbour's B is known

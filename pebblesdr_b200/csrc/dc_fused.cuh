@@ -344,6 +344,9 @@ __host__ __device__ constexpr int dc_arr_slots(int hh, int cap) {
     return ((((hh + cap / 2 + 8) + ((hh + cap / 2 + 8) >> 2) + 1) + 7) & ~7) + 4;   // == dc_stage_arr
 }
 
+#ifndef PB_DC_TILE_LOADS
+#define PB_DC_TILE_LOADS 5
+#endif
 struct SmemSink {          // next stage's arrays; `half` = its hist/2 + (samples already accumulated)/2
     cpx *ev, *od;
     int half;
@@ -396,6 +399,9 @@ __device__ __forceinline__ void dc_tile4(const cpx *e, const cpx *o, int u, int 
                     ai[r] = fma(h, v.y, ai[r]);
                 }
             }
+            // keep at most PB_DC_TILE_LOADS shared loads in flight: without the fence ptxas hoists all E+3 loads (up to
+            // 80 registers for L = 27) and spills the caller's in-flight sample prefetch around the tile
+            if (PB_DC_TILE_LOADS > 0 && (k % PB_DC_TILE_LOADS) == PB_DC_TILE_LOADS - 1) asm volatile("" ::: "memory");
         }
 #pragma unroll
         for (int r = 0; r < 4; ++r) {

@@ -11,7 +11,7 @@
 // Every stage input is double-buffered ("halves"): job j of stage s reads half j&1 while the stage before it fills the
 // other half, and the hist_s samples a job leaves for the next one are copied to the head of the other half in the
 // same phase. Schedule (all compile-time):
-//     tiles per chunk  TPC_s = C / 2^(s+3)          period  P_s = max(1, 32 / TPC_s)       warps  NW_s = max(1, TPC_s / 32)
+//     tiles per chunk  TPC_s = C / 2^(s+3)          period  P_s = max(1, TJ / TPC_s)       warps  NW_s = max(1, TPC_s / 32)
 //     job j of stage s runs in phase  D_s + j P_s,   D_1 = 1,  D_s = D_(s-1) + P_(s-1) (P_s / P_(s-1) - 1) + 1
 // i.e. one phase after the last job of stage s-1 that feeds it. The half it reads is written again no earlier than two
 // phases later (checked in DESIGN.md section 4), so one barrier per phase orders everything.
@@ -20,13 +20,13 @@
 #include "dc_cic.cuh"
 
 #if defined(__CUDACC__)
-
-template <int C, int L1, int L2, int L3, int L4, int L5, int L6> struct DcPipe {
+// TJ = tiles a job of a late stage waits for (32 = a full warp; 16 halves the late stages' buffers: 3 CTAs per SM)
+template <int C, int TJ, int L1, int L2, int L3, int L4, int L5, int L6> struct DcPipe {
     static constexpr int NST = 6;   // half-band stages 1..6 after the CIC3
     __host__ __device__ static constexpr int len(int s) { return s == 1 ? L1 : s == 2 ? L2 : s == 3 ? L3 : s == 4 ? L4 : s == 5 ? L5 : L6; }
     __host__ __device__ static constexpr int hh(int s) { return dc_hh(len(s)); }
     __host__ __device__ static constexpr int tpc(int s) { return C >> (s + 3); }
-    __host__ __device__ static constexpr int per(int s) { return tpc(s) >= 32 ? 1 : 32 / tpc(s); }
+    __host__ __device__ static constexpr int per(int s) { return tpc(s) >= TJ ? 1 : TJ / tpc(s); }
     __host__ __device__ static constexpr int nw(int s) { return tpc(s) >= 32 ? tpc(s) / 32 : 1; }
     __host__ __device__ static constexpr int cap(int s) { return per(s) * (C >> s); }
     __host__ __device__ static constexpr int arr(int s) { return dc_arr_slots(hh(s), cap(s)); }
@@ -40,9 +40,18 @@ template <int C, int L1, int L2, int L3, int L4, int L5, int L6> struct DcPipe {
     __host__ __device__ static constexpr int total() { return base(NST + 1); }
 };
 
+// Per-segment scalars. They live in shared memory and are re-read (volatile) where needed: held in registers across the
+// phase loop they were what ptxas spilled to local memory (28 KB of L1 left beside 2 x 111 KB of shared memory, so every
+// reload went to L2: long-scoreboard 2.0 stall cycles per issue in the first version of this kernel).
+struct DcSeg {
+    int N, len_last, n_transient, phases, last_seg, pad;
+    long long start, first_out;
+    cpx b_state;
+};
+
 // Stage s of the pipeline in phase p (see the header). N = chunks of this segment, len_last = length of the last one.
 template <class G, int C, int s>
-__device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_last, long long start, long long first_out, cpx *gout) {
+__device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_last, const volatile DcSeg *si, cpx *gout) {
     constexpr int P = G::per(s), D = G::delay(s), A = G::arr(s), HH = G::hh(s);
     const int u = (int)threadIdx.x - 32 * G::warp0(s);
     if (u < 0 || u >= 32 * G::nw(s)) return;
@@ -57,7 +66,7 @@ __device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_l
     cpx *ev = smem + G::base(s) + 2 * (j & 1) * A, *od = ev + A;
     if (4 * u < nout) {
         if (s == G::NST) {
-            dc_tile4<G::len(s)>(ev + 5 * u, od + 5 * u, u, nout, GlobalSink{gout, (start + (long long)c0 * C) >> (s + 1), first_out});
+            dc_tile4<G::len(s)>(ev + 5 * u, od + 5 * u, u, nout, GlobalSink{gout, (si->start + (long long)c0 * C) >> (s + 1), si->first_out});
         } else {
             constexpr int sn = s < G::NST ? s + 1 : s;     // (keeps the constexpr calls in range for the last stage)
             constexpr int PN = G::per(sn), AN = G::arr(sn);
@@ -76,9 +85,9 @@ __device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_l
     }
 }
 
-template <int C, int L1, int L2, int L3, int L4, int L5, int L6>
-__global__ void __launch_bounds__(PB_DC_THREADS, 2) dc_pipe_kernel(const DcChain *__restrict__ ch, const DcCall call) {
-    using G = DcPipe<C, L1, L2, L3, L4, L5, L6>;
+template <int C, int TJ, int MINB, int L1, int L2, int L3, int L4, int L5, int L6>
+__global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_pipe_kernel(const DcChain *__restrict__ ch, const DcCall call) {
+    using G = DcPipe<C, TJ, L1, L2, L3, L4, L5, L6>;
     constexpr int T = PB_DC_THREADS, K = C / (2 * T), NS = 2 * K, S = 7;
     static_assert(K == 2 || K == 4, "chunk must be 4*T or 8*T samples");
     static_assert(G::nw(1) <= T / 32, "stage 1 tiles must fit the CTA");
@@ -88,43 +97,51 @@ __global__ void __launch_bounds__(PB_DC_THREADS, 2) dc_pipe_kernel(const DcChain
     const int tid = threadIdx.x;
 
     // single channel only (the batched form of the 10-stage channelizer chain stays on dc_cic_kernel)
-    const long long seg = blockIdx.x;
-    const cpx *state_in = call.state_in;
-    cpx *state_out = call.state_out;
-    cpx *gout = call.out;
-    const long long seg_begin = seg * call.seg_len;
-    long long seg_end = seg_begin + call.seg_len;
-    if (seg_end > call.n) seg_end = call.n;
-    const long long start = seg == 0 ? 0 : seg_begin - ch->preroll;
-    const long long first_out = seg_begin >> S;
-    const bool last_seg = seg_end == call.n;
-
-    // ---- history of the first job of every stage (head of half 0): carried state for segment 0, else zeros + pre-roll
-#pragma unroll
-    for (int s = 1; s <= G::NST; ++s) {
-        const int hist = 2 * G::hh(s);
-        if (tid < hist)
-            smem[G::base(s) + (tid & 1) * G::arr(s) + dc_slot(tid >> 1)] = seg == 0 ? state_in[s * PB_DC_PREFIX + tid] : cpx_make(0.0, 0.0);
-    }
-    cpx b_state = cpx_make(0.0, 0.0);   // CIC3 state = B of the last mixed pair (downconvert.cpp:528-531)
-    if (seg == 0) {
-        const cpx e = state_in[0], o = state_in[1];
-        b_state = cpx_make(fma(.375, o.x, .125 * e.x), fma(.375, o.y, .125 * e.y));
-    }
-
-    const long long total = seg_end - start;
-    const int N = (int)((total + C - 1) / C);
-    const int len_last = (int)(total - (long long)(N - 1) * C);
-    const long long tr = PB_DC_RTAB - (call.stream_pos + start);
-    const int n_transient = tr > 0 ? (int)((tr + C - 1) / C) : 0;
-    int sl[K];   // slot of this thread's q-th CIC3 output inside half 0 of stage 1's arrays (even q -> even array)
-#pragma unroll
-    for (int q = 0; q < K; ++q) sl[q] = G::base(1) + (q & 1) * A1 + dc_slot(HH1 + ((K * tid + q) >> 1));
-
-    const cpx *in_t = call.in + start + NS * tid;
-    const bool halo_lane = (tid & 31) == 0;
+    __shared__ DcSeg seg_info;
+    const volatile DcSeg *si = &seg_info;
+    const cpx *in_t;
     cpx nx0[K], nx1[K], nxh0 = cpx_make(0.0, 0.0), nxh1 = cpx_make(0.0, 0.0);
+    const bool halo_lane = (tid & 31) == 0;
     {
+        const long long seg = blockIdx.x;
+        const cpx *state_in = call.state_in;
+        const long long seg_begin = seg * call.seg_len;
+        long long seg_end = seg_begin + call.seg_len;
+        if (seg_end > call.n) seg_end = call.n;
+        const long long start = seg == 0 ? 0 : seg_begin - ch->preroll;
+        const long long total = seg_end - start;
+        const int N = (int)((total + C - 1) / C);
+        // ---- history of the first job of every stage (head of half 0): carried state for segment 0, else zeros + pre-roll
+#pragma unroll
+        for (int s = 1; s <= G::NST; ++s) {
+            const int hist = 2 * G::hh(s);
+            if (tid < hist)
+                smem[G::base(s) + (tid & 1) * G::arr(s) + dc_slot(tid >> 1)] = seg == 0 ? state_in[s * PB_DC_PREFIX + tid] : cpx_make(0.0, 0.0);
+        }
+        if (tid == 0) {
+            seg_info.N = N;
+            seg_info.len_last = (int)(total - (long long)(N - 1) * C);
+            const long long tr = PB_DC_RTAB - (call.stream_pos + start);
+            seg_info.n_transient = tr > 0 ? (int)((tr + C - 1) / C) : 0;
+            int phases = N;   // last phase in which any stage still has a job
+#pragma unroll
+            for (int s = 1; s <= G::NST; ++s) {
+                const int J = (N + G::per(s) - 1) / G::per(s);
+                const int e = G::delay(s) + (J - 1) * G::per(s) + 1;
+                phases = e > phases ? e : phases;
+            }
+            seg_info.phases = phases;
+            seg_info.last_seg = seg_end == call.n;
+            seg_info.start = start;
+            seg_info.first_out = seg_begin >> S;
+            cpx b_state = cpx_make(0.0, 0.0);   // CIC3 state = B of the last mixed pair (downconvert.cpp:528-531)
+            if (seg == 0) {
+                const cpx e = state_in[0], o = state_in[1];
+                b_state = cpx_make(fma(.375, o.x, .125 * e.x), fma(.375, o.y, .125 * e.y));
+            }
+            seg_info.b_state = b_state;
+        }
+        in_t = call.in + start + NS * tid;
         const int len0 = (int)(total < C ? total : C);
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -133,37 +150,35 @@ __global__ void __launch_bounds__(PB_DC_THREADS, 2) dc_pipe_kernel(const DcChain
         }
         if (halo_lane && tid > 0 && NS * tid < len0) dc_ld256(in_t - 2, nxh0, nxh1);
     }
+    int sl[K];   // slot of this thread's q-th CIC3 output inside half 0 of stage 1's arrays (even q -> even array)
+#pragma unroll
+    for (int q = 0; q < K; ++q) sl[q] = G::base(1) + (q & 1) * A1 + dc_slot(HH1 + ((K * tid + q) >> 1));
     __syncthreads();
 
-    // last phase in which any stage still has a job
-    int phases = N;
-#pragma unroll
-    for (int s = 1; s <= G::NST; ++s) {
-        const int J = (N + G::per(s) - 1) / G::per(s);
-        const int e = G::delay(s) + (J - 1) * G::per(s) + 1;
-        phases = e > phases ? e : phases;
-    }
-
     cpx seed = cpx_make(0.0, 0.0);
-    for (int p = 0; p < phases; ++p) {
+    for (int p = 0; p < si->phases; ++p) {
+        const int N = si->N, len_last = si->len_last;
         if (p < N) {
             // ---------------- oscillator + mix + CIC3 of chunk p in registers -> stage 1, half p&1 -------------------
             const int ci = p;
-            const bool full = ci > 0 && ci >= n_transient && ci < N - 1;
-            const long long pos = start + (long long)ci * C;
+            const bool full = ci > 0 && ci >= si->n_transient && ci < N - 1;
             const int len = ci < N - 1 ? C : len_last;
             const int hoff = (ci & 1) * 2 * A1;
             cpx y[K], ml0, ml1;
             if ((ci & 31) == 0) {
                 seed = cpx_scale(dc_phase_to_osc(dc_phase_at(call.phase_hi, call.phase_lo, call.turn_hi, call.turn_lo,
-                                                             (uint64_t)(pos + NS * tid + 1))), call.r_inf);
+                                                             (uint64_t)(si->start + (long long)ci * C + NS * tid + 1))), call.r_inf);
             } else {
                 seed = cpx_mul(seed, call.wchunk);
             }
             const cpx w1 = call.w1, w2 = cpx_mul(w1, w1);
-            if (full) dc_mix_cic<K, true>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, 0, false, b_state, y, ml0, ml1);
-            else dc_mix_cic<K, false>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, call.stream_pos + pos + NS * tid,
-                                      ci == 0 && tid == 0, b_state, y, ml0, ml1);
+            if (full) {
+                dc_mix_cic<K, true>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, 0, false, cpx_make(0.0, 0.0), y, ml0, ml1);
+            } else {
+                const cpx b_state = cpx_make(si->b_state.x, si->b_state.y);
+                dc_mix_cic<K, false>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, call.stream_pos + si->start + (long long)ci * C + NS * tid,
+                                     ci == 0 && tid == 0, b_state, y, ml0, ml1);
+            }
             // the samples of chunk p+1 are loaded INTO THE SAME REGISTERS as soon as the mix has consumed chunk p's: they
             // are in flight during the stage tiles and the barrier below (no second register set, no copies)
             in_t += C;
@@ -178,28 +193,29 @@ __global__ void __launch_bounds__(PB_DC_THREADS, 2) dc_pipe_kernel(const DcChain
             } else if (NS * tid < len) {
 #pragma unroll
                 for (int q = 0; q < K; ++q) smem[sl[q] + hoff] = y[q];
-                if (last_seg && ci == N - 1 && NS * tid + NS == len) {   // CIC3 delay line for the next call
-                    state_out[0] = ml0;
-                    state_out[1] = ml1;
+                if (si->last_seg && ci == N - 1 && NS * tid + NS == len) {   // CIC3 delay line for the next call
+                    call.state_out[0] = ml0;
+                    call.state_out[1] = ml1;
                 }
             }
         }
-        dc_pipe_stage<G, C, 1>(smem, p, N, len_last, start, first_out, gout);
-        dc_pipe_stage<G, C, 2>(smem, p, N, len_last, start, first_out, gout);
-        dc_pipe_stage<G, C, 3>(smem, p, N, len_last, start, first_out, gout);
-        dc_pipe_stage<G, C, 4>(smem, p, N, len_last, start, first_out, gout);
-        dc_pipe_stage<G, C, 5>(smem, p, N, len_last, start, first_out, gout);
-        dc_pipe_stage<G, C, 6>(smem, p, N, len_last, start, first_out, gout);
+        dc_pipe_stage<G, C, 1>(smem, p, N, len_last, si, call.out);
+        dc_pipe_stage<G, C, 2>(smem, p, N, len_last, si, call.out);
+        dc_pipe_stage<G, C, 3>(smem, p, N, len_last, si, call.out);
+        dc_pipe_stage<G, C, 4>(smem, p, N, len_last, si, call.out);
+        dc_pipe_stage<G, C, 5>(smem, p, N, len_last, si, call.out);
+        dc_pipe_stage<G, C, 6>(smem, p, N, len_last, si, call.out);
         __syncthreads();
     }
 
-    if (last_seg) {
+    if (si->last_seg) {
         // after its last job every stage's carried history sits at the head of half (jobs & 1)
+        const int N = si->N;
 #pragma unroll
         for (int s = 1; s <= G::NST; ++s) {
             const int J = (N + G::per(s) - 1) / G::per(s);
             const int hist = 2 * G::hh(s);
-            if (tid < hist) state_out[s * PB_DC_PREFIX + tid] = smem[G::base(s) + (2 * (J & 1) + (tid & 1)) * G::arr(s) + dc_slot(tid >> 1)];
+            if (tid < hist) call.state_out[s * PB_DC_PREFIX + tid] = smem[G::base(s) + (2 * (J & 1) + (tid & 1)) * G::arr(s) + dc_slot(tid >> 1)];
         }
     }
 }

@@ -74,8 +74,10 @@ static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem) {
     if (ch.nstages != 7 || ch.st[0].len != 3) return nullptr;
     const int l[6] = {ch.st[1].len, ch.st[2].len, ch.st[3].len, ch.st[4].len, ch.st[5].len, ch.st[6].len};
     if (l[0] == 11 && l[1] == 11 && l[2] == 11 && l[3] == 11 && l[4] == 15 && l[5] == 27) {   // 10 MSPS / 15 kHz: BASELINE config 2
-        if (C == 2048) { *smem = sizeof(cpx) * DcPipe<2048, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<2048, 11, 11, 11, 11, 15, 27>; }
-        if (C == 1024) { *smem = sizeof(cpx) * DcPipe<1024, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 11, 11, 11, 11, 15, 27>; }
+        const int minb = getenv("PEBBLE_DC_MINB") ? atoi(getenv("PEBBLE_DC_MINB")) : 3;
+        if (C == 2048) { *smem = sizeof(cpx) * DcPipe<2048, 32, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<2048, 32, 2, 11, 11, 11, 11, 15, 27>; }
+        if (C == 1024 && minb == 2) { *smem = sizeof(cpx) * DcPipe<1024, 32, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 32, 2, 11, 11, 11, 11, 15, 27>; }
+        if (C == 1024) { *smem = sizeof(cpx) * DcPipe<1024, 16, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 16, 3, 11, 11, 11, 11, 15, 27>; }
     }
     return nullptr;
 }
