@@ -31,7 +31,8 @@ template <int C, int TJ, int L1, int L2, int L3, int L4, int L5, int L6> struct 
     __host__ __device__ static constexpr int cap(int s) { return per(s) * (C >> s); }
     __host__ __device__ static constexpr int arr(int s) { return dc_arr_slots(hh(s), cap(s)); }
     __host__ __device__ static constexpr int delay(int s) { return s == 1 ? 1 : delay(s - 1) + per(s - 1) * (per(s) / per(s - 1) - 1) + 1; }
-    __host__ __device__ static constexpr int base(int s) { return s == 1 ? 0 : base(s - 1) + 4 * arr(s - 1); }   // [half][parity]
+    __host__ __device__ static constexpr int slots(int s) { return s == 1 ? 3 : 2; }   // stage 1 input is triple-buffered
+    __host__ __device__ static constexpr int base(int s) { return s == 1 ? 0 : base(s - 1) + 2 * slots(s - 1) * arr(s - 1); }   // [slot][parity]
     __host__ __device__ static constexpr int warp0(int s) {
         int w = 0;
         for (int q = 1; q < s; ++q) w += nw(q);
@@ -63,7 +64,8 @@ __device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_l
     const int c1 = c0 + P < N ? c0 + P : N;
     const int nin = (c1 - c0) * (C >> s) - (c1 == N ? ((C - len_last) >> s) : 0);
     const int nout = nin >> 1;
-    cpx *ev = smem + G::base(s) + 2 * (j & 1) * A, *od = ev + A;
+    constexpr int NSL = G::slots(s);
+    cpx *ev = smem + G::base(s) + 2 * (j % NSL) * A, *od = ev + A;
     if (4 * u < nout) {
         if (s == G::NST) {
             dc_tile4<G::len(s)>(ev + 5 * u, od + 5 * u, u, nout, GlobalSink{gout, (si->start + (long long)c0 * C) >> (s + 1), si->first_out});
@@ -71,7 +73,7 @@ __device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_l
             constexpr int sn = s < G::NST ? s + 1 : s;     // (keeps the constexpr calls in range for the last stage)
             constexpr int PN = G::per(sn), AN = G::arr(sn);
             const int jn = c0 / PN, off = (c0 - jn * PN) * (C >> sn);
-            cpx *nev = smem + G::base(sn) + 2 * (jn & 1) * AN;
+            cpx *nev = smem + G::base(sn) + 2 * (jn % G::slots(sn)) * AN;
             dc_tile4<G::len(s)>(ev + 5 * u, od + 5 * u, u, nout, SmemSink{nev, nev + AN, G::hh(sn) + (off >> 1)});
         }
     }
@@ -80,7 +82,7 @@ __device__ __forceinline__ void dc_pipe_stage(cpx *smem, int p, int N, int len_l
     if (u < 2 * HH) {
         const int par = u & 1, idx = u >> 1;
         const cpx *src = (par ? od : ev);
-        cpx *dst = smem + G::base(s) + (2 * ((j + 1) & 1) + par) * A;
+        cpx *dst = smem + G::base(s) + (2 * ((j + 1) % NSL) + par) * A;
         dst[dc_slot(idx)] = src[dc_slot(idx + (nin >> 1))];
     }
 }
@@ -98,7 +100,10 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_pipe_kernel(const DcCh
 
     // single channel only (the batched form of the 10-stage channelizer chain stays on dc_cic_kernel)
     __shared__ DcSeg seg_info;
+    __shared__ __align__(8) unsigned long long phase_bar;   // mbarrier: completes once per phase, when all T threads arrived
     const volatile DcSeg *si = &seg_info;
+    const unsigned bar_addr = (unsigned)__cvta_generic_to_shared(&phase_bar);
+    if (tid == 0) asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(bar_addr), "r"(T));
     const cpx *in_t;
     cpx nx0[K], nx1[K], nxh0 = cpx_make(0.0, 0.0), nxh1 = cpx_make(0.0, 0.0);
     const bool halo_lane = (tid & 31) == 0;
@@ -163,7 +168,7 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_pipe_kernel(const DcCh
             const int ci = p;
             const bool full = ci > 0 && ci >= si->n_transient && ci < N - 1;
             const int len = ci < N - 1 ? C : len_last;
-            const int hoff = (ci & 1) * 2 * A1;
+            const int hoff = (ci % 3) * 2 * A1;
             cpx y[K], ml0, ml1;
             if ((ci & 31) == 0) {
                 seed = cpx_scale(dc_phase_to_osc(dc_phase_at(call.phase_hi, call.phase_lo, call.turn_hi, call.turn_lo,
@@ -199,14 +204,26 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_pipe_kernel(const DcCh
                 }
             }
         }
+        // Split barrier: the tiles of phase p read what phase p-1 produced, so a warp waits for "everyone finished
+        // phase p-1" only HERE, after its own mix of chunk p (which depends on nothing from phase p-1: stage 1's input
+        // has three slots). Warps with less tile work run ahead by up to one mix and absorb the imbalance.
+        if (p > 0) {
+            const unsigned parity = (unsigned)(p - 1) & 1u;
+            unsigned done;
+            do {
+                asm volatile("{\n\t.reg .pred q;\n\tmbarrier.try_wait.parity.shared.b64 q, [%1], %2;\n\tselp.u32 %0, 1, 0, q;\n\t}"
+                             : "=r"(done) : "r"(bar_addr), "r"(parity) : "memory");
+            } while (!done);
+        }
         dc_pipe_stage<G, C, 1>(smem, p, N, len_last, si, call.out);
         dc_pipe_stage<G, C, 2>(smem, p, N, len_last, si, call.out);
         dc_pipe_stage<G, C, 3>(smem, p, N, len_last, si, call.out);
         dc_pipe_stage<G, C, 4>(smem, p, N, len_last, si, call.out);
         dc_pipe_stage<G, C, 5>(smem, p, N, len_last, si, call.out);
         dc_pipe_stage<G, C, 6>(smem, p, N, len_last, si, call.out);
-        __syncthreads();
+        asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared.b64 st, [%0];\n\t}" ::"r"(bar_addr) : "memory");
     }
+    __syncthreads();
 
     if (si->last_seg) {
         // after its last job every stage's carried history sits at the head of half (jobs & 1)
@@ -215,7 +232,7 @@ __global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_pipe_kernel(const DcCh
         for (int s = 1; s <= G::NST; ++s) {
             const int J = (N + G::per(s) - 1) / G::per(s);
             const int hist = 2 * G::hh(s);
-            if (tid < hist) call.state_out[s * PB_DC_PREFIX + tid] = smem[G::base(s) + (2 * (J & 1) + (tid & 1)) * G::arr(s) + dc_slot(tid >> 1)];
+            if (tid < hist) call.state_out[s * PB_DC_PREFIX + tid] = smem[G::base(s) + (2 * (J % G::slots(s)) + (tid & 1)) * G::arr(s) + dc_slot(tid >> 1)];
         }
     }
 }
