@@ -21,7 +21,7 @@
 
 #if defined(__CUDACC__)
 // TJ = tiles a job of a late stage waits for (32 = a full warp; 16 halves the late stages' buffers: 3 CTAs per SM)
-template <int C, int TJ, int L1, int L2, int L3, int L4, int L5, int L6> struct DcPipe {
+template <int C, int TJ, int T, int L1, int L2, int L3, int L4, int L5, int L6> struct DcPipe {
     static constexpr int NST = 6;   // half-band stages 1..6 after the CIC3
     __host__ __device__ static constexpr int len(int s) { return s == 1 ? L1 : s == 2 ? L2 : s == 3 ? L3 : s == 4 ? L4 : s == 5 ? L5 : L6; }
     __host__ __device__ static constexpr int hh(int s) { return dc_hh(len(s)); }
@@ -36,7 +36,7 @@ template <int C, int TJ, int L1, int L2, int L3, int L4, int L5, int L6> struct 
     __host__ __device__ static constexpr int warp0(int s) {
         int w = 0;
         for (int q = 1; q < s; ++q) w += nw(q);
-        return w < PB_DC_THREADS / 32 - 1 ? w : PB_DC_THREADS / 32 - 1;   // stages that do not fit share the last warp
+        return w < T / 32 - 1 ? w : T / 32 - 1;   // stages that do not fit share the last warp
     }
     __host__ __device__ static constexpr int total() { return base(NST + 1); }
 };
@@ -102,10 +102,10 @@ __device__ __forceinline__ void dc_pipe_stages(cpx *smem, int warp, int p, int N
     }
 }
 
-template <int C, int TJ, int MINB, int L1, int L2, int L3, int L4, int L5, int L6>
-__global__ void __launch_bounds__(PB_DC_THREADS, MINB) dc_pipe_kernel(const DcChain *__restrict__ ch, const DcCall call) {
-    using G = DcPipe<C, TJ, L1, L2, L3, L4, L5, L6>;
-    constexpr int T = PB_DC_THREADS, K = C / (2 * T), NS = 2 * K, S = 7;
+template <int C, int TJ, int T, int MINB, int L1, int L2, int L3, int L4, int L5, int L6>
+__global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restrict__ ch, const DcCall call) {
+    using G = DcPipe<C, TJ, T, L1, L2, L3, L4, L5, L6>;
+    constexpr int K = C / (2 * T), NS = 2 * K, S = 7;
     static_assert(K == 2 || K == 4, "chunk must be 4*T or 8*T samples");
     static_assert(G::nw(1) <= T / 32, "stage 1 tiles must fit the CTA");
     constexpr int HH1 = G::hh(1), A1 = G::arr(1);

@@ -49,7 +49,7 @@ int cfir_upload(pebble_cfir *f) {
     PB_CUDA(cudaMemset(f->d_hist[1], 0, sizeof(cpx) * PB_FIR_MAX), PEBBLE_ERR_CUDA);
     return 0;
 }
-int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStream_t st) {
+int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, bool dup_input) {
     if (n <= 0) return 0;
     if (f->ntaps <= 0) { pebble::set_error("cfir: filter not initialised"); return PEBBLE_ERR_STATE; }
     if (d_in == d_out) { pebble::set_error("cfir: in-place device call not supported"); return PEBBLE_ERR_ARG; }
@@ -57,8 +57,12 @@ int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStre
     memset(&taps, 0, sizeof(taps));
     memcpy(taps.hI, f->hI, sizeof(double) * f->ntaps);
     memcpy(taps.hQ, f->hQ, sizeof(double) * f->ntaps);
-    cfir_kernel<<<grid_for(n, PB_FIR_TILE), PB_FIR_THREADS, 0, st>>>(f->d_hist[f->cur], d_in, n, taps, f->ntaps, d_out,
-                                                                    f->d_hist[f->cur ^ 1]);
+    if (dup_input && memcmp(f->hI, f->hQ, sizeof(double) * f->ntaps) == 0)
+        cfir_dup_kernel<<<grid_for(n, PB_FIR_TILE), PB_FIR_THREADS, 0, st>>>(f->d_hist[f->cur], d_in, n, taps, f->ntaps, d_out,
+                                                                            f->d_hist[f->cur ^ 1]);
+    else
+        cfir_kernel<<<grid_for(n, PB_FIR_TILE), PB_FIR_THREADS, 0, st>>>(f->d_hist[f->cur], d_in, n, taps, f->ntaps, d_out,
+                                                                        f->d_hist[f->cur ^ 1]);
     pebble::count_launch();
     PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
     f->cur ^= 1;
@@ -241,6 +245,7 @@ struct pebble_demod {
     pebble_cfir am_lp;
     double *d_am_last[2] = {nullptr, nullptr};
     int am_cur = 0;
+    bool am_pre_tiles = false;   // the next AM call finds its tile maps already in d_tiles (demod_am_expect_tiles)
     // NFM
     pebble_cfir nfm_lp;
     PllConst pll;
@@ -260,7 +265,7 @@ static int demod_reserve(pebble_demod *h, int n) {
         PB_CUDA(cudaMalloc(&h->d_tmp, sizeof(cpx) * (size_t)n), PEBBLE_ERR_CUDA);
         h->tmp_cap = (size_t)n;
     }
-    const int tiles = (n + PB_SCAN_TILE - 1) / PB_SCAN_TILE;
+    const int tiles = (n + 1023) / 1024;   // enough for the 1024-sample tiles of the FastFIR-fused path as well
     if (tiles > h->tiles_cap) {
         cudaFree(h->d_tiles); cudaFree(h->d_carry);
         h->d_tiles = nullptr; h->d_carry = nullptr; h->tiles_cap = 0;
@@ -270,6 +275,19 @@ static int demod_reserve(pebble_demod *h, int n) {
     }
     return 0;
 }
+// Receiver chain, AM with the AGC off: the FastFIR kernel that produces the demodulator's input also reduces every
+// 1024-sample block to its affine map (fastfir.cu, ff_am_aggregate). Returns the device array it must fill for a call
+// of n samples (n <= 1024 * PB_AM_DIRECT), or nullptr when the demodulator cannot take pre-computed maps.
+void *demod_am_expect_tiles(pebble_demod *h, int n, double *alpha) {
+    if (h->mode != 0 || n <= 0 || (n + 1023) / 1024 > PB_AM_DIRECT) return nullptr;
+    if (demod_reserve(h, n) < 0) return nullptr;
+    *alpha = (double)0.9999f;
+    h->am_pre_tiles = true;
+    return h->d_tiles;
+}
+
+void demod_am_cancel_tiles(pebble_demod *h) { h->am_pre_tiles = false; }
+
 int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough) {
     if (passthrough) *passthrough = 0;
     if (n <= 0) return 0;
@@ -277,16 +295,25 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         int r = demod_reserve(h, n);
         if (r < 0) return r;
         const double alpha = (double)0.9999f;  // DC_ALPHA is a float literal, demod_am.cpp:36
-        const int tiles = (n + PB_SCAN_TILE - 1) / PB_SCAN_TILE;
-        am_tile_kernel<<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, h->d_tiles);
-        const bool direct = tiles <= PB_AM_DIRECT;
-        if (!direct) am_carry_kernel<<<1, PB_SCAN_THREADS, 0, st>>>(h->d_tiles, tiles, h->d_am_last[h->am_cur], h->d_carry);
-        am_apply_kernel<<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, direct ? nullptr : h->d_carry, h->d_tiles,
-                                                          h->d_am_last[h->am_cur], h->d_tmp, h->d_am_last[h->am_cur ^ 1]);
-        pebble::count_launch(direct ? 2 : 3);
+        if (h->am_pre_tiles) {
+            // the tile maps (one per 1024-sample FastFIR block) were produced by the FastFIR kernel that wrote d_in
+            const int tiles = (n + 1023) / 1024;
+            am_apply_kernel<128><<<tiles, 128, 0, st>>>(d_in, n, alpha, nullptr, h->d_tiles, h->d_am_last[h->am_cur], h->d_tmp,
+                                                        h->d_am_last[h->am_cur ^ 1]);
+            pebble::count_launch();
+            h->am_pre_tiles = false;
+        } else {
+            const int tiles = (n + PB_SCAN_TILE - 1) / PB_SCAN_TILE;
+            am_tile_kernel<<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, h->d_tiles);
+            const bool direct = tiles <= PB_AM_DIRECT;
+            if (!direct) am_carry_kernel<<<1, PB_SCAN_THREADS, 0, st>>>(h->d_tiles, tiles, h->d_am_last[h->am_cur], h->d_carry);
+            am_apply_kernel<PB_SCAN_THREADS><<<tiles, PB_SCAN_THREADS, 0, st>>>(d_in, n, alpha, direct ? nullptr : h->d_carry, h->d_tiles,
+                                                                              h->d_am_last[h->am_cur], h->d_tmp, h->d_am_last[h->am_cur ^ 1]);
+            pebble::count_launch(direct ? 2 : 3);
+        }
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
         h->am_cur ^= 1;
-        return cfir_run_device(&h->am_lp, n, h->d_tmp, d_out, st);  // demod_am.cpp:62
+        return cfir_run_device(&h->am_lp, n, h->d_tmp, d_out, st, true);  // demod_am.cpp:62 (input is (y, y))
     }
     if (h->mode == 2) {  // dmFMN
         int r = demod_reserve(h, n);

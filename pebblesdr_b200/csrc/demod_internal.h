@@ -17,12 +17,19 @@ struct pebble_cfir {
 int cfir_alloc(pebble_cfir *f);
 void cfir_release(pebble_cfir *f);
 int cfir_upload(pebble_cfir *f);   // after hI/hQ/ntaps changed: uploads taps and zeroes the history
-int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStream_t st);
+// dup_input: the caller guarantees re == im for every input sample (lets equal I/Q tap sets take the real-only kernel)
+int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, bool dup_input = false);
 
 struct pebble_agc;
 struct pebble_demod;
 // device-pointer forms used by the fused receiver chain
 int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough);
 int agc_run_device(pebble_agc *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st);
+void *demod_am_expect_tiles(pebble_demod *h, int n, double *alpha);
+// fastfir.cu: the next process call also writes, per 1024-sample output block b, tile_map[b] = {alpha^1024,
+// sum_k alpha^(1023-k) |y_k|} (two doubles), the AM detector's affine map of that block. One call only.
+struct pebble_fastfir;
+int fastfir_am_aggregate_next(pebble_fastfir *h, void *tile_map, double alpha, int n);
+void demod_am_cancel_tiles(pebble_demod *h);
 double agc_manual_gain(const pebble_agc *h);
 int agc_is_off(const pebble_agc *h);

@@ -72,6 +72,55 @@ cfir_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, con
     }
 }
 
+// The same filter when the caller guarantees re == im for every input sample and the I and Q tap sets are equal (the AM
+// detector's output (y, y) through its low-pass, demod_am.cpp:53-62): one real convolution, written to both components.
+// Half the FP64 work and half the shared-memory window of cfir_kernel; bit-identical to it under those two conditions.
+static __global__ void __launch_bounds__(PB_FIR_THREADS)
+cfir_dup_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, int n, const __grid_constant__ FirTaps taps, int ntaps,
+                cpx *__restrict__ out, cpx *__restrict__ new_hist) {
+    __shared__ double win[PB_FIR_TILE + PB_FIR_MAX + (PB_FIR_TILE + PB_FIR_MAX) / 8 + 1];
+    const int h = ntaps - 1;
+    if (blockIdx.x == 0 && new_hist) {
+        for (int i = threadIdx.x; i < h; i += PB_FIR_THREADS) {
+            const int v = n + i;
+            new_hist[i] = v < h ? hist[v] : in[v - h];
+        }
+    }
+    const int ntiles = (n + PB_FIR_TILE - 1) / PB_FIR_TILE;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int t0 = tile * PB_FIR_TILE;
+        const int valid = min(PB_FIR_TILE, n - t0);
+        __syncthreads();
+        for (int p = threadIdx.x; p < valid + h; p += PB_FIR_THREADS) {
+            const int v = t0 + p;
+            win[fir_slot(p)] = v < h ? hist[v].x : in[v - h].x;
+        }
+        __syncthreads();
+        const int i0 = threadIdx.x * PB_FIR_R;
+        if (i0 >= valid) continue;
+        double re[PB_FIR_R], w[PB_FIR_R];
+#pragma unroll
+        for (int j = 0; j < PB_FIR_R; ++j) { re[j] = 0.0; w[j] = win[fir_slot(i0 + h + j)]; }
+        for (int k0 = 0; k0 < ntaps; k0 += PB_FIR_R) {
+#pragma unroll
+            for (int kk = 0; kk < PB_FIR_R; ++kk) {
+                const int k = k0 + kk;
+                if (k < ntaps) {
+                    const double cI = taps.hI[k];
+#pragma unroll
+                    for (int j = 0; j < PB_FIR_R; ++j) re[j] += cI * w[j];
+#pragma unroll
+                    for (int j = PB_FIR_R - 1; j > 0; --j) w[j] = w[j - 1];
+                    if (k + 1 < ntaps) w[0] = win[fir_slot(i0 + h - k - 1)];
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < PB_FIR_R; ++j)
+            if (i0 + j < valid) out[t0 + i0 + j] = cpx_make(re[j], re[j]);
+    }
+}
+
 // ---- affine scan helpers (d <- A*d + B composition) ---------------------------------------------------
 struct Aff { double a, b; };
 __device__ __forceinline__ Aff aff_then(Aff first, Aff second) {  // apply `first`, then `second`
@@ -82,9 +131,10 @@ __device__ __forceinline__ Aff aff_then(Aff first, Aff second) {  // apply `firs
 }
 // Exclusive scan of per-thread maps over the CTA (in thread order). Returns the composition of all
 // lower-numbered threads' maps; *total (valid in every thread) = composition of all threads' maps.
+template <int NT = PB_SCAN_THREADS>
 __device__ __forceinline__ Aff block_aff_exclusive(Aff mine, Aff *total) {
-    __shared__ Aff warp_tot[PB_SCAN_THREADS / 32];
-    __shared__ Aff warp_pre[PB_SCAN_THREADS / 32 + 1];
+    __shared__ Aff warp_tot[NT / 32];
+    __shared__ Aff warp_pre[NT / 32 + 1];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     Aff inc = mine;
 #pragma unroll
@@ -98,15 +148,15 @@ __device__ __forceinline__ Aff block_aff_exclusive(Aff mine, Aff *total) {
     __syncthreads();
     if (threadIdx.x == 0) {
         Aff run; run.a = 1.0; run.b = 0.0;
-        for (int i = 0; i < PB_SCAN_THREADS / 32; ++i) { warp_pre[i] = run; run = aff_then(run, warp_tot[i]); }
-        warp_pre[PB_SCAN_THREADS / 32] = run;
+        for (int i = 0; i < NT / 32; ++i) { warp_pre[i] = run; run = aff_then(run, warp_tot[i]); }
+        warp_pre[NT / 32] = run;
     }
     __syncthreads();
     Aff ex;
     ex.a = __shfl_up_sync(0xffffffffu, inc.a, 1);
     ex.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
     if (lane == 0) { ex.a = 1.0; ex.b = 0.0; }
-    *total = warp_pre[PB_SCAN_THREADS / 32];
+    *total = warp_pre[NT / 32];
     return aff_then(warp_pre[w], ex);
 }
 
@@ -148,12 +198,15 @@ static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_carry_kernel(const 
 // carry == nullptr: the CTA folds the maps of all earlier tiles itself (at most PB_AM_DIRECT of them), which
 // removes the carry launch from the short streams the receiver tail sees (2^19 samples = 256 tiles).
 #define PB_AM_DIRECT 512
-static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_apply_kernel(const cpx *__restrict__ in, int n, double alpha,
+// NT threads x PB_SCAN_PER samples per tile: 256 x 8 = PB_SCAN_TILE for the stand-alone demodulator, 128 x 8 = one
+// FastFIR block when the tile maps come from the FastFIR kernel's epilogue (receiver chain, AGC off).
+template <int NT>
+static __global__ void __launch_bounds__(NT) am_apply_kernel(const cpx *__restrict__ in, int n, double alpha,
                                                                    const double *__restrict__ carry,
                                                                    const Aff *__restrict__ tile_map,
                                                                    const double *__restrict__ d_last_in,
                                                                    cpx *__restrict__ out, double *__restrict__ d_last_out) {
-    const int base = blockIdx.x * PB_SCAN_TILE + threadIdx.x * PB_SCAN_PER;
+    const int base = blockIdx.x * (NT * PB_SCAN_PER) + threadIdx.x * PB_SCAN_PER;
     double mag[PB_SCAN_PER];
     Aff m; m.a = 1.0; m.b = 0.0;
 #pragma unroll
@@ -170,16 +223,16 @@ static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_apply_kernel(const 
     if (carry) {
         d_tile = carry[blockIdx.x];
     } else {
-        const int nt = blockIdx.x, per = (nt + PB_SCAN_THREADS - 1) / PB_SCAN_THREADS;
+        const int nt = blockIdx.x, per = (nt + NT - 1) / NT;
         const int j0 = threadIdx.x * per, j1 = min(nt, j0 + per);
         Aff pm; pm.a = 1.0; pm.b = 0.0;
         for (int j = j0; j < j1; ++j) pm = aff_then(pm, tile_map[j]);
         Aff ptot;
-        block_aff_exclusive(pm, &ptot);
+        block_aff_exclusive<NT>(pm, &ptot);
         d_tile = ptot.a * (*d_last_in) + ptot.b;
     }
     Aff tot;
-    const Aff ex = block_aff_exclusive(m, &tot);
+    const Aff ex = block_aff_exclusive<NT>(m, &tot);
     double d = ex.a * d_tile + ex.b;  // m_amDcLast entering this thread's first sample
 #pragma unroll
     for (int k = 0; k < PB_SCAN_PER; ++k) {

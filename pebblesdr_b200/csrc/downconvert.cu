@@ -69,15 +69,22 @@ static const void *dc_pick_kernel(int C, int front, const DcChain &ch, bool *cic
 }
 
 // The fully compile-time, chunk-pipelined kernel (dc_pipe.cuh) for the 7-stage chains it is instantiated for.
-static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem) {
+static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem, int *threads) {
     if (getenv("PEBBLE_DC_NOPIPE") || getenv("PEBBLE_DC_NOCIC") || getenv("PEBBLE_DC_GENERIC")) return nullptr;
     if (ch.nstages != 7 || ch.st[0].len != 3) return nullptr;
     const int l[6] = {ch.st[1].len, ch.st[2].len, ch.st[3].len, ch.st[4].len, ch.st[5].len, ch.st[6].len};
+    *threads = PB_DC_THREADS;
     if (l[0] == 11 && l[1] == 11 && l[2] == 11 && l[3] == 11 && l[4] == 15 && l[5] == 27) {   // 10 MSPS / 15 kHz: BASELINE config 2
         const int minb = getenv("PEBBLE_DC_MINB") ? atoi(getenv("PEBBLE_DC_MINB")) : 3;
-        if (C == 2048) { *smem = sizeof(cpx) * DcPipe<2048, 32, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<2048, 32, 2, 11, 11, 11, 11, 15, 27>; }
-        if (C == 1024 && minb == 2) { *smem = sizeof(cpx) * DcPipe<1024, 32, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 32, 2, 11, 11, 11, 11, 15, 27>; }
-        if (C == 1024) { *smem = sizeof(cpx) * DcPipe<1024, 16, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 16, 3, 11, 11, 11, 11, 15, 27>; }
+        const int thr = getenv("PEBBLE_DC_THREADS") ? atoi(getenv("PEBBLE_DC_THREADS")) : 256;
+        if (C == 2048) { *smem = sizeof(cpx) * DcPipe<2048, 32, 256, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<2048, 32, 256, 2, 11, 11, 11, 11, 15, 27>; }
+        if (C == 1024 && thr == 128) {
+            *threads = 128;
+            *smem = sizeof(cpx) * DcPipe<1024, 16, 128, 11, 11, 11, 11, 15, 27>::total();
+            return (const void *)dc_pipe_kernel<1024, 16, 128, 3, 11, 11, 11, 11, 15, 27>;
+        }
+        if (C == 1024 && minb == 2) { *smem = sizeof(cpx) * DcPipe<1024, 32, 256, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 32, 256, 2, 11, 11, 11, 11, 15, 27>; }
+        if (C == 1024) { *smem = sizeof(cpx) * DcPipe<1024, 16, 256, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<1024, 16, 256, 3, 11, 11, 11, 11, 15, 27>; }
     }
     return nullptr;
 }
@@ -161,7 +168,8 @@ static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, 
         {
             // the chunk-pipelined kernel (one barrier per chunk) runs best at 1024: 0.267 ms vs 0.291 ms per 2^26 samples
             size_t unused = 0;
-            if (dc_pick_pipe(1024, h->chain, &unused)) h->chunk = 1024;
+            int unused_t = 0;
+            if (dc_pick_pipe(1024, h->chain, &unused, &unused_t)) h->chunk = 1024;
         }
         {
             const int c = env_int("PEBBLE_DC_CHUNK", 0);
@@ -287,14 +295,15 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         size_t smem = (size_t)(dc_smem_cpx(h->chain, C, call.front, call.group) -
                                (cic ? 2 * dc_stage_arr(h->chain.st[0], C) : 0)) * sizeof(cpx);
         size_t smem_pipe = 0;
-        if (const void *pf = dc_pick_pipe(C, h->chain, &smem_pipe)) { fn = pf; smem = smem_pipe; }
+        int threads = PB_DC_THREADS;
+        if (const void *pf = dc_pick_pipe(C, h->chain, &smem_pipe, &threads)) { fn = pf; smem = smem_pipe; }
         if (smem > h->smem_set || fn != h->fn_set) {
             PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
             h->smem_set = smem;
             h->fn_set = fn;
         }
         int occ = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, PB_DC_THREADS, smem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, threads, smem);
         if (occ < 1) occ = 1;
         // segments: one wave of resident CTAs (PEBBLE_DC_WAVES to change), never shorter than 8x the pre-roll or
         // 16 chunks, and a whole number of chunks
@@ -307,7 +316,7 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         call.seg_len = seg;
         const int nseg = (int)((n + seg - 1) / seg);
         void *args[2] = {(void *)&h->d_chain, (void *)&call};
-        PB_CUDA(cudaLaunchKernel(fn, dim3(nseg), dim3(PB_DC_THREADS), args, smem, stream), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaLaunchKernel(fn, dim3(nseg), dim3(threads), args, smem, stream), PEBBLE_ERR_CUDA);
         pebble::count_launch();
     }
     PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);

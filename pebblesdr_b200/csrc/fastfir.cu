@@ -164,11 +164,17 @@ __device__ __forceinline__ void ff_mid_phases(cpx *a, const cpx *t1, const cpx *
     else __syncthreads();
 }
 
+// Optional epilogue for the receiver chain (AM, AGC off): the AM detector's recurrence d <- alpha d + |y| over one output
+// block is the affine map {alpha^1024, sum_k alpha^(1023-k) |y_k|}; all 1024 terms share alpha, so the sum is a plain
+// weighted reduction of values the I0 phase already holds in registers. wts[k] = alpha^(1023-k).
+struct FfAgg { double2 *tile_map; const double *wts; double a_pow; };
+
 template <int MINB>
 __global__ void __launch_bounds__(128, MINB)
 fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict__ in, cpx *__restrict__ out,
                    const cpx *__restrict__ ht, const cpx *__restrict__ tw, int blk_first, int nblocks, long long in_stride,
-                   long long out_stride, int state_stride, FfCarry carry) {
+                   long long out_stride, int state_stride, FfCarry carry, FfAgg agg) {
+    __shared__ double agg_red[4];
     constexpr int L = 1024;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx *a = reinterpret_cast<cpx *>(smem_raw);
@@ -199,6 +205,7 @@ fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict_
         __syncthreads();
         ff_mid_phases<128, false>(a, t1, ht, t, 0);
         // ---- I0 -> global
+        double agg_sum = 0.0;
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
             const int i = t + 128 * g;
@@ -209,6 +216,19 @@ fastfir2048_kernel(const cpx *__restrict__ state, int s0, const cpx *__restrict_
             dft8<true>(u);
 #pragma unroll
             for (int k = 4; k < 8; ++k) ff_st_stream(out + v0 + i + 256 * (k - 4), u[k]);
+            if (agg.tile_map) {
+#pragma unroll
+                for (int k = 4; k < 8; ++k)
+                    agg_sum = fma(agg.wts[i + 256 * (k - 4)], sqrt(u[k].x * u[k].x + u[k].y * u[k].y), agg_sum);   // DB::amplitude, db.h:28-30
+            }
+        }
+        if (agg.tile_map) {   // (uniform) block reduction of the 128 partial sums
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) agg_sum += __shfl_xor_sync(0xffffffffu, agg_sum, d);
+            if ((t & 31) == 0) agg_red[t >> 5] = agg_sum;
+            __syncthreads();
+            if (t == 0) agg.tile_map[(long long)blockIdx.y * nblocks + blk] = make_double2(agg.a_pow, (agg_red[0] + agg_red[1]) + (agg_red[2] + agg_red[3]));
+            __syncthreads();
         }
         // no barrier here: the next F0 of thread t overwrites exactly the slots i + 256 k that only thread t read in I0
     }
@@ -311,6 +331,7 @@ struct pebble_fastfir {
     // reference members (fastfir.cpp:140-143): "unset" sentinels so the first setup always runs
     double lo, hi, offset, fs;
     cpx *d_tw, *d_hpos, *d_ht, *d_taps, *d_state[2];   // d_ht: H in the fused 2048 kernel's order
+    double2 *agg_map; double *d_aggw; double agg_alpha, agg_apow;   // AM aggregate epilogue (one call), its weight table
     bool h_scale_valid; double h_scale;               // gain currently folded into d_ht / d_ht4
     cpx *d_tw4, *d_hpos4, *d_ht4;                      // N == 2048 only: 4096-point twiddles and H for the triple-block kernel
     int cur, fill;
@@ -357,7 +378,7 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
         static int occ2 = 0, waves = 2;
         static bool triple = true;
         static void (*kern)(const cpx *, int, const cpx *, cpx *, const cpx *, const cpx *, int, int, long long, long long,
-                            int, FfCarry) = nullptr;
+                            int, FfCarry, FfAgg) = nullptr;
         if (!occ2) {
             const char *mb = getenv("PEBBLE_FF_MINB");   // registers per thread: 4 -> 128, 3 -> 168, 2 -> 255
             const int minb = mb ? atoi(mb) : 4;
@@ -387,7 +408,10 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
         // (the receiver tail: 512 reference blocks per step, 29 us as big + rest vs ~10 us).
         static int big_min = getenv("PEBBLE_FF_BIGMIN") ? atoi(getenv("PEBBLE_FF_BIGMIN")) : 4;
         const int ctas_big = streams > 1 ? (pebble::num_sms() + streams - 1) / streams : pebble::num_sms();
-        const int nbig = (triple && nblocks / 3 >= 2 * ctas_big * big_min) ? nblocks / 3 : 0;
+        // (the AM aggregate epilogue lives in the 2048 kernel only: such calls are the receiver tail, always latency-bound)
+        const int nbig = (triple && !h->agg_map && nblocks / 3 >= 2 * ctas_big * big_min) ? nblocks / 3 : 0;
+        const FfAgg agg = {h->agg_map, h->d_aggw, h->agg_apow};
+        h->agg_map = nullptr;
         const int rest = nblocks - 3 * nbig;
         if (nbig > 0) {
             grid = pebble::num_sms();                       // one 512-thread CTA per SM, two big blocks in flight each
@@ -406,7 +430,7 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
             if (grid > rest) grid = rest;
             kern<<<dim3(grid, streams), 128, smem2, st>>>(
                 h->d_state[h->cur], h->L + h->fill, in, out, h->d_ht, h->d_tw, 3 * nbig, nblocks, in_stride, out_stride,
-                state_stride, carry);
+                state_stride, carry, agg);
             pebble::count_launch();
         }
         return cudaGetLastError();
@@ -416,6 +440,22 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
         out_stride, streams > 1 ? h->N : 0, carry);
     pebble::count_launch();
     return cudaGetLastError();
+}
+
+int fastfir_am_aggregate_next(pebble_fastfir *h, void *tile_map, double alpha, int n) {
+    if (!h || h->N != 2048 || h->streams != 1 || getenv("PEBBLE_FF_GENERIC") || getenv("PEBBLE_FF_NOAGG")) return PEBBLE_ERR_STATE;
+    if (h->fill != 0 || n <= 0 || n % h->L) return PEBBLE_ERR_STATE;   // output block b must be samples [1024 b, 1024 b + 1024)
+    if (!h->d_aggw || alpha != h->agg_alpha) {
+        std::vector<double> w(1024);
+        w[1023] = 1.0;
+        for (int k = 1022; k >= 0; --k) w[k] = w[k + 1] * alpha;
+        if (!h->d_aggw) PB_CUDA(cudaMalloc(&h->d_aggw, sizeof(double) * 1024), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaMemcpy(h->d_aggw, w.data(), sizeof(double) * 1024, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
+        h->agg_alpha = alpha;
+        h->agg_apow = w[0] * alpha;   // alpha^1024
+    }
+    h->agg_map = (double2 *)tile_map;
+    return 0;
 }
 
 #define FF_DISPATCH(h, expr2048, expr4096, expr8192)                 \
@@ -431,7 +471,7 @@ pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size) {
     pebble_fastfir *h = new pebble_fastfir();
     h->N = fft_size; h->fir = fir_size; h->L = fft_size / 2;
     h->lo = -1.0; h->hi = 1.0; h->offset = 1.0; h->fs = 1.0;   // fastfir.cpp:140-143
-    h->d_tw = h->d_hpos = h->d_ht = h->d_taps = nullptr; h->d_tw4 = h->d_hpos4 = h->d_ht4 = nullptr; h->h_scale_valid = false; h->h_scale = 1.0; h->d_state[0] = h->d_state[1] = nullptr;
+    h->d_tw = h->d_hpos = h->d_ht = h->d_taps = nullptr; h->d_tw4 = h->d_hpos4 = h->d_ht4 = nullptr; h->h_scale_valid = false; h->h_scale = 1.0; h->agg_map = nullptr; h->d_aggw = nullptr; h->agg_alpha = 0.0; h->agg_apow = 0.0; h->d_state[0] = h->d_state[1] = nullptr;
     h->cur = 0; h->fill = 0; h->streams = 1; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
     const size_t nb = sizeof(cpx) * (size_t)fft_size;
     std::vector<double> tw;
@@ -459,7 +499,7 @@ pebble_fastfir_t *pebble_fastfir_create(void) { return pebble_fastfir_create_siz
 
 void pebble_fastfir_destroy(pebble_fastfir_t *h) {
     if (!h) return;
-    cudaFree(h->d_tw); cudaFree(h->d_hpos); cudaFree(h->d_ht); cudaFree(h->d_tw4); cudaFree(h->d_hpos4); cudaFree(h->d_ht4); cudaFree(h->d_taps); cudaFree(h->d_state[0]); cudaFree(h->d_state[1]);
+    cudaFree(h->d_tw); cudaFree(h->d_hpos); cudaFree(h->d_ht); cudaFree(h->d_tw4); cudaFree(h->d_hpos4); cudaFree(h->d_ht4); cudaFree(h->d_aggw); cudaFree(h->d_taps); cudaFree(h->d_state[0]); cudaFree(h->d_state[1]);
     if (h->stream) cudaStreamDestroy(h->stream);
     h->stg.release();
     delete h;

@@ -183,6 +183,13 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
     const double gain = pow(10, (gs * 2) / 20.0);
     const bool fuse_agc = agc_is_off(h->agc);
     pebble_fastfir_set_fused_scale(h->bp, gain, fuse_agc ? agc_manual_gain(h->agc) : 1.0);
+    if (fuse_agc) {
+        // AM with the AGC off: the FastFIR output IS the detector's input, so its kernel also reduces each output block
+        // to the detector's affine map (saves the demodulator's first pass over the data and one launch)
+        double alpha = 0.0;
+        if (void *tiles = demod_am_expect_tiles(h->demod, nproc, &alpha))
+            if (fastfir_am_aggregate_next(h->bp, tiles, alpha, nproc) != 0) demod_am_cancel_tiles(h->demod);
+    }
     r = pebble_fastfir_process_device(h->bp, nproc, (const double *)h->d_frames, (double *)h->d_bp, st);  // receiver.cpp:950
     if (r < 0) return r;
     if (r != nproc) { pebble::set_error("receiver: FastFIR returned %d of %d", r, nproc); return PEBBLE_ERR_STATE; }
