@@ -31,6 +31,12 @@ MODES = {"am": (0, -5000.0, 5000.0), "usb": (7, 300.0, 3000.0)}
 ALG_BYTES_PER_SAMPLE_DC = 16.0 + 16.0 / 128.0      # 16 B read + 16/128 B written
 
 
+# stdout carries exactly ONE JSON line: keep NCCL's "NCCL version ..." banner (printed to stdout at NCCL_DEBUG=VERSION)
+# out of it unless the caller asked for NCCL diagnostics explicitly
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -349,7 +355,7 @@ def main_ours(args):
             "e2e": {"value": world * n * K / (ms_e2e * 1e-3) / 1e6, "unit": UNIT,
                     "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e / K,
                     "call": "pebble_receiver_process_pinned (host buffers, H2D + chain + D2H per step)"},
-            "roofline": {"bound": "hbm", "kernel": "dc_cic_kernel (CDownConvert: NCO mix + CIC3 fused in registers + 6 half-band stages)",
+            "roofline": {"bound": "hbm", "kernel": "dc_pipe_kernel (CDownConvert: NCO mix + CIC3 fused in registers + 6 half-band stages, pipelined across chunks)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(n), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": ALG_BYTES_PER_SAMPLE_DC * n, "kernel_ms": dc_ms,
