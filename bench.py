@@ -31,10 +31,15 @@ MODES = {"am": (0, -5000.0, 5000.0), "usb": (7, 300.0, 3000.0)}
 ALG_BYTES_PER_SAMPLE_DC = 16.0 + 16.0 / 128.0      # 16 B read + 16/128 B written
 
 
-# stdout carries exactly ONE JSON line: keep NCCL's "NCCL version ..." banner (printed to stdout at NCCL_DEBUG=VERSION)
-# out of it unless the caller asked for NCCL diagnostics explicitly
-if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"
+# stdout carries exactly ONE JSON line. Libraries write banners to fd 1 (NCCL's "NCCL version ..." line at communicator
+# creation, whatever NCCL_DEBUG says on this image), so fd 1 is pointed at stderr for the life of the process and the
+# JSON line goes to the saved descriptor.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 
 def parse():
@@ -366,7 +371,7 @@ def main_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             base, _, _ = run_cpu_baseline(args, steps=3, warmup=1)
             line["cpu_baseline"] = base
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -200,7 +200,7 @@ def main(args, bench):
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, nch_total)
-        print(json.dumps(line))
+        bench.emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -228,7 +228,7 @@ def main(args, bench):
                                         "note": "FP64 issue and shared-memory wavefronts bound this operator above the HBM floor"}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = _cpu_fastfir(args) if fast else _cpu_spectrum(args, size)
-        print(json.dumps(line))
+        bench.emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
