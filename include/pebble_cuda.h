@@ -104,6 +104,51 @@ int64_t pebble_downconvert_state_size(const pebble_downconvert_t *h);
 int pebble_downconvert_get_state(pebble_downconvert_t *h, void *buf, int64_t bytes);
 int pebble_downconvert_set_state(pebble_downconvert_t *h, const void *buf, int64_t bytes);
 
+/* ---- Decimator : the reference's alternative decimation chain (Matlab-rounded half-bands, merged stages) -----------
+ * Replaces pebblelib/decimator.h:228-284, implementation decimator.cpp:6-1339 (live when Receiver::m_useDemodDecimator,
+ * receiver.cpp:194-195,910-911: Mixer::processBlock then Decimator::process).
+ * pebble_decimator_create()          <-> Decimator::Decimator(sampleRate, bufferSize)   decimator.cpp:6-45
+ * pebble_decimator_build_chain()     <-> Decimator::buildDecimationChain                decimator.cpp:64-149
+ *      returns the decimated rate (float, as the reference); consecutive steps that pick the same design are MERGED into
+ *      one stage that filters once and keeps every 2^k-th sample (m_combineStages, decimator.cpp:130-143).
+ * pebble_decimator_dec_by2_stages()  <-> Decimator::decBy2Stages()                      decimator.h:241
+ * pebble_decimator_process()         <-> Decimator::process                             decimator.cpp:152-226
+ *      n must be a multiple of the total decimation and large enough that every half-band stage sees >= taps samples;
+ *      otherwise PEBBLE_ERR_ARG. (The reference degrades to plain decimation for such calls and refills its delay
+ *      line from beyond the valid input, decimator.cpp:605-626; that path is not reproduced.) No chain -> copy.
+ *      in and out must not overlap. Results are bit-identical to the reference's scalar arithmetic.
+ * pebble_decimator_plan(): host-only planner (no device): per merged stage taps (0 = CIC3) and decimation. */
+typedef struct pebble_decimator pebble_decimator_t;
+pebble_decimator_t *pebble_decimator_create(unsigned sample_rate, unsigned buffer_size);
+void pebble_decimator_destroy(pebble_decimator_t *h);
+float pebble_decimator_build_chain(pebble_decimator_t *h, unsigned rate_in, unsigned protect_bw, unsigned rate_out);
+int pebble_decimator_dec_by2_stages(const pebble_decimator_t *h);
+int pebble_decimator_total_decimation(const pebble_decimator_t *h);
+int pebble_decimator_chain(const pebble_decimator_t *h, int *taps, int *decimate, int max);
+int pebble_decimator_plan(unsigned rate_in, unsigned protect_bw, unsigned rate_out, int *taps, int *decimate, int max,
+                          float *out_rate, int *dec_by2_stages);
+int pebble_decimator_out_count(const pebble_decimator_t *h, int n);
+int pebble_decimator_process(pebble_decimator_t *h, int n, const double *in, double *out);
+int pebble_decimator_process_device(pebble_decimator_t *h, int n, const double *d_in, double *d_out, void *stream);
+/* Carried state = the last `hist` RAW input samples (oldest first): every stage is a pure FIR, so all delay lines
+ * (m_lastXVDsp, m_xOdd/m_xEven) are re-derived from them. *_state_size returns bytes. */
+int64_t pebble_decimator_state_size(const pebble_decimator_t *h);
+int pebble_decimator_get_state(pebble_decimator_t *h, void *buf, int64_t bytes);
+int pebble_decimator_set_state(pebble_decimator_t *h, const void *buf, int64_t bytes);
+
+/* ---- Mixer : frequency shift by the recursive oscillator ------------------------------------------------------------
+ * Replaces pebblelib/mixer.h, implementation mixer.cpp:5-81 (and the NCO primitive nco.cpp:16-45 it inlines).
+ * pebble_mixer_set_frequency() <-> Mixer::setFrequency  mixer.cpp:25-39  (m_frequency = -f; oscillator restarts at (1,0))
+ * pebble_mixer_process()       <-> Mixer::processBlock  mixer.cpp:48-81  (f == 0: the reference returns `in` itself;
+ *                                  here the samples are copied to out and pebble_mixer_is_passthrough() reports 1) */
+typedef struct pebble_mixer pebble_mixer_t;
+pebble_mixer_t *pebble_mixer_create(unsigned sample_rate, unsigned num_samples);
+void pebble_mixer_destroy(pebble_mixer_t *h);
+void pebble_mixer_set_frequency(pebble_mixer_t *h, double f);
+int pebble_mixer_is_passthrough(const pebble_mixer_t *h);
+int pebble_mixer_process(pebble_mixer_t *h, int n, const double *in, double *out);
+int pebble_mixer_process_device(pebble_mixer_t *h, int n, const double *d_in, double *d_out, void *stream);
+
 /* ---- FFT / SignalSpectrum : windowed FFT, unfold, 2-tap averaged amplitude dB -------------------------
  * Replaces pebblelib/fft.h:29-62 (class FFT + FFTfftw, fftw.cpp:17-81) and the FFT use of
  * application/signalspectrum.cpp:54-113.

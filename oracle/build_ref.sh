@@ -25,7 +25,7 @@ cp "$OUT/fftw/include/fftw3.h" "$OUT/inc/fftw-3.3.4/api/fftw3.h"
 rm -rf "$OUT/build/fftw-3.3.4"
 # 3. the reference sources, compiled in place. -O2 without -march=native: the .so must run on the
 #    GPU box's host CPU too. -ffp-contract=off keeps x86-64 SSE2 double semantics (no FMA fusion).
-SRCS="cpx db windowfunction fft fftw fftcute fastfir downconvert nco mixer fir"
+SRCS="cpx db windowfunction fft fftw fftcute fastfir downconvert nco mixer fir decimator"
 OBJS=""
 CXXFLAGS="-O2 -fPIC -std=c++14 -w -ffp-contract=off -DUSE_FFTW -DPEBBLELIB_LIBRARY \
   -I$HERE/qt_shim -I$OUT/inc/pebblelib_inc -I$REF/pebblelib"
@@ -37,9 +37,12 @@ for s in $SRCS; do
         LC_ALL=C sed $'s/[\x80-\xff]/?/g' "$src" > "$OUT/build/$s.ascii.cpp"
         src="$OUT/build/$s.ascii.cpp"
     fi
-    g++ $CXXFLAGS -c "$src" -o "$OUT/build/$s.o"
+    EXTRA=""
+    # decimator.h names QVector/QMutex without including them (the Qt build gets them from its precompiled header)
+    if [ "$s" = "decimator" ]; then EXTRA="-include QVector -include QMutex -include QDebug"; fi
+    g++ $CXXFLAGS $EXTRA -c "$src" -o "$OUT/build/$s.o"
     OBJS="$OBJS $OUT/build/$s.o"
 done
-g++ $CXXFLAGS -c "$HERE/ref_shim.cpp" -o "$OUT/build/ref_shim.o"
+g++ $CXXFLAGS -include QVector -include QMutex -c "$HERE/ref_shim.cpp" -o "$OUT/build/ref_shim.o"
 g++ -shared -o "$OUT/libpebbleref.so" $OBJS "$OUT/build/ref_shim.o" "$OUT/fftw/lib/libfftw3.a" -lm
 echo "build_ref: wrote $OUT/libpebbleref.so"

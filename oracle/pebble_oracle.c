@@ -788,3 +788,132 @@ int orc_receiver_process(void *p, int n, double *in, double *out_) {
     }
     return nout;
 }
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Decimator — the alternative decimation chain (pebblelib/decimator.cpp). Restates the path the reference runs:
+ * m_useVdsp = m_combineStages = true (decimator.cpp:9-10), USE_MATLAB taps (:4), convolveVDsp2 (:593-659) with
+ * vDSP_zrdesampD as the scalar loop Apple documents (quoted at :637-647), processCIC3 (:719-740).
+ * ---------------------------------------------------------------------------------------------------------- */
+#include "dec_coefs_c.h"
+#define ORC_DEC_MAXLEN 32768  /* maxResultLen, decimator.h:193 */
+typedef struct {
+    int taps, D;              /* taps == 0: CIC3 (m_useCIC3) */
+    const double *h;
+    ocpx x_odd, x_even;       /* m_xOdd, m_xEven */
+    ocpx *last_x;             /* m_lastXVDsp: taps-1 carried samples, then the call's input */
+} orc_dec_stage;
+typedef struct {
+    orc_dec_stage st[16];
+    int nst, dec_by2;
+    float rate;
+    ocpx *buf[2];
+    int buf_len;
+} orc_decimator;
+
+void *orc_decimator_create(unsigned sample_rate, unsigned buffer_size) {  /* decimator.cpp:6-45 */
+    orc_decimator *d = (orc_decimator *)calloc(1, sizeof(orc_decimator));
+    d->rate = (float)sample_rate;
+    d->buf_len = ORC_DEC_MAXLEN;   /* the reference sizes its split buffers 2*bufferSize; the stage buffers cap a call at maxResultLen */
+    (void)buffer_size;
+    d->buf[0] = (ocpx *)calloc(d->buf_len, sizeof(ocpx));
+    d->buf[1] = (ocpx *)calloc(d->buf_len, sizeof(ocpx));
+    return d;
+}
+static void orc_dec_clear(orc_decimator *d) {
+    for (int i = 0; i < d->nst; i++) free(d->st[i].last_x);
+    d->nst = 0;
+}
+void orc_decimator_destroy(void *p) {
+    orc_decimator *d = (orc_decimator *)p;
+    if (!d) return;
+    orc_dec_clear(d);
+    free(d->buf[0]); free(d->buf[1]); free(d);
+}
+/* decimator.cpp:64-149 */
+float orc_decimator_build_chain(void *p, unsigned rate_in, unsigned protect_bw, unsigned rate_out) {
+    orc_decimator *d = (orc_decimator *)p;
+    orc_dec_clear(d);
+    float rate = (float)rate_in;                        /* m_decimatedSampleRate is a float (decimator.h:250) */
+    const double bw = (double)protect_bw;               /* m_protectBandWidth is a double (:251) */
+    const unsigned min_out = rate_out > 0 ? rate_out : 15000u;
+    d->dec_by2 = 0;
+    while (rate > min_out) {
+        int taps = -1;
+        const double *h = NULL;
+        if (rate >= (bw / orc_DecCicWpass)) taps = 0;
+        else
+            for (int k = 1; k < ORC_DEC_NUM_HB; k++)    /* hb7 (k = 0) is compiled out of the chain (:81-86) */
+                if (rate >= (bw / orc_DecHbWpass[k])) { taps = orc_DecHbLen[k]; h = orc_DecHbTaps + orc_DecHbOff[k]; break; }
+        if (taps < 0) break;                            /* :124-126 */
+        d->dec_by2++;
+        if (d->nst == 0 || d->st[d->nst - 1].taps != taps) {   /* :130-136 */
+            orc_dec_stage *s = &d->st[d->nst++];
+            memset(s, 0, sizeof(*s));
+            s->taps = taps; s->D = 2; s->h = h;
+            s->last_x = (ocpx *)calloc(ORC_DEC_MAXLEN, sizeof(ocpx));
+        } else {
+            d->st[d->nst - 1].D *= 2;                   /* :141 */
+        }
+        rate /= 2;
+    }
+    d->rate = rate;
+    return rate;
+}
+int orc_decimator_dec_by2_stages(void *p) { return ((orc_decimator *)p)->dec_by2; }
+int orc_decimator_num_stages(void *p) { return ((orc_decimator *)p)->nst; }
+int orc_decimator_stage(void *p, int i, int *taps, int *D) {
+    orc_decimator *d = (orc_decimator *)p;
+    if (i < 0 || i >= d->nst) return -1;
+    *taps = d->st[i].taps; *D = d->st[i].D;
+    return 0;
+}
+static int orc_dec_cic3(orc_dec_stage *s, const ocpx *in, ocpx *out, int n) {   /* decimator.cpp:719-740 */
+    int m = 0;
+    for (int i = 0; i < n; i += s->D) {
+        const ocpx even = in[i], odd = in[i + 1];
+        out[m].re = .125 * (odd.re + s->x_even.re + 3.0 * (s->x_odd.re + even.re));
+        out[m].im = .125 * (odd.im + s->x_even.im + 3.0 * (s->x_odd.im + even.im));
+        s->x_odd = odd; s->x_even = even;
+        m++;
+    }
+    return m;
+}
+static int orc_dec_hb(orc_dec_stage *s, const ocpx *x, ocpx *y, int xLen) {     /* convolveVDsp2, decimator.cpp:593-659 */
+    const int hLen = s->taps, dLen = hLen - 1, D = s->D;
+    if (xLen < hLen) {   /* :604-626 — plain decimation; the refill below indexes x past xLen exactly as the reference does */
+        int yCnt = 0;
+        for (int i = 0; i < xLen; i += D) y[yCnt++] = x[i];
+        const int save = dLen - xLen;
+        for (int i = 0; i < hLen; i++) {
+            if (i < save) { s->last_x[i].re = 0; s->last_x[i].im = 0; }
+            else s->last_x[i] = x[i];
+        }
+        return yCnt;
+    }
+    memcpy(s->last_x + dLen, x, sizeof(ocpx) * xLen);                            /* :635 */
+    const int yLen = xLen / D;
+    for (int n = 0; n < yLen; n++) {                                              /* vDSP_zrdesampD, :637-648 */
+        double sr = 0, si = 0;
+        for (int k = 0; k < hLen; k++) {
+            sr += s->last_x[n * D + k].re * s->h[k];
+            si += s->last_x[n * D + k].im * s->h[k];
+        }
+        y[n].re = sr; y[n].im = si;
+    }
+    memcpy(s->last_x, x + (xLen - dLen), sizeof(ocpx) * dLen);                    /* :652-654 */
+    return yLen;
+}
+/* decimator.cpp:152-226; n <= 32768 - 58 */
+int orc_decimator_process(void *p, int n, const double *in, double *out) {
+    orc_decimator *d = (orc_decimator *)p;
+    if (d->nst == 0) { memcpy(out, in, sizeof(ocpx) * n); return n; }             /* :155-160 */
+    memcpy(d->buf[0], in, sizeof(ocpx) * n);
+    int cur = 0, rem = n;
+    for (int i = 0; i < d->nst; i++) {
+        orc_dec_stage *s = &d->st[i];
+        rem = s->taps ? orc_dec_hb(s, d->buf[cur], d->buf[cur ^ 1], rem) : orc_dec_cic3(s, d->buf[cur], d->buf[cur ^ 1], rem);
+        cur ^= 1;
+    }
+    memcpy(out, d->buf[cur], sizeof(ocpx) * rem);
+    return rem;
+}

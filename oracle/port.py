@@ -14,7 +14,8 @@ _lib = None
 
 def build():
     src = os.path.join(_HERE, "pebble_oracle.c")
-    if not os.path.exists(PATH) or os.path.getmtime(PATH) < os.path.getmtime(src):
+    deps = [src, os.path.join(_HERE, "hb_coefs_c.h"), os.path.join(_HERE, "dec_coefs_c.h")]
+    if not os.path.exists(PATH) or os.path.getmtime(PATH) < max(os.path.getmtime(d) for d in deps):
         subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", PATH, src, "-lm"])
 
 
@@ -43,6 +44,10 @@ def lib():
             "orc_demod_nfm_pll": (None, [_vp, _i, _vp, _vp]),
             "orc_agc_create": (_vp, [_d]), "orc_agc_destroy": (None, [_vp]), "orc_agc_set_mode": (None, [_vp, _i, _i]),
             "orc_agc_manual_gain": (_d, [_vp]), "orc_agc_process": (None, [_vp, _i, _vp, _vp]),
+            "orc_decimator_create": (_vp, [ctypes.c_uint, ctypes.c_uint]), "orc_decimator_destroy": (None, [_vp]),
+            "orc_decimator_build_chain": (ctypes.c_float, [_vp, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint]),
+            "orc_decimator_dec_by2_stages": (_i, [_vp]), "orc_decimator_num_stages": (_i, [_vp]),
+            "orc_decimator_stage": (_i, [_vp, _i, _vp, _vp]), "orc_decimator_process": (_i, [_vp, _i, _vp, _vp]),
             "orc_receiver_create": (_vp, [_d, _i, _d]), "orc_receiver_destroy": (None, [_vp]),
             "orc_receiver_demod_rate": (_d, [_vp]), "orc_receiver_config": (None, [_vp, _d, _d, _d, _i, _i, _i]),
             "orc_receiver_set_am_bandwidth": (None, [_vp, _d]), "orc_receiver_process": (_i, [_vp, _i, _vp, _vp]),
@@ -151,6 +156,31 @@ class CFir(_H):
 
     def ProcessFilter(self, n, inb, outb):
         lib().orc_cfir_process(self.h, n, inb.ctypes.data, outb.ctypes.data)
+
+
+class Decimator(_H):
+    """Decimator (pebblelib/decimator.cpp), calls of at most 32768-58 samples like the reference."""
+    _dtor = "orc_decimator_destroy"
+
+    def __init__(self, sampleRate, bufferSize):
+        self.h = lib().orc_decimator_create(int(sampleRate), int(bufferSize))
+
+    def buildDecimationChain(self, sampleRateIn, protectBw, sampleRateOut=0):
+        return lib().orc_decimator_build_chain(self.h, int(sampleRateIn), int(protectBw), int(sampleRateOut))
+
+    def decBy2Stages(self):
+        return lib().orc_decimator_dec_by2_stages(self.h)
+
+    def chain(self):
+        t, d = ctypes.c_int(), ctypes.c_int()
+        out = []
+        for i in range(lib().orc_decimator_num_stages(self.h)):
+            lib().orc_decimator_stage(self.h, i, ctypes.byref(t), ctypes.byref(d))
+            out.append((t.value, d.value))
+        return out
+
+    def process(self, inb, outb, n):
+        return lib().orc_decimator_process(self.h, n, inb.ctypes.data, outb.ctypes.data)
 
 
 class Demod(_H):

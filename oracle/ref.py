@@ -38,6 +38,9 @@ def lib():
             "ref_cfir_init_lp": (_i, [_vp, _i, _d, _d, _d, _d, _d]), "ref_cfir_init_hp": (_i, [_vp, _i, _d, _d, _d, _d, _d]),
             "ref_cfir_process_cpx": (None, [_vp, _i, _vp, _vp]), "ref_cfir_process_real": (None, [_vp, _i, _vp, _vp]),
             "ref_mixer_create": (_vp, [ctypes.c_uint, ctypes.c_uint]), "ref_mixer_destroy": (None, [_vp]),
+            "ref_decimator_create": (_vp, [ctypes.c_uint, ctypes.c_uint]), "ref_decimator_destroy": (None, [_vp]),
+            "ref_decimator_build_chain": (ctypes.c_float, [_vp, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint]),
+            "ref_decimator_dec_by2_stages": (_i, [_vp]), "ref_decimator_process": (_i, [_vp, _i, _vp, _vp]),
             "ref_mixer_set_frequency": (None, [_vp, _d]), "ref_mixer_process": (_i, [_vp, _i, _vp, _vp]),
         }
         for k, (r, a) in sig.items():
@@ -136,6 +139,23 @@ class Mixer:
 
     def __del__(self):
         lib().ref_mixer_destroy(self.h)
+
+
+class Decimator:
+    def __init__(self, sampleRate, bufferSize):
+        self.h = lib().ref_decimator_create(int(sampleRate), int(bufferSize))
+
+    def buildDecimationChain(self, sampleRateIn, protectBw, sampleRateOut=0):
+        return lib().ref_decimator_build_chain(self.h, int(sampleRateIn), int(protectBw), int(sampleRateOut))
+
+    def decBy2Stages(self):
+        return lib().ref_decimator_dec_by2_stages(self.h)
+
+    def process(self, inb, outb, n):
+        return lib().ref_decimator_process(self.h, n, inb.ctypes.data, outb.ctypes.data)
+
+    def __del__(self):
+        lib().ref_decimator_destroy(self.h)
 
 
 def window(wtype, n):

@@ -12,6 +12,7 @@
 #include "fir.h"
 #include "mixer.h"
 #include "windowfunction.h"
+#include "decimator.h"
 #include <cstring>
 
 // pebblelib_global.h declares this extern; nothing on the hot path dereferences it.
@@ -94,6 +95,17 @@ int ref_mixer_process(void *h, int n, const double *in, double *out) {
     CPX *r = ((Mixer *)h)->processBlock((CPX *)in);
     memcpy(out, r, sizeof(CPX) * n);
     return r == (CPX *)in;
+}
+
+// ---- Decimator (pebblelib/decimator.h:228-284) ----------------------------------------------------
+void *ref_decimator_create(unsigned fs, unsigned nsamples) { return new Decimator(fs, nsamples); }
+void ref_decimator_destroy(void *h) { delete (Decimator *)h; }
+float ref_decimator_build_chain(void *h, unsigned rateIn, unsigned protectBw, unsigned rateOut) {
+    return ((Decimator *)h)->buildDecimationChain(rateIn, protectBw, rateOut);
+}
+int ref_decimator_dec_by2_stages(void *h) { return (int)((Decimator *)h)->decBy2Stages(); }
+int ref_decimator_process(void *h, int n, const double *in, double *out) {
+    return (int)((Decimator *)h)->process((CPX *)in, (CPX *)out, (quint32)n);
 }
 
 }  // extern "C"

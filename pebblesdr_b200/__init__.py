@@ -3,4 +3,4 @@ as hand-written sm_100a CUDA kernels behind a C ABI (include/pebble_cuda.h). The
 `ops` mirror the reference's operator surface (same names, arguments and return conventions) so the
 parity tests read like calls into pebblelib; all arithmetic happens in libpebblecuda.so on the GPU."""
 from ._lib import lib, PebbleError, LIB_PATH  # noqa: F401
-from .ops import CFastFIR, CDownConvert, FFT, WindowFunction, CFir, AGC, Demod, Receiver, Channelizer  # noqa: F401
+from .ops import CFastFIR, CDownConvert, FFT, WindowFunction, CFir, AGC, Demod, Receiver, Channelizer, Decimator, Mixer, decimator_plan  # noqa: F401

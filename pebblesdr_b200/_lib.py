@@ -44,6 +44,27 @@ SIGNATURES = {
     "pebble_downconvert_state_size": (c_i64, [c_vp]),
     "pebble_downconvert_get_state": (c_int, [c_vp, c_vp, c_i64]),
     "pebble_downconvert_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    # Decimator
+    "pebble_decimator_create": (c_vp, [ctypes.c_uint, ctypes.c_uint]),
+    "pebble_decimator_destroy": (None, [c_vp]),
+    "pebble_decimator_build_chain": (ctypes.c_float, [c_vp, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint]),
+    "pebble_decimator_dec_by2_stages": (c_int, [c_vp]),
+    "pebble_decimator_total_decimation": (c_int, [c_vp]),
+    "pebble_decimator_chain": (c_int, [c_vp, c_vp, c_vp, c_int]),
+    "pebble_decimator_plan": (c_int, [ctypes.c_uint, ctypes.c_uint, ctypes.c_uint, c_vp, c_vp, c_int, c_vp, c_vp]),
+    "pebble_decimator_out_count": (c_int, [c_vp, c_int]),
+    "pebble_decimator_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_decimator_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    "pebble_decimator_state_size": (c_i64, [c_vp]),
+    "pebble_decimator_get_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_decimator_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    # Mixer
+    "pebble_mixer_create": (c_vp, [ctypes.c_uint, ctypes.c_uint]),
+    "pebble_mixer_destroy": (None, [c_vp]),
+    "pebble_mixer_set_frequency": (None, [c_vp, c_dbl]),
+    "pebble_mixer_is_passthrough": (c_int, [c_vp]),
+    "pebble_mixer_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_mixer_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
     # FFT / SignalSpectrum
     "pebble_fft_create": (c_vp, []),
     "pebble_fft_destroy": (None, [c_vp]),

@@ -463,3 +463,69 @@ int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, c
 }
 
 }  // extern "C"
+
+// ---- Mixer (pebblelib/mixer.cpp:5-81): the same recursive oscillator as CDownConvert with no decimation stages ----
+struct pebble_mixer {
+    pebble_downconvert *dc;
+    double frequency;      // m_frequency = -f (mixer.cpp:31)
+    unsigned sample_rate, num_samples;
+};
+
+extern "C" {
+
+pebble_mixer_t *pebble_mixer_create(unsigned sample_rate, unsigned num_samples) {
+    if (sample_rate == 0) return nullptr;
+    pebble_downconvert *dc = pebble_downconvert_create();
+    if (!dc) return nullptr;
+    pebble_mixer *m = new pebble_mixer();
+    m->dc = dc;
+    m->sample_rate = sample_rate;
+    m->num_samples = num_samples;
+    dc->in_rate = (double)sample_rate;
+    dc->max_bw = 0.0;
+    dc->lens.clear();
+    pebble_host::dc_fill_chain(dc->chain, dc->lens);   // zero stages: process = dc_mix_kernel
+    pebble_mixer_set_frequency(m, 0.0);                // mixer.cpp:13
+    return m;
+}
+
+void pebble_mixer_destroy(pebble_mixer_t *m) {
+    if (!m) return;
+    pebble_downconvert_destroy(m->dc);
+    delete m;
+}
+
+void pebble_mixer_set_frequency(pebble_mixer_t *m, double f) {
+    if (!m) return;
+    m->frequency = -f;
+    m->dc->nco_freq = -f;
+    dc_update_osc(m->dc);
+    // m_lastOsc = (1, 0): unlike CDownConvert::SetFrequency, the phase AND the amplitude transient restart (mixer.cpp:36-37)
+    m->dc->phase_hi = m->dc->phase_lo = 0;
+    m->dc->stream_pos = 0;
+}
+
+int pebble_mixer_is_passthrough(const pebble_mixer_t *m) { return m ? (m->frequency == 0 ? 1 : 0) : PEBBLE_ERR_ARG; }
+
+int pebble_mixer_process_device(pebble_mixer_t *m, int n, const double *d_in, double *d_out, void *stream) {
+    if (!m || n < 0 || (n && (!d_in || !d_out))) { pebble::set_error("mixer: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    if (m->frequency == 0) {   // mixer.cpp:51-53 returns `in` itself; in the C ABI the samples are copied, the state is untouched
+        if (d_in != d_out)
+            PB_CUDA(cudaMemcpyAsync(d_out, d_in, sizeof(cpx) * (size_t)n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream), PEBBLE_ERR_CUDA);
+        return n;
+    }
+    return pebble_downconvert_process_device(m->dc, n, d_in, d_out, stream);
+}
+
+int pebble_mixer_process(pebble_mixer_t *m, int n, const double *in, double *out) {
+    if (!m || n < 0 || (n && (!in || !out))) { pebble::set_error("mixer: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    if (m->frequency == 0) {
+        if (in != out) memcpy(out, in, sizeof(cpx) * (size_t)n);
+        return n;
+    }
+    return pebble_downconvert_process(m->dc, n, in, out);
+}
+
+}  // extern "C"

@@ -144,6 +144,87 @@ class CDownConvert(_Handle):
         check(lib.pebble_downconvert_set_state(self._h, buf.ctypes.data, buf.size), "SetState")
 
 
+def decimator_plan(sampleRateIn, protectBw, sampleRateOut=0):
+    """Host-only Decimator::buildDecimationChain (decimator.cpp:64-149): ([(taps, decimate)], rate, decBy2Stages);
+    taps == 0 is the CIC3 stage."""
+    t, d = (ctypes.c_int * 16)(), (ctypes.c_int * 16)()
+    r, s2 = ctypes.c_float(), ctypes.c_int()
+    n = lib.pebble_decimator_plan(int(sampleRateIn), int(protectBw), int(sampleRateOut), t, d, 16, ctypes.byref(r),
+                                  ctypes.byref(s2))
+    return [(t[i], d[i]) for i in range(n)], r.value, s2.value
+
+
+class Decimator(_Handle):
+    """The alternative decimation chain (pebblelib/decimator.h:228-284, decimator.cpp:6-1339)."""
+    _destroy = staticmethod(lib.pebble_decimator_destroy)
+
+    def __init__(self, _sampleRate, _bufferSize):
+        super().__init__(lib.pebble_decimator_create(int(_sampleRate), int(_bufferSize)), "Decimator")
+
+    def buildDecimationChain(self, _sampleRateIn, _protectBw, _sampleRateOut=0):
+        return lib.pebble_decimator_build_chain(self._h, int(_sampleRateIn), int(_protectBw), int(_sampleRateOut))
+
+    def decBy2Stages(self):
+        return check(lib.pebble_decimator_dec_by2_stages(self._h))
+
+    def totalDecimation(self):
+        return check(lib.pebble_decimator_total_decimation(self._h))
+
+    def chain(self):
+        t, d = (ctypes.c_int * 16)(), (ctypes.c_int * 16)()
+        n = check(lib.pebble_decimator_chain(self._h, t, d, 16))
+        return [(t[i], d[i]) for i in range(n)]
+
+    def outCount(self, n):
+        return lib.pebble_decimator_out_count(self._h, n)
+
+    def process(self, _in, _out, _numSamples):
+        nout = check(lib.pebble_decimator_out_count(self._h, _numSamples), "process")
+        if _is_cuda_tensor(_in):
+            return check(lib.pebble_decimator_process_device(self._h, _numSamples, _dev_ptr(_in, _numSamples),
+                                                             _dev_ptr(_out, nout), _stream_ptr()), "process")
+        return check(lib.pebble_decimator_process(self._h, _numSamples, _host_ptr(_in, _numSamples),
+                                                  _host_ptr(_out, nout, True)), "process")
+
+    def GetState(self):
+        n = check(lib.pebble_decimator_state_size(self._h))
+        buf = np.empty(max(n, 1), dtype=np.uint8)
+        check(lib.pebble_decimator_get_state(self._h, buf.ctypes.data, n), "GetState")
+        return buf[:n]
+
+    def SetState(self, buf):
+        check(lib.pebble_decimator_set_state(self._h, buf.ctypes.data, buf.size), "SetState")
+
+
+class Mixer(_Handle):
+    """Frequency shift by the recursive oscillator (pebblelib/mixer.cpp:5-81)."""
+    _destroy = staticmethod(lib.pebble_mixer_destroy)
+
+    def __init__(self, _sampleRate, _bufferSize):
+        super().__init__(lib.pebble_mixer_create(int(_sampleRate), int(_bufferSize)), "Mixer")
+        self._n = int(_bufferSize)
+        self._out = None
+
+    def setFrequency(self, f):
+        lib.pebble_mixer_set_frequency(self._h, f)
+
+    def processBlock(self, _in, n=None):
+        """Returns `_in` itself when the frequency is 0 (mixer.cpp:51-53), else the step's own output buffer."""
+        n = self._n if n is None else n
+        if lib.pebble_mixer_is_passthrough(self._h) == 1:
+            return _in
+        if _is_cuda_tensor(_in):
+            if self._out is None or not _is_cuda_tensor(self._out) or self._out.numel() < n:
+                self._out = torch.empty(n, dtype=torch.complex128, device=_in.device)
+            check(lib.pebble_mixer_process_device(self._h, n, _dev_ptr(_in, n), _dev_ptr(self._out, n), _stream_ptr()),
+                  "processBlock")
+            return self._out[:n]
+        if self._out is None or _is_cuda_tensor(self._out) or self._out.size < n:
+            self._out = np.empty(n, dtype=np.complex128)
+        check(lib.pebble_mixer_process(self._h, n, _host_ptr(_in, n), _host_ptr(self._out, n, True)), "processBlock")
+        return self._out[:n]
+
+
 def _np_ptr(a, count, dtype, writable=False):
     if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags.c_contiguous or a.size < count:
         raise PebbleError("expected a C-contiguous numpy %s array with >= %d elements" % (np.dtype(dtype), count))

@@ -29,6 +29,11 @@ CASES = {
     "fft_fwd_2048": dict(kind="fft", size=2048, n=2048, seed=31, fs=2e6, tones=[(1e5, 0.5)], noise=0.1),
     "spectrum_8192": dict(kind="spectrum", size=8192, frames=4, seed=32, fs=20e6, noise=0.01,
                           tones=[(-7e6, 10 ** -0.5), (-1e6, 0.1), (0.3e6, 10 ** -1.5), (4e6, 0.01), (9e6, 10 ** -2.5)]),
+    # Decimator (pebblelib/decimator.cpp): 10 MSPS -> CIC3, hb11 (x16 merged), hb15, hb27, hb59; 2 MSPS -> hb11 (x4), hb15, hb19, hb31
+    "dec_10msps": dict(kind="dec", rate=10e6, bw=30000, n=8192 * 4, seed=51, tones=[(2.0e3, 0.3), (-2e6, 0.5)], noise=0.01,
+                       calls=[8192, 16384, 8192]),
+    "dec_2msps": dict(kind="dec", rate=2e6, bw=30000, n=2048 * 4, seed=52, tones=[(-4e3, 0.4), (6e5, 0.5)], noise=0.02,
+                      calls=[2048] * 4),
     "window_bh_8192": dict(kind="window", wtype=12, n=8192),
     "window_hamming_2048": dict(kind="window", wtype=6, n=2048),
     "cfir_lp": dict(kind="cfir", args=(0, 1.0, 50.0, 5000.0, 9000.0, 78125.0), n=4096, seed=41, fs=78125.0,
@@ -39,7 +44,7 @@ CASES = {
 def case_input(c):
     if c["kind"] in ("fastfir", "cfir", "fft"):
         return iq(c["n"], c["seed"], c["fs"], c["tones"], c["noise"])
-    if c["kind"] == "dc":
+    if c["kind"] in ("dc", "dec"):
         return iq(c["n"], c["seed"], c["rate"], c["tones"], c["noise"])
     if c["kind"] == "spectrum":
         x = iq(c["size"] * c["frames"], c["seed"], c["fs"], c["tones"], c["noise"])
@@ -73,6 +78,15 @@ def run_case(c, impl):
             assert r == n >> S
             outs.append(o.copy()); pos += n
         return dict(out=np.concatenate(outs), rate=np.array([rate]))
+    if k == "dec":
+        d = impl.Decimator(c["rate"], max(c["calls"]))
+        rate = d.buildDecimationChain(c["rate"], c["bw"])
+        outs, counts, pos = [], [], 0
+        for n in c["calls"]:
+            o = np.zeros(n, dtype=np.complex128)
+            r = d.process(np.ascontiguousarray(x[pos:pos + n]), o, n)
+            outs.append(o[:r].copy()); counts.append(r); pos += n
+        return dict(out=np.concatenate(outs), counts=np.array(counts + [d.decBy2Stages()]), rate=np.array([rate]))
     if k == "fft":
         f = impl.FFT()
         f.fftParams(c["size"], 0, c["fs"], c["size"], 14)

@@ -14,7 +14,7 @@ import sys
 import numpy as np
 import pytest
 
-from conftest import rel_rms
+from conftest import rel_rms, iq_noise_tones
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "golden"))
@@ -124,3 +124,30 @@ def test_cpu_chain_matches_receiver_restatement():
     got = cpu_chain.CpuChain().run(x.copy())
     assert len(got) == len(want) == (n >> 7) // 2048 * 2048
     assert rel_rms(got, want) <= TOL
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libpebbleref.so not built (needs /root/reference)")
+@pytest.mark.parametrize("rate,bw,n", [(10e6, 30000, 8192), (2e6, 30000, 2048), (61.44e6, 30000, 16384), (192000, 30000, 2048),
+                                       (2.048e6, 20000, 4096), (10e6, 30000, 2048)])
+def test_c_oracle_decimator_bit_equal_to_reference_live(rate, bw, n):
+    """Decimator restatement vs decimator.cpp compiled unmodified (scalar vDSP stand-ins): chain, rate and every output
+    bit identical, including the (10e6, 2048) case where the reference's last stages see fewer samples than taps and
+    fall back to plain decimation (decimator.cpp:604-626)."""
+    a, b = port.Decimator(rate, n), ref.Decimator(rate, n)
+    assert a.buildDecimationChain(rate, bw) == b.buildDecimationChain(rate, bw)
+    assert a.decBy2Stages() == b.decBy2Stages()
+    x = iq_noise_tones(n * 5, 61, rate, [(1e3, 0.4), (0.3 * rate, 0.5)], 0.05)
+    for c in range(5):
+        xi = np.ascontiguousarray(x[c * n:(c + 1) * n])
+        ya, yb = np.zeros(n, np.complex128), np.zeros(n, np.complex128)
+        ka, kb = a.process(xi.copy(), ya, n), b.process(xi.copy(), yb, n)
+        assert ka == kb and np.array_equal(ya[:ka], yb[:kb])
+
+
+def test_decimator_planner_host_only():
+    """pebble_decimator_plan needs no device: Decimator::buildDecimationChain incl. merged stages (decimator.cpp:64-149)."""
+    import pebblesdr_b200 as pb
+    for rate, bw in [(10e6, 30000), (2e6, 30000), (61.44e6, 30000), (192000, 30000), (2.048e6, 20000), (12000, 30000)]:
+        o = port.Decimator(rate, 2048)
+        r = o.buildDecimationChain(rate, bw)
+        assert pb.decimator_plan(rate, bw) == (o.chain(), r, o.decBy2Stages())
