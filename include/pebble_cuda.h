@@ -47,6 +47,9 @@ uint64_t pebble_launch_count(void);
  * pebble_fastfir_create_sized()   <-> same algorithm with CONV_FFT_SIZE/CONV_FIR_SIZE as parameters
  *                                     (fastfir.cpp:65-66 are compile-time in the reference; BASELINE
  *                                     config 5 needs 131072/65537). fir_size must be fft_size/2+1.
+ *                                     fft_size in {2048, 4096, 8192}: one block per CTA in shared memory;
+ *                                     fft_size in {32768, 131072}: four-step transform (fastfir_long.cu), all
+ *                                     entry points below (incl. set_streams / process_batch_device) unchanged.
  * pebble_fastfir_setup()          <-> CFastFIR::SetupParameters         fastfir.cpp:191-272
  *      returns 0 = new filter installed, 1 = unchanged (fastfir.cpp:195-199),
  *      2 = "Filter Parameter error": old filter kept, new parameters remembered (fastfir.cpp:208-216)

@@ -46,3 +46,21 @@ done
 g++ $CXXFLAGS -include QVector -include QMutex -c "$HERE/ref_shim.cpp" -o "$OUT/build/ref_shim.o"
 g++ -shared -o "$OUT/libpebbleref.so" $OBJS "$OUT/build/ref_shim.o" "$OUT/fftw/lib/libfftw3.a" -lm
 echo "build_ref: wrote $OUT/libpebbleref.so"
+# 4. BASELINE config 5 (long filter): the same CFastFIR with CONV_FFT_SIZE/CONV_FIR_SIZE 131072/65537. Both are plain
+#    #defines (fastfir.cpp:65-66) and FFT clamps sizes at m_maxFFTSize = 65535 (fft.h:21), so this variant is compiled
+#    from SCRATCH copies (under _ref/build, deleted afterwards) with exactly those three constants changed by sed; no
+#    arithmetic is touched (edits listed in BASELINE.md). Separate .so: the class names are the same.
+LD="$OUT/build/long"
+rm -rf "$LD"; mkdir -p "$LD"
+cp "$REF"/pebblelib/*.h "$LD/"
+for s in cpx db windowfunction fft fftw fastfir; do LC_ALL=C sed $'s/[\x80-\xff]/?/g' "$REF/pebblelib/$s.cpp" > "$LD/$s.cpp"; done
+sed -i -e 's/^#define CONV_FFT_SIZE 2048/#define CONV_FFT_SIZE 131072/' -e 's/^#define CONV_FIR_SIZE 1025/#define CONV_FIR_SIZE 65537/' "$LD/fastfir.cpp"
+sed -i -e 's/m_maxFFTSize = 65535/m_maxFFTSize = 1048576/' "$LD/fft.h"
+grep -q 'CONV_FFT_SIZE 131072' "$LD/fastfir.cpp" && grep -q 'CONV_FIR_SIZE 65537' "$LD/fastfir.cpp" && grep -q 'm_maxFFTSize = 1048576' "$LD/fft.h"
+LFLAGS="-O2 -fPIC -std=c++14 -w -ffp-contract=off -DUSE_FFTW -DPEBBLELIB_LIBRARY -DREF_SHIM_FASTFIR_ONLY -I$HERE/qt_shim -I$OUT/inc/pebblelib_inc -I$LD"
+LOBJS=""
+for s in cpx db windowfunction fft fftw fastfir; do g++ $LFLAGS -c "$LD/$s.cpp" -o "$LD/$s.o"; LOBJS="$LOBJS $LD/$s.o"; done
+g++ $LFLAGS -include QVector -include QMutex -c "$HERE/ref_shim.cpp" -o "$LD/ref_shim.o"
+g++ -shared -o "$OUT/libpebbleref_long.so" $LOBJS "$LD/ref_shim.o" "$OUT/fftw/lib/libfftw3.a" -lm
+rm -rf "$LD"
+echo "build_ref: wrote $OUT/libpebbleref_long.so"

@@ -64,6 +64,43 @@ class CFastFIR:
         lib().ref_fastfir_destroy(self.h)
 
 
+_lib_long = None
+
+
+def long_available():
+    return os.path.exists(os.path.join(os.path.dirname(PATH), "libpebbleref_long.so"))
+
+
+def lib_long():
+    """The reference CFastFIR compiled with CONV_FFT_SIZE/CONV_FIR_SIZE 131072/65537 (build_ref.sh step 4)."""
+    global _lib_long
+    if _lib_long is None:
+        L = ctypes.CDLL(os.path.join(os.path.dirname(PATH), "libpebbleref_long.so"))
+        L.ref_fastfir_create.restype, L.ref_fastfir_create.argtypes = _vp, []
+        L.ref_fastfir_destroy.restype, L.ref_fastfir_destroy.argtypes = None, [_vp]
+        L.ref_fastfir_setup.restype, L.ref_fastfir_setup.argtypes = None, [_vp, _d, _d, _d, _d]
+        L.ref_fastfir_process.restype, L.ref_fastfir_process.argtypes = _i, [_vp, _i, _vp, _vp]
+        _lib_long = L
+    return _lib_long
+
+
+class CFastFIRLong:
+    """BASELINE config 5: the reference CFastFIR at 131072/65537."""
+    FFT_SIZE, FIR_SIZE = 131072, 65537
+
+    def __init__(self):
+        self.h = lib_long().ref_fastfir_create()
+
+    def SetupParameters(self, lo, hi, off, fs):
+        lib_long().ref_fastfir_setup(self.h, lo, hi, off, fs)
+
+    def ProcessData(self, n, inb, outb):
+        return lib_long().ref_fastfir_process(self.h, n, inb.ctypes.data, outb.ctypes.data)
+
+    def __del__(self):
+        lib_long().ref_fastfir_destroy(self.h)
+
+
 class CDownConvert:
     def __init__(self):
         self.h = lib().ref_downconvert_create()

@@ -8,11 +8,13 @@
 #include "cpx.h"
 #include "fft.h"
 #include "fastfir.h"
+#ifndef REF_SHIM_FASTFIR_ONLY   // the long-filter build (build_ref.sh step 4) exports the CFastFIR wrappers only
 #include "downconvert.h"
 #include "fir.h"
 #include "mixer.h"
 #include "windowfunction.h"
 #include "decimator.h"
+#endif
 #include <cstring>
 
 // pebblelib_global.h declares this extern; nothing on the hot path dereferences it.
@@ -30,6 +32,7 @@ int ref_fastfir_process(void *h, int n, const double *in, double *out) {
     return ((CFastFIR *)h)->ProcessData(n, (CPX *)in, (CPX *)out);
 }
 
+#ifndef REF_SHIM_FASTFIR_ONLY
 // ---- CDownConvert (pebblelib/downconvert.h:28-37) -------------------------------------------------
 void *ref_downconvert_create() { return new CDownConvert(); }
 void ref_downconvert_destroy(void *h) { delete (CDownConvert *)h; }
@@ -108,4 +111,5 @@ int ref_decimator_process(void *h, int n, const double *in, double *out) {
     return (int)((Decimator *)h)->process((CPX *)in, (CPX *)out, (quint32)n);
 }
 
+#endif  // REF_SHIM_FASTFIR_ONLY
 }  // extern "C"

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpebblecuda.so")
-CU_SRCS = ["lib_common.cu", "downconvert.cu", "decimator.cu", "fastfir.cu", "spectrum.cu", "demod.cu", "receiver.cu", "channelizer.cu"]
+CU_SRCS = ["lib_common.cu", "downconvert.cu", "decimator.cu", "fastfir.cu", "fastfir_long.cu", "spectrum.cu", "demod.cu", "receiver.cu", "channelizer.cu"]
 CPP_SRCS = ["host_design.cpp", "host_window.cpp", "host_demod.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
@@ -62,8 +62,9 @@ def build_oracle():
     if os.path.exists(src) and _newer(out, [src]):
         _run(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", out, src, "-lm"])
     ref = os.path.join(odir, "_ref", "libpebbleref.so")
-    if os.path.isdir("/root/reference/pebblelib") and _newer(
-            ref, [os.path.join(odir, "ref_shim.cpp"), os.path.join(odir, "build_ref.sh")]):
+    ref_long = os.path.join(odir, "_ref", "libpebbleref_long.so")   # config 5 sizes (131072/65537)
+    deps = [os.path.join(odir, "ref_shim.cpp"), os.path.join(odir, "build_ref.sh")]
+    if os.path.isdir("/root/reference/pebblelib") and (_newer(ref, deps) or _newer(ref_long, deps)):
         _run(["bash", os.path.join(odir, "build_ref.sh")])
 
 

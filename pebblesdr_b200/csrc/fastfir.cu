@@ -6,6 +6,7 @@
 #include "lib_common.h"
 #include "fft_kernels.cuh"
 #include "host_design.h"
+#include "fastfir_long.cuh"
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -335,6 +336,7 @@ struct pebble_fastfir {
     bool h_scale_valid; double h_scale;               // gain currently folded into d_ht / d_ht4
     cpx *d_tw4, *d_hpos4, *d_ht4;                      // N == 2048 only: 4096-point twiddles and H for the triple-block kernel
     int cur, fill;
+    LongFir *lf;          // N > 8192: four-step transform through global memory (fastfir_long.cu)
     int streams;          // independent streams sharing this filter (batched form); state is streams x N cpx
     bool have_filter;
     double in_scale, out_scale;
@@ -442,6 +444,19 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
     return cudaGetLastError();
 }
 
+// Long filters: the four-step kernels, then the carried state by its own small launch.
+static cudaError_t ff_launch_long(pebble_fastfir *h, const cpx *in, cpx *out, int nblocks, cudaStream_t st, FfCarry carry,
+                                  long long in_stride, long long out_stride) {
+    const int state_stride = h->streams > 1 ? h->N : 0;
+    cudaError_t e = lf_process(h->lf, h->d_hpos, h->d_state[h->cur], h->L + h->fill, state_stride, in, in_stride, out, out_stride,
+                               nblocks, h->streams, h->in_scale * h->out_scale, st);
+    if (e != cudaSuccess) return e;
+    fastfir_state_kernel<<<dim3((carry.count + 255) / 256, h->streams), 256, 0, st>>>(
+        h->d_state[h->cur], h->L + h->fill, in, carry.new_state, carry.start, carry.count, in_stride, state_stride);
+    pebble::count_launch();
+    return cudaGetLastError();
+}
+
 int fastfir_am_aggregate_next(pebble_fastfir *h, void *tile_map, double alpha, int n) {
     if (!h || h->N != 2048 || h->streams != 1 || getenv("PEBBLE_FF_GENERIC") || getenv("PEBBLE_FF_NOAGG")) return PEBBLE_ERR_STATE;
     if (h->fill != 0 || n <= 0 || n % h->L) return PEBBLE_ERR_STATE;   // output block b must be samples [1024 b, 1024 b + 1024)
@@ -464,15 +479,15 @@ int fastfir_am_aggregate_next(pebble_fastfir *h, void *tile_map, double alpha, i
 extern "C" {
 
 pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size) {
-    if ((fft_size != 2048 && fft_size != 4096 && fft_size != 8192) || fir_size != fft_size / 2 + 1) {
-        pebble::set_error("fastfir: unsupported size %d/%d (fft in {2048,4096,8192}, fir = fft/2+1)", fft_size, fir_size);
+    if ((fft_size != 2048 && fft_size != 4096 && fft_size != 8192 && !lf_size_supported(fft_size)) || fir_size != fft_size / 2 + 1) {
+        pebble::set_error("fastfir: unsupported size %d/%d (fft in {2048,4096,8192,32768,131072}, fir = fft/2+1)", fft_size, fir_size);
         return nullptr;
     }
     pebble_fastfir *h = new pebble_fastfir();
     h->N = fft_size; h->fir = fir_size; h->L = fft_size / 2;
     h->lo = -1.0; h->hi = 1.0; h->offset = 1.0; h->fs = 1.0;   // fastfir.cpp:140-143
     h->d_tw = h->d_hpos = h->d_ht = h->d_taps = nullptr; h->d_tw4 = h->d_hpos4 = h->d_ht4 = nullptr; h->h_scale_valid = false; h->h_scale = 1.0; h->agg_map = nullptr; h->d_aggw = nullptr; h->agg_alpha = 0.0; h->agg_apow = 0.0; h->d_state[0] = h->d_state[1] = nullptr;
-    h->cur = 0; h->fill = 0; h->streams = 1; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
+    h->lf = nullptr; h->cur = 0; h->fill = 0; h->streams = 1; h->have_filter = false; h->in_scale = h->out_scale = 1.0; h->stream = nullptr;
     const size_t nb = sizeof(cpx) * (size_t)fft_size;
     std::vector<double> tw;
     pebble_host::twiddle_table(fft_size, tw);
@@ -492,6 +507,7 @@ pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size) {
              pebble::cuda_ok(cudaMalloc(&h->d_ht4, 2 * nb), "cudaMalloc") && pebble::cuda_ok(cudaMemset(h->d_ht4, 0, 2 * nb), "cudaMemset") &&
              pebble::cuda_ok(cudaMemcpy(h->d_tw4, tw4.data(), 2 * nb, cudaMemcpyHostToDevice), "cudaMemcpy(tw4)");
     }
+    if (ok && lf_size_supported(fft_size)) ok = (h->lf = lf_create(fft_size, h->d_tw)) != nullptr;
     if (!ok) { pebble_fastfir_destroy(h); return nullptr; }
     return h;
 }
@@ -499,6 +515,7 @@ pebble_fastfir_t *pebble_fastfir_create(void) { return pebble_fastfir_create_siz
 
 void pebble_fastfir_destroy(pebble_fastfir_t *h) {
     if (!h) return;
+    lf_destroy(h->lf);
     cudaFree(h->d_tw); cudaFree(h->d_hpos); cudaFree(h->d_ht); cudaFree(h->d_tw4); cudaFree(h->d_hpos4); cudaFree(h->d_ht4); cudaFree(h->d_aggw); cudaFree(h->d_taps); cudaFree(h->d_state[0]); cudaFree(h->d_state[1]);
     if (h->stream) cudaStreamDestroy(h->stream);
     h->stg.release();
@@ -513,7 +530,8 @@ int pebble_fastfir_setup(pebble_fastfir_t *h, double lo, double hi, double offse
     if (!pebble_host::fastfir_design(h->N, h->fir, lo, hi, offset, fs, taps)) return 2;  // fastfir.cpp:208-216
     // in-order with any process call already queued on the legacy stream
     PB_CUDA(cudaMemcpy(h->d_taps, taps.data(), sizeof(cpx) * (size_t)h->N, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
-    cudaError_t e = FF_DISPATCH(h, ff_launch_filter<2048>(h, 0), ff_launch_filter<4096>(h, 0), ff_launch_filter<8192>(h, 0));
+    cudaError_t e = h->lf ? lf_build_filter(h->lf, h->d_taps, h->d_hpos, 0)
+                          : FF_DISPATCH(h, ff_launch_filter<2048>(h, 0), ff_launch_filter<4096>(h, 0), ff_launch_filter<8192>(h, 0));
     PB_CUDA(e, PEBBLE_ERR_CUDA);
     PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
     h->have_filter = true;
@@ -558,7 +576,7 @@ int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double
     const FfCarry carry = {h->d_state[h->cur ^ 1], vlen - count, count};
     if (nblocks > 0) {
         if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
-        cudaError_t e = FF_DISPATCH(h,
+        cudaError_t e = h->lf ? ff_launch_long(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, in_stride, out_stride) : FF_DISPATCH(h,
             ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride),
             ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride),
             ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride));
@@ -589,7 +607,8 @@ int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in
     const FfCarry carry = {h->d_state[h->cur ^ 1], vlen - count, count};
     if (nblocks > 0) {
         if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
-        cudaError_t e = FF_DISPATCH(h, ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),
+        cudaError_t e = h->lf ? ff_launch_long(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, 0, 0) :
+                        FF_DISPATCH(h, ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),
                                     ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),
                                     ff_launch_process<8192>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry));
         PB_CUDA(e, PEBBLE_ERR_CUDA);
@@ -648,7 +667,8 @@ int pebble_fastfir_get_filter(pebble_fastfir_t *h, double *coef_out) {
     PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaMemcpy(hp.data(), h->d_hpos, sizeof(cpx) * h->N, cudaMemcpyDeviceToHost), PEBBLE_ERR_CUDA);
     for (int f = 0; f < h->N; ++f) {
-        int p = FF_DISPATCH(h, FftPlan<2048>::freq2pos(f), FftPlan<4096>::freq2pos(f), FftPlan<8192>::freq2pos(f));
+        int p = h->lf ? lf_freq2index(h->N, f)
+                      : FF_DISPATCH(h, FftPlan<2048>::freq2pos(f), FftPlan<4096>::freq2pos(f), FftPlan<8192>::freq2pos(f));
         coef_out[2 * f] = hp[p].x;
         coef_out[2 * f + 1] = hp[p].y;
     }

@@ -1,0 +1,198 @@
+// fastfir_long.cu — CFastFIR for long filters: N-point overlap-save with N = N1 x 2048 too large for shared memory
+// (BASELINE config 5: CONV_FFT_SIZE 131072 / CONV_FIR_SIZE 65537, fastfir.cpp:65-66 with the sizes lifted; algorithm
+// fastfir.cpp:281-334 unchanged: FFT of L old + L new samples, x H, unnormalised inverse, keep samples L..N-1).
+//
+// Four-step transform, index split n = 2048 n1 + n2, k = k1 + N1 k2 (N1 = R x R, R = 8 for 131072, 4 for 32768):
+//   cols fwd : for every column n2 an N1-point DFT over n1 (stride 2048)                 -> scratch[k1][n2]
+//   rows     : x W_N^(n2 k1), 2048-point DFT over n2 (shared memory, fft_core.cuh), x H (CpxMpy, fastfir.cpp:324-334),
+//              inverse 2048-point DFT, x conj W_N^(n2 k1)                                -> scratch[k1][n2] in place
+//   cols inv : inverse N1-point DFT over k1; only n1 >= N1/2 (the L valid samples) is formed and written.
+// H is kept in the rows kernel's own [k1][slot] order (slot = digit-reversed k2), so nothing is ever reordered.
+//
+// HBM: algorithmic 32 B per input sample (16 read + 16 written). The scratch round trips (3 x 32 B per sample) are kept
+// out of DRAM by processing `chunk` blocks at a time with chunk x N x 16 B well inside the 126 MB L2: the three launches
+// of a chunk run back to back on one stream, so the rows and the inverse columns find their input in L2.
+#include "fastfir_long.cuh"
+#include "fft_kernels.cuh"
+#include <cstdlib>
+#include <vector>
+
+namespace {
+constexpr int LF_N2 = 2048;
+constexpr int LF_TC = 16;   // columns per CTA of the column kernels: 16 x 16 B = 256 B contiguous per row
+
+__device__ __forceinline__ cpx lf_ld_stream(const cpx *p) {
+    cpx r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void lf_st_stream(cpx *p, cpx v) {
+    asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(v.x), "d"(v.y) : "memory");
+}
+
+struct LfGeom {
+    int nblocks;            // blocks per stream in this call
+    int L;                  // N / 2
+    int s0;                 // samples of the virtual stream that come from `state`
+    int state_stride;       // cpx between the states of consecutive streams
+    long long in_stride, out_stride;
+    long long job0;         // first job (stream * nblocks + block) of this launch
+};
+
+// Column transforms of LF_TC adjacent columns of one block. Thread (c, i): column c, butterfly i of each radix-R pass.
+// Forward: pass 0 on rows i + R k (twiddle W_N1^(i q) after the DFT), pass 1 on rows R i + k; slot R i + q = bin i + R q.
+// Inverse: the mirror image (pass 1, conj twiddle, pass 0).
+template <int R, bool INV>
+__global__ void __launch_bounds__(LF_TC *R)
+lf_cols_kernel(const cpx *__restrict__ state, const cpx *__restrict__ in, cpx *__restrict__ out, cpx *__restrict__ scratch,
+               const cpx *__restrict__ twN, LfGeom g, double scale) {
+    constexpr int N1 = R * R;
+    __shared__ __align__(16) cpx a[N1 * LF_TC];
+    __shared__ __align__(16) cpx w[N1];
+    const int t = threadIdx.x, c = t % LF_TC, i = t / LF_TC;
+    const long long job = g.job0 + blockIdx.y;
+    const int s = (int)(job / g.nblocks), b = (int)(job % g.nblocks);
+    const int col = blockIdx.x * LF_TC + c;
+    cpx *sc = scratch + (size_t)blockIdx.y * ((size_t)N1 * LF_N2) + col;
+    if (t < N1) w[t] = twN[(size_t)t * LF_N2];   // W_N1^t = W_N^(2048 t)
+    cpx v[R];
+    if (!INV) {
+        const cpx *st = state + (long long)s * g.state_stride;
+        const cpx *ip = in + s * g.in_stride;
+        const long long v0 = (long long)b * g.L + col;
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            const long long u = v0 + (long long)LF_N2 * (i + R * k);
+            v[k] = lf_ld_stream(u < g.s0 ? st + u : ip + (u - g.s0));
+        }
+        __syncthreads();   // w[]
+        DftR<R, false>::run(v);
+#pragma unroll
+        for (int q = 0; q < R; ++q) a[(i + R * q) * LF_TC + c] = q ? cpx_mul(v[q], w[i * q]) : v[q];
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < R; ++k) v[k] = a[(R * i + k) * LF_TC + c];
+        DftR<R, false>::run(v);
+#pragma unroll
+        for (int q = 0; q < R; ++q) sc[(size_t)(i + R * q) * LF_N2] = v[q];
+    } else {
+#pragma unroll
+        for (int k = 0; k < R; ++k) v[k] = sc[(size_t)(i + R * k) * LF_N2];
+        DftR<R, true>::run(v);
+#pragma unroll
+        for (int q = 0; q < R; ++q) a[(R * i + q) * LF_TC + c] = v[q];
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            v[q] = a[(i + R * q) * LF_TC + c];
+            if (q) v[q] = cpx_mulc(v[q], w[i * q]);
+        }
+        DftR<R, true>::run(v);
+        // v[k] = sample n1 = i + R k of column col; the valid half is n1 >= N1/2 (fastfir.cpp:308-311)
+        cpx *op = out + s * g.out_stride + (long long)b * g.L + col;
+#pragma unroll
+        for (int k = R / 2; k < R; ++k) lf_st_stream(op + (long long)LF_N2 * (i + R * k - N1 / 2), cpx_scale(v[k], scale));
+    }
+}
+
+// One row k1 of one block: twiddle, 2048-point forward, x H, inverse, conj twiddle, in place. FILTER: forward only -> H.
+template <bool FILTER>
+__global__ void __launch_bounds__(FftPlan<LF_N2>::THREADS)
+lf_rows_kernel(cpx *__restrict__ scratch, const cpx *__restrict__ hpos, cpx *__restrict__ hout, const cpx *__restrict__ tw2,
+               const cpx *__restrict__ twN, int N1) {
+    __shared__ __align__(128) cpx a[LF_N2];
+    constexpr int SH = FftPlan<LF_N2>::SH;
+    const int k1 = blockIdx.x;
+    cpx *row = scratch + ((size_t)blockIdx.y * N1 + k1) * LF_N2;
+    for (int n2 = threadIdx.x; n2 < LF_N2; n2 += blockDim.x) a[fft_swz<SH>(n2)] = cpx_mul(row[n2], twN[n2 * k1]);
+    __syncthreads();
+    fft_forward_smem<LF_N2>(a, tw2);
+    if (FILTER) {
+        for (int p = threadIdx.x; p < LF_N2; p += blockDim.x) hout[(size_t)k1 * LF_N2 + p] = a[fft_swz<SH>(p)];
+        return;
+    }
+    for (int p = threadIdx.x; p < LF_N2; p += blockDim.x)
+        a[fft_swz<SH>(p)] = cpx_mul(hpos[(size_t)k1 * LF_N2 + p], a[fft_swz<SH>(p)]);
+    __syncthreads();
+    fft_inverse_smem<LF_N2>(a, tw2);
+    for (int n2 = threadIdx.x; n2 < LF_N2; n2 += blockDim.x) row[n2] = cpx_mulc(a[fft_swz<SH>(n2)], twN[n2 * k1]);
+}
+}  // namespace
+
+struct LongFir {
+    int N, N1, R;
+    const cpx *d_twN;
+    cpx *d_tw2;        // exp(-2 pi j m / 2048)
+    cpx *d_scratch;
+    int chunk;         // blocks per launch triple
+};
+
+bool lf_size_supported(int fft_size) { return fft_size == 32768 || fft_size == 131072; }
+
+LongFir *lf_create(int fft_size, const cpx *d_twN) {
+    if (!lf_size_supported(fft_size)) return nullptr;
+    LongFir *p = new LongFir();
+    p->N = fft_size; p->N1 = fft_size / LF_N2; p->R = p->N1 == 64 ? 8 : 4; p->d_twN = d_twN;
+    p->d_tw2 = nullptr; p->d_scratch = nullptr;
+    // default: 24 blocks x 2 MB = 48 MB of scratch in flight, inside the 126 MB L2 together with the chunk's input
+    const char *e = getenv("PEBBLE_LF_CHUNK_MB");
+    const int mb = e && atoi(e) > 0 ? atoi(e) : 48;
+    p->chunk = (int)(((size_t)mb << 20) / (sizeof(cpx) * (size_t)fft_size));
+    if (p->chunk < 1) p->chunk = 1;
+    bool ok = pebble::cuda_ok(cudaMalloc(&p->d_tw2, sizeof(cpx) * LF_N2), "cudaMalloc") &&
+              pebble::cuda_ok(cudaMalloc(&p->d_scratch, sizeof(cpx) * (size_t)fft_size * p->chunk), "cudaMalloc") &&
+              // W_2048^m = W_N^(N1 m): strided copy out of the caller's table
+              pebble::cuda_ok(cudaMemcpy2D(p->d_tw2, sizeof(cpx), d_twN, sizeof(cpx) * p->N1, sizeof(cpx), LF_N2,
+                                           cudaMemcpyDeviceToDevice), "cudaMemcpy2D(tw2)");
+    if (!ok) { lf_destroy(p); return nullptr; }
+    return p;
+}
+
+void lf_destroy(LongFir *p) {
+    if (!p) return;
+    cudaFree(p->d_tw2); cudaFree(p->d_scratch);
+    delete p;
+}
+
+int lf_freq2index(int fft_size, int f) {
+    const int N1 = fft_size / LF_N2;
+    return (f % N1) * LF_N2 + FftPlan<LF_N2>::freq2pos(f / N1);
+}
+
+template <int R>
+static cudaError_t lf_run(LongFir *p, const cpx *hpos, cpx *hout, const cpx *state, const cpx *in, cpx *out, LfGeom g,
+                          long long jobs, double scale, cudaStream_t st) {
+    const dim3 cgrid(LF_N2 / LF_TC, 1), cblock(LF_TC * R);
+    for (long long j0 = 0; j0 < jobs; j0 += p->chunk) {
+        const unsigned nj = (unsigned)(jobs - j0 < p->chunk ? jobs - j0 : p->chunk);
+        g.job0 = j0;
+        lf_cols_kernel<R, false><<<dim3(cgrid.x, nj), cblock, 0, st>>>(state, in, nullptr, p->d_scratch, p->d_twN, g, 1.0);
+        if (hout) {
+            lf_rows_kernel<true><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, st>>>(p->d_scratch, nullptr, hout, p->d_tw2,
+                                                                                    p->d_twN, p->N1);
+            pebble::count_launch(2);
+            continue;
+        }
+        lf_rows_kernel<false><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, st>>>(p->d_scratch, hpos, nullptr, p->d_tw2,
+                                                                                 p->d_twN, p->N1);
+        lf_cols_kernel<R, true><<<dim3(cgrid.x, nj), cblock, 0, st>>>(nullptr, nullptr, out, p->d_scratch, p->d_twN, g, scale);
+        pebble::count_launch(3);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t lf_build_filter(LongFir *p, const cpx *d_taps, cpx *d_hpos, cudaStream_t st) {
+    // the taps as a one-block stream with no carried state: V = taps
+    LfGeom g = {1, p->N / 2, 0, 0, 0, 0, 0};
+    return p->R == 8 ? lf_run<8>(p, nullptr, d_hpos, d_taps, d_taps, nullptr, g, 1, 1.0, st)
+                     : lf_run<4>(p, nullptr, d_hpos, d_taps, d_taps, nullptr, g, 1, 1.0, st);
+}
+
+cudaError_t lf_process(LongFir *p, const cpx *d_hpos, const cpx *state, int s0, int state_stride, const cpx *in,
+                       long long in_stride, cpx *out, long long out_stride, int nblocks, int streams, double scale,
+                       cudaStream_t st) {
+    LfGeom g = {nblocks, p->N / 2, s0, state_stride, in_stride, out_stride, 0};
+    const long long jobs = (long long)nblocks * streams;
+    return p->R == 8 ? lf_run<8>(p, d_hpos, nullptr, state, in, out, g, jobs, scale, st)
+                     : lf_run<4>(p, d_hpos, nullptr, state, in, out, g, jobs, scale, st);
+}

@@ -141,3 +141,97 @@ def test_fused_gain_rides_on_filter_spectrum():
     y1, _ = _feed(g, x[n:], [n])
     assert rel_rms(y0, 1.25 * yr[:n]) <= TOL
     assert rel_rms(y1, 12.0 * yr[n:]) <= TOL
+
+
+# ---- long filters (BASELINE config 5: 131072-point overlap-save, 65537 taps; four-step kernels, fastfir_long.cu) ----------
+def _long_oracle(N):
+    """The reference compiled at 131072/65537 when present, else the C restatement (pinned to it, tests/test_oracle.py)."""
+    from oracle import ref, port
+    if N == 131072 and ref.long_available():
+        return ref.CFastFIRLong()
+    return port.CFastFIR(N, N // 2 + 1)
+
+
+@pytest.mark.parametrize("N,calls", [(32768, [16384 * 5]), (32768, [7, 16377, 40000, 9152]),
+                                     (131072, [65536 * 3]), (131072, [65536, 5000, 2 * 65536 - 5000, 4096, 61440])])
+def test_long_filter_vs_reference(N, calls):
+    import pebblesdr_b200 as pb
+    L, n = N // 2, sum(calls)
+    x = iq_noise_tones(n, 5000, 100e6, [(7e6, 0.4), (31e6, 0.5)], 0.1)
+    g, r = pb.CFastFIR(N, L + 1), _long_oracle(N)
+    assert g.SetupParameters(-20e6, 20e6, 0.0, 100e6) == 0
+    r.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    yg, yr, pos = [], [], 0
+    for c in calls:
+        xi = np.ascontiguousarray(x[pos:pos + c])
+        og, orr = np.zeros(c + N, complex), np.zeros(c + N, complex)
+        kg, kr = g.ProcessData(c, xi, og), r.ProcessData(c, xi.copy(), orr)
+        assert kg == kr                                            # counts and block boundaries exact
+        yg.append(og[:kg].copy()); yr.append(orr[:kr].copy())
+        pos += c
+    yg, yr = np.concatenate(yg), np.concatenate(yr)
+    assert len(yg) == (n // L) * L
+    assert rel_rms(yg, yr) <= TOL
+
+
+def test_long_filter_spectrum_and_parameter_error():
+    import pebblesdr_b200 as pb
+    from oracle import port
+    N = 131072
+    g = pb.CFastFIR(N, N // 2 + 1)
+    assert g.SetupParameters(-20e6, 20e6, 0.0, 100e6) == 0
+    assert g.SetupParameters(-20e6, 20e6, 0.0, 100e6) == 1        # unchanged (fastfir.cpp:195-199)
+    H = g.GetFilter()
+    assert g.SetupParameters(10e6, 60e6, 0.0, 100e6) == 2          # "Filter Parameter error": old filter kept
+    assert np.array_equal(g.GetFilter(), H)
+    # H = FFT of the reference's taps: the oracle's impulse response through ProcessData is taps * N
+    o = port.CFastFIR(N, N // 2 + 1)
+    o.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    x = np.zeros(N, complex); x[0] = 1.0
+    out = np.zeros(2 * N, complex)
+    assert o.ProcessData(N, x, out) == N
+    h = np.fft.ifft(H) * N
+    assert rel_rms(h[:N // 2 + 1], out[:N // 2 + 1]) <= 1e-9
+    pb_mag = np.abs(H)
+    assert abs(pb_mag[0] - 1.0) < 1e-3 and pb_mag[N // 2] < 1e-6   # unity pass band (1/N folded, x N bins), dead stop band
+
+
+def test_long_filter_streams_batch_equals_single_streams_and_split():
+    """config 5 shape at reduced length: 6 independent streams sharing one filter, device-resident, two calls."""
+    import torch
+    import pebblesdr_b200 as pb
+    from pebblesdr_b200._lib import lib, check
+    N, L, S, n = 131072, 65536, 6, 65536 * 4
+    xs = np.stack([iq_noise_tones(n, 5000 + s, 100e6, [((s - 3) * 5e6, 0.4)], 0.1) for s in range(S)])
+    singles = []
+    for s in range(S):
+        f = pb.CFastFIR(N, L + 1)
+        f.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+        o = np.zeros(n + N, complex)
+        k = f.ProcessData(n, np.ascontiguousarray(xs[s]), o)
+        assert k == n
+        singles.append(o[:k].copy())
+    b = pb.CFastFIR(N, L + 1)
+    b.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    check(lib.pebble_fastfir_set_streams(b._h, S))
+    dx = torch.from_numpy(xs).cuda()
+    dy = torch.zeros((S, n), dtype=torch.complex128, device="cuda")
+    cut = L + 12345                                                # ragged split: second call starts mid-block
+    d1 = dx[:, :cut].contiguous()
+    d2 = dx[:, cut:].contiguous()
+    k1 = check(lib.pebble_fastfir_process_batch_device(b._h, cut, d1.data_ptr(), cut, dy.data_ptr(), n, None))
+    assert k1 == L
+    k2 = check(lib.pebble_fastfir_process_batch_device(b._h, n - cut, d2.data_ptr(), n - cut,
+                                                       dy.data_ptr() + 16 * k1, n, None))
+    assert k1 + k2 == n
+    torch.cuda.synchronize()
+    got = dy.cpu().numpy()
+    for s in range(S):
+        assert rel_rms(got[s], singles[s]) <= 1e-13, s              # same kernels, same block grid: ~bit-equal
+    # linearity at full length (size-independent property): F(a x1 + b x2) = a F(x1) + b F(x2)
+    mix = 0.5 * singles[0] - 2.0 * singles[1]
+    f = pb.CFastFIR(N, L + 1)
+    f.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    o = np.zeros(n + N, complex)
+    f.ProcessData(n, np.ascontiguousarray(0.5 * xs[0] - 2.0 * xs[1]), o)
+    assert rel_rms(o[:n], mix) <= 1e-12

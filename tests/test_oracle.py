@@ -97,6 +97,32 @@ def test_c_oracle_fastfir_vs_reference_live_split_points():
         assert rel_rms(o, outs[0]) <= TOL
 
 
+@pytest.mark.skipif(not ref.long_available(), reason="oracle/_ref/libpebbleref_long.so not built (needs /root/reference)")
+def test_c_oracle_long_fastfir_vs_reference_config5_sizes():
+    # BASELINE config 5: the reference CFastFIR compiled at CONV_FFT_SIZE/CONV_FIR_SIZE 131072/65537 (build_ref.sh
+    # step 4) pins the size-parameterised restatement: 100 MSPS, +-20 MHz, ragged calls, identical counts.
+    from golden.signals import iq
+    N, L = 131072, 65536
+    n = 3 * L + 4096
+    x = iq(n, 5000, 100e6, [(7e6, 0.4), (31e6, 0.5)], 0.1)
+    outs, counts = [], []
+    for f in (port.CFastFIR(N, L + 1), ref.CFastFIRLong()):
+        f.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+        got, cnt, pos = [], [], 0
+        for c in [L, 5000, 2 * L - 5000, 4096]:
+            o = np.zeros(c + N, complex)
+            k = f.ProcessData(c, x[pos:pos + c].copy(), o)
+            got.append(o[:k].copy()); cnt.append(k)
+            pos += c
+        outs.append(np.concatenate(got)); counts.append(cnt)
+    assert counts[0] == counts[1] == [L, 0, 2 * L, 0]
+    assert rel_rms(outs[0], outs[1]) <= TOL
+    # the 31 MHz tone is in the stop band, the 7 MHz tone passes
+    spec = np.abs(np.fft.fft(outs[1][L:2 * L] * np.hanning(L)))
+    k7, k31 = int(round(7e6 / 100e6 * L)), int(round(31e6 / 100e6 * L))
+    assert spec[k31 - 3:k31 + 4].max() < 1e-3 * spec[k7 - 3:k7 + 4].max()
+
+
 def test_known_answer_minus10dbfs_tone():
     # the reference's only worked numeric example (fft.cpp:302-319): a -10 dBFS tone peaks at -10 dB
     n = 8192
