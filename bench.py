@@ -49,9 +49,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log2n", type=int, default=None, help="input samples per step = 2^log2n (26 chain, 24 channelizer)")
-    ap.add_argument("--workload", default="chain", choices=["chain", "channelizer", "fastfir", "spectrum"],
+    ap.add_argument("--workload", default="chain", choices=["chain", "channelizer", "fastfir", "spectrum", "longfir"],
                     help="chain = BASELINE config 2 (default, the metric's configuration); channelizer = config 4; "
-                         "fastfir = config 1; spectrum = config 3")
+                         "fastfir = config 1; spectrum = config 3; longfir = config 5")
     ap.add_argument("--channels", type=int, default=1024, help="channelizer workload: total channels")
     ap.add_argument("--mode", default="am", choices=sorted(MODES))
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -384,6 +384,9 @@ if __name__ == "__main__":
     if a.workload == "channelizer":
         import bench_channelizer
         sys.exit(bench_channelizer.main(a, sys.modules[__name__]))
+    if a.workload == "longfir":
+        import bench_longfir
+        sys.exit(bench_longfir.main(a, sys.modules[__name__]))
     if a.workload in ("fastfir", "spectrum"):
         import bench_operators
         sys.exit(bench_operators.main(a, sys.modules[__name__]))

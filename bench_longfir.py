@@ -1,0 +1,180 @@
+"""bench_longfir.py — `python bench.py --workload longfir [--gpus N]`: BASELINE config 5, the long-filter stress:
+CFastFIR at CONV_FFT_SIZE/CONV_FIR_SIZE 131072/65537 ("65536-tap"), SetupParameters(-20e6, 20e6, 0, 100e6), 64 concurrent
+independent streams x 2^22 samples of 100 MSPS IQ. Streams shard across ranks (64 / world each, no
+data-path collective: SURVEY 8e), so `scaling` is "strong". Same JSON contract as the chain line.
+
+Algorithmic bytes: 32 B per input sample (16 read + 16 written). The four-step transform's scratch round trips are kept
+in L2 by chunking (fastfir_long.cu); whatever still reaches DRAM counts against `achieved`, not the algorithmic figure.
+FP64: 2 x 5 N log2 N = 170 N flop per L = N/2 outputs -> 340 flop per sample (radix-8/16 butterflies need fewer)."""
+import os
+import time
+
+LF_N, LF_FIR, LF_STREAMS = 131072, 65537, 64
+ALG_BYTES = 32.0
+FLOP_PER_SAMPLE = 340.0
+
+
+def _cpu_longfir(args):
+    """The reference CFastFIR compiled at 131072/65537 (oracle/_ref/libpebbleref_long.so), one stream per host thread."""
+    import threading
+    import numpy as np
+    from oracle import ref, port, cpu_chain
+    threads = cpu_chain.host_threads()
+    real = ref.long_available()
+    m = 1 << 20
+    rng = np.random.default_rng(5)
+    src = ((rng.standard_normal(m) + 1j * rng.standard_normal(m)) * 0.1).astype(np.complex128)
+    objs = []
+    for _ in range(threads):
+        o = ref.CFastFIRLong() if real else port.CFastFIR(LF_N, LF_FIR)
+        o.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+        objs.append(o)
+    passes = max(1, int(args.cpu_seconds * (12e6 if real else 2e6) / m))
+    busy = [0.0] * threads
+    gate = threading.Barrier(threads)
+
+    def work(i):
+        out = np.zeros(m + LF_N, dtype=np.complex128)
+        gate.wait()
+        t0 = time.perf_counter()
+        for _p in range(passes):
+            for q in range(0, m, 1 << 18):
+                objs[i].ProcessData(1 << 18, src[q:q + (1 << 18)], out)
+        busy[i] = time.perf_counter() - t0
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    return {"value": m * passes * threads / max(busy) / 1e6, "unit": "MS/s", "cores": threads,
+            "kind": "reference" if real else "port",
+            "sample": "%d independent long CFastFIR streams (one per host thread), %d passes over 2^20 samples in 2^18-sample "
+                      "calls; %s" % (threads, passes, "reference pebblelib CFastFIR compiled at 131072/65537 + FFTW 3.3.4 "
+                                     "(oracle/_ref/libpebbleref_long.so)" if real else "C restatement oracle/pebble_oracle.c")}
+
+
+def main(args, bench):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import pebblesdr_b200 as pb
+    from pebblesdr_b200 import lib
+    from pebblesdr_b200._lib import check
+    from pebblesdr_b200.dist import max_over_ranks, shard_range
+
+    n = 1 << (args.log2n if args.log2n_set else 22)          # samples per stream per step
+    first, end = shard_range(LF_STREAMS, world, rank)
+    S = end - first
+    K, W = args.steps, args.warmup
+    x = torch.empty(S, n, dtype=torch.complex128, device=dev)
+    for s in range(S):                                          # stream `first + s`: seed 5000 + stream
+        g = torch.Generator(device=dev)
+        g.manual_seed(5000 + first + s)
+        x[s] = torch.view_as_complex(torch.randn(n, 2, device=dev, dtype=torch.float64, generator=g) * 0.1)
+    out = torch.zeros(S, n, dtype=torch.complex128, device=dev)
+    op = pb.CFastFIR(LF_N, LF_FIR)
+    assert op.SetupParameters(-20e6, 20e6, 0.0, 100e6) == 0
+    check(lib.pebble_fastfir_set_streams(op._h, S))
+    stream_ptr = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        k = check(lib.pebble_fastfir_process_batch_device(op._h, n, x.data_ptr(), n, out.data_ptr(), n, stream_ptr))
+        assert k == n
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(W):
+        step()
+    barrier()
+    clocks = bench.ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.3)
+    l0 = lib.pebble_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1), dev)
+    launches = lib.pebble_launch_count() - l0
+    clk = clocks.stop() if rank == 0 else None
+    chk = float(torch.view_as_real(out[:, -4096:]).abs().sum().item())
+    assert chk > 0 and chk == chk
+
+    # ---- end to end: one stream's host buffer through pebble_fastfir_process (staging + H2D + kernels + D2H per call) ----
+    import numpy as np
+    m = min(n, 1 << 22)
+    hx = x[0, :m].cpu().numpy()
+    op2 = pb.CFastFIR(LF_N, LF_FIR)
+    op2.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    hout = np.zeros(m + LF_N, dtype=np.complex128)
+    op2.ProcessData(m, hx, hout)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        op2.ProcessData(m, hx, hout)
+    torch.cuda.synchronize()
+    ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3, dev)
+
+    if rank == 0:
+        peak, peak_src = bench.measured_peak()
+        total = LF_STREAMS * n                                   # whole job, all ranks
+        per_gpu_sps = S * n * K / (ms * 1e-3)
+        achieved = ALG_BYTES * per_gpu_sps / 1e9
+        line = {
+            "metric": "complex MS/s through the long-filter CFastFIR (131072-point overlap-save)",
+            "value": total * K / (ms * 1e-3) / 1e6, "unit": "MS/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "BASELINE config 5: long-filter stress, CFastFIR 131072-point overlap-save (65537 taps, +-20 MHz) "
+                                   "over 100 MSPS synthetic IQ, 64 concurrent streams",
+                       "streams": LF_STREAMS, "streams_per_gpu": S, "samples_per_stream_per_step": n,
+                       "l2": "inputs (%d MiB/step/GPU) larger than the 126 MB L2; no flush" % ((16 * n * S) >> 20),
+                       "parallelism": "streams sharded over %d GPU(s), no data-path collective" % world},
+            "e2e": {"value": world * m * K / (ms_e2e * 1e-3) / 1e6, "unit": "MS/s", "h2d_bytes_per_step": 16 * m,
+                    "d2h_bytes_per_step": 16 * m, "ms_per_step": ms_e2e / K,
+                    "call": "pebble_fastfir_process, one stream per GPU (pageable host buffers, staging + H2D + kernels + D2H "
+                            "per call; host wall clock)"},
+            "roofline": {"bound": "hbm", "kernel": "lf_cols_kernel<8,fwd> + lf_rows_kernel + lf_cols_kernel<8,inv> (one chunk = "
+                                                   "three launches, scratch L2-resident)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": bench_traffic(S * n), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": ALG_BYTES * S * n,
+                         "fp64": {"flop_per_sample": FLOP_PER_SAMPLE, "achieved_tflops": FLOP_PER_SAMPLE * per_gpu_sps / 1e12,
+                                  "note": "5 N log2 N convention; nominal B200 FP64 ~37 TFLOP/s: this operator is FP64/L2-bound "
+                                          "above its HBM floor"}},
+            "gpu_launches": int(launches), "clocks": clk,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = _cpu_longfir(args)
+        bench.emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def bench_traffic(samples):
+    import json
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            e = json.load(f).get("longfir_step", {})
+        if int(e.get("samples_per_launch", -1)) == samples:
+            return float(e["dram_bytes"])
+    except Exception:
+        pass
+    return None

@@ -193,7 +193,7 @@ def test_long_filter_spectrum_and_parameter_error():
     h = np.fft.ifft(H) * N
     assert rel_rms(h[:N // 2 + 1], out[:N // 2 + 1]) <= 1e-9
     pb_mag = np.abs(H)
-    assert abs(pb_mag[0] - 1.0) < 1e-3 and pb_mag[N // 2] < 1e-6   # unity pass band (1/N folded, x N bins), dead stop band
+    assert abs(pb_mag[0] * N - 1.0) < 1e-3 and pb_mag[N // 2] * N < 1e-6   # pass band 1/N (fastfir.cpp:243), dead stop band
 
 
 def test_long_filter_streams_batch_equals_single_streams_and_split():
