@@ -328,6 +328,7 @@ int pebble_decimator_chain(const pebble_decimator_t *h, int *taps, int *decimate
 
 int pebble_decimator_out_count(const pebble_decimator_t *h, int n) {
     if (!h || n < 0) return PEBBLE_ERR_ARG;
+    if (n == 0) return 0;
     if (n % h->total_dec) return PEBBLE_ERR_ARG;
     long long m = n;
     for (const Stage &st : h->chain) {

@@ -14,6 +14,7 @@
 // of a chunk run back to back on one stream, so the rows and the inverse columns find their input in L2.
 #include "fastfir_long.cuh"
 #include "fft_kernels.cuh"
+#include "ff_fused.cuh"
 #include <cstdlib>
 #include <vector>
 
@@ -117,6 +118,62 @@ lf_rows_kernel(cpx *__restrict__ scratch, const cpx *__restrict__ hpos, cpx *__r
     fft_inverse_smem<LF_N2>(a, tw2);
     for (int n2 = threadIdx.x; n2 < LF_N2; n2 += blockDim.x) row[n2] = cpx_mulc(a[fft_swz<SH>(n2)], twN[n2 * k1]);
 }
+
+// H of every row from the generic kernel's slot order to the fused schedule's [k][thread] order (ff_fused.cuh).
+__global__ void lf_permute_kernel(const cpx *__restrict__ hpos, cpx *__restrict__ ht) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // idx = k * 128 + t  <->  slot 16 t + k
+    const size_t r = (size_t)blockIdx.y * LF_N2;
+    ht[r + idx] = hpos[r + FftPlan<LF_N2>::freq2pos(ff2048_pos2freq(16 * (idx & 127) + (idx >> 7)))];
+}
+
+// The process-path row kernel on the register-fused 8 x 16 x 16 schedule of fastfir2048_kernel (8 shared-memory accesses
+// per point instead of 16): F0 reads the row from scratch (L2) and applies the inter-step twiddle W_N^(n2 k1) on the way
+// in, I0 applies its conjugate on the way out. n2 = i + 256 k: W_N^(n2 k1) = W_N^(i k1) * W_N^(256 k k1), one gather per
+// (thread, g) and eight CTA-uniform factors, both exact table entries.
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB)
+lf_rows_fused_kernel(cpx *__restrict__ scratch, const cpx *__restrict__ ht_all, const cpx *__restrict__ tw2,
+                     const cpx *__restrict__ twN, int N1, int nmask) {
+    __shared__ __align__(128) cpx a[LF_N2 + 64 + 8];
+    cpx *t1 = a + LF_N2, *pk = a + LF_N2 + 64;
+    const int t = threadIdx.x, k1 = blockIdx.x;
+    cpx *row = scratch + ((size_t)blockIdx.y * N1 + k1) * LF_N2;
+    const cpx *ht = ht_all + (size_t)k1 * LF_N2;
+    if (t < 64) t1[t] = tw2[8 * ((t & 15) << (t >> 4))];   // t = 16 b + i -> exp(-j 2 pi i 2^b / 256)
+    if (t >= 64 && t < 72) pk[t - 64] = twN[(256 * (t - 64) * k1) & nmask];
+    const cpx wa1 = tw2[t], wa2 = tw2[2 * t], wa4 = tw2[4 * t];
+    const cpx wb1 = tw2[t + 128], wb2 = tw2[2 * t + 256], wb4 = tw2[4 * t + 512];
+    const cpx ba = twN[t * k1], bb = twN[(t + 128) * k1];
+    __syncthreads();
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        const int i = t + 128 * g;
+        const cpx bg = g ? bb : ba;
+        cpx u[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) u[k] = __ldcg(row + i + 256 * k);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) u[k] = cpx_mul(u[k], k ? cpx_mul(bg, pk[k]) : bg);
+        dft8<false>(u);
+        ff_tw8<false>(u, g ? wb1 : wa1, g ? wb2 : wa2, g ? wb4 : wa4);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[ff_swz(i + 256 * k)] = u[k];
+    }
+    __syncthreads();
+    ff_mid_phases<128, false>(a, t1, ht, t, 0);
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        const int i = t + 128 * g;
+        const cpx bg = g ? bb : ba;
+        cpx u[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) u[k] = a[ff_swz(i + 256 * k)];
+        ff_tw8<true>(u, g ? wb1 : wa1, g ? wb2 : wa2, g ? wb4 : wa4);
+        dft8<true>(u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) __stcg(row + i + 256 * k, cpx_mulc(u[k], k ? cpx_mul(bg, pk[k]) : bg));
+    }
+}
 }  // namespace
 
 struct LongFir {
@@ -124,7 +181,15 @@ struct LongFir {
     const cpx *d_twN;
     cpx *d_tw2;        // exp(-2 pi j m / 2048)
     cpx *d_scratch;
+    cpx *d_ht;         // H in the fused row kernel's order (lf_permute_kernel)
+    bool fused;        // PEBBLE_LF_GENERIC=1 keeps the generic in-place row kernel (cross-check)
     int chunk;         // blocks per launch triple
+    // Consecutive chunks alternate between `lanes` internal streams (own scratch each), forked from and joined to the
+    // caller's stream by events: the column kernels are L2-bandwidth-bound and the row kernel FP64/shared-memory-bound,
+    // so chunk c's rows overlap chunk c+1's forward columns.
+    int lanes;
+    cudaStream_t lane[2];
+    cudaEvent_t fork, join[2];
 };
 
 bool lf_size_supported(int fft_size) { return fft_size == 32768 || fft_size == 131072; }
@@ -133,24 +198,40 @@ LongFir *lf_create(int fft_size, const cpx *d_twN) {
     if (!lf_size_supported(fft_size)) return nullptr;
     LongFir *p = new LongFir();
     p->N = fft_size; p->N1 = fft_size / LF_N2; p->R = p->N1 == 64 ? 8 : 4; p->d_twN = d_twN;
-    p->d_tw2 = nullptr; p->d_scratch = nullptr;
-    // default: 24 blocks x 2 MB = 48 MB of scratch in flight, inside the 126 MB L2 together with the chunk's input
+    p->d_tw2 = nullptr; p->d_scratch = nullptr; p->d_ht = nullptr; p->fused = !getenv("PEBBLE_LF_GENERIC");
+    // default (N = 131072): 37 blocks per chunk = 2368 row CTAs = 4 full waves of 148 SMs x 4 resident CTAs, and
+    // 4736 column CTAs = 2 full waves of 148 x 16; measured best of {9..37} x {1,2} lanes (profiles/r1_longfir_history.md)
     const char *e = getenv("PEBBLE_LF_CHUNK_MB");
-    const int mb = e && atoi(e) > 0 ? atoi(e) : 48;
+    const int mb = e && atoi(e) > 0 ? atoi(e) : 74;
     p->chunk = (int)(((size_t)mb << 20) / (sizeof(cpx) * (size_t)fft_size));
+    if ((e = getenv("PEBBLE_LF_CHUNK_BLOCKS")) && atoi(e) > 0) p->chunk = atoi(e);
     if (p->chunk < 1) p->chunk = 1;
+    e = getenv("PEBBLE_LF_LANES");
+    p->lanes = e && atoi(e) == 1 ? 1 : 2;
+    p->lane[0] = p->lane[1] = nullptr; p->fork = nullptr; p->join[0] = p->join[1] = nullptr;
     bool ok = pebble::cuda_ok(cudaMalloc(&p->d_tw2, sizeof(cpx) * LF_N2), "cudaMalloc") &&
-              pebble::cuda_ok(cudaMalloc(&p->d_scratch, sizeof(cpx) * (size_t)fft_size * p->chunk), "cudaMalloc") &&
+              pebble::cuda_ok(cudaMalloc(&p->d_ht, sizeof(cpx) * (size_t)fft_size), "cudaMalloc") &&
+              pebble::cuda_ok(cudaMemset(p->d_ht, 0, sizeof(cpx) * (size_t)fft_size), "cudaMemset") &&
+              pebble::cuda_ok(cudaMalloc(&p->d_scratch, sizeof(cpx) * (size_t)fft_size * p->chunk * p->lanes), "cudaMalloc") &&
+              pebble::cuda_ok(cudaEventCreateWithFlags(&p->fork, cudaEventDisableTiming), "cudaEventCreate") &&
               // W_2048^m = W_N^(N1 m): strided copy out of the caller's table
               pebble::cuda_ok(cudaMemcpy2D(p->d_tw2, sizeof(cpx), d_twN, sizeof(cpx) * p->N1, sizeof(cpx), LF_N2,
                                            cudaMemcpyDeviceToDevice), "cudaMemcpy2D(tw2)");
+    for (int l = 0; ok && l < p->lanes && p->lanes > 1; ++l)
+        ok = pebble::cuda_ok(cudaStreamCreateWithFlags(&p->lane[l], cudaStreamNonBlocking), "cudaStreamCreate") &&
+             pebble::cuda_ok(cudaEventCreateWithFlags(&p->join[l], cudaEventDisableTiming), "cudaEventCreate");
     if (!ok) { lf_destroy(p); return nullptr; }
     return p;
 }
 
 void lf_destroy(LongFir *p) {
     if (!p) return;
-    cudaFree(p->d_tw2); cudaFree(p->d_scratch);
+    cudaFree(p->d_tw2); cudaFree(p->d_scratch); cudaFree(p->d_ht);
+    for (int l = 0; l < 2; ++l) {
+        if (p->lane[l]) cudaStreamDestroy(p->lane[l]);
+        if (p->join[l]) cudaEventDestroy(p->join[l]);
+    }
+    if (p->fork) cudaEventDestroy(p->fork);
     delete p;
 }
 
@@ -163,20 +244,35 @@ template <int R>
 static cudaError_t lf_run(LongFir *p, const cpx *hpos, cpx *hout, const cpx *state, const cpx *in, cpx *out, LfGeom g,
                           long long jobs, double scale, cudaStream_t st) {
     const dim3 cgrid(LF_N2 / LF_TC, 1), cblock(LF_TC * R);
-    for (long long j0 = 0; j0 < jobs; j0 += p->chunk) {
+    const int lanes = (hout || jobs <= p->chunk) ? 1 : p->lanes;
+    if (lanes > 1) {
+        cudaEventRecord(p->fork, st);
+        for (int l = 0; l < lanes; ++l) cudaStreamWaitEvent(p->lane[l], p->fork, 0);
+    }
+    int c = 0;
+    for (long long j0 = 0; j0 < jobs; j0 += p->chunk, ++c) {
         const unsigned nj = (unsigned)(jobs - j0 < p->chunk ? jobs - j0 : p->chunk);
+        cudaStream_t cs = lanes > 1 ? p->lane[c % lanes] : st;
+        cpx *scr = p->d_scratch + (size_t)(c % lanes) * p->chunk * (size_t)p->N;
         g.job0 = j0;
-        lf_cols_kernel<R, false><<<dim3(cgrid.x, nj), cblock, 0, st>>>(state, in, nullptr, p->d_scratch, p->d_twN, g, 1.0);
+        lf_cols_kernel<R, false><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(state, in, nullptr, scr, p->d_twN, g, 1.0);
         if (hout) {
-            lf_rows_kernel<true><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, st>>>(p->d_scratch, nullptr, hout, p->d_tw2,
-                                                                                    p->d_twN, p->N1);
+            lf_rows_kernel<true><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, cs>>>(scr, nullptr, hout, p->d_tw2, p->d_twN, p->N1);
             pebble::count_launch(2);
             continue;
         }
-        lf_rows_kernel<false><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, st>>>(p->d_scratch, hpos, nullptr, p->d_tw2,
-                                                                                 p->d_twN, p->N1);
-        lf_cols_kernel<R, true><<<dim3(cgrid.x, nj), cblock, 0, st>>>(nullptr, nullptr, out, p->d_scratch, p->d_twN, g, scale);
+        if (p->fused)
+            lf_rows_fused_kernel<4><<<dim3(p->N1, nj), 128, 0, cs>>>(scr, p->d_ht, p->d_tw2, p->d_twN, p->N1, p->N - 1);
+        else
+            lf_rows_kernel<false><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, cs>>>(scr, hpos, nullptr, p->d_tw2, p->d_twN, p->N1);
+        lf_cols_kernel<R, true><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(nullptr, nullptr, out, scr, p->d_twN, g, scale);
         pebble::count_launch(3);
+    }
+    if (lanes > 1) {
+        for (int l = 0; l < lanes; ++l) {
+            cudaEventRecord(p->join[l], p->lane[l]);
+            cudaStreamWaitEvent(st, p->join[l], 0);
+        }
     }
     return cudaGetLastError();
 }
@@ -184,8 +280,12 @@ static cudaError_t lf_run(LongFir *p, const cpx *hpos, cpx *hout, const cpx *sta
 cudaError_t lf_build_filter(LongFir *p, const cpx *d_taps, cpx *d_hpos, cudaStream_t st) {
     // the taps as a one-block stream with no carried state: V = taps
     LfGeom g = {1, p->N / 2, 0, 0, 0, 0, 0};
-    return p->R == 8 ? lf_run<8>(p, nullptr, d_hpos, d_taps, d_taps, nullptr, g, 1, 1.0, st)
-                     : lf_run<4>(p, nullptr, d_hpos, d_taps, d_taps, nullptr, g, 1, 1.0, st);
+    cudaError_t e = p->R == 8 ? lf_run<8>(p, nullptr, d_hpos, d_taps, d_taps, nullptr, g, 1, 1.0, st)
+                              : lf_run<4>(p, nullptr, d_hpos, d_taps, d_taps, nullptr, g, 1, 1.0, st);
+    if (e != cudaSuccess) return e;
+    lf_permute_kernel<<<dim3(LF_N2 / 256, p->N1), 256, 0, st>>>(d_hpos, p->d_ht);
+    pebble::count_launch();
+    return cudaGetLastError();
 }
 
 cudaError_t lf_process(LongFir *p, const cpx *d_hpos, const cpx *state, int s0, int state_stride, const cpx *in,
