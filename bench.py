@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--log2n", type=int, default=None, help="input samples per step = 2^log2n (26 chain, 24 channelizer)")
+    ap.add_argument("--log2n", type=int, default=None, help="input samples per step = 2^log2n (27 chain = SURVEY 8(d) config 2 input, 24 channelizer/fastfir/spectrum, 22 per stream longfir)")
     ap.add_argument("--workload", default="chain", choices=["chain", "channelizer", "fastfir", "spectrum", "longfir"],
                     help="chain = BASELINE config 2 (default, the metric's configuration); channelizer = config 4; "
                          "fastfir = config 1; spectrum = config 3; longfir = config 5")
@@ -59,7 +59,7 @@ def parse():
     a = ap.parse_args()
     a.log2n_set = a.log2n is not None
     if a.log2n is None:
-        a.log2n = 26
+        a.log2n = 27   # "Input: 2^27 CPX" (2 GiB per step)
     return a
 
 

@@ -199,10 +199,12 @@ LongFir *lf_create(int fft_size, const cpx *d_twN) {
     LongFir *p = new LongFir();
     p->N = fft_size; p->N1 = fft_size / LF_N2; p->R = p->N1 == 64 ? 8 : 4; p->d_twN = d_twN;
     p->d_tw2 = nullptr; p->d_scratch = nullptr; p->d_ht = nullptr; p->fused = !getenv("PEBBLE_LF_GENERIC");
-    // default (N = 131072): 37 blocks per chunk = 2368 row CTAs = 4 full waves of 148 SMs x 4 resident CTAs, and
-    // 4736 column CTAs = 2 full waves of 148 x 16; measured best of {9..37} x {1,2} lanes (profiles/r1_longfir_history.md)
+    // default (N = 131072): 18 blocks per chunk = 36 MB of scratch per lane, 72 MB for both lanes: inside the 126 MB L2
+    // together with the streaming input/output. 1152 row CTAs = 1.95 waves of 148 SMs x 4. Larger chunks (37 blocks =
+    // exactly 4 row waves) measured 2 % faster but spill the scratch to DRAM (3.6x the algorithmic traffic instead of
+    // ~1.5x): profiles/r1_longfir_history.md.
     const char *e = getenv("PEBBLE_LF_CHUNK_MB");
-    const int mb = e && atoi(e) > 0 ? atoi(e) : 74;
+    const int mb = e && atoi(e) > 0 ? atoi(e) : 36;
     p->chunk = (int)(((size_t)mb << 20) / (sizeof(cpx) * (size_t)fft_size));
     if ((e = getenv("PEBBLE_LF_CHUNK_BLOCKS")) && atoi(e) > 0) p->chunk = atoi(e);
     if (p->chunk < 1) p->chunk = 1;
