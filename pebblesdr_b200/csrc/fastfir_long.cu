@@ -223,6 +223,31 @@ LongFir *lf_create(int fft_size, const cpx *d_twN) {
         ok = pebble::cuda_ok(cudaStreamCreateWithFlags(&p->lane[l], cudaStreamNonBlocking), "cudaStreamCreate") &&
              pebble::cuda_ok(cudaEventCreateWithFlags(&p->join[l], cudaEventDisableTiming), "cudaEventCreate");
     if (!ok) { lf_destroy(p); return nullptr; }
+    // Keep the scratch in L2: a persisting-access window over each lane's scratch on that lane's stream (the set-aside is
+    // a device-wide limit, sized to the scratch and capped by the device maximum). Everything else the kernels touch
+    // (input, output, H, twiddles) lies outside the windows and keeps the normal policy. PEBBLE_LF_NOPERSIST=1 disables.
+    if (p->lanes > 1 && !getenv("PEBBLE_LF_NOPERSIST")) {
+        int dev = 0, max_persist = 0, max_win = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+        cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+        const size_t lane_bytes = sizeof(cpx) * (size_t)fft_size * p->chunk;
+        size_t want = lane_bytes * p->lanes;
+        if (want > (size_t)max_persist) want = (size_t)max_persist;
+        if (want > 0 && max_win > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+            for (int l = 0; l < p->lanes; ++l) {
+                cudaStreamAttrValue v = {};
+                v.accessPolicyWindow.base_ptr = p->d_scratch + (size_t)l * p->chunk * (size_t)fft_size;
+                v.accessPolicyWindow.num_bytes = lane_bytes < (size_t)max_win ? lane_bytes : (size_t)max_win;
+                const double share = (double)(want / p->lanes) / (double)v.accessPolicyWindow.num_bytes;
+                v.accessPolicyWindow.hitRatio = share < 1.0 ? (float)share : 1.0f;
+                v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                cudaStreamSetAttribute(p->lane[l], cudaStreamAttributeAccessPolicyWindow, &v);
+            }
+        }
+        cudaGetLastError();   // the policy is an optimisation: a refusal is not an error
+    }
     return p;
 }
 

@@ -9,8 +9,8 @@
 // pass, slot p holds X[freq_of_pos(p)] (mixed-radix digit reversal). The inverse runs the mirrored
 // decimation-in-time passes in reverse order, so forward -> pointwise multiply -> inverse needs no
 // reordering at all (that is the CFastFIR hot loop, fastfir.cpp:305-307).
-// Bank conflicts: slot index i is stored at i ^ ((i >> SH) & 7), SH = log2(last radix); every pass
-// then touches 8 distinct 16-byte lanes per quarter warp.
+// Bank conflicts: slot index i is stored at fft_swz<SH>(i) (two XOR terms, see below); every pass and the natural-order
+// epilogues then touch 8 distinct 16-byte lanes per quarter warp.
 #pragma once
 #include "common.cuh"
 
@@ -91,7 +91,15 @@ template <bool INV> struct DftR<4, INV> {
 template <bool INV> struct DftR<8, INV> { static PB_HD void run(cpx (&v)[8]) { dft8<INV>(v); } };
 template <bool INV> struct DftR<16, INV> { static PB_HD void run(cpx (&v)[16]) { dft16<INV>(v); } };
 
-template <int SH> PB_HD int fft_swz(int i) { return i ^ ((i >> SH) & 7); }
+// SH encodes two shifts, SH = s1 + 100 * s2: slot i is stored at i ^ ((i >> s1) & 7) ^ ((i >> s2) & 7). s1 = log2(last radix)
+// makes the last pass (R contiguous slots per thread) conflict-free; s2 = log2(N / first radix) does the same for reads in
+// NATURAL bin order (consecutive bins sit N / R0 slots apart after digit reversal: the spectrum epilogue and the
+// natural-order copy-out were 8-way conflicted without it, ncu: 41 % of all shared wavefronts). Both terms are constant
+// inside every aligned group of 8 consecutive slots, so the passes that walk consecutive slots stay conflict-free.
+template <int SH> PB_HD int fft_swz(int i) {
+    constexpr int s1 = SH % 100, s2 = SH / 100;
+    return s2 ? (i ^ ((i >> s1) & 7) ^ ((i >> s2) & 7)) : (i ^ ((i >> s1) & 7));
+}
 
 // Twiddle powers w^1..w^(R-1) of one butterfly from FOUR table reads (w^1, w^2, w^4, w^8) and R-5 complex
 // multiplies (depth <= 3), instead of R-1 scattered 16-byte gathers: the gathers kept the L1/LSU data pipe (which the
@@ -150,7 +158,7 @@ PB_HD void fft_pass(cpx *a, const cpx *tw, int tid, int nthreads) {
 template <int N> struct FftPlan;
 
 template <> struct FftPlan<2048> {
-    static constexpr int NP = 3, SH = 3, THREADS = 128;
+    static constexpr int NP = 3, SH = 3 + 100 * 7, THREADS = 128;
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<2048, 16, 2048, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<2048, 16, 128, INV, SH>(a, tw, tid, nt);
@@ -161,7 +169,7 @@ template <> struct FftPlan<2048> {
 };
 
 template <> struct FftPlan<4096> {
-    static constexpr int NP = 3, SH = 4, THREADS = 256;
+    static constexpr int NP = 3, SH = 4 + 100 * 8, THREADS = 256;
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<4096, 16, 4096, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<4096, 16, 256, INV, SH>(a, tw, tid, nt);
@@ -172,7 +180,7 @@ template <> struct FftPlan<4096> {
 };
 
 template <> struct FftPlan<8192> {
-    static constexpr int NP = 4, SH = 4, THREADS = 512;
+    static constexpr int NP = 4, SH = 4 + 100 * 10, THREADS = 512;
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<8192, 8, 8192, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<8192, 8, 1024, INV, SH>(a, tw, tid, nt);

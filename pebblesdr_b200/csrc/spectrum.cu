@@ -32,17 +32,19 @@ __device__ __forceinline__ bool spec_load_frame(cpx *a, const cpx *__restrict__ 
 }
 
 // amplitude (already / coherentGain / maxBinPower) of unfolded bin j
-template <int N> __device__ __forceinline__ double spec_asd(const cpx *a, int j, double cg, double maxbin) {
+template <int N> __device__ __forceinline__ double spec_asd(const cpx *a, int j, double inv_cg, double inv_maxbin) {
     const int f = (j + N / 2) & (N - 1);  // m_unfoldInOrder, fft.cpp:183-225
     const cpx X = a[fft_swz<FftPlan<N>::SH>(FftPlan<N>::freq2pos(f))];
-    double asd = sqrt(X.x * X.x + X.y * X.y) / cg;  // DB::amplitude / coherentGain, fft.cpp:350
-    return asd / maxbin;                           // fft.cpp:358
+    // DB::amplitude / coherentGain (fft.cpp:350) / maxBinPower (fft.cpp:358). cg and maxbin arrive as RECIPROCALS: two
+    // FP64 divisions per bin were ~60 instructions of the ~300 per sample; the products differ from the quotients by
+    // <= 1 ulp each (1e-15 dB), far inside the 1e-6 dB tolerance; 1/maxbin is exact for power-of-two buffer sizes.
+    return sqrt(X.x * X.x + X.y * X.y) * inv_cg * inv_maxbin;
 }
 
 template <int N>
 __global__ void __launch_bounds__(FftPlan<N>::THREADS)
 spectrum_kernel(const cpx *__restrict__ in, int frames, int n, const double *__restrict__ win, int windowed,
-                double cg, double maxbin, double over_limit, const double *__restrict__ prev_in,
+                double cg, double maxbin /* both reciprocals, see spec_asd */, double over_limit, const double *__restrict__ prev_in,
                 double *__restrict__ prev_out, const int *__restrict__ flag_in, int *__restrict__ flag_out,
                 double *__restrict__ out_db, int *__restrict__ out_flags, int run, const cpx *__restrict__ tw) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -145,13 +147,15 @@ template <int N> static cudaError_t spec_launch(pebble_fft *h, int frames, int n
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spectrum_kernel<N>, FftPlan<N>::THREADS, smem);
     if (occ < 1) occ = 1;
     // runs of consecutive frames per CTA: >= 8 frames (pre-roll <= 12.5 %) once there is enough work
-    int target = pebble::num_sms() * occ * 2;
+    // ONE wave: with a single resident CTA per SM (128 KB of shared memory at N = 8192) a grid of 2 x SMs quantised to
+    // 256 CTAs = 1.73 waves (ncu), i.e. 13 % of the machine idle in the second wave.
+    int target = pebble::num_sms() * occ;
     int run = (frames + target - 1) / target;
     if (run < 8) run = 8;
     if (run > frames) run = frames;
     const int grid = (frames + run - 1) / run;
     const bool windowed = h->wtype != PEBBLE_WINDOW_NONE && n == h->spb;
-    spectrum_kernel<N><<<grid, FftPlan<N>::THREADS, smem, st>>>(in, frames, n, h->d_win, windowed ? 1 : 0, h->cg, h->maxbin, 0.9,
+    spectrum_kernel<N><<<grid, FftPlan<N>::THREADS, smem, st>>>(in, frames, n, h->d_win, windowed ? 1 : 0, 1.0 / h->cg, 1.0 / h->maxbin, 0.9,
                                                                h->d_prev[h->cur], h->d_prev[h->cur ^ 1], h->d_flag[h->cur],
                                                                h->d_flag[h->cur ^ 1], out, flags, run, h->d_tw);
     pebble::count_launch();
