@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log2n", type=int, default=None, help="input samples per step = 2^log2n (27 chain = SURVEY 8(d) config 2 input, 24 channelizer/fastfir/spectrum, 22 per stream longfir)")
-    ap.add_argument("--workload", default="chain", choices=["chain", "channelizer", "fastfir", "spectrum", "longfir"],
+    ap.add_argument("--workload", default="chain", choices=["chain", "channelizer", "fastfir", "spectrum", "longfir", "decimator"],
                     help="chain = BASELINE config 2 (default, the metric's configuration); channelizer = config 4; "
                          "fastfir = config 1; spectrum = config 3; longfir = config 5")
     ap.add_argument("--channels", type=int, default=1024, help="channelizer workload: total channels")
@@ -387,7 +387,7 @@ if __name__ == "__main__":
     if a.workload == "longfir":
         import bench_longfir
         sys.exit(bench_longfir.main(a, sys.modules[__name__]))
-    if a.workload in ("fastfir", "spectrum"):
+    if a.workload in ("fastfir", "spectrum", "decimator"):
         import bench_operators
         sys.exit(bench_operators.main(a, sys.modules[__name__]))
     sys.exit(main_ours(a))

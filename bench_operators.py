@@ -101,6 +101,47 @@ def _cpu_spectrum(args, size):
                       "oracle/pebble_oracle.c (window + FFT + dB + averaging)" % (threads, passes, frames, size)}
 
 
+def _cpu_decimator(args):
+    """Unmodified reference Decimator (pebblelib/decimator.cpp against the scalar vDSP stub, oracle/_ref), one object per
+    host thread, 32768-sample calls, bounded sample. Falls back to the C restatement (bit-equal) where _ref is absent."""
+    import threading
+    import numpy as np
+    from oracle import ref, port, cpu_chain
+    impl = ref if ref.available() else port
+    threads = cpu_chain.host_threads()
+    m, call = 1 << 20, 32768
+    rng = np.random.default_rng(6)
+    src = ((rng.standard_normal(m) + 1j * rng.standard_normal(m)) * 0.1).astype(np.complex128)
+    objs = []
+    for _ in range(threads):
+        o = impl.Decimator(10e6, call)
+        o.buildDecimationChain(10e6, 30000)
+        objs.append(o)
+    passes = max(1, int(args.cpu_seconds * 12e6 / m))      # ~12 MS/s per core for the portable path
+    busy = [0.0] * threads
+    gate = threading.Barrier(threads)
+
+    def work(i):
+        out = np.zeros(call, dtype=np.complex128)
+        gate.wait()
+        t0 = time.perf_counter()
+        for _p in range(passes):
+            for q in range(0, m, call):
+                objs[i].process(src[q:q + call].copy(), out, call)
+        busy[i] = time.perf_counter() - t0
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    return {"value": m * passes * threads / max(busy) / 1e6, "unit": "MS/s", "cores": threads,
+            "kind": "reference" if impl is ref else "port",
+            "sample": "%d independent Decimator objects (one per host thread), %d passes over 2^20 samples in 32768-sample calls, "
+                      "%s" % (threads, passes, "unmodified pebblelib Decimator, portable (non-vDSP) arithmetic (oracle/_ref)"
+                              if impl is ref else "C restatement oracle/pebble_oracle.c")}
+
+
 def main(args, bench):
     import torch
     import torch.distributed as dist
@@ -118,14 +159,22 @@ def main(args, bench):
     from pebblesdr_b200.dist import max_over_ranks
 
     fast = args.workload == "fastfir"
-    log2n = args.log2n if args.log2n_set else 24
+    deci = args.workload == "decimator"
+    log2n = args.log2n if args.log2n_set else (26 if deci else 24)
     n = 1 << log2n
     K, W = args.steps, args.warmup
     g = torch.Generator(device=dev)
     g.manual_seed(777 + rank)
     x = torch.view_as_complex(torch.randn(n, 2, device=dev, dtype=torch.float64, generator=g) * 0.1).contiguous()
     size = 8192
-    if fast:
+    if deci:
+        op = pb.Decimator(10e6, 32768)
+        assert op.buildDecimationChain(10e6, 30000) == 39062.5     # CIC3, hb11 x16 (4 merged steps), hb15, hb27, hb59: /256
+        dtot = op.totalDecimation()
+        out = torch.zeros(n // dtot, dtype=torch.complex128, device=dev)
+        step = lambda: op.process(x, out, n)
+        alg = 16.0 + 16.0 / dtot
+    elif fast:
         op = pb.CFastFIR()
         assert op.SetupParameters(-3000.0, 3000.0, 0.0, 2e6) == 0
         out = torch.zeros(n, dtype=torch.complex128, device=dev)
@@ -163,13 +212,20 @@ def main(args, bench):
     ms = max_over_ranks(e0.elapsed_time(e1), dev)
     launches = lib.pebble_launch_count() - l0
     clk = clocks.stop() if rank == 0 else None
-    chk = float(out.abs().sum().item()) if not fast else float(torch.view_as_real(out).abs().sum().item())
+    chk = float(out.abs().sum().item()) if not (fast or deci) else float(torch.view_as_real(out).abs().sum().item())
     assert chk > 0 and chk == chk
 
     # ---- end to end: host buffers through the host-pointer C-ABI call (H2D + kernel + D2H inside the call) ----
     m = min(n, 1 << 22)                                         # the host-pointer call stages through one pinned buffer
     hx = x[:m].cpu().numpy()
-    if fast:
+    if deci:
+        import numpy as np
+        op2 = pb.Decimator(10e6, 32768)
+        op2.buildDecimationChain(10e6, 30000)
+        hout = np.zeros(m // dtot, dtype=np.complex128)
+        host_step = lambda: op2.process(hx, hout, m)
+        d2h = 16 * (m // dtot)
+    elif fast:
         import numpy as np
         op2 = pb.CFastFIR()
         op2.SetupParameters(-3000.0, 3000.0, 0.0, 2e6)
@@ -199,11 +255,13 @@ def main(args, bench):
         peak, peak_src = bench.measured_peak()
         achieved = alg * n * K / (ms * 1e-3) / 1e9
         line = {
-            "metric": "complex MS/s through " + ("CFastFIR overlap-save band-pass" if fast else "the SignalSpectrum FFT path"),
+            "metric": "complex MS/s through " + ("the Decimator chain" if deci else "CFastFIR overlap-save band-pass" if fast else "the SignalSpectrum FFT path"),
             "value": world * n * K / (ms * 1e-3) / 1e6, "unit": "MS/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": ("BASELINE config 1: CFastFIR overlap-save band-pass (2048-point FFT, 1025 taps, +-3 kHz), "
+            "config": {"workload": ("SURVEY a18 (alternative front end of config 2): Decimator::process, 10 MSPS, protect 30 kHz: "
+                                    "CIC3, hb11 (4 merged steps, keep every 16th), hb15, hb27, hb59 => /256, 39062.5 S/s" if deci else
+                                    "BASELINE config 1: CFastFIR overlap-save band-pass (2048-point FFT, 1025 taps, +-3 kHz), "
                                     "1 channel, 2 MSPS synthetic complex IQ" if fast else
                                     "BASELINE config 3: SignalSpectrum path, 8192-point Blackman-Harris windowed FFT + dB + "
                                     "2-tap averaging, one frame per 8192 samples of 20 MSPS synthetic IQ"),
@@ -211,12 +269,12 @@ def main(args, bench):
                        "parallelism": "%d GPU(s), independent replicas" % world},
             "e2e": {"value": world * m * K / (ms_e2e * 1e-3) / 1e6, "unit": "MS/s", "h2d_bytes_per_step": 16 * m,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K,
-                    "call": ("pebble_fastfir_process" if fast else "pebble_fft_spectrum x 64 frames") +
+                    "call": ("pebble_decimator_process" if deci else "pebble_fastfir_process" if fast else "pebble_fft_spectrum x 64 frames") +
                             " (pageable host buffers, staging + H2D + kernel + D2H per call; host wall clock)"},
-            "roofline": {"bound": "hbm", "kernel": "fastfir4096x3_kernel (+ fastfir2048_kernel for the left-over blocks)" if fast
+            "roofline": {"bound": "hbm", "kernel": "dec_chain_kernel" if deci else "fastfir4096x3_kernel (+ fastfir2048_kernel for the left-over blocks)" if fast
                          else "spectrum_kernel", "achieved": achieved / world, "peak": peak, "unit": "GB/s",
                          "frac": achieved / world / peak,
-                         "traffic": _ncu_traffic("fastfir4096x3_kernel" if fast else "spectrum_kernel", n), "peak_source": peak_src,
+                         "traffic": _ncu_traffic("dec_chain_kernel" if deci else "fastfir4096x3_kernel" if fast else "spectrum_kernel", n), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg * n},
             "gpu_launches": int(launches), "clocks": clk,
         }
@@ -227,7 +285,7 @@ def main(args, bench):
                                         "frac_of_issue_floor": floor_ms / (ms / K),
                                         "note": "FP64 issue and shared-memory wavefronts bound this operator above the HBM floor"}
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = _cpu_fastfir(args) if fast else _cpu_spectrum(args, size)
+            line["cpu_baseline"] = _cpu_decimator(args) if deci else _cpu_fastfir(args) if fast else _cpu_spectrum(args, size)
         bench.emit(line)
     if world > 1:
         dist.destroy_process_group()

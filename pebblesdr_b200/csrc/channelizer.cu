@@ -13,6 +13,7 @@
 #include "lib_common.h"
 #include "demod_kernels.cuh"
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -121,6 +122,13 @@ struct pebble_channelizer {
     double am_bandwidth = 16000.0;     // Demod_AM ctor default (demod_am.cpp:9)
     cpx *d_dec = nullptr, *d_bp = nullptr, *d_tmp = nullptr;
     size_t row_cap = 0;                // samples per channel the work buffers hold
+    // The per-channel demodulators are serial recurrences (PLL feedback): one thread per channel walks its row, and that
+    // walk takes the same ~1 us per decimated sample whether 1024 or 128 channels are resident. A call is therefore cut
+    // into `parts` runs of whole receiver frames; the demodulator + CFir of part k run on `tail` while the caller's stream
+    // already down-converts and filters part k+1 (all operators carry their state, so split == unsplit).
+    cudaStream_t tail = nullptr;
+    cudaEvent_t ev_front = nullptr, ev_tail = nullptr;
+    int parts = 1;
 };
 
 static int chz_upload_taps(pebble_channelizer *h) {
@@ -156,6 +164,13 @@ pebble_channelizer_t *pebble_channelizer_create(int nchannels, double in_rate, d
     h->dc = pebble_downconvert_create();
     h->bp = pebble_fastfir_create();
     if (!h->dc || !h->bp) { pebble_channelizer_destroy(h); return nullptr; }
+    if (const char *e = getenv("PEBBLE_CHZ_PARTS")) h->parts = atoi(e) > 0 ? atoi(e) : 1;
+    if (!pebble::cuda_ok(cudaStreamCreateWithFlags(&h->tail, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming), "cudaEventCreate") ||
+        !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_tail, cudaEventDisableTiming), "cudaEventCreate")) {
+        pebble_channelizer_destroy(h);
+        return nullptr;
+    }
     h->out_rate = pebble_downconvert_set_data_rate(h->dc, in_rate, max_bw);
     h->S = pebble_downconvert_num_stages(h->dc);
     bool ok = pebble_downconvert_set_channels(h->dc, nchannels) == 0 && pebble_fastfir_set_streams(h->bp, nchannels) == 0;
@@ -184,6 +199,9 @@ void pebble_channelizer_destroy(pebble_channelizer_t *h) {
     if (h->bp) pebble_fastfir_destroy(h->bp);
     cudaFree(h->d_modes); cudaFree(h->d_state); cudaFree(h->d_taps); cudaFree(h->d_hist[0]); cudaFree(h->d_hist[1]);
     cudaFree(h->d_dec); cudaFree(h->d_bp); cudaFree(h->d_tmp);
+    if (h->tail) cudaStreamDestroy(h->tail);
+    if (h->ev_front) cudaEventDestroy(h->ev_front);
+    if (h->ev_tail) cudaEventDestroy(h->ev_tail);
     delete h;
 }
 double pebble_channelizer_out_rate(const pebble_channelizer_t *h) { return h ? h->out_rate : 0.0; }
@@ -246,23 +264,42 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
         h->modes_dirty = false;
     }
     const long long row = (long long)h->row_cap;
-    r = pebble_downconvert_process_channels_device(h->dc, n, d_in, (double *)h->d_dec, row, st);     // receiver.cpp:908
-    if (r < 0) return r;
     const double gain = pow(10, (h->S * 2) / 20.0);                                                  // receiver.cpp:935-938
     const double agc_gain = pow(10, (h->agc_threshold / 5) / 20.0);                                  // agc.cpp:86-94 (integer division)
     pebble_fastfir_set_fused_scale(h->bp, gain, agc_gain);
-    r = pebble_fastfir_process_batch_device(h->bp, nd, (const double *)h->d_dec, row, (double *)h->d_bp, row, st);   // :950
-    if (r < 0) return r;
-    if (r != nd) { pebble::set_error("channelizer: FastFIR returned %d of %d", r, nd); return PEBBLE_ERR_STATE; }
-    chan_demod_kernel<<<(h->nch + 31) / 32, 32, 0, st>>>(h->d_bp, h->d_tmp, nd, row, h->nch, h->d_modes, h->pll,
-                                                        (double)0.9999f, h->d_state);                                 // :987
-    int gx = (nd + 255) / 256;
-    if (gx > 64) gx = 64;
-    chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, st>>>(h->d_hist[h->hcur], h->d_tmp, row, nd, h->d_taps, h->ntaps_am, h->ntaps_fm,
-                                                      h->d_modes, (cpx *)d_out, out_stride, h->d_hist[h->hcur ^ 1]);
-    pebble::count_launch(2);
-    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
-    h->hcur ^= 1;
+    const int frames = nd / h->fpb;
+    const int parts = h->parts < frames ? h->parts : frames;
+    // `tail` starts after everything already queued on the caller's stream (mode upload, the consumer of the last output)
+    PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
+    int f0 = 0;
+    for (int k = 0; k < parts; ++k) {
+        const int f1 = (int)((long long)frames * (k + 1) / parts);
+        const int pd = (f1 - f0) * h->fpb;             // decimated samples of this part
+        const long long pos = (long long)f0 * h->fpb;  // its column in the work rows and in the output rows
+        const long long pn = (long long)pd << h->S;
+        r = pebble_downconvert_process_channels_device(h->dc, (int)pn, d_in + 2 * (pos << h->S), (double *)(h->d_dec + pos), row, st);   // receiver.cpp:908
+        if (r < 0) return r;
+        r = pebble_fastfir_process_batch_device(h->bp, pd, (const double *)(h->d_dec + pos), row, (double *)(h->d_bp + pos), row, st);   // :950
+        if (r < 0) return r;
+        if (r != pd) { pebble::set_error("channelizer: FastFIR returned %d of %d", r, pd); return PEBBLE_ERR_STATE; }
+        PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
+        chan_demod_kernel<<<(h->nch + 31) / 32, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->pll,
+                                                                 (double)0.9999f, h->d_state);                                 // :987
+        int gx = (pd + 255) / 256;
+        if (gx > 64) gx = 64;
+        chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, h->tail>>>(h->d_hist[h->hcur], h->d_tmp + pos, row, pd, h->d_taps, h->ntaps_am,
+                                                               h->ntaps_fm, h->d_modes, (cpx *)d_out + pos, out_stride,
+                                                               h->d_hist[h->hcur ^ 1]);
+        pebble::count_launch(2);
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+        h->hcur ^= 1;
+        f0 = f1;
+    }
+    // the call is complete on the caller's stream when the last tail is
+    PB_CUDA(cudaEventRecord(h->ev_tail, h->tail), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamWaitEvent(st, h->ev_tail, 0), PEBBLE_ERR_CUDA);
     return nd;
 }
 

@@ -43,8 +43,8 @@ struct LfGeom {
 // Column transforms of LF_TC adjacent columns of one block. Thread (c, i): column c, butterfly i of each radix-R pass.
 // Forward: pass 0 on rows i + R k (twiddle W_N1^(i q) after the DFT), pass 1 on rows R i + k; slot R i + q = bin i + R q.
 // Inverse: the mirror image (pass 1, conj twiddle, pass 0).
-template <int R, bool INV>
-__global__ void __launch_bounds__(LF_TC *R)
+template <int R, bool INV, int MINB>
+__global__ void __launch_bounds__(LF_TC *R, MINB)
 lf_cols_kernel(const cpx *__restrict__ state, const cpx *__restrict__ in, cpx *__restrict__ out, cpx *__restrict__ scratch,
                const cpx *__restrict__ twN, LfGeom g, double scale) {
     constexpr int N1 = R * R;
@@ -188,6 +188,7 @@ struct LongFir {
     // caller's stream by events: the column kernels are L2-bandwidth-bound and the row kernel FP64/shared-memory-bound,
     // so chunk c's rows overlap chunk c+1's forward columns.
     int lanes;
+    bool cols12;       // column kernels compiled for 12 CTAs per SM (40 registers) instead of 9 (54)
     cudaStream_t lane[2];
     cudaEvent_t fork, join[2];
 };
@@ -208,6 +209,8 @@ LongFir *lf_create(int fft_size, const cpx *d_twN) {
     p->chunk = (int)(((size_t)mb << 20) / (sizeof(cpx) * (size_t)fft_size));
     if ((e = getenv("PEBBLE_LF_CHUNK_BLOCKS")) && atoi(e) > 0) p->chunk = atoi(e);
     if (p->chunk < 1) p->chunk = 1;
+    e = getenv("PEBBLE_LF_COLS_MINB");
+    p->cols12 = e && atoi(e) == 12;
     e = getenv("PEBBLE_LF_LANES");
     p->lanes = e && atoi(e) == 1 ? 1 : 2;
     p->lane[0] = p->lane[1] = nullptr; p->fork = nullptr; p->join[0] = p->join[1] = nullptr;
@@ -282,7 +285,8 @@ static cudaError_t lf_run(LongFir *p, const cpx *hpos, cpx *hout, const cpx *sta
         cudaStream_t cs = lanes > 1 ? p->lane[c % lanes] : st;
         cpx *scr = p->d_scratch + (size_t)(c % lanes) * p->chunk * (size_t)p->N;
         g.job0 = j0;
-        lf_cols_kernel<R, false><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(state, in, nullptr, scr, p->d_twN, g, 1.0);
+        if (p->cols12) lf_cols_kernel<R, false, 12><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(state, in, nullptr, scr, p->d_twN, g, 1.0);
+        else lf_cols_kernel<R, false, 1><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(state, in, nullptr, scr, p->d_twN, g, 1.0);
         if (hout) {
             lf_rows_kernel<true><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, cs>>>(scr, nullptr, hout, p->d_tw2, p->d_twN, p->N1);
             pebble::count_launch(2);
@@ -292,7 +296,8 @@ static cudaError_t lf_run(LongFir *p, const cpx *hpos, cpx *hout, const cpx *sta
             lf_rows_fused_kernel<4><<<dim3(p->N1, nj), 128, 0, cs>>>(scr, p->d_ht, p->d_tw2, p->d_twN, p->N1, p->N - 1);
         else
             lf_rows_kernel<false><<<dim3(p->N1, nj), FftPlan<LF_N2>::THREADS, 0, cs>>>(scr, hpos, nullptr, p->d_tw2, p->d_twN, p->N1);
-        lf_cols_kernel<R, true><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(nullptr, nullptr, out, scr, p->d_twN, g, scale);
+        if (p->cols12) lf_cols_kernel<R, true, 12><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(nullptr, nullptr, out, scr, p->d_twN, g, scale);
+        else lf_cols_kernel<R, true, 1><<<dim3(cgrid.x, nj), cblock, 0, cs>>>(nullptr, nullptr, out, scr, p->d_twN, g, scale);
         pebble::count_launch(3);
     }
     if (lanes > 1) {
