@@ -128,7 +128,7 @@ struct pebble_channelizer {
     // already down-converts and filters part k+1 (all operators carry their state, so split == unsplit).
     cudaStream_t tail = nullptr;
     cudaEvent_t ev_front = nullptr, ev_tail = nullptr;
-    int parts = 1;
+    int parts = 4;
 };
 
 static int chz_upload_taps(pebble_channelizer *h) {
@@ -165,7 +165,10 @@ pebble_channelizer_t *pebble_channelizer_create(int nchannels, double in_rate, d
     h->bp = pebble_fastfir_create();
     if (!h->dc || !h->bp) { pebble_channelizer_destroy(h); return nullptr; }
     if (const char *e = getenv("PEBBLE_CHZ_PARTS")) h->parts = atoi(e) > 0 ? atoi(e) : 1;
-    if (!pebble::cuda_ok(cudaStreamCreateWithFlags(&h->tail, cudaStreamNonBlocking), "cudaStreamCreate") ||
+    // highest priority: the tail's few serial warps should get SM slots ahead of the next part's many front CTAs
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (!pebble::cuda_ok(cudaStreamCreateWithPriority(&h->tail, cudaStreamNonBlocking, prio_hi), "cudaStreamCreate") ||
         !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming), "cudaEventCreate") ||
         !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_tail, cudaEventDisableTiming), "cudaEventCreate")) {
         pebble_channelizer_destroy(h);
