@@ -27,10 +27,14 @@ struct ChanState {      // per-channel demod state
 
 // one thread per channel: in/out rows of `stride` cpx
 static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__restrict__ out, int n, long long stride, int nch,
-                                         const int *__restrict__ modes, PllConst pc, double am_alpha,
-                                         ChanState *__restrict__ st) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= nch) return;
+                                         const int *__restrict__ modes, const int *__restrict__ order, int slots,
+                                         PllConst pc, double am_alpha, ChanState *__restrict__ st) {
+    // order[]: channels grouped by demodulator and padded to whole warps (-1), so a warp runs ONE of the recurrences
+    // below; with channels in natural order (NBFM and AM alternating in config 4) every warp ran both, one after the other.
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= slots) return;
+    const int c = order[slot];
+    if (c < 0 || c >= nch) return;
     const cpx *x = in + (long long)c * stride;
     cpx *y = out + (long long)c * stride;
     const int mode = modes[c];
@@ -109,7 +113,8 @@ struct pebble_channelizer {
     pebble_downconvert_t *dc = nullptr;
     pebble_fastfir_t *bp = nullptr;
     std::vector<int> modes;
-    int *d_modes = nullptr;
+    int *d_modes = nullptr, *d_order = nullptr;
+    int slots = 0;                     // entries of d_order (multiple of 32)
     bool modes_dirty = true;
     PllConst pll;
     ChanState *d_state = nullptr;
@@ -179,6 +184,7 @@ pebble_channelizer_t *pebble_channelizer_create(int nchannels, double in_rate, d
     bool ok = pebble_downconvert_set_channels(h->dc, nchannels) == 0 && pebble_fastfir_set_streams(h->bp, nchannels) == 0;
     const size_t hb = sizeof(cpx) * PB_FIR_MAX * (size_t)nchannels;
     ok = ok && pebble::cuda_ok(cudaMalloc(&h->d_modes, sizeof(int) * nchannels), "cudaMalloc") &&
+         pebble::cuda_ok(cudaMalloc(&h->d_order, sizeof(int) * ((size_t)nchannels + 3 * 32)), "cudaMalloc") &&
          pebble::cuda_ok(cudaMalloc(&h->d_state, sizeof(ChanState) * nchannels), "cudaMalloc") &&
          pebble::cuda_ok(cudaMemset(h->d_state, 0, sizeof(ChanState) * nchannels), "cudaMemset") &&
          pebble::cuda_ok(cudaMalloc(&h->d_taps, sizeof(h->taps)), "cudaMalloc") &&
@@ -200,7 +206,7 @@ void pebble_channelizer_destroy(pebble_channelizer_t *h) {
     if (!h) return;
     if (h->dc) pebble_downconvert_destroy(h->dc);
     if (h->bp) pebble_fastfir_destroy(h->bp);
-    cudaFree(h->d_modes); cudaFree(h->d_state); cudaFree(h->d_taps); cudaFree(h->d_hist[0]); cudaFree(h->d_hist[1]);
+    cudaFree(h->d_modes); cudaFree(h->d_order); cudaFree(h->d_state); cudaFree(h->d_taps); cudaFree(h->d_hist[0]); cudaFree(h->d_hist[1]);
     cudaFree(h->d_dec); cudaFree(h->d_bp); cudaFree(h->d_tmp);
     if (h->tail) cudaStreamDestroy(h->tail);
     if (h->ev_front) cudaEventDestroy(h->ev_front);
@@ -264,6 +270,17 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
     if (r < 0) return r;
     if (h->modes_dirty) {
         PB_CUDA(cudaMemcpyAsync(h->d_modes, h->modes.data(), sizeof(int) * h->nch, cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
+        // thread slots of chan_demod_kernel: NBFM channels, then AM, then pass-through, each group padded to a whole warp
+        std::vector<int> order;
+        for (int grp = 0; grp < 3; ++grp) {
+            for (int c = 0; c < h->nch; ++c) {
+                const int g = h->modes[c] == CH_FMN ? 0 : h->modes[c] == CH_AM ? 1 : 2;
+                if (g == grp) order.push_back(c);
+            }
+            while (order.size() % 32) order.push_back(-1);
+        }
+        h->slots = (int)order.size();
+        PB_CUDA(cudaMemcpy(h->d_order, order.data(), sizeof(int) * order.size(), cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
         h->modes_dirty = false;
     }
     const long long row = (long long)h->row_cap;
@@ -288,8 +305,8 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
         if (r != pd) { pebble::set_error("channelizer: FastFIR returned %d of %d", r, pd); return PEBBLE_ERR_STATE; }
         PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
         PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
-        chan_demod_kernel<<<(h->nch + 31) / 32, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->pll,
-                                                                 (double)0.9999f, h->d_state);                                 // :987
+        chan_demod_kernel<<<h->slots / 32, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->d_order,
+                                                            h->slots, h->pll, (double)0.9999f, h->d_state);                                 // :987
         int gx = (pd + 255) / 256;
         if (gx > 64) gx = 64;
         chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, h->tail>>>(h->d_hist[h->hcur], h->d_tmp + pos, row, pd, h->d_taps, h->ntaps_am,

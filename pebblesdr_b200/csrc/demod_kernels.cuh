@@ -275,8 +275,10 @@ struct PllState { float phase, freq, dc; };
 // The PLL recurrence over one stream (demod_nfm.cpp:225-257); state and constants are `float` like the reference's.
 __device__ __forceinline__ void pll_step(const cpx xi, cpx &yo, const PllConst &c, PllState &v) {
     // sin/cos of a float resolve to the float overloads in the reference build
-    const double ncoSin = (double)sinf(v.phase);
-    const double ncoCos = (double)cosf(v.phase);
+    float sn, cs;
+    sincosf(v.phase, &sn, &cs);   // one argument reduction for both (same values as sinf / cosf)
+    const double ncoSin = (double)sn;
+    const double ncoCos = (double)cs;
     const double tr = ncoCos * xi.x - ncoSin * xi.y;
     const double ti = ncoCos * xi.y + ncoSin * xi.x;
     const double phzerror = -atan2(ti, tr);
