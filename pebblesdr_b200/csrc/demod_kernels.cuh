@@ -197,7 +197,7 @@ static __global__ void __launch_bounds__(PB_SCAN_THREADS) am_carry_kernel(const 
 }
 // carry == nullptr: the CTA folds the maps of all earlier tiles itself (at most PB_AM_DIRECT of them), which
 // removes the carry launch from the short streams the receiver tail sees (2^19 samples = 256 tiles).
-#define PB_AM_DIRECT 512
+#define PB_AM_DIRECT 2048   // 2^21 decimated samples = one 2^28-sample call of the 10 MSPS chain; <= 16 maps folded per thread
 // NT threads x PB_SCAN_PER samples per tile: 256 x 8 = PB_SCAN_TILE for the stand-alone demodulator, 128 x 8 = one
 // FastFIR block when the tile maps come from the FastFIR kernel's epilogue (receiver chain, AGC off).
 template <int NT>
