@@ -235,3 +235,35 @@ def test_long_filter_streams_batch_equals_single_streams_and_split():
     o = np.zeros(n + N, complex)
     f.ProcessData(n, np.ascontiguousarray(0.5 * xs[0] - 2.0 * xs[1]), o)
     assert rel_rms(o[:n], mix) <= 1e-12
+
+
+def test_long_filter_small_calls_and_state_round_trip():
+    """n = 0, calls shorter than a block, and a stream continued by a fresh object restarted from the saved state."""
+    import pebblesdr_b200 as pb
+    N, L = 32768, 16384
+    x = iq_noise_tones(3 * L + 700, 5100, 100e6, [(3e6, 0.4)], 0.1)
+    a = pb.CFastFIR(N, L + 1)
+    a.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    whole = np.zeros(4 * L, complex)
+    kw = a.ProcessData(len(x), x, whole)
+    assert kw == 3 * L
+    b = pb.CFastFIR(N, L + 1)
+    b.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    out = np.zeros(2 * L, complex)
+    assert b.ProcessData(0, x[:0], out) == 0                               # fastfir.cpp:287-288
+    assert b.ProcessData(100, np.ascontiguousarray(x[:100]), out) == 0     # fill only
+    assert b.OutCount(L - 100) == L and b.OutCount(L - 101) == 0
+    got = []
+    k = b.ProcessData(L + 5, np.ascontiguousarray(x[100:L + 105]), out)
+    assert k == L
+    got.append(out[:k].copy())
+    st = b.GetState()
+    c = pb.CFastFIR(N, L + 1)                                              # fresh object, same filter, saved state
+    c.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    c.SetState(st)
+    rest = np.ascontiguousarray(x[L + 105:])
+    out2 = np.zeros(len(rest) + N, complex)
+    k2 = c.ProcessData(len(rest), rest, out2)
+    assert k + k2 == kw
+    got.append(out2[:k2].copy())
+    assert rel_rms(np.concatenate(got), whole[:kw]) <= 1e-13

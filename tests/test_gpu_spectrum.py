@@ -93,3 +93,33 @@ def test_window_tables_bit_exact():
             w = pb.WindowFunction(t, n)
             rw, rcg = ref.window(t, n)
             assert np.array_equal(w.window, rw) and w.coherentGain == rcg
+
+
+def test_spectrum_db_edges_zero_tiny_and_full_scale_frames():
+    """The table-reduced dB conversion (spec_db) against the oracle on the edges of its range: an all-zero frame (bin == 0
+    -> -120 exactly, db.h:44-48), amplitudes whose spectrum clips at -120, a wide dynamic range (1e-7 .. 0.9 across the
+    band) and a full-scale tone that sets the overload flag. Clipped bins equal, others within 1e-6 dB, flags exact."""
+    import pebblesdr_b200 as pb
+    from oracle import port
+    size = 8192
+    g, o = pb.FFT(), port.FFT()
+    g.fftParams(size, 0, 20e6, size, 12)
+    o.fftParams(size, 0, 20e6, size, 12)
+    t = np.arange(size)
+    rng = np.random.default_rng(99)
+    frames = [
+        np.zeros(size, complex),
+        1e-9 * np.exp(2j * np.pi * 0.11 * t),
+        sum(10.0 ** (-k) * np.exp(2j * np.pi * (0.03 + 0.06 * k) * t) for k in range(1, 8)) + 1e-7 * rng.standard_normal(size),
+        0.95 * np.exp(2j * np.pi * (1024 / size) * t),
+        np.zeros(size, complex),
+    ]
+    for f, x in enumerate(frames):
+        x = np.ascontiguousarray(x.astype(np.complex128))
+        yg, yo = np.zeros(size), np.zeros(size)
+        fg, fo = g.fftSpectrum(x, yg, size), o.fftSpectrum(x, yo, size)
+        assert bool(fg) == bool(fo), f
+        clipped = (yo <= -120.0) | (yo >= 0.0)
+        assert np.array_equal(yg[clipped], yo[clipped]), f
+        assert np.max(np.abs(yg[~clipped] - yo[~clipped]), initial=0.0) <= 1e-6, f
+    assert np.all(yg == -120.0)   # second zero frame after a loud one: (0 + prev)/2 of the previous frame is NOT carried twice
