@@ -184,13 +184,13 @@ struct LongFir {
     cpx *d_ht;         // H in the fused row kernel's order (lf_permute_kernel)
     bool fused;        // PEBBLE_LF_GENERIC=1 keeps the generic in-place row kernel (cross-check)
     int chunk;         // blocks per launch triple
-    // Consecutive chunks alternate between `lanes` internal streams (own scratch each), forked from and joined to the
+    // Consecutive chunks rotate over `lanes` (default 3) internal streams (own scratch each), forked from and joined to the
     // caller's stream by events: the column kernels are L2-bandwidth-bound and the row kernel FP64/shared-memory-bound,
     // so chunk c's rows overlap chunk c+1's forward columns.
     int lanes;
     bool cols12;       // column kernels compiled for 12 CTAs per SM (40 registers) instead of 9 (54)
-    cudaStream_t lane[2];
-    cudaEvent_t fork, join[2];
+    cudaStream_t lane[3];
+    cudaEvent_t fork, join[3];
 };
 
 bool lf_size_supported(int fft_size) { return fft_size == 32768 || fft_size == 131072; }
@@ -200,20 +200,21 @@ LongFir *lf_create(int fft_size, const cpx *d_twN) {
     LongFir *p = new LongFir();
     p->N = fft_size; p->N1 = fft_size / LF_N2; p->R = p->N1 == 64 ? 8 : 4; p->d_twN = d_twN;
     p->d_tw2 = nullptr; p->d_scratch = nullptr; p->d_ht = nullptr; p->fused = !getenv("PEBBLE_LF_GENERIC");
-    // default (N = 131072): 18 blocks per chunk = 36 MB of scratch per lane, 72 MB for both lanes: inside the 126 MB L2
-    // together with the streaming input/output. 1152 row CTAs = 1.95 waves of 148 SMs x 4. Larger chunks (37 blocks =
-    // exactly 4 row waves) measured 2 % faster but spill the scratch to DRAM (3.6x the algorithmic traffic instead of
-    // ~1.5x): profiles/r1_longfir_history.md.
+    // default (N = 131072): 9 blocks per chunk and three lanes = 54 MB of scratch in flight, inside the 126 MB L2 together
+    // with the streaming input/output. 9 x 64 = 576 row CTAs = one wave of 148 SMs x 4; 1152 column CTAs = 0.86 wave of
+    // 148 x 9: every launch is a single wave and three of them (one per lane) are in flight. Sweep in
+    // profiles/r1_longfir_history.md: lanes x chunk = 2x18 9.51 ms, 3x12 9.48, 3x9 9.12-9.15, 3x6 9.82, 3x18 12.3 (L2 spill).
     const char *e = getenv("PEBBLE_LF_CHUNK_MB");
-    const int mb = e && atoi(e) > 0 ? atoi(e) : 36;
+    const int mb = e && atoi(e) > 0 ? atoi(e) : 18;
     p->chunk = (int)(((size_t)mb << 20) / (sizeof(cpx) * (size_t)fft_size));
     if ((e = getenv("PEBBLE_LF_CHUNK_BLOCKS")) && atoi(e) > 0) p->chunk = atoi(e);
     if (p->chunk < 1) p->chunk = 1;
     e = getenv("PEBBLE_LF_COLS_MINB");
     p->cols12 = e && atoi(e) == 12;
     e = getenv("PEBBLE_LF_LANES");
-    p->lanes = e && atoi(e) == 1 ? 1 : 2;
-    p->lane[0] = p->lane[1] = nullptr; p->fork = nullptr; p->join[0] = p->join[1] = nullptr;
+    p->lanes = e && atoi(e) >= 1 && atoi(e) <= 3 ? atoi(e) : 3;
+    for (int l = 0; l < 3; ++l) { p->lane[l] = nullptr; p->join[l] = nullptr; }
+    p->fork = nullptr;
     bool ok = pebble::cuda_ok(cudaMalloc(&p->d_tw2, sizeof(cpx) * LF_N2), "cudaMalloc") &&
               pebble::cuda_ok(cudaMalloc(&p->d_ht, sizeof(cpx) * (size_t)fft_size), "cudaMalloc") &&
               pebble::cuda_ok(cudaMemset(p->d_ht, 0, sizeof(cpx) * (size_t)fft_size), "cudaMemset") &&
@@ -257,7 +258,7 @@ LongFir *lf_create(int fft_size, const cpx *d_twN) {
 void lf_destroy(LongFir *p) {
     if (!p) return;
     cudaFree(p->d_tw2); cudaFree(p->d_scratch); cudaFree(p->d_ht);
-    for (int l = 0; l < 2; ++l) {
+    for (int l = 0; l < 3; ++l) {
         if (p->lane[l]) cudaStreamDestroy(p->lane[l]);
         if (p->join[l]) cudaEventDestroy(p->join[l]);
     }
