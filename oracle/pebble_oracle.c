@@ -677,6 +677,10 @@ void orc_agc_set_mode(void *p, int mode, int threshold) {
     if (mode == 1) decay = 100; else if (mode == 3) decay = 500; else if (mode == 2) decay = 250; else if (mode == 4) decay = 2000;
     orc_agc_set_parameters(h, 0, threshold, 0, decay);
 }
+void orc_agc_set_threshold(void *p, int g) {  /* AGC::setAgcThreshold, agc.cpp:43-50: the delay line and averages are kept */
+    orc_agc *h = (orc_agc *)p;
+    orc_agc_set_parameters(h, h->use_hang, g, h->slope, h->decay);
+}
 void *orc_agc_create(double sample_rate) {
     orc_agc *h = (orc_agc *)calloc(1, sizeof(orc_agc));
     h->sample_rate = sample_rate; h->params_rate = 100.0;
@@ -916,4 +920,37 @@ int orc_decimator_process(void *p, int n, const double *in, double *out) {
     }
     memcpy(out, d->buf[cur], sizeof(ocpx) * rem);
     return rem;
+}
+
+/* ------------------------------------------------------------------------------------------------------------
+ * DeviceInterfaceBase::normalizeIQ, block forms (pebblelib/deviceinterfacebase.cpp:648-878; sample structs
+ * pebblelib/cpx.h:43-92). fmt: 0 CPX8 (qint8 re,im), 1 CPXU8 (quint8, offset binary), 2 CPX16 (qint16),
+ * 3 CPXFLOAT (float), 4 CPX (double). order: DeviceInterface::IQOrder 0 IQ, 1 QI, 2 I only, 3 Q only
+ * (device_interfaces.h:140-145); `reverse` swaps IQ <-> QI (:653-657). scale is formed left to right as the
+ * reference writes it: (1/128.0 * userGain) * normalizeGain, (1/32768.0 * ...) or userGain * normalizeGain.
+ * ---------------------------------------------------------------------------------------------------------- */
+void orc_normalize_iq(int fmt, int order, double user_gain, double norm_gain, int reverse, unsigned n, const void *in, double *out_) {
+    ocpx *out = (ocpx *)out_;
+    double scale;
+    if (fmt == 0 || fmt == 1) scale = 1 / 128.0 * user_gain * norm_gain;
+    else if (fmt == 2) scale = 1 / 32768.0 * user_gain * norm_gain;
+    else scale = user_gain * norm_gain;
+    if (order == 0 && reverse) order = 1;
+    else if (order == 1 && reverse) order = 0;
+    for (unsigned i = 0; i < n; i++) {
+        double I, Q;
+        switch (fmt) {
+            case 0: I = ((const signed char *)in)[2 * i]; Q = ((const signed char *)in)[2 * i + 1]; break;
+            case 1: I = ((const unsigned char *)in)[2 * i] - 128.0; Q = ((const unsigned char *)in)[2 * i + 1] - 128.0; break;  /* :700-701 */
+            case 2: I = ((const short *)in)[2 * i]; Q = ((const short *)in)[2 * i + 1]; break;
+            case 3: I = ((const float *)in)[2 * i]; Q = ((const float *)in)[2 * i + 1]; break;
+            default: I = ((const double *)in)[2 * i]; Q = ((const double *)in)[2 * i + 1]; break;
+        }
+        switch (order) {
+            case 0: out[i].re = I * scale; out[i].im = Q * scale; break;
+            case 1: out[i].re = Q * scale; out[i].im = I * scale; break;
+            case 2: out[i].re = I * scale; out[i].im = out[i].re; break;
+            default: out[i].im = Q * scale; out[i].re = out[i].im; break;
+        }
+    }
 }

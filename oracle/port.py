@@ -43,11 +43,12 @@ def lib():
             "orc_demod_am": (None, [_vp, _i, _vp, _vp]), "orc_demod_fm2": (None, [_vp, _i, _vp, _vp]),
             "orc_demod_nfm_pll": (None, [_vp, _i, _vp, _vp]),
             "orc_agc_create": (_vp, [_d]), "orc_agc_destroy": (None, [_vp]), "orc_agc_set_mode": (None, [_vp, _i, _i]),
-            "orc_agc_manual_gain": (_d, [_vp]), "orc_agc_process": (None, [_vp, _i, _vp, _vp]),
+            "orc_agc_manual_gain": (_d, [_vp]), "orc_agc_set_threshold": (None, [_vp, _i]), "orc_agc_process": (None, [_vp, _i, _vp, _vp]),
             "orc_decimator_create": (_vp, [ctypes.c_uint, ctypes.c_uint]), "orc_decimator_destroy": (None, [_vp]),
             "orc_decimator_build_chain": (ctypes.c_float, [_vp, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint]),
             "orc_decimator_dec_by2_stages": (_i, [_vp]), "orc_decimator_num_stages": (_i, [_vp]),
             "orc_decimator_stage": (_i, [_vp, _i, _vp, _vp]), "orc_decimator_process": (_i, [_vp, _i, _vp, _vp]),
+            "orc_normalize_iq": (None, [_i, _i, _d, _d, _i, ctypes.c_uint, _vp, _vp]),
             "orc_receiver_create": (_vp, [_d, _i, _d]), "orc_receiver_destroy": (None, [_vp]),
             "orc_receiver_demod_rate": (_d, [_vp]), "orc_receiver_config": (None, [_vp, _d, _d, _d, _i, _i, _i]),
             "orc_receiver_set_am_bandwidth": (None, [_vp, _d]), "orc_receiver_process": (_i, [_vp, _i, _vp, _vp]),
@@ -216,6 +217,9 @@ class AGC(_H):
     def setAgcMode(self, m, thr):
         lib().orc_agc_set_mode(self.h, m, thr)
 
+    def setAgcThreshold(self, g):
+        lib().orc_agc_set_threshold(self.h, g)
+
     def processBlock(self, inb, n):
         out = np.empty(n, dtype=np.complex128)
         lib().orc_agc_process(self.h, n, inb.ctypes.data, out.ctypes.data)
@@ -248,3 +252,16 @@ def window(wtype, n):
     w = np.zeros(n)
     cg = lib().orc_window(wtype, n, w.ctypes.data)
     return w, cg
+
+
+FMT_CPX8, FMT_CPXU8, FMT_CPX16, FMT_CPXFLOAT, FMT_CPX = range(5)
+_FMT_DTYPE = {FMT_CPX8: np.int8, FMT_CPXU8: np.uint8, FMT_CPX16: np.int16, FMT_CPXFLOAT: np.float32, FMT_CPX: np.float64}
+
+
+def normalizeIQ(fmt, raw, order=0, user_gain=1.0, norm_gain=1.0, reverse=False):
+    """DeviceInterfaceBase::normalizeIQ block forms (deviceinterfacebase.cpp:648-878). raw: interleaved I,Q array."""
+    raw = np.ascontiguousarray(raw, dtype=_FMT_DTYPE[fmt]).reshape(-1)
+    n = raw.size // 2
+    out = np.empty(n, dtype=np.complex128)
+    lib().orc_normalize_iq(fmt, order, user_gain, norm_gain, 1 if reverse else 0, n, raw.ctypes.data, out.ctypes.data)
+    return out

@@ -6,13 +6,35 @@
 //   * by bench.py's cpu_baseline / --impl reference leg (kind "reference").
 // Nothing here re-implements arithmetic: every function forwards to the reference object.
 #include "cpx.h"
+// Which wrapper groups a build exports (build_ref.sh): the full library exports all of them; the long-filter build
+// (step 4) CFastFIR only; the MAX_DECSTAGES-12 build (step 6) CDownConvert only; the Ooura build (step 7) FFT only.
+#if defined(REF_SHIM_FASTFIR_ONLY)
+#define REF_HAVE_FASTFIR 1
+#elif defined(REF_SHIM_DOWNCONVERT_ONLY)
+#define REF_HAVE_DOWNCONVERT 1
+#elif defined(REF_SHIM_FFT_ONLY)
+#define REF_HAVE_FFT 1
+#else
+#define REF_HAVE_FASTFIR 1
+#define REF_HAVE_DOWNCONVERT 1
+#define REF_HAVE_FFT 1
+#define REF_HAVE_REST 1
+#endif
+#if REF_HAVE_FASTFIR || REF_HAVE_FFT
 #include "fft.h"
+#endif
+#if REF_HAVE_FASTFIR
 #include "fastfir.h"
-#ifndef REF_SHIM_FASTFIR_ONLY   // the long-filter build (build_ref.sh step 4) exports the CFastFIR wrappers only
+#endif
+#if REF_HAVE_DOWNCONVERT
 #include "downconvert.h"
+#endif
+#if REF_HAVE_FFT
+#include "windowfunction.h"
+#endif
+#if REF_HAVE_REST
 #include "fir.h"
 #include "mixer.h"
-#include "windowfunction.h"
 #include "decimator.h"
 #endif
 #include <cstring>
@@ -22,6 +44,7 @@ PebbleLibGlobal *pebbleLibGlobal = nullptr;
 
 extern "C" {
 
+#if REF_HAVE_FASTFIR
 // ---- CFastFIR (pebblelib/fastfir.h:50-77) -------------------------------------------------------
 void *ref_fastfir_create() { return new CFastFIR(); }
 void ref_fastfir_destroy(void *h) { delete (CFastFIR *)h; }
@@ -32,7 +55,8 @@ int ref_fastfir_process(void *h, int n, const double *in, double *out) {
     return ((CFastFIR *)h)->ProcessData(n, (CPX *)in, (CPX *)out);
 }
 
-#ifndef REF_SHIM_FASTFIR_ONLY
+#endif
+#if REF_HAVE_DOWNCONVERT
 // ---- CDownConvert (pebblelib/downconvert.h:28-37) -------------------------------------------------
 void *ref_downconvert_create() { return new CDownConvert(); }
 void ref_downconvert_destroy(void *h) { delete (CDownConvert *)h; }
@@ -49,6 +73,8 @@ int ref_downconvert_process(void *h, int n, double *in, double *out) {
     return ((CDownConvert *)h)->ProcessData(n, (CPX *)in, (CPX *)out);
 }
 
+#endif
+#if REF_HAVE_FFT
 // ---- FFT (pebblelib/fft.h:29-62) via FFT::factory (USE_FFTW or USE_FFTCUTE at build time) ----------
 void *ref_fft_create() { return FFT::factory("oracle"); }
 void ref_fft_destroy(void *h) { delete (FFT *)h; }
@@ -73,6 +99,8 @@ double ref_window(int type, int n, double *w_out) {
     return w.coherentGain;
 }
 
+#endif
+#if REF_HAVE_REST
 // ---- CFir (pebblelib/fir.h:31-56) -----------------------------------------------------------------
 void *ref_cfir_create() { return new CFir(); }
 void ref_cfir_destroy(void *h) { delete (CFir *)h; }
@@ -111,5 +139,5 @@ int ref_decimator_process(void *h, int n, const double *in, double *out) {
     return (int)((Decimator *)h)->process((CPX *)in, (CPX *)out, (quint32)n);
 }
 
-#endif  // REF_SHIM_FASTFIR_ONLY
+#endif  // REF_HAVE_REST
 }  // extern "C"

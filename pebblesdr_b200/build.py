@@ -63,8 +63,10 @@ def build_oracle():
         _run(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", out, src, "-lm"])
     ref = os.path.join(odir, "_ref", "libpebbleref.so")
     ref_long = os.path.join(odir, "_ref", "libpebbleref_long.so")   # config 5 sizes (131072/65537)
-    deps = [os.path.join(odir, "ref_shim.cpp"), os.path.join(odir, "build_ref.sh")]
-    if os.path.isdir("/root/reference/pebblelib") and (_newer(ref, deps) or _newer(ref_long, deps)):
+    others = [os.path.join(odir, "_ref", n) for n in ("libpebbleref_app.so", "libpebbleref_dec12.so", "libpebbleref_cute.so")]
+    deps = [os.path.join(odir, "ref_shim.cpp"), os.path.join(odir, "ref_app_shim.cpp"), os.path.join(odir, "build_ref.sh")]
+    deps += [os.path.join(odir, "qt_shim_app", f) for f in os.listdir(os.path.join(odir, "qt_shim_app"))]
+    if os.path.isdir("/root/reference/pebblelib") and any(_newer(t, deps) for t in [ref, ref_long] + others):
         _run(["bash", os.path.join(odir, "build_ref.sh")])
 
 
