@@ -51,6 +51,10 @@ def build_lib(force=False, verbose=False):
                 print(out)
     if force or _newer(LIB, objs):
         _run(["nvcc", "-shared", "-o", LIB] + objs + ["-lquadmath"])
+    # stand-alone FP64-peak microbenchmark (tools/measure_fp64_peak.py runs it on the GPU box)
+    peak_src, peak_exe = os.path.join(ROOT, "tools", "fp64_peak.cu"), os.path.join(ROOT, "tools", "fp64_peak")
+    if os.path.exists(peak_src) and (force or _newer(peak_exe, [peak_src])):
+        _run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-o", peak_exe, peak_src])
     return LIB
 
 
