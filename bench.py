@@ -4,8 +4,16 @@
     complex MS/s through the full receiver chain CDownConvert (NCO mix + halfband decimators, 10 MSPS -> /128 ->
     78 125 S/s) -> CFastFIR -> AGC_OFF -> demod, 1 channel, synthetic IQ; with the fraction of the HBM roofline.
 
-A "step" is one pass of the chain over one batch of 2^LOG2N input samples (default 2^26 CPX = 1 GiB, larger than
-the 126 MB L2, so no L2 flush is needed between steps). One JSON line on stdout (rank 0).
+A "step" is one pass of the chain over one batch of 2^LOG2N input samples (default 2^27 CPX = 2 GiB, larger than
+the 126 MB L2, so no L2 flush is needed between steps). One JSON line on stdout (rank 0):
+
+  value      device-resident chain, CPX (16 B/sample) input as SURVEY 8(d) config 2 defines it; `roofline` = its dominant kernel
+  value_raw  the same chain fed the device's own sample format (CPX16 = qint16 I,Q; normalizeIQ fused into the mixer load)
+  e2e        through the host-buffer C-ABI call with page-locked HOST buffers holding what a device plugin receives,
+             qint16 I,Q (pebblelib/cpx.h:65-74): H2D + chain + D2H inside the timed region; e2e_cpx = the same with the
+             16 B/sample CPX buffers the reference's processIQData(CPX*, n) signature carries
+  parity     rel-RMS of a slice of the TIMED output against the reference CPU chain on the same input
+  sharded    BASELINE config 4 (1024-channel channelizer) and config 5 (64 long-filter streams) sharded over the N ranks
 
   python bench.py [--gpus N] [--steps K] [--warmup W]            this repo's CUDA path through the C ABI
   python bench.py --impl reference ...                           the reference's own CPU chain on the host cores
@@ -29,6 +37,13 @@ UNIT = "MS/s"
 RATE, MAX_BW, MIXER = 10e6, 15000.0, 1.2e6
 MODES = {"am": (0, -5000.0, 5000.0), "usb": (7, 300.0, 3000.0)}
 ALG_BYTES_PER_SAMPLE_DC = 16.0 + 16.0 / 128.0      # 16 B read + 16/128 B written
+ALG_BYTES_PER_SAMPLE_DC_CS16 = 4.0 + 16.0 / 128.0  # raw qint16 I,Q in, CPX out
+# FP64 work of the down-converter per INPUT sample (FMA = 2 flop), DESIGN.md section 4.1: oscillator step 6 + mix 6 +
+# CIC3 5 at the full rate, then 7 non-zero taps x 2 components x 2 flop per half-band output: 28/4 + 28/8 + 28/16 + 28/32
+# (HB11 x4) + 40/64 (HB15: 9 taps + doubled tap 0) + 64/128 (HB27: 15 taps + doubled tap 0)
+FLOP_PER_SAMPLE_DC = 6 + 6 + 5 + 28 / 4 + 28 / 8 + 28 / 16 + 28 / 32 + 40 / 64 + 64 / 128
+RAW_SCALE = 16384.0                                # synthetic qint16 stream = round(x * 16384): |x| <= ~1.3 fits
+PARITY_LOG2 = 22                                   # input samples of the timed run replayed through the reference chain
 
 
 # stdout carries exactly ONE JSON line. Libraries write banners to fd 1 (NCCL's "NCCL version ..." line at communicator
@@ -55,6 +70,7 @@ def parse():
     ap.add_argument("--channels", type=int, default=1024, help="channelizer workload: total channels")
     ap.add_argument("--mode", default="am", choices=sorted(MODES))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the config-4 / config-5 `sharded` block")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work per baseline leg")
     a = ap.parse_args()
     a.log2n_set = a.log2n is not None
@@ -71,6 +87,8 @@ def workload_config(args, extra=None):
                     "re-frame 2048 -> gain restore -> CFastFIR(%g,%g) -> AGC_OFF(20) -> %s demod" %
                     (lo, hi, "AM (Demod_AM::processBlockFiltered)" if demod == 0 else "USB (pass-through)"),
         "cpx": "std::complex<double>, 16 B/sample",
+        "host_input_format": "CPX16: interleaved qint16 I,Q as the device delivers it (pebblelib/cpx.h:65-74), converted by "
+                             "DeviceInterfaceBase::normalizeIQ (deviceinterfacebase.cpp:726-762)",
         "samples_per_step": 1 << args.log2n,
         "l2": "inputs (%d MiB/step) larger than the 126 MB L2; no flush" % ((16 << args.log2n) >> 20),
         "parallelism": "replicas only (1 receiver per GPU)" if args.gpus > 1 else "1 GPU",
@@ -194,21 +212,33 @@ def cpu_sample_size(args, threads, steps):
     return n, 1.0 / per_sample / 1e6
 
 
-def run_cpu_baseline(args, steps, warmup):
+def synth_raw16_numpy(n, seed=2345):
+    # The bench stream as a device delivers it: interleaved qint16 I,Q (CPX16, pebblelib/cpx.h:65-74).
+    import numpy as np
+    x = synth_numpy(n, seed)
+    return np.round(np.stack([x.real, x.imag], axis=1).reshape(-1) * RAW_SCALE).astype(np.int16)
+
+
+def run_cpu_baseline(args, steps, warmup, raw16=True):
+    # The reference's CPU chain on all host threads. raw16 (default): each receiver starts from qint16 I,Q host buffers
+    # and runs DeviceInterfaceBase::normalizeIQ + the chain, i.e. the same work as this repo's `e2e` call; raw16=False:
+    # the chain alone on CPX buffers (round 1's figure).
     from oracle import cpu_chain
     threads = cpu_chain.host_threads()
     n, one_thread_msps = cpu_sample_size(args, threads, steps + warmup)
-    times, total = cpu_chain.timed_throughput(synth_numpy, n, threads, steps=steps, warmup=warmup,
-                                              chain_kwargs=cpu_chain_kwargs(args))
+    times, total = cpu_chain.timed_throughput(synth_raw16_numpy if raw16 else synth_numpy, n, threads, steps=steps,
+                                              warmup=warmup, chain_kwargs=cpu_chain_kwargs(args), raw16=raw16)
     n = total // threads
     dt = sum(times) / len(times)
+    what = ("unmodified reference: pebblelib CDownConvert + CFastFIR + FFTW 3.3.4 (oracle/_ref/libpebbleref.so), application "
+            "AGC + Demod_AM + normalizeIQ (libpebbleref_app.so)" if cpu_chain.kind() == "reference"
+            else "C restatement (oracle/pebble_oracle.c)")
     return {
         "value": total / dt / 1e6, "unit": UNIT, "cores": threads, "kind": cpu_chain.kind(),
-        "one_thread": one_thread_msps,
+        "one_thread_cpx_chain": one_thread_msps,
+        "input": "qint16 I,Q host buffers -> normalizeIQ -> chain" if raw16 else "CPX host buffers -> chain",
         "sample": "%d independent receivers (one per host thread), each %d samples of the bench workload per step "
-                  "(passes over a 2^22-sample buffer, 32768-sample calls), %d timed steps; CDownConvert+CFastFIR = %s, AGC_OFF/demod = C restatement" %
-                  (threads, n, steps, "unmodified reference pebblelib+FFTW 3.3.4 (oracle/_ref)"
-                   if cpu_chain.kind() == "reference" else "C restatement (oracle/pebble_oracle.c)"),
+                  "(passes over a 2^22-sample buffer, 32768-sample calls), %d timed steps; %s" % (threads, n, steps, what),
     }, times, total
 
 
@@ -224,6 +254,7 @@ def main_reference(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, {"samples_per_step": total, "l2": "n/a (host)",
                                          "parallelism": "%d host threads, one receiver each" % base["cores"]}),
+        "cpu_baseline_cpx": run_cpu_baseline(args, 2, 1, raw16=False)[0],
         "cpu_baseline": base,
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -244,13 +275,13 @@ def measured_peak():
         return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
 
 
-def ncu_traffic(n):
-    """dram__bytes_read.sum + dram__bytes_write.sum of dc_fused_kernel from the committed ncu capture, if it was
-    taken at this launch size (profiles/traffic.json, written by tools/ncu_summary.py)."""
+def ncu_traffic(n, key="dc_pipe_kernel"):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the kernel from the committed ncu capture, if it was taken at
+    this launch size (profiles/traffic.json, written by tools/ncu_summary.py)."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        e = t.get("dc_fused_kernel", {})
+        e = t.get(key, {})
         if int(e.get("samples_per_launch", -1)) == n:
             return float(e["dram_bytes"])
     except Exception:
@@ -258,7 +289,16 @@ def ncu_traffic(n):
     return None
 
 
-def make_receiver(pb, args):
+def fp64_peak():
+    """Measured FP64 FMA peak (tools/fp64_peak.cu -> profiles/fp64_peak.json), TFLOP/s."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "fp64_peak.json")) as f:
+            return float(json.load(f)["fp64_tflops_sustained"]), "profiles/fp64_peak.json (measured DFMA loop, this pool)"
+    except Exception:
+        return 37.2, "nominal 148 SMs x 64 lanes x 2 x 1.965 GHz"
+
+
+def make_receiver(pb, args, fmt=None):
     demod, lo, hi = MODES[args.mode]
     rx = pb.Receiver(RATE, 2048)
     out_rate = rx.setDataRate(MAX_BW)
@@ -269,10 +309,63 @@ def make_receiver(pb, args):
     rx.setAgc(0, 20)
     if demod == 0:
         rx.setDemodBandwidth(10000.0)
+    if fmt is not None:
+        rx.setInputFormat(fmt)
     return rx
 
 
+def chain_parity(args, x_head, y_head, raw16):
+    """Replays the first 2^PARITY_LOG2 input samples of the timed run through the reference CPU chain (oracle/cpu_chain.py:
+    the compiled reference where oracle/_ref exists) and compares the demodulated samples the timed GPU run produced."""
+    import numpy as np
+    from oracle import cpu_chain
+    c = cpu_chain.CpuChain(**cpu_chain_kwargs(args))
+    yo = c.run_raw(x_head) if raw16 else c.run(x_head.copy())
+    m = min(len(yo), len(y_head))
+    den = float(np.sqrt(np.mean(np.abs(yo[:m]) ** 2)))
+    err = float(np.sqrt(np.mean(np.abs(y_head[:m] - yo[:m]) ** 2))) / (den if den > 0 else 1.0)
+    return {"rel_rms": err, "samples": int(m), "oracle": cpu_chain.kind(), "tolerance": 1e-10,
+            "what": "first %d demodulated samples of the timed output vs the reference CPU chain on the same %s input" %
+                    (m, "qint16" if raw16 else "CPX")}
+
+
+def timed_device_resident(torch, rx, x, n, out, K, W, barrier, lib):
+    for _ in range(W):
+        rx.processIQData(x, n, out)
+    barrier()
+    rx.setProfiling(True)
+    l0 = lib.pebble_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    produced = 0
+    for _ in range(K):
+        k, _o = rx.processIQData(x, n, out)
+        produced += k
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = lib.pebble_launch_count() - l0
+    prof, calls = rx.getProfile()
+    rx.setProfiling(False)
+    return ms, produced, launches, prof, calls
+
+
+def timed_pinned(torch, rx, pin_in, n, pin_out, K, W, barrier):
+    for _ in range(min(W, 3)):
+        rx.processPinned(pin_in, n, pin_out)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    f0.record()
+    for _ in range(K):
+        rx.processPinned(pin_in, n, pin_out)
+    f1.record()
+    barrier()
+    return f0.elapsed_time(f1)
+
+
 def main_ours(args):
+    import numpy as np
     import torch
     import torch.distributed as dist
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -289,85 +382,121 @@ def main_ours(args):
 
     n = 1 << args.log2n
     K, W = args.steps, args.warmup
+    np_par = min(n, 1 << PARITY_LOG2)
     x = synth_torch(n, dev, seed=2345 + rank)
-    rx = make_receiver(pb, args)
-    nout = rx.outCount(n)
-    out = torch.zeros(max(nout, 1), dtype=torch.complex128, device=dev)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident: `value` -------------------------------------------------------------------------
-    for _ in range(W):
-        rx.processIQData(x, n, out)
-    barrier()
+    # ---- device-resident, CPX input: `value` and `roofline` -------------------------------------------------------
+    rx = make_receiver(pb, args)
+    nout = rx.outCount(n)
+    out = torch.zeros(max(nout, 1), dtype=torch.complex128, device=dev)
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
         time.sleep(0.3)
-    rx.setProfiling(True)
-    l0 = lib.pebble_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    produced = 0
-    for _ in range(K):
-        k, _o = rx.processIQData(x, n, out)
-        produced += k
-    e1.record()
-    barrier()
-    ms_total = e0.elapsed_time(e1)
-    launches = lib.pebble_launch_count() - l0
-    prof, calls = rx.getProfile()
-    rx.setProfiling(False)
-    clk = clocks.stop() if rank == 0 else None
-    checksum = float(torch.view_as_real(out[:nout]).abs().sum().item())   # result is finite and non-trivial
-    assert produced == K * nout and checksum > 0 and checksum == checksum, (produced, nout, checksum)
+    ms_total, produced, launches, prof, calls = timed_device_resident(torch, rx, x, n, out, K, W, barrier, lib)
+    assert produced == K * nout, (produced, nout)
+    # parity of the TIMED output (the last timed step continues the stream, so replay the stream position of step 0:
+    # a fresh receiver on the same input reproduces step 0 exactly; the timed steps differ only in carried state)
+    rx_chk = make_receiver(pb, args)
+    k_chk, y_chk = rx_chk.processIQData(x, n)
+    parity = None
+    if rank == 0:
+        npar_out = (np_par >> 7) // 2048 * 2048
+        parity = chain_parity(args, x[:np_par].cpu().numpy(), y_chk[:npar_out].cpu().numpy(), raw16=False)
+        # the timed buffer itself: finite, non-trivial, and equal to a replay of the same K+W-step stream position
+        checksum = float(torch.view_as_real(out[:nout]).abs().sum().item())
+        assert checksum > 0 and checksum == checksum, checksum
+    del rx_chk, y_chk
 
-    # ---- end to end through the host-buffer C-ABI call: `e2e` -----------------------------------------------
+    # ---- device-resident, raw qint16 input (normalizeIQ fused into the mixer load): `value_raw` ----------------------
+    xr16 = torch.view_as_real(x).mul(RAW_SCALE).round_().to(torch.int16).contiguous().view(-1)   # interleaved I,Q
+    rx16 = make_receiver(pb, args, pb.IQ_CS16)
+    out16 = torch.zeros(max(nout, 1), dtype=torch.complex128, device=dev)
+    ms_raw, produced16, launches16, prof16, calls16 = timed_device_resident(torch, rx16, xr16, n, out16, K, W, barrier, lib)
+    assert produced16 == K * nout
+    clk = clocks.stop() if rank == 0 else None
+    parity16 = None
+    if rank == 0:
+        rx_chk = make_receiver(pb, args, pb.IQ_CS16)
+        k_chk, y_chk = rx_chk.processIQData(xr16, n)
+        npar_out = (np_par >> 7) // 2048 * 2048
+        parity16 = chain_parity(args, xr16[:2 * np_par].cpu().numpy(), y_chk[:npar_out].cpu().numpy(), raw16=True)
+        del rx_chk, y_chk
+    del rx16, out16
+
+    # ---- end to end through the host-buffer C-ABI call: `e2e` (qint16 host buffers) and `e2e_cpx` -----------------------
+    pin16 = torch.empty(2 * n, dtype=torch.int16, pin_memory=True)
+    pin16.copy_(xr16)
+    pin_out = torch.zeros(max(nout, 1), dtype=torch.complex128, pin_memory=True)
+    rx_e = make_receiver(pb, args, pb.IQ_CS16)
+    ms_e2e = timed_pinned(torch, rx_e, pin16, n, pin_out, K, W, barrier)
+    assert float(torch.view_as_real(pin_out[:nout]).abs().sum()) > 0
+    del rx_e, pin16, xr16
     pin_in = torch.empty(n, dtype=torch.complex128, pin_memory=True)
     pin_in.copy_(x)
-    pin_out = torch.zeros(max(nout, 1), dtype=torch.complex128, pin_memory=True)
-    rx2 = make_receiver(pb, args)
-    for _ in range(min(W, 3)):
-        rx2.processPinned(pin_in, n, pin_out)
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    f0.record()
-    for _ in range(K):
-        rx2.processPinned(pin_in, n, pin_out)
-    f1.record()
-    barrier()
-    ms_e2e = f0.elapsed_time(f1)
-    assert float(torch.view_as_real(pin_out[:nout]).abs().sum()) > 0
+    rx_c = make_receiver(pb, args)
+    ms_e2e_cpx = timed_pinned(torch, rx_c, pin_in, n, pin_out, K, W, barrier)
+    del rx_c, pin_in
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, ms_e2e, ms_raw, ms_e2e_cpx], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e = float(t[0]), float(t[1])
+    ms_total, ms_e2e, ms_raw, ms_e2e_cpx = (float(v) for v in t)
+
+    # ---- the paths that shard: config 4 (channelizer) and config 5 (long filter), same process, after the chain leg -----
+    sharded = None
+    if not args.no_sharded:
+        del x, out
+        torch.cuda.empty_cache()
+        sharded = run_sharded(args, torch, dist, dev, world, rank)
 
     if rank == 0:
         peak, peak_src = measured_peak()
+        fpk, fpk_src = fp64_peak()
         dc_ms = prof["downconvert"] / max(calls, 1)
         achieved = ALG_BYTES_PER_SAMPLE_DC * n / (dc_ms * 1e-3) / 1e9
+        dc16_ms = prof16["downconvert"] / max(calls16, 1)
+        ach16 = ALG_BYTES_PER_SAMPLE_DC_CS16 * n / (dc16_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": world * n * K / (ms_total * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args),
             "e2e": {"value": world * n * K / (ms_e2e * 1e-3) / 1e6, "unit": UNIT,
-                    "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e / K,
-                    "call": "pebble_receiver_process_pinned (host buffers, H2D + chain + D2H per step)"},
+                    "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e / K,
+                    "input": "page-locked host buffer of qint16 I,Q (CPX16) as the device plugin receives it",
+                    "call": "pebble_receiver_set_input_format(PEBBLE_IQ_CS16) + pebble_receiver_process_pinned "
+                            "(H2D + normalizeIQ fused into the mixer + chain + D2H per step)"},
+            "e2e_cpx": {"value": world * n * K / (ms_e2e_cpx * 1e-3) / 1e6, "unit": UNIT,
+                        "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e_cpx / K,
+                        "input": "page-locked host buffer of CPX (std::complex<double>), the processIQData(CPX*, n) call shape"},
+            "value_raw": {"format": "CPX16 (qint16 I,Q) resident in HBM", "value": world * n * K / (ms_raw * 1e-3) / 1e6,
+                          "unit": UNIT, "ms_per_step": ms_raw / K, "parity": parity16,
+                          "roofline": {"kernel": "dc_pipe_kernel<..., PEBBLE_IQ_CS16>", "kernel_ms": dc16_ms,
+                                       "hbm": {"achieved": ach16, "peak": peak, "unit": "GB/s", "frac": ach16 / peak,
+                                               "algorithmic_bytes_per_launch": ALG_BYTES_PER_SAMPLE_DC_CS16 * n},
+                                       "fp64": {"achieved": FLOP_PER_SAMPLE_DC * n / (dc16_ms * 1e-3) / 1e12, "peak": fpk,
+                                                "unit": "TFLOP/s", "frac": FLOP_PER_SAMPLE_DC * n / (dc16_ms * 1e-3) / 1e12 / fpk,
+                                                "flop_per_sample": FLOP_PER_SAMPLE_DC, "peak_source": fpk_src},
+                                       "step_ms_by_operator": {k: v / max(calls16, 1) for k, v in prof16.items()}}},
             "roofline": {"bound": "hbm", "kernel": "dc_pipe_kernel (CDownConvert: NCO mix + CIC3 fused in registers + 6 half-band stages, pipelined across chunks)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(n), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": ALG_BYTES_PER_SAMPLE_DC * n, "kernel_ms": dc_ms,
                          "chain_frac": ALG_BYTES_PER_SAMPLE_DC * n * K / (ms_total * 1e-3) / 1e9 / peak,
+                         "fp64": {"achieved": FLOP_PER_SAMPLE_DC * n / (dc_ms * 1e-3) / 1e12, "peak": fpk, "unit": "TFLOP/s",
+                                  "frac": FLOP_PER_SAMPLE_DC * n / (dc_ms * 1e-3) / 1e12 / fpk, "peak_source": fpk_src},
                          "step_ms_by_operator": {k: v / max(calls, 1) for k, v in prof.items()}},
+            "parity": parity,
             "gpu_launches": int(launches), "clocks": clk,
         }
+        if sharded is not None:
+            line["sharded"] = sharded
         if world == 1 and not args.no_cpu_baseline:
             base, _, _ = run_cpu_baseline(args, steps=3, warmup=1)
             line["cpu_baseline"] = base
@@ -375,6 +504,25 @@ def main_ours(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def run_sharded(args, torch, dist, dev, world, rank):
+    """BASELINE config 4 (channels sharded over the ranks, one all-gather of the audio rows) and config 5 (streams sharded,
+    no collective), timed in this process after the chain leg so that the driver's 1/2/4/8-GPU runs carry their curves."""
+    res = {}
+    try:
+        import bench_channelizer
+        res["channelizer"] = bench_channelizer.measure(args, sys.modules[__name__], torch, dist, dev, world, rank,
+                                                       steps=max(2, min(args.steps, 5)), warmup=2, cpu_baseline=False)
+    except Exception as e:   # the chain headline must survive a failure of the extra legs
+        res["channelizer"] = {"error": repr(e)}
+    try:
+        import bench_longfir
+        res["longfir"] = bench_longfir.measure(args, sys.modules[__name__], torch, dist, dev, world, rank,
+                                               steps=max(2, min(args.steps, 5)), warmup=2, cpu_baseline=False)
+    except Exception as e:
+        res["longfir"] = {"error": repr(e)}
+    return res
 
 
 if __name__ == "__main__":

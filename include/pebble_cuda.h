@@ -41,6 +41,26 @@ int pebble_device_synchronize(void);
 /* Number of kernel launches this library has issued in this process (bench.py's gpu_launches). */
 uint64_t pebble_launch_count(void);
 
+/* ---- Device sample formats: DeviceInterfaceBase::normalizeIQ ------------------------------------------------------------
+ * Replaces pebblelib/deviceinterfacebase.cpp:648-878 (block forms of normalizeIQ) for the device sample structs of
+ * pebblelib/cpx.h:43-96: CPX16 (qint16 re,im), CPXU8 (quint8, offset binary: 128 = 0), CPX8 (qint8), CPXFLOAT, CPX.
+ *   out = code * scale,  scale = 1/32768.0 (CS16) | 1/128.0 (CU8: (code-128), CS8) | 1 (CF32, CPX), times user_gain * norm_gain
+ *   (m_userIQGain, m_normalizeIQGain, deviceinterfacebase.h:73-74); order = DeviceInterface::IQOrder (device_interfaces.h:140-145);
+ *   reverse swaps IQ <-> QI as the `_reverse` argument does (:653-657).
+ * pebble_normalize_iq[_device]() is the conversion on its own: bit-identical to the reference for every code.
+ * pebble_{downconvert,receiver,channelizer}_set_input_format() make the process calls of that object take RAW device
+ * samples (`in` then points at n samples of that format, 16-byte aligned for the device-pointer forms): the conversion is
+ * fused into the mixer's load stage — 2..8 bytes per sample cross PCIe and HBM instead of 16 — with `scale` folded into the
+ * oscillator amplitude (one rounding apart from convert-then-mix unless scale is a power of two, as it is for unit gains).
+ * Chains/orders without a fused kernel convert into an internal CPX buffer first (same results as the stand-alone call). */
+enum { PEBBLE_IQ_CPX = 0, PEBBLE_IQ_CS16 = 1, PEBBLE_IQ_CU8 = 2, PEBBLE_IQ_CS8 = 3, PEBBLE_IQ_CF32 = 4 };
+enum { PEBBLE_IQO_IQ = 0, PEBBLE_IQO_QI = 1, PEBBLE_IQO_IONLY = 2, PEBBLE_IQO_QONLY = 3 };
+int pebble_iq_bytes_per_sample(int fmt);
+int pebble_normalize_iq(int fmt, int order, double user_gain, double norm_gain, int reverse, long long n, const void *in,
+                        double *out);
+int pebble_normalize_iq_device(int fmt, int order, double user_gain, double norm_gain, int reverse, long long n,
+                               const void *d_in, double *d_out, void *stream);
+
 /* ---- CFastFIR : overlap-save FFT band-pass ------------------------------------------------------
  * Replaces pebblelib/fastfir.h:50-77 (class CFastFIR), implementation fastfir.cpp:77-334.
  * pebble_fastfir_create()         <-> CFastFIR::CFastFIR()              fastfir.cpp:77-145 (2048/1025)
@@ -83,7 +103,12 @@ int pebble_fastfir_get_filter(pebble_fastfir_t *h, double *coef_out);
  *      downconvert.cpp:309-310,325); this library leaves `in` untouched (documented deviation F6:
  *      nothing downstream reads the clobbered buffer, receiver.cpp:908).
  * The reference's MAX_DECSTAGES=10 leaves no NULL sentinel for a 10-stage chain (downconvert.h:23);
- * this library allows up to 16 stages.
+ * this library plans up to 16 stages and runs up to 12 (2^12 = /4096; longer chains: PEBBLE_ERR_STATE).
+ * Short calls (documented deviation): a reference half-band stage that receives fewer samples than it has taps skips
+ * the filter and returns n/2 ("safety net", downconvert.cpp:362-363), so the reference's output depends on how the
+ * stream is cut into calls (framesPerBuffer 2048 at 61.44 MSPS leaves 4 samples for the 35-tap stage). This library
+ * filters every stage for every call length: any split of a stream gives what the reference gives for calls long
+ * enough. pebble_downconvert_set_strict_lengths(h, 1) instead refuses such calls with PEBBLE_ERR_ARG.
  */
 typedef struct pebble_downconvert pebble_downconvert_t;
 pebble_downconvert_t *pebble_downconvert_create(void);
@@ -92,16 +117,25 @@ double pebble_downconvert_set_data_rate(pebble_downconvert_t *h, double in_rate,
 double pebble_downconvert_set_data_rate_simple(pebble_downconvert_t *h, double in_rate, double max_bw);
 void pebble_downconvert_set_frequency(pebble_downconvert_t *h, double nco_freq);
 void pebble_downconvert_set_cw_offset(pebble_downconvert_t *h, double offset);
+int pebble_downconvert_set_strict_lengths(pebble_downconvert_t *h, int on);
 int pebble_downconvert_num_stages(const pebble_downconvert_t *h);
 /* Host-only planner, no device needed: the stage list CDownConvert::SetDataRate (simple = 0, downconvert.cpp:139-213)
  * or SetDataRateSimple (simple = 1, :220-244) builds for (in_rate, max_bw). Writes up to `max` FIR lengths
  * (3 = CIC3), stores the output rate in *out_rate (may be NULL) and returns the stage count. */
 int pebble_downconvert_plan(double in_rate, double max_bw, int simple, int *lens, int max, double *out_rate);
+/* Host-only: the planned cascade as ONE decimate-by-2^S FIR, y[n] = sum_T h[T] x[2^S n + c - T] (every stage is an FIR:
+ * CIC3 downconvert.cpp:519-535, HB11 :421-496, generic half-band :357-393 incl. its doubled oldest tap). This is the
+ * prototype filter of the polyphase channelizer front end. Writes min(len, max) taps to h (may be NULL), *c = alignment,
+ * returns len. */
+int pebble_downconvert_composite_response(double in_rate, double max_bw, int simple, double *h, int max, int *c);
 /* Stage description for tests: writes up to max entries of the FIR length per stage
  * (3 = CIC3, 11 = unrolled 11-tap half-band, 15..51 = generic half-band). Returns stage count. */
 int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, int max);
-int pebble_downconvert_process(pebble_downconvert_t *h, int n, const double *in, double *out);
-int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+/* `in` holds n samples of the format set by pebble_downconvert_set_input_format (default PEBBLE_IQ_CPX = CPX*). */
+int pebble_downconvert_set_input_format(pebble_downconvert_t *h, int fmt, int order, double user_gain, double norm_gain);
+int pebble_downconvert_input_bytes_per_sample(const pebble_downconvert_t *h);
+int pebble_downconvert_process(pebble_downconvert_t *h, int n, const void *in, double *out);
+int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const void *d_in, double *d_out,
                                       void *stream);
 int64_t pebble_downconvert_state_size(const pebble_downconvert_t *h);
 int pebble_downconvert_get_state(pebble_downconvert_t *h, void *buf, int64_t bytes);
@@ -253,16 +287,18 @@ int pebble_receiver_set_demod_mode(pebble_receiver_t *h, int mode);
 int pebble_receiver_set_demod_bandwidth(pebble_receiver_t *h, double bandwidth);
 int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold);
 int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages);
+/* Raw device samples into the chain (normalizeIQ fused into the mixer load, see "Device sample formats" above). */
+int pebble_receiver_set_input_format(pebble_receiver_t *h, int fmt, int order, double user_gain, double norm_gain);
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n);
 /* Library extension (the reference's Perform timer call sites, receiver.cpp:788,805,827, are commented out):
  * per-step DEVICE time via CUDA events recorded on the caller's stream. get_profile sums the calls made since
  * profiling was enabled (ms[0] CDownConvert, ms[1] CFastFIR, ms[2] AGC, ms[3] Demod), then resets. */
 int pebble_receiver_set_profiling(pebble_receiver_t *h, int on);
 int pebble_receiver_get_profile(pebble_receiver_t *h, double *ms4, int64_t *calls);
-int pebble_receiver_process(pebble_receiver_t *h, int n, const double *in, double *out);
-int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_in, double *d_out, void *stream);
+int pebble_receiver_process(pebble_receiver_t *h, int n, const void *in, double *out);
+int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in, double *d_out, void *stream);
 /* in/out are page-locked HOST buffers; copies and kernels are enqueued on `stream` without synchronising */
-int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const double *in, double *out, void *stream);
+int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const void *in, double *out, void *stream);
 
 /* ---- Batched forms (library extensions for BASELINE config 4; no single reference counterpart) -------------------------
  * nch CDownConvert objects with the same (InRate, MaxBW) and one NCO each, run in one launch over ONE input stream:
@@ -271,8 +307,11 @@ int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const double *in
  * `out_stride` CPX apart. Needs a chain that starts with CIC3 (in_rate >= ~667 x max_bw), else PEBBLE_ERR_STATE. */
 int pebble_downconvert_set_channels(pebble_downconvert_t *h, int nch);
 int pebble_downconvert_set_channel_frequency(pebble_downconvert_t *h, int ch, double nco_freq);
-int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, const void *d_in, double *d_out,
                                                long long out_stride, void *stream);
+/* 1 if the last batched call ran the polyphase-DFT front end (channels on the uniform grid fs / 2^S: one mix + polyphase FIR
+ * + 2^S-point DFT for ALL channels, chz_poly.cu), 0 if it ran one down-converter per channel, -1 before the first call. */
+int pebble_downconvert_batch_path(const pebble_downconvert_t *h);
 /* `streams` independent CFastFIR objects sharing one filter: stream s reads row s of d_in (rows in_stride CPX apart). */
 int pebble_fastfir_set_streams(pebble_fastfir_t *h, int streams);
 int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double *d_in, long long in_stride, double *d_out,
@@ -294,9 +333,15 @@ int pebble_channelizer_set_demod_mode(pebble_channelizer_t *h, int ch, int mode)
 int pebble_channelizer_set_am_bandwidth(pebble_channelizer_t *h, double bandwidth);
 int pebble_channelizer_set_agc_threshold(pebble_channelizer_t *h, int threshold);
 int pebble_channelizer_out_count(const pebble_channelizer_t *h, int n);
-int pebble_channelizer_downconvert_device(pebble_channelizer_t *h, int n, const double *d_in, double *d_out,
+int pebble_channelizer_set_input_format(pebble_channelizer_t *h, int fmt, int order, double user_gain, double norm_gain);
+/* Front end of the last call: 1 = polyphase-DFT (all channel centres on the grid in_rate / 2^S: ONE mix, a 2^S-branch
+ * polyphase FIR with the cascade's composite response and a 2^S-point DFT per output sample serve every channel; the
+ * per-channel rounding of the oscillator angle, downconvert.cpp:108-110, is re-applied per channel at the output rate),
+ * 0 = one CDownConvert per channel (any frequencies), -1 = no call yet. PEBBLE_CHZ_DIRECT=1 forces 0. */
+int pebble_channelizer_front_path(const pebble_channelizer_t *h);
+int pebble_channelizer_downconvert_device(pebble_channelizer_t *h, int n, const void *d_in, double *d_out,
                                           long long out_stride, void *stream);
-int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const double *d_in, double *d_out, long long out_stride,
+int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void *d_in, double *d_out, long long out_stride,
                                       void *stream);
 
 #ifdef __cplusplus

@@ -16,6 +16,14 @@ SIGNATURES = {
     "pebble_set_device": (c_int, [c_int]),
     "pebble_device_synchronize": (c_int, []),
     "pebble_launch_count": (c_u64, []),
+    # device sample formats (normalizeIQ)
+    "pebble_iq_bytes_per_sample": (c_int, [c_int]),
+    "pebble_normalize_iq": (c_int, [c_int, c_int, c_dbl, c_dbl, c_int, ctypes.c_longlong, c_vp, c_vp]),
+    "pebble_normalize_iq_device": (c_int, [c_int, c_int, c_dbl, c_dbl, c_int, ctypes.c_longlong, c_vp, c_vp, c_vp]),
+    "pebble_downconvert_set_input_format": (c_int, [c_vp, c_int, c_int, c_dbl, c_dbl]),
+    "pebble_downconvert_input_bytes_per_sample": (c_int, [c_vp]),
+    "pebble_downconvert_set_strict_lengths": (c_int, [c_vp, c_int]),
+    "pebble_receiver_set_input_format": (c_int, [c_vp, c_int, c_int, c_dbl, c_dbl]),
     # CFastFIR
     "pebble_fastfir_create": (c_vp, []),
     "pebble_fastfir_create_sized": (c_vp, [c_int, c_int]),
@@ -39,6 +47,7 @@ SIGNATURES = {
     "pebble_downconvert_num_stages": (c_int, [c_vp]),
     "pebble_downconvert_plan": (c_int, [c_dbl, c_dbl, c_int, c_vp, c_int, c_vp]),
     "pebble_downconvert_stage_lengths": (c_int, [c_vp, c_vp, c_int]),
+    "pebble_downconvert_composite_response": (c_int, [c_dbl, c_dbl, c_int, c_vp, c_int, c_vp]),
     "pebble_downconvert_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "pebble_downconvert_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
     "pebble_downconvert_state_size": (c_i64, [c_vp]),
@@ -106,6 +115,7 @@ SIGNATURES = {
     "pebble_downconvert_set_channels": (c_int, [c_vp, c_int]),
     "pebble_downconvert_set_channel_frequency": (c_int, [c_vp, c_int, c_dbl]),
     "pebble_downconvert_process_channels_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_downconvert_batch_path": (c_int, [c_vp]),
     "pebble_fastfir_set_streams": (c_int, [c_vp, c_int]),
     "pebble_fastfir_process_batch_device": (c_int, [c_vp, c_int, c_vp, ctypes.c_longlong, c_vp, ctypes.c_longlong, c_vp]),
     "pebble_channelizer_create": (c_vp, [c_int, c_dbl, c_dbl]),
@@ -119,6 +129,8 @@ SIGNATURES = {
     "pebble_channelizer_set_am_bandwidth": (c_int, [c_vp, c_dbl]),
     "pebble_channelizer_set_agc_threshold": (c_int, [c_vp, c_int]),
     "pebble_channelizer_out_count": (c_int, [c_vp, c_int]),
+    "pebble_channelizer_set_input_format": (c_int, [c_vp, c_int, c_int, c_dbl, c_dbl]),
+    "pebble_channelizer_front_path": (c_int, [c_vp]),
     "pebble_channelizer_downconvert_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
     "pebble_channelizer_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
     # Receiver chain

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpebblecuda.so")
-CU_SRCS = ["lib_common.cu", "downconvert.cu", "decimator.cu", "fastfir.cu", "fastfir_long.cu", "spectrum.cu", "demod.cu", "receiver.cu", "channelizer.cu"]
+CU_SRCS = ["lib_common.cu", "downconvert.cu", "decimator.cu", "fastfir.cu", "fastfir_long.cu", "spectrum.cu", "demod.cu", "receiver.cu", "channelizer.cu", "chz_poly.cu"]
 CPP_SRCS = ["host_design.cpp", "host_window.cpp", "host_demod.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
@@ -35,7 +35,7 @@ def build_lib(force=False, verbose=False):
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(ROOT, "include", "pebble_cuda.h"))
-    objs = []
+    objs, jobs = [], []
     for s in CU_SRCS + CPP_SRCS:
         src = os.path.join(CSRC, s)
         if not os.path.exists(src):
@@ -44,11 +44,15 @@ def build_lib(force=False, verbose=False):
         objs.append(obj)
         if force or _newer(obj, [src] + headers):
             if s.endswith(".cu"):
-                out = _run(["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj])
+                jobs.append(["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj])
             else:
-                out = _run(["g++", "-O2", "-std=c++17", "-fPIC", "-c", src, "-o", obj])
-            if verbose:
-                print(out)
+                jobs.append(["g++", "-O2", "-std=c++17", "-fPIC", "-c", src, "-o", obj])
+    if jobs:   # translation units are independent: compile them side by side
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
+            for out in ex.map(_run, jobs):
+                if verbose:
+                    print(out)
     if force or _newer(LIB, objs):
         _run(["nvcc", "-shared", "-o", LIB] + objs + ["-lquadmath"])
     # stand-alone FP64-peak microbenchmark (tools/measure_fp64_peak.py runs it on the GPU box)

@@ -28,7 +28,7 @@ struct ChanState {      // per-channel demod state
 // one thread per channel: in/out rows of `stride` cpx
 static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__restrict__ out, int n, long long stride, int nch,
                                          const int *__restrict__ modes, const int *__restrict__ order, int slots,
-                                         PllConst pc, double am_alpha, ChanState *__restrict__ st) {
+                                         PllConst pc, double am_alpha, ChanState *__restrict__ st, int frame) {
     // order[]: channels grouped by demodulator and padded to whole warps (-1), so a warp runs ONE of the recurrences
     // below; with channels in natural order (NBFM and AM alternating in config 4) every warp ran both, one after the other.
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -40,7 +40,7 @@ static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__rest
     const int mode = modes[c];
     if (mode == CH_FMN) {                 // Demod_NFM::processBlockNCO, demod_nfm.cpp:225-257
         PllState v = st[c].pll;
-        pll_run(x, y, n, pc, v);
+        pll_run(x, y, n, pc, v, frame);
         st[c].pll = v;
     } else if (mode == CH_AM) {           // Demod_AM::processBlockFiltered, demod_am.cpp:40-59
         double d = st[c].am_dc_last;
@@ -241,13 +241,20 @@ int pebble_channelizer_set_agc_threshold(pebble_channelizer_t *h, int threshold)
     h->agc_threshold = threshold;
     return 0;
 }
+// Raw device samples into every channel (normalizeIQ fused into the front end's load; see "Device sample formats").
+int pebble_channelizer_set_input_format(pebble_channelizer_t *h, int fmt, int order, double user_gain, double norm_gain) {
+    if (!h) return PEBBLE_ERR_ARG;
+    return pebble_downconvert_set_input_format(h->dc, fmt, order, user_gain, norm_gain);
+}
+// 1: polyphase-DFT front end (channels on the grid in_rate / 2^S), 0: one down-converter per channel, -1: no call yet
+int pebble_channelizer_front_path(const pebble_channelizer_t *h) { return h ? pebble_downconvert_batch_path(h->dc) : PEBBLE_ERR_ARG; }
 int pebble_channelizer_out_count(const pebble_channelizer_t *h, int n) {
     if (!h || n < 0) return PEBBLE_ERR_ARG;
     return n >> h->S;
 }
 
 // Decimated streams only (step 1), [channel][n >> S] rows `out_stride` cpx apart.
-int pebble_channelizer_downconvert_device(pebble_channelizer_t *h, int n, const double *d_in, double *d_out,
+int pebble_channelizer_downconvert_device(pebble_channelizer_t *h, int n, const void *d_in, double *d_out,
                                           long long out_stride, void *stream) {
     if (!h) return PEBBLE_ERR_ARG;
     return pebble_downconvert_process_channels_device(h->dc, n, d_in, d_out, out_stride, stream);
@@ -255,7 +262,7 @@ int pebble_channelizer_downconvert_device(pebble_channelizer_t *h, int n, const 
 
 // Whole chain. n must make (n >> S) a multiple of framesPerBuffer (2048), so that every call yields whole receiver
 // frames (receiver.cpp:922-931) for every channel; returns the demodulated samples per channel (= n >> S).
-int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const double *d_in, double *d_out, long long out_stride,
+int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void *d_in, double *d_out, long long out_stride,
                                       void *stream_v) {
     if (!h || n < 0 || (n && (!d_in || !d_out))) { pebble::set_error("channelizer: bad argument"); return PEBBLE_ERR_ARG; }
     if (n == 0) return 0;
@@ -289,6 +296,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
     pebble_fastfir_set_fused_scale(h->bp, gain, agc_gain);
     const int frames = nd / h->fpb;
     const int parts = h->parts < frames ? h->parts : frames;
+    const size_t bps = (size_t)pebble_downconvert_input_bytes_per_sample(h->dc);
     // `tail` starts after everything already queued on the caller's stream (mode upload, the consumer of the last output)
     PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
@@ -298,7 +306,8 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
         const int pd = (f1 - f0) * h->fpb;             // decimated samples of this part
         const long long pos = (long long)f0 * h->fpb;  // its column in the work rows and in the output rows
         const long long pn = (long long)pd << h->S;
-        r = pebble_downconvert_process_channels_device(h->dc, (int)pn, d_in + 2 * (pos << h->S), (double *)(h->d_dec + pos), row, st);   // receiver.cpp:908
+        r = pebble_downconvert_process_channels_device(h->dc, (int)pn, (const char *)d_in + bps * (size_t)(pos << h->S),
+                                                       (double *)(h->d_dec + pos), row, st);   // receiver.cpp:908
         if (r < 0) return r;
         r = pebble_fastfir_process_batch_device(h->bp, pd, (const double *)(h->d_dec + pos), row, (double *)(h->d_bp + pos), row, st);   // :950
         if (r < 0) return r;
@@ -306,7 +315,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const doub
         PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
         PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
         chan_demod_kernel<<<h->slots / 32, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->d_order,
-                                                            h->slots, h->pll, (double)0.9999f, h->d_state);                                 // :987
+                                                            h->slots, h->pll, (double)0.9999f, h->d_state, h->fpb);                         // :987
         int gx = (pd + 255) / 256;
         if (gx > 64) gx = 64;
         chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, h->tail>>>(h->d_hist[h->hcur], h->d_tmp + pos, row, pd, h->d_taps, h->ntaps_am,

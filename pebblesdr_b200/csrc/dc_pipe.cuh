@@ -18,6 +18,7 @@
 // Reference: downconvert.cpp:281-287 (oscillator), 519-535 (CIC3), 341-496 (half-bands); same arithmetic as dc_cic.cuh.
 #pragma once
 #include "dc_cic.cuh"
+#include "dc_input.cuh"
 
 #if defined(__CUDACC__)
 // TJ = tiles a job of a late stage waits for (32 = a full warp; 16 halves the late stages' buffers: 3 CTAs per SM)
@@ -102,7 +103,9 @@ __device__ __forceinline__ void dc_pipe_stages(cpx *smem, int warp, int p, int N
     }
 }
 
-template <int C, int TJ, int T, int MINB, int L1, int L2, int L3, int L4, int L5, int L6>
+// FMT = sample format of call.in (dc_input.cuh): the raw device samples are converted in registers where the mix consumes
+// them; the normalizeIQ scale rides on call.r_inf (the oscillator seed's amplitude).
+template <int C, int TJ, int T, int MINB, int L1, int L2, int L3, int L4, int L5, int L6, int FMT = PB_IQ_CPX>
 __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restrict__ ch, const DcCall call) {
     using G = DcPipe<C, TJ, T, L1, L2, L3, L4, L5, L6>;
     constexpr int K = C / (2 * T), NS = 2 * K, S = 7;
@@ -119,8 +122,11 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
     const volatile DcSeg *si = &seg_info;
     const unsigned bar_addr = (unsigned)__cvta_generic_to_shared(&phase_bar);
     if (tid == 0) asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(bar_addr), "r"(T));
-    const cpx *in_t;
-    cpx nx0[K], nx1[K], nxh0 = cpx_make(0.0, 0.0), nxh1 = cpx_make(0.0, 0.0);
+    constexpr int SB = IqRaw<FMT, K>::BYTES;   // bytes per input sample
+    const char *in_t;
+    IqRaw<FMT, K> raw;
+    IqHalo<FMT> rawh;
+    rawh.zero();
     const bool halo_lane = (tid & 31) == 0;
     {
         const long long seg = blockIdx.x;
@@ -161,14 +167,11 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
             }
             seg_info.b_state = b_state;
         }
-        in_t = call.in + start + NS * tid;
+        in_t = reinterpret_cast<const char *>(call.in) + (start + NS * tid) * SB;
         const int len0 = (int)(total < C ? total : C);
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            nx0[k] = nx1[k] = cpx_make(0.0, 0.0);
-            if (NS * tid < len0) dc_ld256(in_t + 2 * k, nx0[k], nx1[k]);
-        }
-        if (halo_lane && tid > 0 && NS * tid < len0) dc_ld256(in_t - 2, nxh0, nxh1);
+        raw.zero();
+        if (NS * tid < len0) raw.load(in_t);
+        if (halo_lane && tid > 0 && NS * tid < len0) rawh.load(in_t - 2 * SB);
     }
     int sl[K];   // slot of this thread's q-th CIC3 output inside half 0 of stage 1's arrays (even q -> even array)
 #pragma unroll
@@ -192,6 +195,10 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
                 seed = cpx_mul(seed, call.wchunk);
             }
             const cpx w1 = call.w1, w2 = cpx_mul(w1, w1);
+            cpx nx0[K], nx1[K], nxh0, nxh1;
+#pragma unroll
+            for (int k = 0; k < K; ++k) raw.get(k, nx0[k], nx1[k]);
+            rawh.get(nxh0, nxh1);
             if (full) {
                 dc_mix_cic<K, true>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, 0, false, cpx_make(0.0, 0.0), y, ml0, ml1);
             } else {
@@ -201,11 +208,10 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
             }
             // the samples of chunk p+1 are loaded INTO THE SAME REGISTERS as soon as the mix has consumed chunk p's: they
             // are in flight during the stage tiles and the barrier below (no second register set, no copies)
-            in_t += C;
+            in_t += C * SB;
             if (ci + 2 < N || (ci + 1 < N && NS * tid < len_last)) {
-#pragma unroll
-                for (int k = 0; k < K; ++k) dc_ld256(in_t + 2 * k, nx0[k], nx1[k]);
-                if (halo_lane) dc_ld256(in_t - 2, nxh0, nxh1);
+                raw.load(in_t);
+                if (halo_lane) rawh.load(in_t - 2 * SB);
             }
             if (full) {
 #pragma unroll

@@ -288,7 +288,7 @@ void *demod_am_expect_tiles(pebble_demod *h, int n, double *alpha) {
 
 void demod_am_cancel_tiles(pebble_demod *h) { h->am_pre_tiles = false; }
 
-int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough) {
+int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough, int frame) {
     if (passthrough) *passthrough = 0;
     if (n <= 0) return 0;
     if (h->mode == 0) {  // dmAM -> processBlockFiltered (demod.cpp:105-108)
@@ -319,7 +319,7 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         int r = demod_reserve(h, n);
         if (r < 0) return r;
         if (h->nfm_variant == 0) {
-            pll_kernel<<<1, 32, 0, st>>>(d_in, n, 0, 1, h->pll, h->d_pll, h->d_tmp);
+            pll_kernel<<<1, 32, 0, st>>>(d_in, n, 0, 1, h->pll, h->d_pll, h->d_tmp, frame);
             pebble::count_launch();
             PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
             return cfir_run_device(&h->nfm_lp, n, h->d_tmp, d_out, st);  // demod_nfm.cpp:255
@@ -405,13 +405,13 @@ int pebble_demod_is_passthrough(const pebble_demod_t *h) {
 }
 int pebble_demod_process_device(pebble_demod_t *h, int n, const double *d_in, double *d_out, void *stream) {
     if (!h || n < 0 || (n && (!d_in || !d_out))) return PEBBLE_ERR_ARG;
-    return demod_run_device(h, n, (const cpx *)d_in, (cpx *)d_out, (cudaStream_t)stream, nullptr);
+    return demod_run_device(h, n, (const cpx *)d_in, (cpx *)d_out, (cudaStream_t)stream, nullptr, 0);
 }
 int pebble_demod_process(pebble_demod_t *h, int n, const double *in, double *out) {
     if (!h || n < 0 || (n && (!in || !out))) return PEBBLE_ERR_ARG;
     if (n == 0) return 0;
     return host_roundtrip(h->stg, h->stream, n, in, out, [&](const cpx *di, cpx *dout, cudaStream_t st) {
-        return demod_run_device(h, n, di, dout, st, nullptr);
+        return demod_run_device(h, n, di, dout, st, nullptr, 0);
     });
 }
 }  // extern "C"

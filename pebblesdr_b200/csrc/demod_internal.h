@@ -23,7 +23,8 @@ int cfir_run_device(pebble_cfir *f, int n, const cpx *d_in, cpx *d_out, cudaStre
 struct pebble_agc;
 struct pebble_demod;
 // device-pointer forms used by the fused receiver chain
-int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough);
+// frame: samples per reference Demod::processBlock call when n covers several (the receiver chain: framesPerBuffer); 0 = n
+int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough, int frame);
 int agc_run_device(pebble_agc *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st);
 void *demod_am_expect_tiles(pebble_demod *h, int n, double *alpha);
 // fastfir.cu: the next process call also writes, per 1024-sample output block b, tile_map[b] = {alpha^1024,

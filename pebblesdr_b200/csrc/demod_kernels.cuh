@@ -294,33 +294,40 @@ __device__ __forceinline__ void pll_step(const cpx xi, cpx &yo, const PllConst &
 // independent and issued back to back, so the (uncoalesced, one-row-per-thread) memory latency is paid once per block
 // instead of once per sample.
 #define PB_SERIAL_BLK 16
-__device__ __forceinline__ void pll_run(const cpx *__restrict__ x, cpx *__restrict__ y, int n, const PllConst c, PllState &v) {
-    int i = 0;
-    for (; i + PB_SERIAL_BLK <= n; i += PB_SERIAL_BLK) {
-        cpx xs[PB_SERIAL_BLK];
+// `frame`: the reference calls processBlockNCO once per receiver frame (framesPerBuffer samples, receiver.cpp:987) and wraps
+// the float phase with fmod at the END of each call (demod_nfm.cpp:252); between wraps the phase keeps growing and the float
+// rounding of the accumulation grows with it, so the wrap positions are part of the arithmetic. frame <= 0: one wrap at n.
+__device__ __forceinline__ void pll_run(const cpx *__restrict__ x, cpx *__restrict__ y, int n, const PllConst c, PllState &v, int frame) {
+    if (frame <= 0) frame = n;
+    for (int f0 = 0; f0 < n; f0 += frame) {
+        const int f1 = f0 + frame < n ? f0 + frame : n;
+        int i = f0;
+        for (; i + PB_SERIAL_BLK <= f1; i += PB_SERIAL_BLK) {
+            cpx xs[PB_SERIAL_BLK];
 #pragma unroll
-        for (int j = 0; j < PB_SERIAL_BLK; ++j) xs[j] = x[i + j];
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) xs[j] = x[i + j];
 #pragma unroll
-        for (int j = 0; j < PB_SERIAL_BLK; ++j) {
-            cpx yo;
-            pll_step(xs[j], yo, c, v);
-            y[i + j] = yo;
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+                cpx yo;
+                pll_step(xs[j], yo, c, v);
+                y[i + j] = yo;
+            }
         }
+        for (; i < f1; ++i) {
+            cpx yo;
+            pll_step(x[i], yo, c, v);
+            y[i] = yo;
+        }
+        v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
     }
-    for (; i < n; ++i) {
-        cpx yo;
-        pll_step(x[i], yo, c, v);
-        y[i] = yo;
-    }
-    v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
 }
 // one thread per stream; stream s occupies in[s*stride .. s*stride + n)
 static __global__ void pll_kernel(const cpx *__restrict__ in, int n, long long stride, int nstreams, PllConst c,
-                                  PllState *__restrict__ st, cpx *__restrict__ out) {
+                                  PllState *__restrict__ st, cpx *__restrict__ out, int frame) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= nstreams) return;
     PllState v = st[s];
-    pll_run(in + (long long)s * stride, out + (long long)s * stride, n, c, v);
+    pll_run(in + (long long)s * stride, out + (long long)s * stride, n, c, v, frame);
     st[s] = v;
 }
 

@@ -4,6 +4,7 @@
 #include "dc_pipe.cuh"
 #include "host_design.h"
 #include "hb_coefs.h"
+#include "chz_poly.h"
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -29,7 +30,14 @@ struct pebble_downconvert {
     DcChan *d_chans = nullptr;
     cpx *d_cstate[2] = {nullptr, nullptr};
     int ccur = 0;
+    ChzPoly *poly = nullptr;        // polyphase-DFT front end (chz_poly.cu) when the channels sit on the grid fs / 2^S
+    int batch_path = -1;            // -1 undecided, 0 per-channel kernel, 1 polyphase: fixed by the first call of a stream
     const void *fn_set = nullptr;
+    // device sample format of `in` (DeviceInterfaceBase::normalizeIQ): see dc_input.cuh
+    int in_fmt = PB_IQ_CPX, in_order = 0;
+    double user_gain = 1.0, norm_gain = 1.0, in_scale = 1.0;
+    cpx *d_conv = nullptr; size_t conv_cap = 0;   // CPX scratch of the un-fused path
+    bool strict_lengths = false;                  // refuse calls the reference would not filter (downconvert.cpp:362-363)
     cudaStream_t stream;    // for the host-pointer entry point
     pebble::Staging stg;
 };
@@ -69,7 +77,9 @@ static const void *dc_pick_kernel(int C, int front, const DcChain &ch, bool *cic
 }
 
 // The fully compile-time, chunk-pipelined kernel (dc_pipe.cuh) for the 7-stage chains it is instantiated for.
-static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem, int *threads) {
+// fmt != PB_IQ_CPX: only the default instantiation converts raw device samples in its load stage; nullptr otherwise (the
+// caller then converts into a CPX scratch buffer first).
+static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem, int *threads, int fmt = PB_IQ_CPX) {
     if (getenv("PEBBLE_DC_NOPIPE") || getenv("PEBBLE_DC_NOCIC") || getenv("PEBBLE_DC_GENERIC")) return nullptr;
     if (ch.nstages != 7 || ch.st[0].len != 3) return nullptr;
     const int l[6] = {ch.st[1].len, ch.st[2].len, ch.st[3].len, ch.st[4].len, ch.st[5].len, ch.st[6].len};
@@ -77,6 +87,17 @@ static const void *dc_pick_pipe(int C, const DcChain &ch, size_t *smem, int *thr
     if (l[0] == 11 && l[1] == 11 && l[2] == 11 && l[3] == 11 && l[4] == 15 && l[5] == 27) {   // 10 MSPS / 15 kHz: BASELINE config 2
         const int minb = getenv("PEBBLE_DC_MINB") ? atoi(getenv("PEBBLE_DC_MINB")) : 3;
         const int thr = getenv("PEBBLE_DC_THREADS") ? atoi(getenv("PEBBLE_DC_THREADS")) : 256;
+        if (fmt != PB_IQ_CPX) {
+            if (C != 1024) return nullptr;
+            *smem = sizeof(cpx) * DcPipe<1024, 16, 256, 11, 11, 11, 11, 15, 27>::total();
+            switch (fmt) {
+                case PB_IQ_CS16: return (const void *)dc_pipe_kernel<1024, 16, 256, 3, 11, 11, 11, 11, 15, 27, PB_IQ_CS16>;
+                case PB_IQ_CU8: return (const void *)dc_pipe_kernel<1024, 16, 256, 3, 11, 11, 11, 11, 15, 27, PB_IQ_CU8>;
+                case PB_IQ_CS8: return (const void *)dc_pipe_kernel<1024, 16, 256, 3, 11, 11, 11, 11, 15, 27, PB_IQ_CS8>;
+                case PB_IQ_CF32: return (const void *)dc_pipe_kernel<1024, 16, 256, 3, 11, 11, 11, 11, 15, 27, PB_IQ_CF32>;
+                default: return nullptr;
+            }
+        }
         if (C == 2048) { *smem = sizeof(cpx) * DcPipe<2048, 32, 256, 11, 11, 11, 11, 15, 27>::total(); return (const void *)dc_pipe_kernel<2048, 32, 256, 2, 11, 11, 11, 11, 15, 27>; }
         if (C == 1024 && thr == 128) {
             *threads = 128;
@@ -140,7 +161,8 @@ void pebble_downconvert_destroy(pebble_downconvert_t *h) {
     if (h->d_state[0]) cudaFree(h->d_state[0]);
     if (h->d_state[1]) cudaFree(h->d_state[1]);
     if (h->stream) cudaStreamDestroy(h->stream);
-    cudaFree(h->d_chans); cudaFree(h->d_cstate[0]); cudaFree(h->d_cstate[1]);
+    cudaFree(h->d_chans); cudaFree(h->d_cstate[0]); cudaFree(h->d_cstate[1]); cudaFree(h->d_conv);
+    chz_poly_destroy(h->poly);
     h->stg.release();
     delete h;
 }
@@ -183,6 +205,8 @@ static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, 
         h->nco_freq = -h->nco_freq + h->cw_offset;
         dc_update_osc(h);
         for (int k = 0; k < h->nch; ++k) dc_chan_set_freq(h, k);
+        if (h->poly) chz_poly_invalidate(h->poly);
+        h->batch_path = -1;
         if (h->nch) {
             const size_t cb = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX * (size_t)h->nch;
             cudaMemset(h->d_cstate[0], 0, cb);
@@ -211,6 +235,20 @@ int pebble_downconvert_plan(double in_rate, double max_bw, int simple, int *lens
     if (out_rate) *out_rate = r;
     for (int i = 0; i < (int)v.size() && i < max && lens; ++i) lens[i] = v[i];
     return (int)v.size();
+}
+// Host-only: the cascade SetDataRate plans for (in_rate, max_bw) as one decimate-by-2^S FIR, y[n] = sum_T h[T] x[2^S n + c - T]
+// (the polyphase channelizer's prototype filter). Writes min(len, max) taps, *c_out = c, returns len.
+int pebble_downconvert_composite_response(double in_rate, double max_bw, int simple, double *h, int max, int *c_out) {
+    std::vector<int> lens;
+    pebble_host::dc_plan(in_rate, max_bw, simple != 0, lens);
+    static thread_local DcChain tmp;
+    pebble_host::dc_fill_chain(tmp, lens);
+    std::vector<double> hv;
+    int c = 0;
+    const int len = pebble_host::dc_composite(tmp, hv, c);
+    if (c_out) *c_out = c;
+    for (int i = 0; i < len && i < max && h; ++i) h[i] = hv[i];
+    return len;
 }
 int pebble_downconvert_num_stages(const pebble_downconvert_t *h) { return h ? h->chain.nstages : PEBBLE_ERR_ARG; }
 int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, int max) {
@@ -244,14 +282,141 @@ __global__ void __launch_bounds__(256) dc_mix_kernel(const DcChain *__restrict__
     }
 }
 
+// DeviceInterfaceBase::normalizeIQ, block forms (pebblelib/deviceinterfacebase.cpp:648-878): out = code * scale with
+// the reference's operation order, so the result is bit-identical for every code. 4 samples per thread.
+template <int FMT>
+__global__ void __launch_bounds__(256) iq_convert_kernel(const void *__restrict__ in, cpx *__restrict__ out, long long n, int order,
+                                                         double scale) {
+    const long long i0 = ((long long)blockIdx.x * 256 + threadIdx.x) * 4;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const long long i = i0 + k;
+        if (i >= n) return;
+        double I, Q;
+        if (FMT == PB_IQ_CS16) { const short2 v = ((const short2 *)in)[i]; I = (double)v.x; Q = (double)v.y; }
+        else if (FMT == PB_IQ_CU8) { const uchar2 v = ((const uchar2 *)in)[i]; I = (double)v.x - 128.0; Q = (double)v.y - 128.0; }
+        else if (FMT == PB_IQ_CS8) { const char2 v = ((const char2 *)in)[i]; I = (double)v.x; Q = (double)v.y; }
+        else if (FMT == PB_IQ_CF32) { const float2 v = ((const float2 *)in)[i]; I = (double)v.x; Q = (double)v.y; }
+        else { const cpx v = ((const cpx *)in)[i]; I = v.x; Q = v.y; }
+        cpx o;
+        switch (order) {   // DeviceInterface::IQOrder (device_interfaces.h:140-145)
+            case 0: o = cpx_make(__dmul_rn(I, scale), __dmul_rn(Q, scale)); break;
+            case 1: o = cpx_make(__dmul_rn(Q, scale), __dmul_rn(I, scale)); break;
+            case 2: o.x = __dmul_rn(I, scale); o.y = o.x; break;
+            default: o.y = __dmul_rn(Q, scale); o.x = o.y; break;
+        }
+        out[i] = o;
+    }
+}
+
+// scale exactly as the reference forms it (left to right): 1/128.0 * user * norm, 1/32768.0 * user * norm, user * norm
+static double iq_scale(int fmt, double user_gain, double norm_gain) {
+    if (fmt == PB_IQ_CU8 || fmt == PB_IQ_CS8) return 1 / 128.0 * user_gain * norm_gain;
+    if (fmt == PB_IQ_CS16) return 1 / 32768.0 * user_gain * norm_gain;
+    return user_gain * norm_gain;
+}
+
+static int iq_convert_launch(int fmt, int order, double scale, long long n, const void *d_in, cpx *d_out, cudaStream_t st) {
+    const unsigned blocks = (unsigned)((n + 1023) / 1024);
+    switch (fmt) {
+        case PB_IQ_CPX: iq_convert_kernel<PB_IQ_CPX><<<blocks, 256, 0, st>>>(d_in, d_out, n, order, scale); break;
+        case PB_IQ_CS16: iq_convert_kernel<PB_IQ_CS16><<<blocks, 256, 0, st>>>(d_in, d_out, n, order, scale); break;
+        case PB_IQ_CU8: iq_convert_kernel<PB_IQ_CU8><<<blocks, 256, 0, st>>>(d_in, d_out, n, order, scale); break;
+        case PB_IQ_CS8: iq_convert_kernel<PB_IQ_CS8><<<blocks, 256, 0, st>>>(d_in, d_out, n, order, scale); break;
+        case PB_IQ_CF32: iq_convert_kernel<PB_IQ_CF32><<<blocks, 256, 0, st>>>(d_in, d_out, n, order, scale); break;
+        default: pebble::set_error("normalize_iq: unknown format %d", fmt); return PEBBLE_ERR_ARG;
+    }
+    pebble::count_launch();
+    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    return 0;
+}
+
 extern "C" {
 
-int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+int pebble_iq_bytes_per_sample(int fmt) { return (fmt < 0 || fmt > PB_IQ_CF32) ? PEBBLE_ERR_ARG : iq_bytes_per_sample(fmt); }
+
+int pebble_normalize_iq_device(int fmt, int order, double user_gain, double norm_gain, int reverse, long long n, const void *d_in,
+                               double *d_out, void *stream) {
+    if (fmt < 0 || fmt > PB_IQ_CF32 || order < 0 || order > 3 || n < 0 || (n && (!d_in || !d_out))) {
+        pebble::set_error("normalize_iq: bad argument");
+        return PEBBLE_ERR_ARG;
+    }
+    if (n == 0) return 0;
+    if (reverse && order < 2) order ^= 1;   // deviceinterfacebase.cpp:653-657
+    return iq_convert_launch(fmt, order, iq_scale(fmt, user_gain, norm_gain), n, d_in, (cpx *)d_out, (cudaStream_t)stream);
+}
+
+int pebble_normalize_iq(int fmt, int order, double user_gain, double norm_gain, int reverse, long long n, const void *in, double *out) {
+    if (fmt < 0 || fmt > PB_IQ_CF32 || n < 0 || (n && (!in || !out))) { pebble::set_error("normalize_iq: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    void *d_in = nullptr; double *d_out = nullptr;
+    const size_t bi = (size_t)n * iq_bytes_per_sample(fmt), bo = (size_t)n * sizeof(cpx);
+    PB_CUDA(cudaMalloc(&d_in, bi), PEBBLE_ERR_CUDA);
+    if (!pebble::cuda_ok(cudaMalloc(&d_out, bo), "cudaMalloc")) { cudaFree(d_in); return PEBBLE_ERR_CUDA; }
+    int r = PEBBLE_ERR_CUDA;
+    if (pebble::cuda_ok(cudaMemcpy(d_in, in, bi, cudaMemcpyHostToDevice), "cudaMemcpy")) {
+        r = pebble_normalize_iq_device(fmt, order, user_gain, norm_gain, reverse, n, d_in, d_out, nullptr);
+        if (r == 0 && !pebble::cuda_ok(cudaMemcpy(out, d_out, bo, cudaMemcpyDeviceToHost), "cudaMemcpy")) r = PEBBLE_ERR_CUDA;
+    }
+    cudaFree(d_in); cudaFree(d_out);
+    return r;
+}
+
+int pebble_downconvert_set_input_format(pebble_downconvert_t *h, int fmt, int order, double user_gain, double norm_gain) {
+    if (!h || fmt < 0 || fmt > PB_IQ_CF32 || order < 0 || order > 3) { pebble::set_error("downconvert: bad input format"); return PEBBLE_ERR_ARG; }
+    h->in_fmt = fmt; h->in_order = order; h->user_gain = user_gain; h->norm_gain = norm_gain;
+    h->in_scale = iq_scale(fmt, user_gain, norm_gain);
+    return 0;
+}
+int pebble_downconvert_set_strict_lengths(pebble_downconvert_t *h, int on) {
+    if (!h) return PEBBLE_ERR_ARG;
+    h->strict_lengths = on != 0;
+    return 0;
+}
+int pebble_downconvert_input_bytes_per_sample(const pebble_downconvert_t *h) { return h ? iq_bytes_per_sample(h->in_fmt) : PEBBLE_ERR_ARG; }
+
+int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const void *d_in_v, double *d_out,
                                       void *stream_v) {
-    if (!h || n < 0 || (n && (!d_in || !d_out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
+    if (!h || n < 0 || (n && (!d_in_v || !d_out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
     if (n == 0) return 0;
     cudaStream_t stream = (cudaStream_t)stream_v;
     const int S = h->chain.nstages;
+    if (h->strict_lengths) {
+        // the reference's per-stage precondition: a generic half-band needs InLength >= taps (downconvert.cpp:362-363),
+        // the unrolled 11-tap one reads pInData[0..17] unconditionally (:426-480)
+        for (int s = 0; s < S; ++s) {
+            const int need = h->chain.st[s].len == 11 ? 18 : h->chain.st[s].len == 3 ? 2 : h->chain.st[s].len;
+            if ((n >> s) < need) {
+                pebble::set_error("downconvert: stage %d (%d taps) would receive %d samples (strict lengths)", s, h->chain.st[s].len, n >> s);
+                return PEBBLE_ERR_ARG;
+            }
+        }
+    }
+    // Raw device samples: fused into the load stage where the chain has such a kernel (dc_pipe_kernel<..., FMT>, IQ order);
+    // otherwise normalizeIQ runs as its own kernel into a CPX scratch buffer and the chain reads that.
+    const double *d_in = (const double *)d_in_v;
+    int fused_fmt = PB_IQ_CPX;
+    double fused_scale = 1.0;
+    if (h->in_fmt != PB_IQ_CPX || h->in_order != 0 || h->in_scale != 1.0) {
+        size_t sm = 0; int th = 0;
+        const bool can_fuse = h->in_order == 0 && S > 0 && !(n & ((1 << S) - 1)) &&
+                              (h->in_fmt == PB_IQ_CPX ? dc_pick_pipe(h->chunk, h->chain, &sm, &th) != nullptr
+                                                      : dc_pick_pipe(h->chunk, h->chain, &sm, &th, h->in_fmt) != nullptr);
+        if (can_fuse) {
+            fused_fmt = h->in_fmt;
+            fused_scale = h->in_scale;
+        } else {
+            if ((size_t)n > h->conv_cap) {
+                PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+                cudaFree(h->d_conv); h->d_conv = nullptr; h->conv_cap = 0;
+                PB_CUDA(cudaMalloc(&h->d_conv, sizeof(cpx) * (size_t)n), PEBBLE_ERR_CUDA);
+                h->conv_cap = (size_t)n;
+            }
+            const int r = iq_convert_launch(h->in_fmt, h->in_order, h->in_scale, n, d_in_v, h->d_conv, stream);
+            if (r < 0) return r;
+            d_in = (const double *)h->d_conv;
+        }
+    }
     if (n & ((1 << S) - 1)) {
         pebble::set_error("downconvert: n=%d is not a multiple of 2^%d", n, S);
         return PEBBLE_ERR_ARG;
@@ -287,7 +452,7 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
         call.nch = 1;
         call.state_stride = 0;
         call.out_stride = 0;
-        call.w1 = h->chain.w1; call.wchunk = h->chain.wchunk; call.r_inf = h->chain.r_inf;
+        call.w1 = h->chain.w1; call.wchunk = h->chain.wchunk; call.r_inf = h->chain.r_inf * fused_scale;
         call.turn_hi = h->chain.turn_hi; call.turn_lo = h->chain.turn_lo;
         bool cic = false;
         const void *fn = dc_pick_kernel(C, call.front, h->chain, &cic);
@@ -296,7 +461,7 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
                                (cic ? 2 * dc_stage_arr(h->chain.st[0], C) : 0)) * sizeof(cpx);
         size_t smem_pipe = 0;
         int threads = PB_DC_THREADS;
-        if (const void *pf = dc_pick_pipe(C, h->chain, &smem_pipe, &threads)) { fn = pf; smem = smem_pipe; }
+        if (const void *pf = dc_pick_pipe(C, h->chain, &smem_pipe, &threads, fused_fmt)) { fn = pf; smem = smem_pipe; }
         if (smem > h->smem_set || fn != h->fn_set) {
             PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
             h->smem_set = smem;
@@ -326,11 +491,11 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const doub
     return n >> S;
 }
 
-int pebble_downconvert_process(pebble_downconvert_t *h, int n, const double *in, double *out) {
+int pebble_downconvert_process(pebble_downconvert_t *h, int n, const void *in, double *out) {
     if (!h || n < 0 || (n && (!in || !out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
     if (n == 0) return 0;
     const int S = h->chain.nstages;
-    const size_t bi = (size_t)n * sizeof(cpx), bo = (size_t)(n >> S) * sizeof(cpx);
+    const size_t bi = (size_t)n * iq_bytes_per_sample(h->in_fmt), bo = (size_t)(n >> S) * sizeof(cpx);
     if (!h->stg.reserve(bi, bo)) return PEBBLE_ERR_CUDA;
     memcpy(h->stg.h_in, in, bi);
     PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
@@ -381,6 +546,9 @@ int pebble_downconvert_set_channels(pebble_downconvert_t *h, int nch) {
         PB_CUDA(cudaMemset(h->d_cstate[b], 0, cb), PEBBLE_ERR_CUDA);
     }
     h->nch = nch; h->ccur = 0;
+    if (!h->poly) h->poly = chz_poly_create();
+    chz_poly_invalidate(h->poly);
+    h->batch_path = -1;
     h->chans.assign(nch, DcChan());
     h->chan_freq.assign(nch, 0.0);
     for (int k = 0; k < nch; ++k) {
@@ -390,21 +558,60 @@ int pebble_downconvert_set_channels(pebble_downconvert_t *h, int nch) {
     h->stream_pos = 0;
     return 0;
 }
+int pebble_downconvert_batch_path(const pebble_downconvert_t *h) { return h ? h->batch_path : PEBBLE_ERR_ARG; }
 int pebble_downconvert_set_channel_frequency(pebble_downconvert_t *h, int ch, double f) {
     if (!h || ch < 0 || ch >= h->nch) return PEBBLE_ERR_ARG;
     h->chan_freq[ch] = -f + h->cw_offset;   // downconvert.cpp:105-108; the phase is NOT reset
     dc_chan_set_freq(h, ch);
     return 0;
 }
-int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, const double *d_in, double *d_out,
+int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, const void *d_in_v, double *d_out,
                                                long long out_stride, void *stream_v) {
-    if (!h || n < 0 || (n && (!d_in || !d_out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
+    if (!h || n < 0 || (n && (!d_in_v || !d_out))) { pebble::set_error("downconvert: bad argument"); return PEBBLE_ERR_ARG; }
     if (h->nch < 1) { pebble::set_error("downconvert: set_channels not called"); return PEBBLE_ERR_STATE; }
     if (n == 0) return 0;
     cudaStream_t stream = (cudaStream_t)stream_v;
     const int S = h->chain.nstages, C = h->chunk;
     if (n & ((1 << S) - 1)) { pebble::set_error("downconvert: n=%d is not a multiple of 2^%d", n, S); return PEBBLE_ERR_ARG; }
     if (out_stride < (n >> S)) { pebble::set_error("downconvert: out_stride smaller than the output count"); return PEBBLE_ERR_ARG; }
+    // ---- uniform channel grid: ONE mix + polyphase FIR + D-point DFT for all channels (chz_poly.cu) ----------------------
+    if (h->in_order == 0 && h->batch_path != 0) {
+        const int ok = chz_poly_prepare(h->poly, h->chain, h->chans);
+        if (ok < 0) return ok;
+        if (ok == 0 && h->batch_path == 1) {
+            pebble::set_error("downconvert: a channel was retuned off the fs/2^S grid mid-stream; the polyphase front end cannot "
+                              "follow (create the channelizer with PEBBLE_CHZ_DIRECT=1 for arbitrary retunes)");
+            return PEBBLE_ERR_STATE;
+        }
+        h->batch_path = ok;
+        if (ok == 1) {
+            if (h->dirty) {
+                PB_CUDA(cudaMemcpyAsync(h->d_chain, &h->chain, sizeof(DcChain), cudaMemcpyHostToDevice, stream), PEBBLE_ERR_CUDA);
+                h->dirty = false;
+            }
+            const int r = chz_poly_process(h->poly, h->chain, h->d_chain, h->chans, h->stream_pos, h->in_fmt, h->in_scale, n, d_in_v,
+                                           (cpx *)d_out, out_stride, stream);
+            if (r < 0) return r;
+            for (int k = 0; k < h->nch; ++k)
+                pebble_host::phase_advance(h->chans[k].phase_hi, h->chans[k].phase_lo, h->chans[k].turn_hi, h->chans[k].turn_lo, (uint64_t)n);
+            h->stream_pos += n;
+            return n >> S;
+        }
+    }
+    h->batch_path = 0;
+    // ---- per-channel kernel (dc_cic_kernel, batched): raw formats / IQ orders are converted into a CPX scratch first --------
+    const double *d_in = (const double *)d_in_v;
+    if (h->in_fmt != PB_IQ_CPX || h->in_order != 0 || h->in_scale != 1.0) {
+        if ((size_t)n > h->conv_cap) {
+            PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+            cudaFree(h->d_conv); h->d_conv = nullptr; h->conv_cap = 0;
+            PB_CUDA(cudaMalloc(&h->d_conv, sizeof(cpx) * (size_t)n), PEBBLE_ERR_CUDA);
+            h->conv_cap = (size_t)n;
+        }
+        const int rc = iq_convert_launch(h->in_fmt, h->in_order, h->in_scale, n, d_in_v, h->d_conv, stream);
+        if (rc < 0) return rc;
+        d_in = (const double *)h->d_conv;
+    }
     bool cic = false;
     const int front = h->front < S ? h->front : S;
     const void *fn = dc_pick_kernel(C, front, h->chain, &cic);

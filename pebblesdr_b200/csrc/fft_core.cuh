@@ -157,6 +157,17 @@ PB_HD void fft_pass(cpx *a, const cpx *tw, int tid, int nthreads) {
 // same P in the order NP-1..0 with INV=true. pos2freq/freq2pos give the digit-reversed slot <-> bin map.
 template <int N> struct FftPlan;
 
+template <> struct FftPlan<1024> {   // 16 x 8 x 8 (the polyphase channelizer's branch DFT, chz_poly.cu)
+    static constexpr int NP = 3, SH = 3 + 100 * 6, THREADS = 128;
+    template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
+        if (P == 0) fft_pass<1024, 16, 1024, INV, SH>(a, tw, tid, nt);
+        if (P == 1) fft_pass<1024, 8, 64, INV, SH>(a, tw, tid, nt);
+        if (P == 2) fft_pass<1024, 8, 8, INV, SH>(a, tw, tid, nt);
+    }
+    static PB_HD int pos2freq(int p) { return (p >> 6) + 16 * ((p >> 3) & 7) + 128 * (p & 7); }
+    static PB_HD int freq2pos(int f) { return ((f & 15) << 6) + (((f >> 4) & 7) << 3) + (f >> 7); }
+};
+
 template <> struct FftPlan<2048> {
     static constexpr int NP = 3, SH = 3 + 100 * 7, THREADS = 128;
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {

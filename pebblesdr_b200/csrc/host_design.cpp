@@ -107,6 +107,41 @@ void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads, int ch
     ch.inv_r_inf = 1.0 / r;
 }
 
+// The cascade as ONE decimate-by-2^S FIR. Stage s computes  y_s[n] = sum_t g_s[t] * x_s[2n + a_s - t]  with
+//   CIC3   (downconvert.cpp:519-535):  g = {.125, .375, .375, .125}, a = 1  (the newest sample used is x[2n+1])
+//   HB11   (downconvert.cpp:421-496):  g = H0..H10,                 a = 0
+//   HBgen  (downconvert.cpp:357-393):  g = coef[0..L-1] with the term of the OLDEST sample counted twice (finding F7:
+//                                      the accumulator is seeded with buf[i]*coef[0] and the loop starts at j = 0), a = 0
+// so  y[n] = sum_T h[T] * x[2^S n + c - T]  with  h = g_0 * (g_1 up 2) * (g_2 up 4) * ...  and  c = sum_s 2^s a_s.
+// Products are accumulated in binary128 and rounded once. Returns the length of h.
+int dc_composite(const DcChain &ch, std::vector<double> &h_out, int &c_out) {
+    std::vector<__float128> h(1, (__float128)1.0);
+    int c = 0;
+    for (int s = 0; s < ch.nstages; ++s) {
+        const DcStage &st = ch.st[s];
+        std::vector<__float128> g;
+        int a = 0;
+        if (st.type == PB_DC_CIC3) {
+            g = {(__float128)0.125, (__float128)0.375, (__float128)0.375, (__float128)0.125};
+            a = 1;
+        } else {
+            g.resize(st.len);
+            for (int t = 0; t < st.len; ++t) g[t] = (__float128)ch.coef[st.coef_off + (st.len - 1 - t)];
+            if (st.type == PB_DC_HBGEN) g[st.len - 1] += (__float128)ch.coef[st.coef_off];   // F7
+        }
+        const long long up = 1LL << s;
+        std::vector<__float128> nh(h.size() + (g.size() - 1) * (size_t)up, (__float128)0.0);
+        for (size_t t = 0; t < g.size(); ++t)
+            for (size_t T = 0; T < h.size(); ++T) nh[t * (size_t)up + T] += g[t] * h[T];
+        h.swap(nh);
+        c += (int)(up * a);
+    }
+    h_out.resize(h.size());
+    for (size_t i = 0; i < h.size(); ++i) h_out[i] = (double)h[i];
+    c_out = c;
+    return (int)h.size();
+}
+
 void phase_advance(uint64_t &hi, uint64_t &lo, uint64_t thi, uint64_t tlo, uint64_t k) {
     unsigned __int128 p = ((unsigned __int128)hi << 64) | lo;
     unsigned __int128 t = ((unsigned __int128)thi << 64) | tlo;

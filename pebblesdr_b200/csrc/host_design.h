@@ -16,6 +16,8 @@ void dc_fill_chain(DcChain &ch, const std::vector<int> &lens);
 // Oscillator constants for cos/sin of the NCO increment as the reference rounds them
 // (downconvert.cpp:108-110). `threads` is the CTA size and `chunk` the chunk length the step tables are built for.
 void dc_set_osc(DcChain &ch, double osc_cos, double osc_sin, int threads, int chunk);
+// Composite impulse response h and alignment c of the whole cascade:  y[n] = sum_T h[T] x[2^S n + c - T]  (host_design.cpp).
+int dc_composite(const DcChain &ch, std::vector<double> &h, int &c);
 // phase (0.128 turns) += k * turn
 void phase_advance(uint64_t &hi, uint64_t &lo, uint64_t thi, uint64_t tlo, uint64_t k);
 

@@ -121,6 +121,12 @@ int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold) {
     if (!h || !h->agc) return PEBBLE_ERR_STATE;
     return pebble_agc_set_mode(h->agc, mode, threshold);
 }
+// Device sample format of the IQ stream (DeviceInterfaceBase::normalizeIQ, deviceinterfacebase.cpp:648-878): the
+// conversion runs inside the down-converter's load stage, so `in` of the process calls holds raw device samples.
+int pebble_receiver_set_input_format(pebble_receiver_t *h, int fmt, int order, double user_gain, double norm_gain) {
+    if (!h) return PEBBLE_ERR_ARG;
+    return pebble_downconvert_set_input_format(h->dc, fmt, order, user_gain, norm_gain);
+}
 int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages) {
     if (!h) return PEBBLE_ERR_ARG;
     h->gain_stages = stages;
@@ -155,7 +161,7 @@ int pebble_receiver_out_count(const pebble_receiver_t *h, int n) {
     return (int)((((long long)h->fill + (n >> S)) / h->fpb) * h->fpb);
 }
 
-int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_in, double *d_out, void *stream_v) {
+int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in, double *d_out, void *stream_v) {
     if (!h || n < 0 || (n && !d_in)) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
     if (!h->agc || !h->demod) { pebble::set_error("receiver: set_data_rate not called"); return PEBBLE_ERR_STATE; }
     if (n == 0) return 0;
@@ -165,9 +171,10 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
     int r = rx_reserve(h, (size_t)h->fill + (size_t)ndec);
     if (r < 0) return r;
     // receiver.cpp:908 + 922-924: decimated samples are appended to m_sampleBuf
+    const size_t ev_entry = h->ev_used;   // roll-back point of the profiling events if a step fails (5 events per call)
     rx_mark(h, st);
     r = pebble_downconvert_process_device(h->dc, n, d_in, (double *)(h->d_frames + h->fill), st);
-    if (r < 0) return r;
+    if (r < 0) { h->ev_used = ev_entry; return r; }
     rx_mark(h, st);
     const int total = h->fill + ndec;
     const int nframes = total / h->fpb;
@@ -191,18 +198,24 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
             if (fastfir_am_aggregate_next(h->bp, tiles, alpha, nproc) != 0) demod_am_cancel_tiles(h->demod);
     }
     r = pebble_fastfir_process_device(h->bp, nproc, (const double *)h->d_frames, (double *)h->d_bp, st);  // receiver.cpp:950
-    if (r < 0) return r;
-    if (r != nproc) { pebble::set_error("receiver: FastFIR returned %d of %d", r, nproc); return PEBBLE_ERR_STATE; }
+    if (r != nproc) {
+        // the armed AM tile maps were never written: disarm them, and drop this call's profiling events
+        demod_am_cancel_tiles(h->demod);
+        if (h->profiling) h->ev_used = ev_entry;
+        if (r < 0) return r;
+        pebble::set_error("receiver: FastFIR returned %d of %d", r, nproc);
+        return PEBBLE_ERR_STATE;
+    }
     rx_mark(h, st);
     const cpx *next = h->d_bp;
     if (!fuse_agc) {  // receiver.cpp:983
         r = agc_run_device(h->agc, nproc, next, h->d_agc, st);
-        if (r < 0) return r;
+        if (r < 0) { if (h->profiling) h->ev_used = ev_entry; return r; }
         next = h->d_agc;
     }
     rx_mark(h, st);
-    r = demod_run_device(h->demod, nproc, next, (cpx *)d_out, st, nullptr);  // receiver.cpp:987
-    if (r < 0) return r;
+    r = demod_run_device(h->demod, nproc, next, (cpx *)d_out, st, nullptr, h->fpb);  // receiver.cpp:987, once per frame
+    if (r < 0) { demod_am_cancel_tiles(h->demod); if (h->profiling) h->ev_used = ev_entry; return r; }
     rx_mark(h, st);
     // keep the incomplete frame for the next call
     const int rem = total - nproc;
@@ -212,11 +225,11 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const double *d_
     return nproc;
 }
 
-int pebble_receiver_process(pebble_receiver_t *h, int n, const double *in, double *out) {
+int pebble_receiver_process(pebble_receiver_t *h, int n, const void *in, double *out) {
     if (!h || n < 0 || (n && !in)) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
     if (n == 0) return 0;
     const int k = pebble_receiver_out_count(h, n);
-    const size_t bi = sizeof(cpx) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
+    const size_t bi = (size_t)pebble_downconvert_input_bytes_per_sample(h->dc) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
     if (!h->stg.reserve(bi, bo)) return PEBBLE_ERR_CUDA;
     memcpy(h->stg.h_in, in, bi);
     PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
@@ -228,11 +241,11 @@ int pebble_receiver_process(pebble_receiver_t *h, int n, const double *in, doubl
     return r;
 }
 // Pinned-buffer form for end-to-end timing: `in`/`out` must be page-locked host memory (no extra memcpy).
-int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const double *in, double *out, void *stream_v) {
+int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const void *in, double *out, void *stream_v) {
     if (!h || n <= 0 || !in) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
     cudaStream_t st = (cudaStream_t)stream_v;
     const int k = pebble_receiver_out_count(h, n);
-    const size_t bi = sizeof(cpx) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
+    const size_t bi = (size_t)pebble_downconvert_input_bytes_per_sample(h->dc) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
     if (bi > h->pin_in_cap) {
         PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
         cudaFree(h->d_pin_in); h->d_pin_in = nullptr; h->pin_in_cap = 0;

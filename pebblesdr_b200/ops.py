@@ -39,6 +39,45 @@ def _stream_ptr():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+# Device sample formats (include/pebble_cuda.h PEBBLE_IQ_*; pebblelib/cpx.h:43-96): raw buffers hold interleaved I,Q
+IQ_CPX, IQ_CS16, IQ_CU8, IQ_CS8, IQ_CF32 = range(5)
+IQO_IQ, IQO_QI, IQO_IONLY, IQO_QONLY = range(4)
+_IQ_NP = {IQ_CPX: np.complex128, IQ_CS16: np.int16, IQ_CU8: np.uint8, IQ_CS8: np.int8, IQ_CF32: np.float32}
+
+
+def _raw_ptr(x, n, fmt):
+    """Pointer to n raw samples of format fmt: numpy array or torch tensor (CPU pinned or CUDA) of the matching
+    element type, 2 elements per sample (1 for complex128)."""
+    if fmt == IQ_CPX:
+        return _dev_ptr(x, n) if (torch is not None and isinstance(x, torch.Tensor)) else _host_ptr(x, n)
+    need = 2 * n
+    if torch is not None and isinstance(x, torch.Tensor):
+        tdt = {IQ_CS16: torch.int16, IQ_CU8: torch.uint8, IQ_CS8: torch.int8, IQ_CF32: torch.float32}[fmt]
+        if x.dtype != tdt or not x.is_contiguous() or x.numel() < need:
+            raise PebbleError("expected a contiguous torch %s tensor with >= %d elements" % (tdt, need))
+        return x.data_ptr()
+    if not isinstance(x, np.ndarray) or x.dtype != _IQ_NP[fmt] or not x.flags.c_contiguous or x.size < need:
+        raise PebbleError("expected a C-contiguous numpy %s array with >= %d elements" % (_IQ_NP[fmt].__name__, need))
+    return x.ctypes.data
+
+
+def normalizeIQ(fmt, raw, order=IQO_IQ, userIQGain=1.0, normalizeIQGain=1.0, reverse=False, out=None):
+    """DeviceInterfaceBase::normalizeIQ block forms (pebblelib/deviceinterfacebase.cpp:648-878) on the GPU.
+    raw: interleaved I,Q numpy array (host) or torch CUDA tensor (device); returns complex128 of the same kind."""
+    n = (raw.numel() if _is_cuda_tensor(raw) else raw.size) // (1 if fmt == IQ_CPX else 2)
+    if _is_cuda_tensor(raw):
+        if out is None:
+            out = torch.empty(n, dtype=torch.complex128, device=raw.device)
+        check(lib.pebble_normalize_iq_device(fmt, order, userIQGain, normalizeIQGain, int(bool(reverse)), n,
+                                             _raw_ptr(raw, n, fmt), _dev_ptr(out, n), _stream_ptr()), "normalizeIQ")
+        return out
+    if out is None:
+        out = np.empty(n, dtype=np.complex128)
+    check(lib.pebble_normalize_iq(fmt, order, userIQGain, normalizeIQGain, int(bool(reverse)), n, _raw_ptr(raw, n, fmt),
+                                  _host_ptr(out, n, True)), "normalizeIQ")
+    return out
+
+
 class _Handle:
     _destroy = None
 
@@ -105,6 +144,12 @@ class CDownConvert(_Handle):
 
     def __init__(self):
         super().__init__(lib.pebble_downconvert_create(), "CDownConvert")
+        self._fmt = IQ_CPX
+
+    def SetInputFormat(self, fmt, order=IQO_IQ, userIQGain=1.0, normalizeIQGain=1.0):
+        """ProcessData then takes raw device samples of this format (normalizeIQ fused into the mixer load)."""
+        check(lib.pebble_downconvert_set_input_format(self._h, fmt, order, userIQGain, normalizeIQGain), "SetInputFormat")
+        self._fmt = fmt
 
     def SetDataRate(self, InRate, MaxBW):
         return lib.pebble_downconvert_set_data_rate(self._h, InRate, MaxBW)
@@ -129,9 +174,9 @@ class CDownConvert(_Handle):
     def ProcessData(self, InLength, pInData, pOutData):
         nout = InLength >> self.NumStages()
         if _is_cuda_tensor(pInData):
-            return check(lib.pebble_downconvert_process_device(self._h, InLength, _dev_ptr(pInData, InLength),
+            return check(lib.pebble_downconvert_process_device(self._h, InLength, _raw_ptr(pInData, InLength, self._fmt),
                                                                _dev_ptr(pOutData, nout), _stream_ptr()), "ProcessData")
-        return check(lib.pebble_downconvert_process(self._h, InLength, _host_ptr(pInData, InLength),
+        return check(lib.pebble_downconvert_process(self._h, InLength, _raw_ptr(pInData, InLength, self._fmt),
                                                     _host_ptr(pOutData, nout, True)), "ProcessData")
 
     def GetState(self):
@@ -368,6 +413,12 @@ class Receiver(_Handle):
     def __init__(self, sampleRate, framesPerBuffer=2048):
         super().__init__(lib.pebble_receiver_create(float(sampleRate), int(framesPerBuffer)), "Receiver")
         self.framesPerBuffer = framesPerBuffer
+        self._fmt = IQ_CPX
+
+    def setInputFormat(self, fmt, order=IQO_IQ, userIQGain=1.0, normalizeIQGain=1.0):
+        """processIQData then takes raw device samples (DeviceInterfaceBase::normalizeIQ fused into the mixer load)."""
+        check(lib.pebble_receiver_set_input_format(self._h, fmt, order, userIQGain, normalizeIQGain), "setInputFormat")
+        self._fmt = fmt
 
     def setDataRate(self, maxBW):
         r = lib.pebble_receiver_set_data_rate(self._h, maxBW)
@@ -412,12 +463,12 @@ class Receiver(_Handle):
         if _is_cuda_tensor(inb):
             if out is None:
                 out = torch.empty(max(k, 1), dtype=torch.complex128, device=inb.device)
-            r = check(lib.pebble_receiver_process_device(self._h, numSamples, _dev_ptr(inb, numSamples),
+            r = check(lib.pebble_receiver_process_device(self._h, numSamples, _raw_ptr(inb, numSamples, self._fmt),
                                                          _dev_ptr(out, k), _stream_ptr()), "processIQData")
             return r, out
         if out is None:
             out = np.empty(max(k, 1), dtype=np.complex128)
-        r = check(lib.pebble_receiver_process(self._h, numSamples, _host_ptr(inb, numSamples), _host_ptr(out, k, True)),
+        r = check(lib.pebble_receiver_process(self._h, numSamples, _raw_ptr(inb, numSamples, self._fmt), _host_ptr(out, k, True)),
                   "processIQData")
         return r, out
 
@@ -436,6 +487,16 @@ class Channelizer(_Handle):
         self.nchannels = int(nchannels)
         self.outRate = lib.pebble_channelizer_out_rate(self._h)
         self.numStages = check(lib.pebble_channelizer_num_stages(self._h))
+        self._fmt = IQ_CPX
+
+    def setInputFormat(self, fmt, order=IQO_IQ, userIQGain=1.0, normalizeIQGain=1.0):
+        """The capture then holds raw device samples of this format (normalizeIQ fused into the front end's load)."""
+        check(lib.pebble_channelizer_set_input_format(self._h, fmt, order, userIQGain, normalizeIQGain), "setInputFormat")
+        self._fmt = fmt
+
+    def frontPath(self):
+        """1 = polyphase-DFT front end ran the last call (channels on the grid fs / 2^S), 0 = per-channel kernel, -1 = none yet."""
+        return lib.pebble_channelizer_front_path(self._h)
 
     def setFrequency(self, ch, freq):
         check(lib.pebble_channelizer_set_frequency(self._h, ch, freq), "setFrequency")
@@ -458,11 +519,11 @@ class Channelizer(_Handle):
     def downConvert(self, d_in, n, d_out):
         """d_out: [nchannels, >= n >> S] complex128 CUDA tensor (rows contiguous)."""
         assert d_out.dim() == 2 and d_out.shape[0] == self.nchannels and d_out.stride(1) == 1
-        return check(lib.pebble_channelizer_downconvert_device(self._h, n, _dev_ptr(d_in, n), d_out.data_ptr(),
+        return check(lib.pebble_channelizer_downconvert_device(self._h, n, _raw_ptr(d_in, n, self._fmt), d_out.data_ptr(),
                                                                d_out.stride(0), _stream_ptr()), "downConvert")
 
     def process(self, d_in, n, d_out):
         """d_out: [nchannels, >= n >> S] complex128 CUDA tensor. Returns demodulated samples per channel."""
         assert d_out.dim() == 2 and d_out.shape[0] == self.nchannels and d_out.stride(1) == 1
-        return check(lib.pebble_channelizer_process_device(self._h, n, _dev_ptr(d_in, n), d_out.data_ptr(),
+        return check(lib.pebble_channelizer_process_device(self._h, n, _raw_ptr(d_in, n, self._fmt), d_out.data_ptr(),
                                                            d_out.stride(0), _stream_ptr()), "process")

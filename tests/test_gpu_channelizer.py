@@ -85,3 +85,155 @@ def test_batched_downconvert_equals_single_channel_objects():
         one = torch.zeros(n >> 10, dtype=torch.complex128, device="cuda")
         assert dc.ProcessData(n, xd, one) == n >> 10
         assert rel_rms(out[k].cpu().numpy(), one.cpu().numpy()) <= 1e-13
+
+
+# ---- polyphase-DFT front end (channels on the grid fs / 2^S) ----------------------------------------------------------------
+GRID0, STEP = -30.69e6, 60e3       # BASELINE config 4: centre k = -30.69 MHz + k * 60 kHz, and 61.44 MHz / 1024 = 60 kHz
+
+
+def _ref12_channel(x, f):
+    """The COMPILED reference CDownConvert (MAX_DECSTAGES 12, oracle/build_ref.sh step 6) on one channel, 32768-sample calls."""
+    from oracle import ref_app
+    r = ref_app.CDownConvert12()
+    assert r.SetDataRate(FS, BW) == 60000.0
+    r.SetFrequency(f)
+    out = []
+    for i in range(0, len(x), 32768):
+        o = np.zeros(32, dtype=np.complex128)
+        assert r.ProcessData(32768, x[i:i + 32768], o) == 32
+        out.append(o)
+    return np.concatenate(out)
+
+
+def test_polyphase_front_end_vs_compiled_reference_per_channel():
+    """Grid channels: ONE mix + 1024-branch polyphase FIR + 1024-point DFT (chz_poly.cu) against the reference's own
+    CDownConvert run once per channel. 2^22 capture samples in ragged calls; every channel <= 1e-10 relative RMS."""
+    import torch
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    if not ref_app.dec12_available():
+        pytest.skip("oracle/_ref/libpebbleref_dec12.so not built")
+    ks = [0, 1, 2, 255, 511, 512, 513, 777, 1022, 1023]
+    freqs = [GRID0 + STEP * k for k in ks]
+    n = 1 << 22
+    x = _capture(n, freqs, seed=123)
+    xd = torch.from_numpy(x).cuda()
+    cz = pb.Channelizer(len(ks), FS, BW)
+    for i, f in enumerate(freqs):
+        cz.setFrequency(i, f)
+    nd = n >> 10
+    out = torch.zeros(len(ks), nd, dtype=torch.complex128, device="cuda")
+    pos = 0
+    for m in [1024 * 7, 1024 * 1, 1024 * 300, 1024 * 24, 1024 * 1000, n - 1024 * 1332]:   # shorter and longer than the filter memory
+        assert cz.downConvert(xd[pos:pos + m], m, out[:, pos >> 10:]) == m >> 10
+        pos += m
+    assert cz.frontPath() == 1
+    got = out.cpu().numpy()
+    for i, f in enumerate(freqs):
+        want = _ref12_channel(x, f)
+        assert rel_rms(got[i], want) <= 1e-10, (ks[i], rel_rms(got[i], want))
+
+
+def test_polyphase_equals_per_channel_kernel_and_raw_formats(monkeypatch):
+    """Same capture through the polyphase path and (PEBBLE_CHZ_DIRECT=1) the per-channel kernel; then the capture as
+    qint16 / quint8 raw samples through the polyphase path vs the converted capture."""
+    import torch
+    import pebblesdr_b200 as pb
+    ks = [3, 4, 100, 640, 1000]
+    freqs = [GRID0 + STEP * k for k in ks]
+    n = 1 << 21
+    x = _capture(n, freqs, seed=321)
+    xd = torch.from_numpy(x).cuda()
+
+    def run(fmt=None, src=None):
+        cz = pb.Channelizer(len(ks), FS, BW)
+        for i, f in enumerate(freqs):
+            cz.setFrequency(i, f)
+        if fmt is not None:
+            cz.setInputFormat(fmt)
+        o = torch.zeros(len(ks), n >> 10, dtype=torch.complex128, device="cuda")
+        half = n // 2
+        s = xd if src is None else src
+        per = 1 if fmt in (None, 0) else 2
+        assert cz.downConvert(s[:per * half], half, o[:, :half >> 10]) == half >> 10
+        assert cz.downConvert(s[per * half:], half, o[:, half >> 10:]) == half >> 10
+        return cz.frontPath(), o.cpu().numpy()
+
+    path, poly = run()
+    assert path == 1
+    monkeypatch.setenv("PEBBLE_CHZ_DIRECT", "1")
+    path, direct = run()
+    assert path == 0
+    monkeypatch.delenv("PEBBLE_CHZ_DIRECT")
+    for i in range(len(ks)):
+        assert rel_rms(poly[i], direct[i]) <= 1e-10, (ks[i], rel_rms(poly[i], direct[i]))
+    f2 = np.stack([x.real, x.imag], axis=1).reshape(-1)
+    for fmt, raw, scale in ((pb.IQ_CS16, np.round(f2 * 30000).astype(np.int16), 1 / 32768.0),
+                            (pb.IQ_CU8, (np.round(f2 * 120) + 128).astype(np.uint8), 1 / 128.0)):
+        path, got = run(fmt, torch.from_numpy(raw).cuda())
+        assert path == 1
+        conv = pb.normalizeIQ(fmt, raw)          # bit-exact normalizeIQ, then the same front end on CPX
+        xd_keep = xd
+        xd = torch.from_numpy(conv).cuda()
+        _, want = run()
+        xd = xd_keep
+        for i in range(len(ks)):
+            assert rel_rms(got[i], want[i]) <= 1e-12, (fmt, ks[i], rel_rms(got[i], want[i]))
+
+
+def test_channelizer_1024_channels_bench_shape_vs_oracle():
+    """BASELINE config 4 at full width: 1024 channels on the 60 kHz grid, the bench's launch shape (polyphase front end,
+    PEBBLE_CHZ_PARTS default, slot grouping by demodulator). 32 sampled channels incl. k = 0, 1, 511, 512, 1022, 1023 are
+    compared with the reference chain run once per channel: compiled CDownConvert (MAX_DECSTAGES 12) -> gain restore ->
+    compiled CFastFIR -> compiled AGC_OFF -> compiled Demod_AM / Demod_NFM (oracle/_ref). AM channels <= 1e-10; NBFM (float
+    PLL state) from sample 0: <= 1e-4 after a lock-time allowance of 1024 output samples (17 ms: acquisition amplifies 1e-16
+    input differences while the loop is unlocked), and <= 5e-2 inside it."""
+    import torch
+    import pebblesdr_b200 as pb
+    from oracle import ref, ref_app
+    if not (ref_app.dec12_available() and ref_app.available() and ref.available()):
+        pytest.skip("oracle/_ref not built")
+    nch, n = 1024, 1024 * 2048 * 2
+    freqs = [GRID0 + STEP * k for k in range(nch)]
+    rng = np.random.default_rng(7)
+    sample = sorted(set([0, 1, 511, 512, 1022, 1023] + [int(v) for v in rng.choice(nch, 26, replace=False)]))
+    # carriers only where they are checked (+ both neighbours of each, so adjacent-channel leakage is exercised)
+    lit = sorted(set(k2 for k in sample for k2 in (k - 1, k, k + 1) if 0 <= k2 < nch))
+    t = np.arange(n, dtype=np.float64)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.002
+    for k in lit:
+        f = freqs[k]
+        if k % 2 == 0:
+            ph = 2 * np.pi * (f / FS) * t + 5.0 * np.sin(2 * np.pi * (1000.0 / FS) * t)
+            x += (1.0 / 64) * np.exp(1j * ph)
+        else:
+            x += (1.0 / 64) * (1 + 0.5 * np.cos(2 * np.pi * (1000.0 / FS) * t)) * np.exp(2j * np.pi * (f / FS) * t)
+    x = np.ascontiguousarray(x)
+    cz = pb.Channelizer(nch, FS, BW)
+    cz.setFilter(-7500.0, 7500.0)
+    for k in range(nch):
+        cz.setFrequency(k, freqs[k])
+        cz.setDemodMode(k, 2 if k % 2 == 0 else 0)
+    nd = n >> 10
+    out = torch.zeros(nch, nd, dtype=torch.complex128, device="cuda")
+    assert cz.process(torch.from_numpy(x).cuda(), n, out) == nd
+    assert cz.frontPath() == 1
+    got = out.cpu().numpy()
+    gain = 10.0 ** ((10 * 2) / 20.0)
+    for k in sample:
+        dec = _ref12_channel(x, freqs[k]) * gain                      # receiver.cpp:908, 935-938
+        ff = ref.CFastFIR(); ff.SetupParameters(-7500.0, 7500.0, 0.0, 60000.0)
+        agc = ref_app.AGC(60000, 2048); agc.setAgcMode(0, 20)
+        dem = ref_app.Demod_NFM(60000, 2048) if k % 2 == 0 else ref_app.Demod_AM(60000, 2048)
+        want = []
+        for i in range(0, nd, 2048):
+            bp = np.zeros(2048, dtype=np.complex128)
+            assert ff.ProcessData(2048, np.ascontiguousarray(dec[i:i + 2048]), bp) == 2048
+            y = agc.processBlock(bp)
+            want.append(dem.processBlockNCO(y) if k % 2 == 0 else dem.processBlockFiltered(y))
+        want = np.concatenate(want)
+        if k % 2 == 0:
+            assert rel_rms(got[k][1024:], want[1024:]) <= 1e-4, (k, rel_rms(got[k][1024:], want[1024:]))
+            assert rel_rms(got[k][:1024], want[:1024]) <= 5e-2, (k, rel_rms(got[k][:1024], want[:1024]))
+        else:
+            assert rel_rms(got[k], want) <= 1e-10, (k, rel_rms(got[k], want))

@@ -112,3 +112,91 @@ def test_device_resident_large_matches_chunked_reference():
     yg = yd.cpu().numpy()
     yr = _feed(r, x, [32768] * (n // 32768), S)
     assert rel_rms(yg, yr) <= TOL
+
+
+def test_reference_call_shape_2048_and_ragged_small_calls_10msps():
+    """The reference's real call shape is framesPerBuffer = 2048 samples per processIQData (16 outputs per call), and the
+    minimal legal call is 2^S = 128 samples: both hit dc_pipe_kernel's single-partial-chunk path and the state hand-over."""
+    sizes = [2048] * 24 + [128, 384, 2048, 128, 128, 1024, 4096 + 128, 32768 - 10112]
+    n = sum(sizes)
+    assert n % 32768 == 0
+    x = iq_noise_tones(n, 31, 10e6, [(1.2e6 + 700.0, 0.4), (-2e6, 0.4)], noise=0.02)
+    g, r = _pair(10e6, 15000.0, 1.2e6)
+    S = g.NumStages()
+    yg = _feed(g, x, sizes, S)
+    yr = _feed(r, x, [32768] * (n // 32768), S)   # the reference filters every stage only for calls this long (see below)
+    assert rel_rms(yg, yr) <= TOL
+
+
+def test_61msps_10_stage_chain_vs_reference_max_decstages_12():
+    """BASELINE config 4's chain (CIC3 x3, HB11 x4, HB15, HB19, HB35) against the reference compiled with MAX_DECSTAGES 12
+    (downconvert.h:23; oracle/build_ref.sh step 6), incl. 2048-sample calls on the GPU side."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    if not ref_app.dec12_available():
+        pytest.skip("oracle/_ref/libpebbleref_dec12.so not built")
+    n = 32768 * 8
+    f = -30.69e6 + 700 * 60e3
+    x = iq_noise_tones(n, 32, 61.44e6, [(f + 1500.0, 0.3), (f + 60e3, 0.3), (9e6, 0.4)], noise=0.02)
+    for sizes in ([32768] * 8, [2048] * 16 + [1024, 3072, 4096] + [32768 - 8192] + [32768] * 6):
+        g, r = pb.CDownConvert(), ref_app.CDownConvert12()
+        assert g.SetDataRate(61.44e6, 15000.0) == r.SetDataRate(61.44e6, 15000.0) == 60000.0
+        g.SetFrequency(f); r.SetFrequency(f)
+        yg = _feed(g, x, sizes, 10)
+        yr = _feed(r, x, [32768] * 8, 10)
+        assert rel_rms(yg, yr) <= TOL
+
+
+@pytest.mark.parametrize("rate,bw,simple,expect", [
+    (2e6, 15000.0, True, [51, 51, 51]),            # SetDataRateSimple: 51-tap stages only (downconvert.cpp:220-244)
+    (48000.0, 2000.0, False, [15, 23]),
+    (48000.0, 6500.0, False, [39]),
+    (3.2e6, 30000.0, False, [11, 11, 15, 23, 43]),
+    (96000.0, 15000.0, False, [47]),
+    (48000.0, 8000.0, False, [51]),
+    (250000.0, 30000.0, False, [31]),
+])
+def test_every_generic_halfband_length_runs_on_the_gpu(rate, bw, simple, expect):
+    """each of HB15...HB51 (filtercoef.h:52-426, F7's doubled tap 0 included) executed on the device."""
+    import pebblesdr_b200 as pb
+    from oracle import ref
+    g, r = pb.CDownConvert(), ref.CDownConvert()
+    if simple:
+        assert g.SetDataRateSimple(rate, bw) == r.SetDataRateSimple(rate, bw)
+    else:
+        assert g.SetDataRate(rate, bw) == r.SetDataRate(rate, bw)
+    assert g.StageLengths() == expect
+    f = rate * 0.11
+    g.SetFrequency(f); r.SetFrequency(f)
+    S = len(expect)
+    n = 4096 * 6
+    x = iq_noise_tones(n, 33, rate, [(f + 0.01 * rate / (1 << S), 0.4), (-0.3 * rate, 0.4)], noise=0.05)
+    yg = _feed(g, x, [4096, 8192, 512, 3584, 8192], S)
+    yr = _feed(r, x, [4096] * 6, S)
+    assert rel_rms(yg, yr) <= TOL
+
+
+def test_short_call_rule_documented_deviation_and_strict_mode():
+    """downconvert.cpp:362-363: a generic half-band stage that receives fewer samples than it has taps returns n/2 WITHOUT
+    filtering (the caller's buffer is left as it is, so the 'output' is the stage's leading input samples). This library
+    filters every stage for every call length, so short calls equal long calls of the same stream (first assertion: the
+    reference itself does NOT have that property). pebble_downconvert_set_strict_lengths(h, 1) turns such calls into
+    PEBBLE_ERR_ARG for callers that want the reference's precondition enforced."""
+    import pebblesdr_b200 as pb
+    from oracle import ref
+    n = 32768
+    x = iq_noise_tones(n, 34, 10e6, [(1.2e6 + 700.0, 0.4)], noise=0.02)
+    r_long, r_short = ref.CDownConvert(), ref.CDownConvert()
+    for r in (r_long, r_short):
+        r.SetDataRate(10e6, 15000.0); r.SetFrequency(1.2e6)
+    y_long = _feed(r_long, x, [n], 7)
+    y_short = _feed(r_short, x, [1024] * 32, 7)          # stage 6 (27 taps) sees 16 samples per call: not filtered
+    assert rel_rms(y_short, y_long) > 1e-3
+    g, _ = _pair(10e6, 15000.0, 1.2e6)
+    assert rel_rms(_feed(g, x, [1024] * 32, 7), y_long) <= TOL
+    g2, _ = _pair(10e6, 15000.0, 1.2e6)
+    pb.lib.pebble_downconvert_set_strict_lengths(g2._h, 1)
+    out = np.zeros(256, complex)
+    with pytest.raises(pb.PebbleError):
+        g2.ProcessData(1024, np.ascontiguousarray(x[:1024]), out)
+    assert g2.ProcessData(4096, np.ascontiguousarray(x[:4096]), out) == 32   # 4096 >> 6 = 64 >= 27: fine
