@@ -105,10 +105,12 @@ int pebble_fastfir_get_filter(pebble_fastfir_t *h, double *coef_out);
  * The reference's MAX_DECSTAGES=10 leaves no NULL sentinel for a 10-stage chain (downconvert.h:23);
  * this library plans up to 16 stages and runs up to 12 (2^12 = /4096; longer chains: PEBBLE_ERR_STATE).
  * Short calls (documented deviation): a reference half-band stage that receives fewer samples than it has taps skips
- * the filter and returns n/2 ("safety net", downconvert.cpp:362-363), so the reference's output depends on how the
- * stream is cut into calls (framesPerBuffer 2048 at 61.44 MSPS leaves 4 samples for the 35-tap stage). This library
- * filters every stage for every call length: any split of a stream gives what the reference gives for calls long
- * enough. pebble_downconvert_set_strict_lengths(h, 1) instead refuses such calls with PEBBLE_ERR_ARG.
+ * the filter and returns n/2 ("safety net", downconvert.cpp:362-363), and one that receives fewer than 2*(taps-1)
+ * re-reads its carried history from the caller's buffer after its in-place outputs overwrote it (:387-390), so the
+ * reference's output depends on how the stream is cut into calls (framesPerBuffer 2048 at 61.44 MSPS leaves 4 samples
+ * for the 35-tap stage; 32768-sample calls leave 64 < 68). This library filters every stage for every call length:
+ * any split of a stream gives what the reference gives for calls long enough (>= 2*(taps-1) samples into every
+ * stage). pebble_downconvert_set_strict_lengths(h, 1) instead refuses shorter calls with PEBBLE_ERR_ARG.
  */
 typedef struct pebble_downconvert pebble_downconvert_t;
 pebble_downconvert_t *pebble_downconvert_create(void);
@@ -271,6 +273,36 @@ int pebble_demod_is_passthrough(const pebble_demod_t *h);
 int pebble_demod_process(pebble_demod_t *h, int n, const double *in, double *out);
 int pebble_demod_process_device(pebble_demod_t *h, int n, const double *d_in, double *d_out, void *stream);
 
+/* ---- CFractResampler : fractional resampler to the audio rate -----------------------------------------------
+ * Replaces pebblelib/fractresampler.h:20-40, implementation fractresampler.cpp:64-187 (complex form) and :196-250 (stereo
+ * int16 form), called by Receiver::processIQData after the demodulator (application/receiver.cpp:994-1002) with
+ * Rate = demodRate / audioRate.
+ * pebble_resampler_create()     <-> CFractResampler() + Init(MaxInputSize)            fractresampler.cpp:64-121
+ * pebble_resampler_resample()   <-> Resample(InLength, Rate, TYPECPX*, TYPECPX*)      fractresampler.cpp:146-187 (one call)
+ * pebble_resampler_resample_device(): `frame` > 0 reproduces the call structure of a batch: the n samples are resampled as
+ *      n/frame consecutive Resample calls of `frame` samples (the receiver calls it once per framesPerBuffer frame; the
+ *      time accumulator m_FloatTime is rounded differently depending on where the calls end). streams > 1: row s of
+ *      d_in/d_out (in_stride/out_stride CPX apart), all rows with the same Rate. clip != 0 also applies the +-0.9999 clip
+ *      of AudioQT::SendToOutput (pebblelib/audioqt.cpp:190-201). Returns the output samples per stream.
+ * Output counts and every output sample are bit-identical to the reference (separate multiply and add roundings in its
+ * order). pebble_resampler_out_count() = what the next call WOULD return (the times depend only on Rate and lengths).
+ * pebble_resampler_plan*(): host-only planner (no device). */
+typedef struct pebble_resampler pebble_resampler_t;
+pebble_resampler_t *pebble_resampler_create(int max_input_size);
+void pebble_resampler_destroy(pebble_resampler_t *h);
+int pebble_resampler_set_streams(pebble_resampler_t *h, int streams);
+int pebble_resampler_out_count(pebble_resampler_t *h, int n, int frame, double rate);
+int pebble_resampler_resample(pebble_resampler_t *h, int n, double rate, const double *in, double *out);
+int pebble_resampler_resample_device(pebble_resampler_t *h, int n, int frame, double rate, const double *d_in, long long in_stride,
+                                     double *d_out, long long out_stride, int clip, void *stream);
+int pebble_resampler_resample_stereo16_device(pebble_resampler_t *h, int n, int frame, double rate, const double *d_in,
+                                              long long in_stride, short *d_out, long long out_stride, double gain, void *stream);
+int64_t pebble_resampler_state_size(const pebble_resampler_t *h);   /* double m_FloatTime + 28 CPX per stream */
+int pebble_resampler_get_state(pebble_resampler_t *h, void *buf, int64_t bytes);
+int pebble_resampler_set_state(pebble_resampler_t *h, const void *buf, int64_t bytes);
+int pebble_resampler_plan(double float_time, double rate, int n, double *float_time_out);
+int pebble_resampler_plan_times(double float_time, double rate, int n, double *times, int max);
+
 /* ---- Receiver chain : the non-WFM branch of Receiver::processIQData ------------------------------------
  * Replaces application/receiver.cpp:903-996: m_downConvert1.ProcessData -> m_sampleBuf re-framing to
  * framesPerBuffer (:922-931) -> scaleCPX gain restore (:935-938) -> m_bpFilter->process (:950) ->
@@ -289,6 +321,10 @@ int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold);
 int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages);
 /* Raw device samples into the chain (normalizeIQ fused into the mixer load, see "Device sample formats" above). */
 int pebble_receiver_set_input_format(pebble_receiver_t *h, int fmt, int order, double user_gain, double norm_gain);
+/* Audio tail (receiver.cpp:994-1007): CFractResampler::Resample once per frame with Rate = (int)demodRate / audio_rate, and,
+ * with clip != 0, the audio sink's +-0.9999 clip (AudioQT::SendToOutput, pebblelib/audioqt.cpp:190-201). The process calls
+ * then return AUDIO samples (a data-independent count, pebble_receiver_out_count). audio_rate <= 0 switches it off. */
+int pebble_receiver_set_audio(pebble_receiver_t *h, int audio_rate, int clip);
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n);
 /* Library extension (the reference's Perform timer call sites, receiver.cpp:788,805,827, are commented out):
  * per-step DEVICE time via CUDA events recorded on the caller's stream. get_profile sums the calls made since

@@ -133,6 +133,19 @@ SIGNATURES = {
     "pebble_channelizer_front_path": (c_int, [c_vp]),
     "pebble_channelizer_downconvert_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
     "pebble_channelizer_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    # CFractResampler
+    "pebble_resampler_create": (c_vp, [c_int]),
+    "pebble_resampler_destroy": (None, [c_vp]),
+    "pebble_resampler_set_streams": (c_int, [c_vp, c_int]),
+    "pebble_resampler_out_count": (c_int, [c_vp, c_int, c_int, c_dbl]),
+    "pebble_resampler_resample": (c_int, [c_vp, c_int, c_dbl, c_vp, c_vp]),
+    "pebble_resampler_resample_device": (c_int, [c_vp, c_int, c_int, c_dbl, c_vp, ctypes.c_longlong, c_vp, ctypes.c_longlong, c_int, c_vp]),
+    "pebble_resampler_resample_stereo16_device": (c_int, [c_vp, c_int, c_int, c_dbl, c_vp, ctypes.c_longlong, c_vp, ctypes.c_longlong, c_dbl, c_vp]),
+    "pebble_resampler_state_size": (c_i64, [c_vp]),
+    "pebble_resampler_get_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_resampler_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_resampler_plan": (c_int, [c_dbl, c_dbl, c_int, c_vp]),
+    "pebble_resampler_plan_times": (c_int, [c_dbl, c_dbl, c_int, c_vp, c_int]),
     # Receiver chain
     "pebble_receiver_create": (c_vp, [c_dbl, c_int]),
     "pebble_receiver_destroy": (None, [c_vp]),
@@ -144,6 +157,7 @@ SIGNATURES = {
     "pebble_receiver_set_agc": (c_int, [c_vp, c_int, c_int]),
     "pebble_receiver_set_gain_stages": (c_int, [c_vp, c_int]),
     "pebble_receiver_out_count": (c_int, [c_vp, c_int]),
+    "pebble_receiver_set_audio": (c_int, [c_vp, c_int, c_int]),
     "pebble_receiver_set_profiling": (c_int, [c_vp, c_int]),
     "pebble_receiver_get_profile": (c_int, [c_vp, c_vp, c_vp]),
     "pebble_receiver_process": (c_int, [c_vp, c_int, c_vp, c_vp]),

@@ -382,10 +382,11 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const void
     cudaStream_t stream = (cudaStream_t)stream_v;
     const int S = h->chain.nstages;
     if (h->strict_lengths) {
-        // the reference's per-stage precondition: a generic half-band needs InLength >= taps (downconvert.cpp:362-363),
-        // the unrolled 11-tap one reads pInData[0..17] unconditionally (:426-480)
+        // the reference's per-stage preconditions: a generic half-band filters only for InLength >= taps (downconvert.cpp:
+        // 362-363) and, run in place as CDownConvert runs it (:325), keeps a correct history only for InLength >= 2*(taps-1)
+        // (:387-390 re-read the caller's buffer after the outputs were written); the 11-tap one reads pInData[0..17] (:426-480)
         for (int s = 0; s < S; ++s) {
-            const int need = h->chain.st[s].len == 11 ? 18 : h->chain.st[s].len == 3 ? 2 : h->chain.st[s].len;
+            const int need = h->chain.st[s].len == 11 ? 18 : h->chain.st[s].len == 3 ? 2 : 2 * (h->chain.st[s].len - 1);
             if ((n >> s) < need) {
                 pebble::set_error("downconvert: stage %d (%d taps) would receive %d samples (strict lengths)", s, h->chain.st[s].len, n >> s);
                 return PEBBLE_ERR_ARG;

@@ -9,6 +9,11 @@
 #include <cstring>
 #include <vector>
 
+// resampler.cu
+struct pebble_resampler;
+int resampler_run_device(pebble_resampler *h, int n, int frame, double rate, const cpx *d_in, cpx *d_out, bool clip, cudaStream_t st);
+long long resampler_peek_count(pebble_resampler *h, int n, int frame, double rate);
+
 struct pebble_receiver {
     double sample_rate = 0, demod_rate = 0;
     int fpb = 2048;                // framesPerBuffer (settings.cpp:57)
@@ -17,6 +22,11 @@ struct pebble_receiver {
     pebble_agc *agc = nullptr;
     pebble_demod *demod = nullptr;
     int gain_stages = -1;          // -1: use the CDownConvert stage count
+    // audio tail (receiver.cpp:994-1007): fractional resampler demodRate -> audioRate once per frame, then the sink's clip
+    pebble_resampler *rs = nullptr;
+    double resamp_rate = 1.0;      // resampRate = demodSampleRate / audioOutRate (:994)
+    bool audio_on = false, audio_clip = false;
+    cpx *d_demod = nullptr; size_t demod_cap = 0;
     cpx *d_frames = nullptr; size_t frames_cap = 0;   // m_sampleBuf: decimated samples waiting for a full frame
     int fill = 0;                                      // m_sampleBufLen
     cpx *d_bp = nullptr, *d_agc = nullptr; size_t work_cap = 0;
@@ -87,7 +97,8 @@ void pebble_receiver_destroy(pebble_receiver_t *h) {
     if (h->bp) pebble_fastfir_destroy(h->bp);
     if (h->agc) pebble_agc_destroy(h->agc);
     if (h->demod) pebble_demod_destroy(h->demod);
-    cudaFree(h->d_frames); cudaFree(h->d_bp); cudaFree(h->d_agc); cudaFree(h->d_pin_in); cudaFree(h->d_pin_out);
+    cudaFree(h->d_frames); cudaFree(h->d_bp); cudaFree(h->d_agc); cudaFree(h->d_pin_in); cudaFree(h->d_pin_out); cudaFree(h->d_demod);
+    if (h->rs) pebble_resampler_destroy(h->rs);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     h->stg.release();
@@ -132,6 +143,21 @@ int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages) {
     h->gain_stages = stages;
     return 0;
 }
+// Audio tail of Receiver::processIQData (receiver.cpp:994-1007): resampRate = demodSampleRate / audioOutRate; if it is not 1
+// every demodulated frame goes through CFractResampler::Resample (else it is copied), then to the audio sink, whose only
+// arithmetic is the +-0.9999 clip (AudioQT::SendToOutput, audioqt.cpp:190-201; clip != 0). audio_rate <= 0 switches the tail
+// off again (the chain then ends at the demodulator, as before). The demod rate is truncated to an integer like
+// m_demodSampleRate.
+int pebble_receiver_set_audio(pebble_receiver_t *h, int audio_rate, int clip) {
+    if (!h) return PEBBLE_ERR_ARG;
+    if (audio_rate <= 0) { h->audio_on = false; return 0; }
+    if (!h->rs) h->rs = pebble_resampler_create(h->fpb);
+    if (!h->rs) return PEBBLE_ERR_CUDA;
+    h->resamp_rate = ((int)h->demod_rate * 1.0) / (audio_rate * 1.0);
+    h->audio_on = true;
+    h->audio_clip = clip != 0;
+    return 0;
+}
 int pebble_receiver_set_profiling(pebble_receiver_t *h, int on) {
     if (!h) return PEBBLE_ERR_ARG;
     h->profiling = on != 0;
@@ -158,7 +184,9 @@ int pebble_receiver_get_profile(pebble_receiver_t *h, double *ms, int64_t *calls
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n) {
     if (!h || n < 0) return PEBBLE_ERR_ARG;
     const int S = pebble_downconvert_num_stages(h->dc);
-    return (int)((((long long)h->fill + (n >> S)) / h->fpb) * h->fpb);
+    const int nproc = (int)((((long long)h->fill + (n >> S)) / h->fpb) * h->fpb);
+    if (h->audio_on && h->resamp_rate != 1.0 && nproc > 0) return (int)resampler_peek_count(h->rs, nproc, h->fpb, h->resamp_rate);
+    return nproc;
 }
 
 int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in, double *d_out, void *stream_v) {
@@ -214,15 +242,31 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in
         next = h->d_agc;
     }
     rx_mark(h, st);
-    r = demod_run_device(h->demod, nproc, next, (cpx *)d_out, st, nullptr, h->fpb);  // receiver.cpp:987, once per frame
+    const bool resample = h->audio_on && h->resamp_rate != 1.0;
+    cpx *demod_out = (cpx *)d_out;
+    if (resample) {
+        if ((size_t)nproc > h->demod_cap) {
+            PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+            cudaFree(h->d_demod); h->d_demod = nullptr; h->demod_cap = 0;
+            PB_CUDA(cudaMalloc(&h->d_demod, sizeof(cpx) * (size_t)nproc), PEBBLE_ERR_CUDA);
+            h->demod_cap = (size_t)nproc;
+        }
+        demod_out = h->d_demod;
+    }
+    r = demod_run_device(h->demod, nproc, next, demod_out, st, nullptr, h->fpb);  // receiver.cpp:987, once per frame
     if (r < 0) { demod_am_cancel_tiles(h->demod); if (h->profiling) h->ev_used = ev_entry; return r; }
+    int produced = nproc;
+    if (resample) {   // receiver.cpp:1000-1002, one Resample call per frame
+        produced = resampler_run_device(h->rs, nproc, h->fpb, h->resamp_rate, h->d_demod, (cpx *)d_out, h->audio_clip, st);
+        if (produced < 0) { if (h->profiling) h->ev_used = ev_entry; return produced; }
+    }
     rx_mark(h, st);
     // keep the incomplete frame for the next call
     const int rem = total - nproc;
     if (rem > 0)
         PB_CUDA(cudaMemcpyAsync(h->d_frames, h->d_frames + nproc, sizeof(cpx) * (size_t)rem, cudaMemcpyDeviceToDevice, st), PEBBLE_ERR_CUDA);
     h->fill = rem;
-    return nproc;
+    return produced;
 }
 
 int pebble_receiver_process(pebble_receiver_t *h, int n, const void *in, double *out) {

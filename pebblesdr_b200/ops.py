@@ -406,6 +406,64 @@ class Demod(_Handle):
         return out
 
 
+class CFractResampler(_Handle):
+    """Fractional resampler (pebblelib/fractresampler.cpp:64-250)."""
+    _destroy = staticmethod(lib.pebble_resampler_destroy)
+
+    def __init__(self, MaxInputSize=2048, streams=1):
+        super().__init__(lib.pebble_resampler_create(int(MaxInputSize)), "CFractResampler")   # = ctor + Init(MaxInputSize)
+        self.streams = streams
+        if streams != 1:
+            check(lib.pebble_resampler_set_streams(self._h, streams), "set_streams")
+
+    def OutCount(self, InLength, Rate, frame=0):
+        return check(lib.pebble_resampler_out_count(self._h, InLength, frame, Rate), "OutCount")
+
+    def Resample(self, InLength, Rate, pInBuf, pOutBuf=None, frame=0, clip=False):
+        """Host numpy arrays: one reference call. CUDA tensors ([streams, n] rows or 1-D): `frame` > 0 = a batch of
+        consecutive reference calls of `frame` samples. Returns (count, out)."""
+        k = self.OutCount(InLength, Rate, frame)
+        if _is_cuda_tensor(pInBuf):
+            rows = pInBuf if pInBuf.dim() == 2 else pInBuf.view(1, -1)
+            if pOutBuf is None:
+                pOutBuf = torch.zeros(rows.shape[0], max(k, 1), dtype=torch.complex128, device=pInBuf.device)
+            orows = pOutBuf if pOutBuf.dim() == 2 else pOutBuf.view(1, -1)
+            r = check(lib.pebble_resampler_resample_device(self._h, InLength, frame, Rate, rows.data_ptr(), rows.stride(0),
+                                                           orows.data_ptr(), orows.stride(0), int(bool(clip)), _stream_ptr()), "Resample")
+            return r, pOutBuf
+        if pOutBuf is None:
+            pOutBuf = np.empty(max(k, 1), dtype=np.complex128)
+        r = check(lib.pebble_resampler_resample(self._h, InLength, Rate, _host_ptr(pInBuf, InLength), _host_ptr(pOutBuf, k, True)),
+                  "Resample")
+        return r, pOutBuf
+
+    def ResampleStereo16(self, InLength, Rate, d_in, gain, frame=0):
+        k = self.OutCount(InLength, Rate, frame)
+        rows = d_in if d_in.dim() == 2 else d_in.view(1, -1)
+        out = torch.zeros(rows.shape[0], max(k, 1), 2, dtype=torch.int16, device=d_in.device)
+        r = check(lib.pebble_resampler_resample_stereo16_device(self._h, InLength, frame, Rate, rows.data_ptr(), rows.stride(0),
+                                                                out.data_ptr(), out.stride(0), float(gain), _stream_ptr()), "Resample")
+        return r, out
+
+    def GetState(self):
+        n = check(lib.pebble_resampler_state_size(self._h))
+        buf = np.empty(n, dtype=np.uint8)
+        check(lib.pebble_resampler_get_state(self._h, buf.ctypes.data, n), "GetState")
+        return buf
+
+    def SetState(self, buf):
+        check(lib.pebble_resampler_set_state(self._h, buf.ctypes.data, buf.size), "SetState")
+
+
+def resampler_plan(float_time, rate, n):
+    """Host-only planner: (output count, m_FloatTime afterwards, output times) of one Resample call."""
+    te = ctypes.c_double(0.0)
+    cnt = check(lib.pebble_resampler_plan(float(float_time), float(rate), int(n), ctypes.byref(te)), "plan")
+    times = np.empty(max(cnt, 1))
+    check(lib.pebble_resampler_plan_times(float(float_time), float(rate), int(n), times.ctypes.data, cnt), "plan_times")
+    return cnt, te.value, times[:cnt]
+
+
 class Receiver(_Handle):
     """The non-WFM branch of Receiver::processIQData (application/receiver.cpp:903-996) as one chain."""
     _destroy = staticmethod(lib.pebble_receiver_destroy)
@@ -443,6 +501,10 @@ class Receiver(_Handle):
 
     def setGainStages(self, stages):
         check(lib.pebble_receiver_set_gain_stages(self._h, stages))
+
+    def setAudio(self, audioRate, clip=True):
+        """Resample the demodulated frames to audioRate (receiver.cpp:994-1002) and clip like the audio sink."""
+        check(lib.pebble_receiver_set_audio(self._h, int(audioRate), int(bool(clip))), "setAudio")
 
     def outCount(self, n):
         return check(lib.pebble_receiver_out_count(self._h, n))

@@ -117,9 +117,10 @@ def test_device_resident_large_matches_chunked_reference():
 def test_reference_call_shape_2048_and_ragged_small_calls_10msps():
     """The reference's real call shape is framesPerBuffer = 2048 samples per processIQData (16 outputs per call), and the
     minimal legal call is 2^S = 128 samples: both hit dc_pipe_kernel's single-partial-chunk path and the state hand-over."""
-    sizes = [2048] * 24 + [128, 384, 2048, 128, 128, 1024, 4096 + 128, 32768 - 10112]
+    sizes = [2048] * 24 + [128, 384, 2048, 128, 128, 1024, 4096 + 128]
+    sizes.append(3 * 32768 - sum(sizes))
     n = sum(sizes)
-    assert n % 32768 == 0
+    assert n % 32768 == 0 and sizes[-1] % 128 == 0
     x = iq_noise_tones(n, 31, 10e6, [(1.2e6 + 700.0, 0.4), (-2e6, 0.4)], noise=0.02)
     g, r = _pair(10e6, 15000.0, 1.2e6)
     S = g.NumStages()
@@ -135,15 +136,17 @@ def test_61msps_10_stage_chain_vs_reference_max_decstages_12():
     from oracle import ref_app
     if not ref_app.dec12_available():
         pytest.skip("oracle/_ref/libpebbleref_dec12.so not built")
-    n = 32768 * 8
+    n = 65536 * 4
     f = -30.69e6 + 700 * 60e3
     x = iq_noise_tones(n, 32, 61.44e6, [(f + 1500.0, 0.3), (f + 60e3, 0.3), (9e6, 0.4)], noise=0.02)
-    for sizes in ([32768] * 8, [2048] * 16 + [1024, 3072, 4096] + [32768 - 8192] + [32768] * 6):
+    for sizes in ([32768] * 8, [2048] * 16 + [1024, 3072, 4096] + [32768 - 8192] + [32768] * 6 + [1024] * 32):
         g, r = pb.CDownConvert(), ref_app.CDownConvert12()
         assert g.SetDataRate(61.44e6, 15000.0) == r.SetDataRate(61.44e6, 15000.0) == 60000.0
         g.SetFrequency(f); r.SetFrequency(f)
+        assert sum(sizes) == n
         yg = _feed(g, x, sizes, 10)
-        yr = _feed(r, x, [32768] * 8, 10)
+        # 65536-sample reference calls: the 35-tap stage then receives 128 >= 2 * 34 samples (see the short-call test below)
+        yr = _feed(r, x, [65536] * 4, 10)
         assert rel_rms(yg, yr) <= TOL
 
 
@@ -178,10 +181,12 @@ def test_every_generic_halfband_length_runs_on_the_gpu(rate, bw, simple, expect)
 
 def test_short_call_rule_documented_deviation_and_strict_mode():
     """downconvert.cpp:362-363: a generic half-band stage that receives fewer samples than it has taps returns n/2 WITHOUT
-    filtering (the caller's buffer is left as it is, so the 'output' is the stage's leading input samples). This library
-    filters every stage for every call length, so short calls equal long calls of the same stream (first assertion: the
-    reference itself does NOT have that property). pebble_downconvert_set_strict_lengths(h, 1) turns such calls into
-    PEBBLE_ERR_ARG for callers that want the reference's precondition enforced."""
+    filtering (the caller's buffer is left as it is, so the 'output' is the stage's leading input samples); and with fewer
+    than 2*(taps-1) samples it re-reads its carried history from the caller's buffer AFTER the in-place outputs overwrote
+    it (:387-390; CDownConvert always calls DecBy2 in place, :325). So the reference's output depends on how the stream is
+    cut into calls (first two assertions). This library filters every stage for every call length: short calls equal long
+    calls of the same stream. pebble_downconvert_set_strict_lengths(h, 1) turns such calls into PEBBLE_ERR_ARG for
+    callers that want the reference's precondition enforced."""
     import pebblesdr_b200 as pb
     from oracle import ref
     n = 32768
@@ -192,6 +197,10 @@ def test_short_call_rule_documented_deviation_and_strict_mode():
     y_long = _feed(r_long, x, [n], 7)
     y_short = _feed(r_short, x, [1024] * 32, 7)          # stage 6 (27 taps) sees 16 samples per call: not filtered
     assert rel_rms(y_short, y_long) > 1e-3
+    r_mid = ref.CDownConvert()
+    r_mid.SetDataRate(10e6, 15000.0); r_mid.SetFrequency(1.2e6)
+    y_mid = _feed(r_mid, x, [2048] * 16, 7)               # 32 samples into the 27-tap stage: filtered, but 32 < 2 * 26
+    assert 1e-9 < rel_rms(y_mid, y_long) < 1e-2
     g, _ = _pair(10e6, 15000.0, 1.2e6)
     assert rel_rms(_feed(g, x, [1024] * 32, 7), y_long) <= TOL
     g2, _ = _pair(10e6, 15000.0, 1.2e6)
@@ -199,4 +208,6 @@ def test_short_call_rule_documented_deviation_and_strict_mode():
     out = np.zeros(256, complex)
     with pytest.raises(pb.PebbleError):
         g2.ProcessData(1024, np.ascontiguousarray(x[:1024]), out)
-    assert g2.ProcessData(4096, np.ascontiguousarray(x[:4096]), out) == 32   # 4096 >> 6 = 64 >= 27: fine
+    with pytest.raises(pb.PebbleError):
+        g2.ProcessData(2048, np.ascontiguousarray(x[:2048]), out)            # 32 < 2 * 26
+    assert g2.ProcessData(4096, np.ascontiguousarray(x[:4096]), out) == 32   # 4096 >> 6 = 64 >= 52: fine
