@@ -54,27 +54,36 @@ def _cpu_longfir(args):
                                      "(oracle/_ref/libpebbleref_long.so)" if real else "C restatement oracle/pebble_oracle.c")}
 
 
-def main(args, bench):
-    import torch
-    import torch.distributed as dist
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; this arm has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+def longfir_parity(x_head, y_head):
+    """The first samples stream 0 produced in the run's first step vs the reference CFastFIR compiled at 131072/65537
+    (oracle/_ref/libpebbleref_long.so) — or the C restatement where oracle/_ref is absent — on the same input."""
+    import numpy as np
+    from oracle import ref, port
+    real = ref.long_available()
+    o = ref.CFastFIRLong() if real else port.CFastFIR(LF_N, LF_FIR)
+    o.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+    want = np.zeros(len(x_head) + LF_N, dtype=np.complex128)
+    k = o.ProcessData(len(x_head), np.ascontiguousarray(x_head), want)
+    m = min(k, len(y_head))
+    den = float(np.sqrt(np.mean(np.abs(want[:m]) ** 2)))
+    err = float(np.sqrt(np.mean(np.abs(y_head[:m] - want[:m]) ** 2))) / (den if den > 0 else 1.0)
+    return {"rel_rms": err, "samples": int(m), "oracle": "reference" if real else "port", "tolerance": 1e-10,
+            "what": "first %d output samples of stream 0 in the run's first step vs %s on the same input" %
+                    (m, "the reference CFastFIR compiled at 131072/65537 + FFTW 3.3.4" if real else "the C restatement")}
+
+
+def measure(args, bench, torch, dist, dev, world, rank, steps, warmup, cpu_baseline=False, e2e=False):
+    """Times the stream-sharded long filter on an already initialised process group. Returns the result dict on rank 0."""
+    import numpy as np
     import pebblesdr_b200 as pb
     from pebblesdr_b200 import lib
     from pebblesdr_b200._lib import check
     from pebblesdr_b200.dist import max_over_ranks, shard_range
 
-    n = 1 << (args.log2n if args.log2n_set else 22)          # samples per stream per step
+    n = 1 << (args.log2n if (args.log2n_set and args.workload == "longfir") else 22)          # samples per stream per step
     first, end = shard_range(LF_STREAMS, world, rank)
     S = end - first
-    K, W = args.steps, args.warmup
+    K, W = steps, max(warmup, 1)
     x = torch.empty(S, n, dtype=torch.complex128, device=dev)
     for s in range(S):                                          # stream `first + s`: seed 5000 + stream (SURVEY 8d)
         g = torch.Generator(device=dev)
@@ -95,10 +104,14 @@ def main(args, bench):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(W):
+    y_head = None
+    npar = min(n, 1 << 20)
+    for w in range(W):
         step()
+        if w == 0 and rank == 0:
+            y_head = out[0, :npar].cpu().numpy()                # first step of the stream: what the parity check replays
     barrier()
-    clocks = bench.ClockSampler(local)
+    clocks = bench.ClockSampler(torch.cuda.current_device())
     if rank == 0:
         clocks.start()
         time.sleep(0.3)
@@ -116,49 +129,84 @@ def main(args, bench):
     chk = float(torch.view_as_real(out[:, -4096:]).abs().sum().item())
     assert chk > 0 and chk == chk
 
-    # ---- end to end: one stream's host buffer through pebble_fastfir_process (staging + H2D + kernels + D2H per call) ----
-    import numpy as np
-    m = min(n, 1 << 22)
-    hx = x[0, :m].cpu().numpy()
-    op2 = pb.CFastFIR(LF_N, LF_FIR)
-    op2.SetupParameters(-20e6, 20e6, 0.0, 100e6)
-    hout = np.zeros(m + LF_N, dtype=np.complex128)
-    op2.ProcessData(m, hx, hout)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(K):
-        op2.ProcessData(m, hx, hout)
-    torch.cuda.synchronize()
-    ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3, dev)
+    ms_e2e, m = None, min(n, 1 << 22)
+    if e2e:
+        # ---- end to end: stream 0 from a PAGE-LOCKED host buffer: H2D + kernels + D2H per step, device-timed ----
+        hx = torch.empty(m, dtype=torch.complex128, pin_memory=True)
+        hx.copy_(x[0, :m])
+        hy = torch.zeros(m, dtype=torch.complex128, pin_memory=True)
+        dx = torch.empty(m, dtype=torch.complex128, device=dev)
+        dy = torch.empty(m, dtype=torch.complex128, device=dev)
+        op2 = pb.CFastFIR(LF_N, LF_FIR)
+        op2.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+        for it in range(2 + K):
+            if it == 2:
+                f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                barrier()
+                f0.record()
+            dx.copy_(hx, non_blocking=True)
+            op2.ProcessData(m, dx, dy)
+            hy.copy_(dy, non_blocking=True)
+        f1.record()
+        barrier()
+        ms_e2e = max_over_ranks(f0.elapsed_time(f1), dev)
 
+    if rank != 0:
+        return None
+    peak, peak_src = bench.measured_peak()
+    fpk, fpk_src = bench.fp64_peak()
+    total = LF_STREAMS * n                                   # whole job, all ranks
+    per_gpu_sps = S * n * K / (ms * 1e-3)
+    achieved = ALG_BYTES * per_gpu_sps / 1e9
+    res = {
+        "workload": "BASELINE config 5: long-filter stress, CFastFIR 131072-point overlap-save (65537 taps, +-20 MHz) over 100 MSPS "
+                    "synthetic IQ, 64 concurrent streams sharded over %d GPU(s), no data-path collective" % world,
+        "metric": "complex MS/s through the long-filter CFastFIR (131072-point overlap-save)",
+        "value": total * K / (ms * 1e-3) / 1e6, "unit": "MS/s", "n_gpus": world, "steps": K, "warmup": W,
+        "streams": LF_STREAMS, "streams_per_gpu": S, "samples_per_stream_per_step": n, "ms_per_step": ms / K,
+        "scaling": "strong", "collective": "none (streams are independent; outputs stay on their GPU)",
+        "l2": "inputs (%d MiB/step/GPU) larger than the 126 MB L2; no flush" % ((16 * n * S) >> 20),
+        "parity": longfir_parity(x[0, :npar].cpu().numpy(), y_head) if y_head is not None else None,
+        "roofline": {"hbm": {"achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                             "traffic": bench_traffic(S * n), "algorithmic_bytes_per_step": ALG_BYTES * S * n, "per": "GPU"},
+                     "fp64": {"achieved": FLOP_PER_SAMPLE * per_gpu_sps / 1e12, "peak": fpk, "unit": "TFLOP/s",
+                              "frac": FLOP_PER_SAMPLE * per_gpu_sps / 1e12 / fpk, "flop_per_sample": FLOP_PER_SAMPLE,
+                              "peak_source": fpk_src, "note": "5 N log2 N convention (radix-8/16 butterflies need fewer)"},
+                     "kernel": "lf_cols_kernel<8,fwd> + lf_rows_fused_kernel + lf_cols_kernel<8,inv> (four-step, scratch L2-resident)"},
+        "gpu_launches": int(launches), "clocks": clk,
+    }
+    if ms_e2e is not None:
+        res["e2e"] = {"value": world * m * K / (ms_e2e * 1e-3) / 1e6, "unit": "MS/s", "h2d_bytes_per_step": 16 * m,
+                      "d2h_bytes_per_step": 16 * m, "ms_per_step": ms_e2e / K,
+                      "call": "one stream per GPU from page-locked host buffers: H2D + pebble_fastfir_process_device + D2H per step "
+                              "(CUDA events)"}
+    return res
+
+
+def main(args, bench):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    r = measure(args, bench, torch, dist, dev, world, rank, args.steps, args.warmup, e2e=True)
     if rank == 0:
-        peak, peak_src = bench.measured_peak()
-        total = LF_STREAMS * n                                   # whole job, all ranks
-        per_gpu_sps = S * n * K / (ms * 1e-3)
-        achieved = ALG_BYTES * per_gpu_sps / 1e9
         line = {
-            "metric": "complex MS/s through the long-filter CFastFIR (131072-point overlap-save)",
-            "value": total * K / (ms * 1e-3) / 1e6, "unit": "MS/s", "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "metric": r["metric"], "value": r["value"], "unit": "MS/s", "n_gpus": world, "steps": r["steps"], "warmup": r["warmup"],
+            "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": "BASELINE config 5: long-filter stress, CFastFIR 131072-point overlap-save (65537 taps, +-20 MHz) "
-                                   "over 100 MSPS synthetic IQ, 64 concurrent streams",
-                       "streams": LF_STREAMS, "streams_per_gpu": S, "samples_per_stream_per_step": n,
-                       "l2": "inputs (%d MiB/step/GPU) larger than the 126 MB L2; no flush" % ((16 * n * S) >> 20),
+            "config": {"workload": r["workload"], "streams": LF_STREAMS, "streams_per_gpu": r["streams_per_gpu"],
+                       "samples_per_stream_per_step": r["samples_per_stream_per_step"], "l2": r["l2"],
                        "parallelism": "streams sharded over %d GPU(s), no data-path collective" % world},
-            "e2e": {"value": world * m * K / (ms_e2e * 1e-3) / 1e6, "unit": "MS/s", "h2d_bytes_per_step": 16 * m,
-                    "d2h_bytes_per_step": 16 * m, "ms_per_step": ms_e2e / K,
-                    "call": "pebble_fastfir_process, one stream per GPU (pageable host buffers, staging + H2D + kernels + D2H "
-                            "per call; host wall clock)"},
-            "roofline": {"bound": "hbm", "kernel": "lf_cols_kernel<8,fwd> + lf_rows_kernel + lf_cols_kernel<8,inv> (one chunk = "
-                                                   "three launches, scratch L2-resident)",
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": bench_traffic(S * n), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": ALG_BYTES * S * n,
-                         "fp64": {"flop_per_sample": FLOP_PER_SAMPLE, "achieved_tflops": FLOP_PER_SAMPLE * per_gpu_sps / 1e12,
-                                  "note": "5 N log2 N convention; nominal B200 FP64 ~37 TFLOP/s: this operator is FP64/L2-bound "
-                                          "above its HBM floor"}},
-            "gpu_launches": int(launches), "clocks": clk,
+            "e2e": r.get("e2e"),
+            "roofline": dict(r["roofline"]["hbm"], bound="hbm", kernel=r["roofline"]["kernel"], fp64=r["roofline"]["fp64"]),
+            "parity": r["parity"], "gpu_launches": r["gpu_launches"], "clocks": r["clocks"],
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = _cpu_longfir(args)

@@ -66,19 +66,22 @@ def _cpu_fastfir(args):
 
 
 def _cpu_spectrum(args, size):
+    """The reference's own FFTfftw::fftSpectrum (pebblelib fft.cpp/fftw.cpp + FFTW 3.3.4, oracle/_ref) on every host thread;
+    the C restatement only where oracle/_ref is absent."""
     import threading
     import numpy as np
-    from oracle import port, cpu_chain
+    from oracle import port, ref, cpu_chain
+    impl = ref if ref.available() else port
     threads = cpu_chain.host_threads()
     frames = 64
     rng = np.random.default_rng(4)
     src = ((rng.standard_normal(frames * size) + 1j * rng.standard_normal(frames * size)) * 0.1).astype(np.complex128)
     objs = []
     for _ in range(threads):
-        o = port.FFT()
+        o = impl.FFT()
         o.fftParams(size, 0, 20e6, size, 12)
         objs.append(o)
-    passes = max(1, int(args.cpu_seconds * 4e6 / (frames * size)))
+    passes = max(1, int(args.cpu_seconds * (20e6 if impl is ref else 4e6) / (frames * size)))
     busy = [0.0] * threads
     gate = threading.Barrier(threads)
 
@@ -96,9 +99,54 @@ def _cpu_spectrum(args, size):
         t.start()
     for t in ts:
         t.join()
-    return {"value": frames * size * passes * threads / max(busy) / 1e6, "unit": "MS/s", "cores": threads, "kind": "port",
-            "sample": "%d independent FFT objects (one per host thread), %d passes over %d frames of %d samples, C restatement "
-                      "oracle/pebble_oracle.c (window + FFT + dB + averaging)" % (threads, passes, frames, size)}
+    return {"value": frames * size * passes * threads / max(busy) / 1e6, "unit": "MS/s", "cores": threads,
+            "kind": "reference" if impl is ref else "port",
+            "sample": "%d independent FFT objects (one per host thread), %d passes over %d frames of %d samples, %s "
+                      "(window + FFT + unfold + dB + averaging)" % (threads, passes, frames, size,
+                      "unmodified pebblelib FFTfftw::fftSpectrum + FFTW 3.3.4 (oracle/_ref)" if impl is ref else
+                      "C restatement oracle/pebble_oracle.c")}
+
+
+def _parity(kind, x_head, y_head, size=8192, dtot=256):
+    """A slice of the run's own first-step output against the compiled reference (oracle/_ref) on the same input."""
+    import numpy as np
+    from oracle import ref, port
+    impl = ref if ref.available() else port
+    name = "reference" if impl is ref else "port"
+    if kind == "fastfir":
+        o = impl.CFastFIR()
+        o.SetupParameters(-3000.0, 3000.0, 0.0, 2e6)
+        want = np.zeros(len(x_head) + 2048, dtype=np.complex128)
+        k = o.ProcessData(len(x_head), np.ascontiguousarray(x_head), want)
+        want, got = want[:k], y_head[:k]
+    elif kind == "decimator":
+        o = impl.Decimator(10e6, 32768)
+        o.buildDecimationChain(10e6, 30000)
+        outs = []
+        for q in range(0, len(x_head), 32768):
+            w = np.zeros(32768, dtype=np.complex128)
+            k = o.process(np.ascontiguousarray(x_head[q:q + 32768]), w, 32768)
+            outs.append(w[:k].copy())
+        want = np.concatenate(outs)
+        got = y_head[:len(want)]
+    else:
+        o = impl.FFT()
+        o.fftParams(size, 0, 20e6, size, 12)
+        frames = len(x_head) // size
+        want = np.zeros((frames, size))
+        for f in range(frames):
+            o.fftSpectrum(np.ascontiguousarray(x_head[f * size:(f + 1) * size]), want[f], size)
+        # frame 0 averages with the reference's uninitialised previous-amplitude buffer (fft.cpp:348-397): compare from frame 1
+        want, got = want[1:], y_head[1:frames]
+        un = (want > -120.0) & (want < 0.0)
+        return {"max_abs_db": float(np.max(np.abs(got[un] - want[un]))), "clipped_bins_equal": bool(np.array_equal(got[~un], want[~un])),
+                "samples": int(want.size), "oracle": name, "tolerance_db": 1e-6,
+                "what": "%d frames of the run's first step vs FFTfftw::fftSpectrum on the same input" % (frames - 1)}
+    den = float(np.sqrt(np.mean(np.abs(want) ** 2)))
+    err = float(np.sqrt(np.mean(np.abs(got - want) ** 2))) / (den if den > 0 else 1.0)
+    return {"rel_rms": err, "bit_exact": bool(np.array_equal(got, want)), "samples": int(len(want)), "oracle": name,
+            "tolerance": 0.0 if kind == "decimator" else 1e-10,
+            "what": "first %d output samples of the run's first step vs the compiled reference on the same input" % len(want)}
 
 
 def _cpu_decimator(args):
@@ -194,8 +242,12 @@ def main(args, bench):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(W):
+    npar = min(n, 1 << 20)
+    y_head = None
+    for w in range(max(W, 1)):
         step()
+        if w == 0 and rank == 0:      # the stream's first step: what the parity check replays
+            y_head = (out[:npar // size].cpu().numpy() if not (fast or deci) else out[:npar if fast else npar // dtot].cpu().numpy())
     barrier()
     clocks = bench.ClockSampler(local)
     if rank == 0:
@@ -215,41 +267,40 @@ def main(args, bench):
     chk = float(out.abs().sum().item()) if not (fast or deci) else float(torch.view_as_real(out).abs().sum().item())
     assert chk > 0 and chk == chk
 
-    # ---- end to end: host buffers through the host-pointer C-ABI call (H2D + kernel + D2H inside the call) ----
-    m = min(n, 1 << 22)                                         # the host-pointer call stages through one pinned buffer
-    hx = x[:m].cpu().numpy()
+    # ---- end to end: PAGE-LOCKED host buffers, H2D + device call + D2H per step, CUDA events ----
+    m = min(n, 1 << 24)
+    hx = torch.empty(m, dtype=torch.complex128, pin_memory=True)
+    hx.copy_(x[:m])
+    dx = torch.empty(m, dtype=torch.complex128, device=dev)
     if deci:
-        import numpy as np
         op2 = pb.Decimator(10e6, 32768)
         op2.buildDecimationChain(10e6, 30000)
-        hout = np.zeros(m // dtot, dtype=np.complex128)
-        host_step = lambda: op2.process(hx, hout, m)
-        d2h = 16 * (m // dtot)
+        dy = torch.zeros(m // dtot, dtype=torch.complex128, device=dev)
+        dev_step = lambda: op2.process(dx, dy, m)
     elif fast:
-        import numpy as np
         op2 = pb.CFastFIR()
         op2.SetupParameters(-3000.0, 3000.0, 0.0, 2e6)
-        hout = np.zeros(m + 2048, dtype=np.complex128)
-        host_step = lambda: op2.ProcessData(m, hx, hout)
-        d2h = 16 * m
+        dy = torch.zeros(m, dtype=torch.complex128, device=dev)
+        dev_step = lambda: op2.ProcessData(m, dx, dy)
     else:
-        import numpy as np
         op2 = pb.FFT()
         op2.fftParams(size, 0, 20e6, size, 12)
-        hout = np.zeros(size)
-        m = size * 64
-
-        def host_step():
-            for f in range(64):
-                op2.fftSpectrum(hx[f * size:(f + 1) * size], hout, size)
-        d2h = 8 * size * 64
-    host_step()
+        dy = torch.zeros(m // size, size, dtype=torch.float64, device=dev)
+        fl2 = torch.zeros(m // size, dtype=torch.int32, device=dev)
+        dev_step = lambda: op2.fftSpectrumBatch(m // size, size, dx, dy, fl2)
+    hy = torch.zeros(dy.shape, dtype=dy.dtype, pin_memory=True)
+    d2h = hy.numel() * hy.element_size()
+    for it in range(2 + K):
+        if it == 2:
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            f0.record()
+        dx.copy_(hx, non_blocking=True)
+        dev_step()
+        hy.copy_(dy, non_blocking=True)
+    f1.record()
     barrier()
-    t0 = time.perf_counter()
-    for _ in range(K):
-        host_step()
-    torch.cuda.synchronize()
-    ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3, dev)
+    ms_e2e = max_over_ranks(f0.elapsed_time(f1), dev)
 
     if rank == 0:
         peak, peak_src = bench.measured_peak()
@@ -269,13 +320,15 @@ def main(args, bench):
                        "parallelism": "%d GPU(s), independent replicas" % world},
             "e2e": {"value": world * m * K / (ms_e2e * 1e-3) / 1e6, "unit": "MS/s", "h2d_bytes_per_step": 16 * m,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K,
-                    "call": ("pebble_decimator_process" if deci else "pebble_fastfir_process" if fast else "pebble_fft_spectrum x 64 frames") +
-                            " (pageable host buffers, staging + H2D + kernel + D2H per call; host wall clock)"},
+                    "call": ("pebble_decimator_process_device" if deci else "pebble_fastfir_process_device" if fast else "pebble_fft_spectrum_batch_device") +
+                            " between an H2D copy from and a D2H copy to page-locked host buffers, every step (CUDA events)"},
             "roofline": {"bound": "hbm", "kernel": "dec_chain_kernel" if deci else "fastfir4096x3_kernel (+ fastfir2048_kernel for the left-over blocks)" if fast
                          else "spectrum_kernel", "achieved": achieved / world, "peak": peak, "unit": "GB/s",
                          "frac": achieved / world / peak,
                          "traffic": _ncu_traffic("dec_chain_kernel" if deci else "fastfir4096x3_kernel" if fast else "spectrum_kernel", n), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg * n},
+            "parity": _parity("decimator" if deci else "fastfir" if fast else "spectrum", x[:npar].cpu().numpy(), y_head, size,
+                              dtot if deci else 256) if y_head is not None else None,
             "gpu_launches": int(launches), "clocks": clk,
         }
         if fast:

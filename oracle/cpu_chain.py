@@ -167,3 +167,49 @@ def timed_throughput(make_input, samples_per_thread, threads, steps=1, warmup=0,
         if step >= warmup:
             times.append(max(busy))
     return times, per_pass * passes * threads
+
+
+class ChannelChain:
+    """One channel of BASELINE config 4 on the CPU, every step the COMPILED reference: CDownConvert built with
+    MAX_DECSTAGES 12 (oracle/build_ref.sh step 6; the stock build overflows on this 10-stage chain) ->
+    gain restore 10^(2*stages/20) (receiver.cpp:935-938) -> CFastFIR(lo, hi) -> AGC_OFF(threshold) -> Demod_NFM::processBlockNCO
+    (mode 2) / Demod_AM::processBlockFiltered (mode 0) / pass-through, once per 2048-sample frame (receiver.cpp:903-996).
+    Fed in 65536-sample calls: the 35-tap last stage needs >= 2*34 samples per call (downconvert.cpp:387-390)."""
+    CALL = 65536
+
+    def __init__(self, rate, max_bw, freq, mode, lo=-7500.0, hi=7500.0, agc_threshold=20, fpb=2048):
+        self.dc = ref_app.CDownConvert12()
+        self.demod_rate = self.dc.SetDataRate(rate, max_bw)
+        self.dc.SetFrequency(freq)
+        self.S = int(round(np.log2(rate / self.demod_rate)))
+        self.gain = 10.0 ** ((self.S * 2) / 20.0)
+        self.ff = ref.CFastFIR()
+        self.ff.SetupParameters(lo, hi, 0.0, self.demod_rate)
+        self.agc = ref_app.AGC(self.demod_rate, fpb)
+        self.agc.setAgcMode(0, agc_threshold)
+        self.mode, self.fpb = mode, fpb
+        self.dem = ref_app.Demod_NFM(self.demod_rate, fpb) if mode == 2 else ref_app.Demod_AM(self.demod_rate, fpb) if mode == 0 else None
+        self.pend = np.zeros(0, dtype=np.complex128)
+        self._bp = np.zeros(fpb, dtype=np.complex128)
+
+    def run(self, x):
+        out = []
+        for i in range(0, len(x), self.CALL):
+            n = min(self.CALL, len(x) - i)
+            dec = np.zeros(n >> self.S, dtype=np.complex128)
+            assert self.dc.ProcessData(n, x[i:i + n], dec) == n >> self.S
+            self.pend = np.concatenate([self.pend, dec * self.gain])
+            while len(self.pend) >= self.fpb:
+                self.ff.ProcessData(self.fpb, np.ascontiguousarray(self.pend[:self.fpb]), self._bp)
+                y = self.agc.processBlock(self._bp)
+                if self.mode == 2:
+                    y = self.dem.processBlockNCO(y)
+                elif self.mode == 0:
+                    y = self.dem.processBlockFiltered(y)
+                out.append(np.array(y, copy=True))
+                self.pend = self.pend[self.fpb:]
+        return np.concatenate(out) if out else np.zeros(0, dtype=np.complex128)
+
+
+def channel_chain_available():
+    return ref.available() and ref_app.available() and ref_app.dec12_available()

@@ -139,7 +139,7 @@ def test_61msps_10_stage_chain_vs_reference_max_decstages_12():
     n = 65536 * 4
     f = -30.69e6 + 700 * 60e3
     x = iq_noise_tones(n, 32, 61.44e6, [(f + 1500.0, 0.3), (f + 60e3, 0.3), (9e6, 0.4)], noise=0.02)
-    for sizes in ([32768] * 8, [2048] * 16 + [1024, 3072, 4096] + [32768 - 8192] + [32768] * 6 + [1024] * 32):
+    for sizes in ([32768] * 8, [2048] * 16 + [1024, 3072, 4096] + [32768 - 8192] + [32768] * 5 + [1024] * 32):
         g, r = pb.CDownConvert(), ref_app.CDownConvert12()
         assert g.SetDataRate(61.44e6, 15000.0) == r.SetDataRate(61.44e6, 15000.0) == 60000.0
         g.SetFrequency(f); r.SetFrequency(f)
