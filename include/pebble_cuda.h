@@ -223,9 +223,41 @@ int pebble_fft_spectrum_batch_device(pebble_fft_t *h, int frames, int n, const d
 /* Window table + coherent gain exactly as WindowFunction::regenerate builds them (float-rounded
  * constants, windowfunction.cpp:51-235). w_out may be NULL. */
 double pebble_window(int window_type, int n, double *w_out);
+/* Which reference FFT class's contract the forward / inverse calls follow (fft.cpp:45-65 selects one at compile time):
+ * PEBBLE_FFT_FFTW  = FFTfftw (fftw.cpp): forward e^{-j}, inverse e^{+j}, both unnormalised;
+ * PEBBLE_FFT_OOURA = CFft (fftcute.cpp:183-277): fftForward swaps I and Q before Ooura's transform (:194-201), which makes
+ *                    its output the FFTW_FORWARD result with re and im exchanged; fftInverse (bitrv2conj + cftbsub) is again the
+ *                    e^{-j} transform, so inverse(forward(x)) = N * (x with I and Q swapped). fftSpectrum is the same for both. */
+enum { PEBBLE_FFT_FFTW = 0, PEBBLE_FFT_OOURA = 1 };
+int pebble_fft_set_backend(pebble_fft_t *h, int backend);
 /* averaging state (m_fftPower, m_fftAmplitude: 2*fft_size doubles) */
 int pebble_fft_get_state(pebble_fft_t *h, double *buf, int64_t count);
 int pebble_fft_set_state(pebble_fft_t *h, const double *buf, int64_t count);
+
+/* ---- SignalSpectrum : the display-rate spectrum operator ------------------------------------------------------------------
+ * Replaces application/signalspectrum.h (class SignalSpectrum : ProcessStep), signalspectrum.cpp:6-133: two FFT objects
+ * (full-rate `unprocessed`, default 4096 bins, and the post-decimation `zoomed` / hi-res one, default 2048 bins), both
+ * BLACKMANHARRIS over bufferSize samples, each behind an update gate of 1000 / updatesPerSec milliseconds.
+ * create <-> SignalSpectrum(sampleRate, hiResSampleRate, bufferSize) with global->settings {numSpectrumBins,
+ * numHiResSpectrumBins, updatesPerSecond} (:8-33); unprocessed / zoomed <-> :63-106 (the first call of each only starts
+ * its timer; return 1 = a new spectrum was made, where the reference emits newFftData()); now_ms replaces QElapsedTimer.
+ * get_unprocessed / get_hires return the dB arrays (amplitude dB, -f..0..+f, bin_count doubles), valid until the next call. */
+typedef struct pebble_spectrum pebble_spectrum_t;
+pebble_spectrum_t *pebble_spectrum_create(unsigned sample_rate, unsigned hires_sample_rate, unsigned buffer_size, int num_bins,
+                                          int num_hires_bins, int updates_per_sec);
+void pebble_spectrum_destroy(pebble_spectrum_t *h);
+int pebble_spectrum_set_sample_rate(pebble_spectrum_t *h, unsigned sample_rate, unsigned hires_sample_rate);
+void pebble_spectrum_set_hires(pebble_spectrum_t *h, int on);
+void pebble_spectrum_set_updates_per_sec(pebble_spectrum_t *h, int updates_per_sec);
+int pebble_spectrum_unprocessed(pebble_spectrum_t *h, const double *in, int n, long long now_ms);
+int pebble_spectrum_zoomed(pebble_spectrum_t *h, const double *in, int n, long long now_ms);
+int pebble_spectrum_bin_count(const pebble_spectrum_t *h);
+int pebble_spectrum_hires_bin_count(const pebble_spectrum_t *h);
+int pebble_spectrum_overload(const pebble_spectrum_t *h);
+int pebble_spectrum_overrun(const pebble_spectrum_t *h);
+void pebble_spectrum_ack_update(pebble_spectrum_t *h);
+const double *pebble_spectrum_get_unprocessed(const pebble_spectrum_t *h);
+const double *pebble_spectrum_get_hires(const pebble_spectrum_t *h);
 
 /* Library extension (no reference counterpart): scalar gains fused into the FastFIR kernel's load and
  * store, used by the receiver chain for receiver.cpp:935-938 (gain restore) and AGC_OFF (agc.cpp:86-94). */

@@ -86,6 +86,22 @@ SIGNATURES = {
     "pebble_window": (c_dbl, [c_int, c_int, c_vp]),
     "pebble_fft_get_state": (c_int, [c_vp, c_vp, c_i64]),
     "pebble_fft_set_state": (c_int, [c_vp, c_vp, c_i64]),
+    "pebble_fft_set_backend": (c_int, [c_vp, c_int]),
+    # SignalSpectrum
+    "pebble_spectrum_create": (c_vp, [ctypes.c_uint, ctypes.c_uint, ctypes.c_uint, c_int, c_int, c_int]),
+    "pebble_spectrum_destroy": (None, [c_vp]),
+    "pebble_spectrum_set_sample_rate": (c_int, [c_vp, ctypes.c_uint, ctypes.c_uint]),
+    "pebble_spectrum_set_hires": (None, [c_vp, c_int]),
+    "pebble_spectrum_set_updates_per_sec": (None, [c_vp, c_int]),
+    "pebble_spectrum_unprocessed": (c_int, [c_vp, c_vp, c_int, ctypes.c_longlong]),
+    "pebble_spectrum_zoomed": (c_int, [c_vp, c_vp, c_int, ctypes.c_longlong]),
+    "pebble_spectrum_bin_count": (c_int, [c_vp]),
+    "pebble_spectrum_hires_bin_count": (c_int, [c_vp]),
+    "pebble_spectrum_overload": (c_int, [c_vp]),
+    "pebble_spectrum_overrun": (c_int, [c_vp]),
+    "pebble_spectrum_ack_update": (None, [c_vp]),
+    "pebble_spectrum_get_unprocessed": (c_vp, [c_vp]),
+    "pebble_spectrum_get_hires": (c_vp, [c_vp]),
     # CFir
     "pebble_cfir_create": (c_vp, []),
     "pebble_cfir_destroy": (None, [c_vp]),

@@ -154,6 +154,7 @@ fft_c2c_kernel(const cpx *__restrict__ in, int n, const double *__restrict__ win
 
 struct pebble_fft {
     int N = 0, spb = 0, wtype = 14;
+    int backend = 0;                          // PEBBLE_FFT_FFTW / PEBBLE_FFT_OOURA: which reference class's contract
     double cg = 1.0, maxbin = 1.0, fs = 0.0;
     bool params_set = false;
     cpx *d_tw = nullptr;
@@ -195,11 +196,11 @@ template <int N> static cudaError_t spec_launch(pebble_fft *h, int frames, int n
     pebble::count_launch();
     return cudaGetLastError();
 }
-template <int N, bool INV> static cudaError_t c2c_launch(pebble_fft *h, int n, const cpx *in, cpx *out, cudaStream_t st) {
+template <int N, bool INV> static cudaError_t c2c_launch(pebble_fft *h, int n, const cpx *in, cpx *out, cudaStream_t st, bool allow_window = true) {
     const size_t smem = sizeof(cpx) * N;
     cudaError_t e = cudaFuncSetAttribute(fft_c2c_kernel<N, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    const bool windowed = !INV && h->wtype != PEBBLE_WINDOW_NONE && n == h->spb;
+    const bool windowed = allow_window && !INV && h->wtype != PEBBLE_WINDOW_NONE && n == h->spb;
     fft_c2c_kernel<N, INV><<<1, FftPlan<N>::THREADS, smem, st>>>(in, n, h->d_win, windowed ? 1 : 0, 0.9, out, h->d_flag[h->cur],
                                                                 h->d_flag[h->cur ^ 1], h->d_tw);
     pebble::count_launch();
@@ -267,6 +268,11 @@ int pebble_fft_params(pebble_fft_t *h, unsigned fft_size, double db_comp, double
     return 0;
 }
 int pebble_fft_size(const pebble_fft_t *h) { return h ? h->N : PEBBLE_ERR_ARG; }
+int pebble_fft_set_backend(pebble_fft_t *h, int backend) {
+    if (!h || (backend != PEBBLE_FFT_FFTW && backend != PEBBLE_FFT_OOURA)) return PEBBLE_ERR_ARG;
+    h->backend = backend;
+    return 0;
+}
 
 int pebble_fft_spectrum_batch_device(pebble_fft_t *h, int frames, int n, const double *d_in, double *d_out, int *d_flags,
                                      void *stream_v) {
@@ -312,7 +318,15 @@ static int fft_c2c_host(pebble_fft_t *h, const double *in, double *out, int n, b
     memcpy(h->stg.h_in, in, bi);
     PB_CUDA(cudaMemcpyAsync(h->stg.d_in, h->stg.h_in, bi, cudaMemcpyHostToDevice, h->stream), PEBBLE_ERR_CUDA);
     cudaError_t e;
-    if (inverse) {
+    if (inverse && h->backend == PEBBLE_FFT_OOURA) {
+        // CFft::fftInverse = bitrv2conj + cftbsub (fftcute.cpp:262-263): Ooura's "backward" transform is the e^{-j} one, i.e.
+        // the same sign as FFTW_FORWARD; no window on this path
+#define X(NN) c2c_launch<NN, false>(h, n, (const cpx *)h->stg.d_in, (cpx *)h->stg.d_out, h->stream, false)
+        e = FFT_DISPATCH(h, X);
+#undef X
+        h->cur ^= 1;
+        cudaMemcpyAsync(h->d_prev[h->cur], h->d_prev[h->cur ^ 1], sizeof(double) * (size_t)h->N, cudaMemcpyDeviceToDevice, h->stream);
+    } else if (inverse) {
 #define X(NN) c2c_launch<NN, true>(h, n, (const cpx *)h->stg.d_in, (cpx *)h->stg.d_out, h->stream)
         e = FFT_DISPATCH(h, X);
 #undef X
@@ -326,7 +340,14 @@ static int fft_c2c_host(pebble_fft_t *h, const double *in, double *out, int n, b
     PB_CUDA(e, PEBBLE_ERR_CUDA);
     PB_CUDA(cudaMemcpyAsync(h->stg.h_out, h->stg.d_out, bo, cudaMemcpyDeviceToHost, h->stream), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamSynchronize(h->stream), PEBBLE_ERR_CUDA);
-    memcpy(out, h->stg.h_out, bo);
+    if (!inverse && h->backend == PEBBLE_FFT_OOURA) {
+        // CFft::fftForward swaps I and Q of the windowed input before Ooura's transform (fftcute.cpp:194-201); for that
+        // transform's sign this equals the FFTW_FORWARD result with re and im exchanged, bin for bin
+        const double *src = (const double *)h->stg.h_out;
+        for (int i = 0; i < h->N; ++i) { out[2 * i] = src[2 * i + 1]; out[2 * i + 1] = src[2 * i]; }
+    } else {
+        memcpy(out, h->stg.h_out, bo);
+    }
     return h->N;
 }
 int pebble_fft_forward(pebble_fft_t *h, const double *in, double *out, int n) { return fft_c2c_host(h, in, out, n, false); }
@@ -353,5 +374,99 @@ int pebble_fft_set_state(pebble_fft_t *h, const double *buf, int64_t count) {
     PB_CUDA(cudaMemcpy(h->d_prev[h->cur], buf + h->N, sizeof(double) * (size_t)h->N, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
     return 0;
 }
+
+
+// ---- SignalSpectrum (application/signalspectrum.cpp:6-131): two FFT objects behind the display-rate gate -------------------
+struct pebble_spectrum {
+    pebble_fft *fft_un = nullptr, *fft_hi = nullptr;    // m_fftUnprocessed, m_fftHiRes
+    unsigned sample_rate = 0, hires_rate = 0, num_samples = 0;
+    int bins = 0, hires_bins = 0;
+    int updates_per_sec = 0;
+    long long timer_update = 0, hires_timer_update = 0;   // ms between spectra (1000 / updatesPerSec, integer division)
+    bool timer_valid = false, hires_timer_valid = false;
+    long long timer_t0 = 0, hires_timer_t0 = 0;
+    bool use_hires = false, overload = false, update_complete = true;
+    int overrun = 0;
+    std::vector<double> un, hi;                           // m_unprocessedSpectrum, m_hiResSpectrum
+};
+
+pebble_spectrum_t *pebble_spectrum_create(unsigned sample_rate, unsigned hires_sample_rate, unsigned buffer_size, int num_bins,
+                                          int num_hires_bins, int updates_per_sec) {
+    if (updates_per_sec <= 0 || num_bins <= 0 || num_hires_bins <= 0 || buffer_size == 0) {
+        pebble::set_error("spectrum: bad argument (the reference divides 1000 by updatesPerSec in its constructor)");
+        return nullptr;
+    }
+    pebble_spectrum *h = new pebble_spectrum();
+    h->fft_un = pebble_fft_create();
+    h->fft_hi = pebble_fft_create();
+    if (!h->fft_un || !h->fft_hi) { pebble_spectrum_destroy(h); return nullptr; }
+    h->num_samples = buffer_size; h->bins = num_bins; h->hires_bins = num_hires_bins;
+    h->updates_per_sec = updates_per_sec;
+    h->timer_update = h->hires_timer_update = 1000 / updates_per_sec;        // signalspectrum.cpp:32-33
+    if (pebble_spectrum_set_sample_rate(h, sample_rate, hires_sample_rate) < 0) { pebble_spectrum_destroy(h); return nullptr; }
+    return h;
+}
+void pebble_spectrum_destroy(pebble_spectrum_t *h) {
+    if (!h) return;
+    pebble_fft_destroy(h->fft_un);
+    pebble_fft_destroy(h->fft_hi);
+    delete h;
+}
+// SignalSpectrum::setSampleRate (signalspectrum.cpp:54-61): both objects BLACKMANHARRIS over numSamples
+int pebble_spectrum_set_sample_rate(pebble_spectrum_t *h, unsigned sample_rate, unsigned hires_sample_rate) {
+    if (!h) return PEBBLE_ERR_ARG;
+    h->sample_rate = sample_rate; h->hires_rate = hires_sample_rate;
+    int r = pebble_fft_params(h->fft_un, (unsigned)h->bins, 0.0, (double)sample_rate, (int)h->num_samples, PEBBLE_WINDOW_BLACKMANHARRIS);
+    if (r < 0) return r;
+    r = pebble_fft_params(h->fft_hi, (unsigned)h->hires_bins, 0.0, (double)hires_sample_rate, (int)h->num_samples, PEBBLE_WINDOW_BLACKMANHARRIS);
+    if (r < 0) return r;
+    h->bins = pebble_fft_size(h->fft_un);            // fftParams clamps to >= 2048 (fft.cpp:74-79)
+    h->hires_bins = pebble_fft_size(h->fft_hi);
+    h->un.assign((size_t)h->bins, 0.0);
+    h->hi.assign((size_t)h->hires_bins, 0.0);
+    return 0;
+}
+void pebble_spectrum_set_hires(pebble_spectrum_t *h, int on) { if (h) h->use_hires = on != 0; }
+// SignalSpectrum::setUpdatesPerSec (signalspectrum.cpp:124-133): 0 stops the updates and keeps the old interval
+void pebble_spectrum_set_updates_per_sec(pebble_spectrum_t *h, int u) {
+    if (!h) return;
+    h->updates_per_sec = u;
+    if (u > 0) h->timer_update = h->hires_timer_update = 1000 / u;
+}
+// SignalSpectrum::unprocessed (signalspectrum.cpp:63-86). now_ms = the caller's monotonic clock in milliseconds (the
+// reference reads a QElapsedTimer). Returns 1 when a new spectrum was made (the reference emits newFftData()), 0 when the
+// gate skipped the call, < 0 on error.
+int pebble_spectrum_unprocessed(pebble_spectrum_t *h, const double *in, int n, long long now_ms) {
+    if (!h || !in) return PEBBLE_ERR_ARG;
+    if (!h->timer_valid) { h->timer_valid = true; h->timer_t0 = now_ms; return 0; }       // first call only starts the timer
+    if (h->updates_per_sec == 0 || now_ms - h->timer_t0 < h->timer_update) return 0;
+    h->timer_t0 = now_ms;
+    if (!h->update_complete) h->overrun++;
+    const int r = pebble_fft_spectrum(h->fft_un, in, h->un.data(), n);                     // makeSpectrum, :108-112
+    if (r < 0) return r;
+    h->overload = r == 1;
+    h->update_complete = false;
+    return 1;
+}
+// SignalSpectrum::zoomed (signalspectrum.cpp:89-106)
+int pebble_spectrum_zoomed(pebble_spectrum_t *h, const double *in, int n, long long now_ms) {
+    if (!h || !in) return PEBBLE_ERR_ARG;
+    if (!h->use_hires) return 0;
+    if (!h->hires_timer_valid) { h->hires_timer_valid = true; h->hires_timer_t0 = now_ms; return 0; }
+    if (h->updates_per_sec == 0 || now_ms - h->hires_timer_t0 < h->hires_timer_update) return 0;
+    h->hires_timer_t0 = now_ms;
+    const int r = pebble_fft_spectrum(h->fft_hi, in, h->hi.data(), n);
+    if (r < 0) return r;
+    h->overload = r == 1;
+    return 1;
+}
+int pebble_spectrum_bin_count(const pebble_spectrum_t *h) { return h ? h->bins : PEBBLE_ERR_ARG; }
+int pebble_spectrum_hires_bin_count(const pebble_spectrum_t *h) { return h ? h->hires_bins : PEBBLE_ERR_ARG; }
+int pebble_spectrum_overload(const pebble_spectrum_t *h) { return h ? (h->overload ? 1 : 0) : PEBBLE_ERR_ARG; }
+int pebble_spectrum_overrun(const pebble_spectrum_t *h) { return h ? h->overrun : PEBBLE_ERR_ARG; }
+// m_displayUpdateComplete: set false by unprocessed(), set true again by the consumer (the widget) through ack
+void pebble_spectrum_ack_update(pebble_spectrum_t *h) { if (h) h->update_complete = true; }
+const double *pebble_spectrum_get_unprocessed(const pebble_spectrum_t *h) { return h ? h->un.data() : nullptr; }
+const double *pebble_spectrum_get_hires(const pebble_spectrum_t *h) { return h ? h->hi.data() : nullptr; }
 
 }  // extern "C"

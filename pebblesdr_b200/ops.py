@@ -302,6 +302,10 @@ class FFT(_Handle):
     def getFFTSize(self):
         return check(lib.pebble_fft_size(self._h))
 
+    def setBackend(self, backend):
+        """0 = FFTfftw contract (default), 1 = CFft / Ooura contract (pebblelib/fftcute.cpp:183-277)."""
+        check(lib.pebble_fft_set_backend(self._h, backend), "setBackend")
+
     def fftForward(self, inb, outb, numSamples):
         check(lib.pebble_fft_forward(self._h, _host_ptr(inb, numSamples), _host_ptr(outb, self.getFFTSize(), True),
                                      numSamples), "fftForward")
@@ -329,6 +333,52 @@ class FFT(_Handle):
 
     def SetState(self, buf):
         check(lib.pebble_fft_set_state(self._h, buf.ctypes.data, buf.size))
+
+
+class SignalSpectrum(_Handle):
+    """application/signalspectrum.h: `unprocessed` + `zoomed` spectra behind the display-rate gate. now_ms = caller's clock."""
+    _destroy = staticmethod(lib.pebble_spectrum_destroy)
+
+    def __init__(self, sampleRate, hiResSampleRate, bufferSize, numSpectrumBins=4096, numHiResSpectrumBins=2048, updatesPerSecond=10):
+        super().__init__(lib.pebble_spectrum_create(int(sampleRate), int(hiResSampleRate), int(bufferSize), int(numSpectrumBins),
+                                                    int(numHiResSpectrumBins), int(updatesPerSecond)), "SignalSpectrum")
+
+    def setHiRes(self, on):
+        lib.pebble_spectrum_set_hires(self._h, int(bool(on)))
+
+    def setUpdatesPerSec(self, u):
+        lib.pebble_spectrum_set_updates_per_sec(self._h, int(u))
+
+    def setSampleRate(self, fs, hires_fs):
+        check(lib.pebble_spectrum_set_sample_rate(self._h, int(fs), int(hires_fs)), "setSampleRate")
+
+    def unprocessed(self, inb, numSamples, now_ms):
+        return check(lib.pebble_spectrum_unprocessed(self._h, _host_ptr(inb, numSamples), numSamples, int(now_ms)), "unprocessed")
+
+    def zoomed(self, inb, numSamples, now_ms):
+        return check(lib.pebble_spectrum_zoomed(self._h, _host_ptr(inb, numSamples), numSamples, int(now_ms)), "zoomed")
+
+    def binCount(self):
+        return check(lib.pebble_spectrum_bin_count(self._h))
+
+    def getOverload(self):
+        return bool(lib.pebble_spectrum_overload(self._h))
+
+    def overrun(self):
+        return lib.pebble_spectrum_overrun(self._h)
+
+    def ackUpdate(self):
+        lib.pebble_spectrum_ack_update(self._h)
+
+    def getUnprocessed(self):
+        n = self.binCount()
+        p = lib.pebble_spectrum_get_unprocessed(self._h)
+        return np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_double)), shape=(n,)).copy()
+
+    def getHiRes(self):
+        n = check(lib.pebble_spectrum_hires_bin_count(self._h))
+        p = lib.pebble_spectrum_get_hires(self._h)
+        return np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_double)), shape=(n,)).copy()
 
 
 class CFir(_Handle):

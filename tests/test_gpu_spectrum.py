@@ -124,3 +124,77 @@ def test_spectrum_db_edges_zero_tiny_and_full_scale_frames():
         assert np.max(np.abs(yg[~clipped] - yo[~clipped]), initial=0.0) <= 1e-6, f
     # last frame: zeros after a loud frame -> (0 + previous UNAVERAGED amplitude) / 2 (F14), not all -120
     assert yg.max() > -120.0 and np.count_nonzero(yg == -120.0) > size // 2
+
+
+def test_ooura_backend_contract_vs_compiled_cfft():
+    """class CFft (pebblelib/fftcute.cpp, the -DUSE_FFTCUTE build of oracle/build_ref.sh step 7). fftForward swaps I
+    and Q before Ooura's transform (:194-201), fftInverse is Ooura's e^{-j} 'backward' transform, fftSpectrum equals FFTW's."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    if not ref_app.cute_available():
+        pytest.skip("oracle/_ref/libpebbleref_cute.so not built")
+    for N, wtype in ((2048, 14), (4096, 12), (8192, 6)):
+        x = iq_noise_tones(N, 70 + N, 2e6, [(1.23e5, 0.4), (-3e5, 0.2)], noise=0.05)
+        c = ref_app.CFft(); c.fftParams(N, 0, 2e6, N, wtype)
+        g = pb.FFT(); g.fftParams(N, 0, 2e6, N, wtype); g.setBackend(1)
+        a, b = np.zeros(N, dtype=np.complex128), np.zeros(N, dtype=np.complex128)
+        c.fftForward(x, a, N); g.fftForward(x, b, N)
+        assert rel_rms(b, a) <= 1e-12
+        xi = iq_noise_tones(N, 80 + N, 2e6, [(5e4, 0.3)], noise=0.1)
+        c.fftInverse(xi, a, N); g.fftInverse(xi, b, N)
+        assert rel_rms(b, a) <= 1e-12
+        # and the FFTW contract differs from it exactly by the I/Q exchange
+        g2 = pb.FFT(); g2.fftParams(N, 0, 2e6, N, wtype)
+        b2 = np.zeros(N, dtype=np.complex128)
+        g2.fftForward(x, b2, N); g.fftForward(x, b, N)
+        assert np.array_equal(b, b2.imag + 1j * b2.real)
+        da, db = np.zeros(N), np.zeros(N)
+        for _ in range(3):
+            fa = c.fftSpectrum(x, da, N); fb = g.fftSpectrum(x, db, N)
+        un = (da > -120) & (da < 0)
+        assert fa == fb and np.max(np.abs(da[un] - db[un])) <= 1e-6 and np.array_equal(da[~un], db[~un])
+
+
+def test_signal_spectrum_operator_gate_and_two_ffts_vs_compiled_reference():
+    """SURVEY a10: SignalSpectrum::unprocessed / zoomed / setUpdatesPerSec / setSampleRate (signalspectrum.cpp:54-133) against
+    the class itself compiled from the reference with a settable clock in place of QElapsedTimer (oracle/qt_shim_app)."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    fs, hfs, n = 2000000, 62500, 2048
+    ref_app.set_clock_ms(0)
+    r = ref_app.SignalSpectrum(fs, hfs, n, bins=4096, hires_bins=2048, updates_per_sec=10)
+    g = pb.SignalSpectrum(fs, hfs, n, 4096, 2048, 10)
+    assert g.binCount() == 4096
+    r.setHiRes(True); g.setHiRes(True)
+    made = 0
+    # 1 ms steps would take long: walk the clock in uneven steps around the 100 ms gate, change the rate mid-way
+    clock = [0, 5, 99, 100, 150, 199, 200, 201, 330, 331, 400, 433, 434, 500, 533, 534, 535, 600, 635, 1000, 1001, 1100]
+    for i, t in enumerate(clock):
+        if i == 9:
+            r.setUpdatesPerSec(30); g.setUpdatesPerSec(30)          # 1000 / 30 = 33 ms (integer division, :129-130)
+        if i == 17:
+            r.setUpdatesPerSec(0); g.setUpdatesPerSec(0)            # 0: no more updates, interval kept (:126-131)
+        if i == 19:
+            r.setUpdatesPerSec(10); g.setUpdatesPerSec(10)
+        x = iq_noise_tones(n, 500 + i, fs, [(2e5 + 1e3 * i, 0.3), (-6e5, 0.05)], noise=0.01)
+        if i == 12:
+            x[7] = 0.95                                             # trips the overload flag (fft.cpp:138)
+        z = iq_noise_tones(n, 600 + i, hfs, [(1e3, 0.3)], noise=0.01)
+        ref_app.set_clock_ms(t)
+        before, ov_before = r.updatePending(), r.overrun()
+        r.unprocessed(x, n); r.zoomed(z, n)
+        new_ref = (r.updatePending() and not before) or r.overrun() > ov_before
+        new_g = g.unprocessed(x, n, t)
+        g.zoomed(z, n, t)
+        assert bool(new_g) == bool(new_ref), (i, t)
+        if new_g:
+            made += 1
+            a, b = r.getUnprocessed(), g.getUnprocessed()
+            if made > 1:      # the first spectrum averages with the reference's uninitialised buffer (fft.cpp:348-397)
+                un = (a > -120) & (a < 0)
+                assert np.max(np.abs(a[un] - b[un])) <= 1e-6 and np.array_equal(a[~un], b[~un])
+            assert r.getOverload() == g.getOverload()
+            if made % 3:
+                r.ackUpdate(); g.ackUpdate()                        # the widget marks the update consumed (else: an overrun next time)
+        assert r.overrun() == g.overrun()
+    assert made >= 8 and g.overrun() >= 2
