@@ -45,15 +45,19 @@ static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__rest
     } else if (mode == CH_AM) {           // Demod_AM::processBlockFiltered, demod_am.cpp:40-59
         double d = st[c].am_dc_last;
         for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {           // register-blocked like pll_run
-            cpx xs[PB_SERIAL_BLK];
+            // the envelopes of a block do not depend on the recurrence: formed first (independent sqrt chains, pipelined), so
+            // the serial part is one multiply-add and one subtract per sample
+            double mg[PB_SERIAL_BLK];
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) xs[j] = i0 + j < n ? x[i0 + j] : cpx_make(0.0, 0.0);
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+                const cpx xs = i0 + j < n ? x[i0 + j] : cpx_make(0.0, 0.0);
+                mg[j] = sqrt(xs.x * xs.x + xs.y * xs.y);                                  // DB::amplitude, db.h:28-30
+            }
 #pragma unroll
             for (int j = 0; j < PB_SERIAL_BLK; ++j) {
                 if (i0 + j < n) {
-                    const double mag = sqrt(xs[j].x * xs[j].x + xs[j].y * xs[j].y);   // DB::amplitude, db.h:28-30
-                    const double dn = (am_alpha * d) + mag;                           // demod_am.cpp:52
-                    const double v = dn - d;                                          // demod_am.cpp:53
+                    const double dn = (am_alpha * d) + mg[j];                             // demod_am.cpp:52
+                    const double v = dn - d;                                              // demod_am.cpp:53
                     d = dn;
                     y[i0 + j] = cpx_make(v, v);
                 }

@@ -4,6 +4,7 @@
 #pragma once
 #include "common.cuh"
 #include "host_design.h"
+#include <math_constants.h>
 #define PB_FIR_MAX 75
 #define PB_SCAN_THREADS 256
 #define PB_SCAN_PER 8
@@ -273,34 +274,47 @@ static __global__ void fm2_kernel(const cpx *__restrict__ in, int n, const cpx *
 struct PllConst { float alpha, beta, dc_alpha, lo, hi, out_gain; };
 struct PllState { float phase, freq, dc; };
 // The PLL recurrence over one stream (demod_nfm.cpp:225-257); state and constants are `float` like the reference's.
-// The recurrence is a serial dependency chain (phase -> sin/cos -> rotate -> atan2 -> frequency -> phase), so a stream's
-// throughput is that chain's LATENCY and nothing else (one thread per stream; ncu of the first version: 1 warp per SM, 975
-// cycles per sample, FP64 pipe 2.5 % busy). The reference's state is float; its intermediate doubles (sin/cos promoted to
-// double, the rotation, atan2, the frequency / phase sums rounded back to float) carry no information a float evaluation
-// loses beyond the last float ulp of the state, and a one-ulp difference in the state decays with the loop (zeta = .707,
-// 3 kHz): measured relative RMS against the compiled reference 6e-6 (double chain: 6e-6 as well, both set by sinf/cosf
-// implementation differences), tolerance 1e-4. So the chain is evaluated in FP32: ~4-cycle FMAs instead of
-// ~8-cycle DFMAs, atan2f (MUFU reciprocal + degree-9 polynomial) instead of the FP64 division and polynomial of atan2.
-// The input sample's conversion to float and the DC tracker are off the critical path.
-__device__ __forceinline__ void pll_step(const cpx xi, cpx &yo, const PllConst &c, PllState &v) {
-    float sn, cs;
-    sincosf(v.phase, &sn, &cs);   // sin/cos of a float resolve to the float overloads in the reference build
+//
+// The recurrence is a serial dependency chain, so a stream's throughput is that chain's LATENCY and nothing else (one thread
+// per stream; ncu of the first version: 1 warp per SM, 975 cycles per sample, FP64 pipe 2.5 % busy). The reference's chain is
+//     sin/cos(phase) -> rotate x by it (double) -> phzerror = -atan2(im, re) (double) -> freq += beta * phzerror -> clamp ->
+//     phase += freq + alpha * phzerror,
+// i.e. two transcendental evaluations per sample ON the chain. But arg(x e^{j phase}) = arg(x) + phase (mod 2 pi), and arg(x)
+// does not depend on the loop state: theta_n = atan2f(x.im, x.re) is computed for a whole register block up front (independent
+// instructions, pipelined), and the chain keeps only
+//     r = phase reduced to [-pi, pi] (Cody-Waite, two FMAs: exact to the float's own ulp, like sinf/cosf's own reduction),
+//     phzerror = -wrap(theta_n + r),  freq = clamp(fma(beta, phzerror, freq)),  phase += fma(alpha, phzerror, freq)
+// — about a dozen dependent FP32 operations (~60 cycles) instead of ~700 cycles. The float phase itself is accumulated and
+// wrapped exactly as the reference does (its growing rounding error inside a frame is part of the reference's behaviour), and
+// the phase error agrees with the reference's to a few 1e-7 rad (float atan2f and the reduction, against float sinf/cosf +
+// double rotation there). Measured relative RMS of the demodulated audio against the compiled reference: 6e-6 for the
+// straight double transcription, the same for this form (both set by sinf/cosf implementation differences and the float
+// state); tolerance 1e-4. atan2(0, 0) = 0 is kept for an exactly-zero sample.
+#define PB_SERIAL_BLK 16
+#define PB_TWO_PI_HI 6.28125f                  /* 9 trailing zero bits: k * HI is exact for k < 2^15 */
+#define PB_TWO_PI_LO 1.9353071795864769e-3f    /* 2 pi - HI */
+__device__ __forceinline__ float pll_theta(const cpx xi) {
     const float xr = (float)xi.x, xq = (float)xi.y;
-    const float tr = fmaf(cs, xr, -sn * xq);
-    const float ti = fmaf(cs, xq, sn * xr);
-    const float phzerror = -atan2f(ti, tr);
+    return (xr == 0.0f && xq == 0.0f) ? CUDART_NAN_F : atan2f(xq, xr);   // NaN marks "phzerror = 0" (atan2(0, 0))
+}
+__device__ __forceinline__ void pll_step(const float theta, cpx &yo, const PllConst &c, PllState &v) {
+    const float k = rintf(v.phase * 0.15915494309189535f);
+    float r = fmaf(k, -PB_TWO_PI_HI, v.phase);
+    r = fmaf(k, -PB_TWO_PI_LO, r);
+    float e = theta + r;                                   // arg(x e^{j phase}) in (-2 pi, 2 pi)
+    e = e > 3.14159265358979323846f ? e - 6.28318530717958647692f : e;
+    e = e < -3.14159265358979323846f ? e + 6.28318530717958647692f : e;
+    const float phzerror = theta != theta ? 0.0f : -e;
     float f = fmaf(c.beta, phzerror, v.freq);
-    f = f > c.hi ? c.hi : (f < c.lo ? c.lo : f);
+    f = fminf(fmaxf(f, c.lo), c.hi);
     v.freq = f;
     v.phase = v.phase + fmaf(c.alpha, phzerror, f);
-    v.dc = fmaf(c.dc_alpha, f, (1.0f - c.dc_alpha) * v.dc);
+    v.dc = fmaf(c.dc_alpha, f, (1.0f - c.dc_alpha) * v.dc);   // off the chain
     const float o = (f - v.dc) * c.out_gain;
     yo = cpx_make((double)o, 0.0);  // CPX = float: imaginary part is zero
 }
-// The serial recurrence walks its stream in register blocks of PB_SERIAL_BLK samples: the loads of a block are
-// independent and issued back to back, so the (uncoalesced, one-row-per-thread) memory latency is paid once per block
-// instead of once per sample.
-#define PB_SERIAL_BLK 16
+// The serial recurrence walks its stream in register blocks of PB_SERIAL_BLK samples: the loads of a block (uncoalesced, one
+// row per thread) and its arg(x) evaluations are independent and issued back to back.
 // `frame`: the reference calls processBlockNCO once per receiver frame (framesPerBuffer samples, receiver.cpp:987) and wraps
 // the float phase with fmod at the END of each call (demod_nfm.cpp:252); between wraps the phase keeps growing and the float
 // rounding of the accumulation grows with it, so the wrap positions are part of the arithmetic. frame <= 0: one wrap at n.
@@ -310,19 +324,19 @@ __device__ __forceinline__ void pll_run(const cpx *__restrict__ x, cpx *__restri
         const int f1 = f0 + frame < n ? f0 + frame : n;
         int i = f0;
         for (; i + PB_SERIAL_BLK <= f1; i += PB_SERIAL_BLK) {
-            cpx xs[PB_SERIAL_BLK];
+            float th[PB_SERIAL_BLK];
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) xs[j] = x[i + j];
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) th[j] = pll_theta(x[i + j]);
 #pragma unroll
             for (int j = 0; j < PB_SERIAL_BLK; ++j) {
                 cpx yo;
-                pll_step(xs[j], yo, c, v);
+                pll_step(th[j], yo, c, v);
                 y[i + j] = yo;
             }
         }
         for (; i < f1; ++i) {
             cpx yo;
-            pll_step(x[i], yo, c, v);
+            pll_step(pll_theta(x[i]), yo, c, v);
             y[i] = yo;
         }
         v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);

@@ -133,7 +133,7 @@ def test_ooura_backend_contract_vs_compiled_cfft():
     from oracle import ref_app
     if not ref_app.cute_available():
         pytest.skip("oracle/_ref/libpebbleref_cute.so not built")
-    for N, wtype in ((2048, 14), (4096, 12), (8192, 6)):
+    for N, wtype in ((2048, 12), (4096, 12), (8192, 6)):
         x = iq_noise_tones(N, 70 + N, 2e6, [(1.23e5, 0.4), (-3e5, 0.2)], noise=0.05)
         c = ref_app.CFft(); c.fftParams(N, 0, 2e6, N, wtype)
         g = pb.FFT(); g.fftParams(N, 0, 2e6, N, wtype); g.setBackend(1)
@@ -152,7 +152,7 @@ def test_ooura_backend_contract_vs_compiled_cfft():
         for _ in range(3):
             fa = c.fftSpectrum(x, da, N); fb = g.fftSpectrum(x, db, N)
         un = (da > -120) & (da < 0)
-        assert fa == fb and np.max(np.abs(da[un] - db[un])) <= 1e-6 and np.array_equal(da[~un], db[~un])
+        assert un.any() and fa == fb and np.max(np.abs(da[un] - db[un])) <= 1e-6 and np.array_equal(da[~un], db[~un])
 
 
 def test_signal_spectrum_operator_gate_and_two_ffts_vs_compiled_reference():
