@@ -188,6 +188,35 @@ int pebble_mixer_is_passthrough(const pebble_mixer_t *h);
 int pebble_mixer_process(pebble_mixer_t *h, int n, const double *in, double *out);
 int pebble_mixer_process_device(pebble_mixer_t *h, int n, const double *d_in, double *d_out, void *stream);
 
+/* ---- NCO : the quadrature oscillator primitive -------------------------------------------------------------------------------
+ * Replaces pebblelib/nco.h:20-60, nco.cpp:5-81.
+ * pebble_nco_set_frequency() <-> NCO::setFrequency (nco.cpp:16-45): the "safety net" limits |f| to (sampleRate / 2) - 1
+ *      (integer arithmetic) and the oscillator restarts at (1, 0); returns the frequency actually set. (Mixer::setFrequency,
+ *      mixer.cpp:25-39, and CDownConvert::SetFrequency, downconvert.cpp:102-113, do NOT clamp in the reference, and do not here.)
+ * pebble_nco_gen_single() <-> NCO::genSingle (nco.cpp:65-81): n x nextSample() (nco.h:29-38) scaled by `gain`, written over
+ *      (mix == 0) or added to (mix != 0) the buffer. */
+typedef struct pebble_nco pebble_nco_t;
+pebble_nco_t *pebble_nco_create(unsigned sample_rate, unsigned buffer_size);
+void pebble_nco_destroy(pebble_nco_t *h);
+double pebble_nco_set_frequency(pebble_nco_t *h, double f);
+double pebble_nco_frequency(const pebble_nco_t *h);
+int pebble_nco_gen_single(pebble_nco_t *h, double *io, int n, double gain, int mix);
+int pebble_nco_gen_single_device(pebble_nco_t *h, double *d_io, int n, double gain, int mix, void *stream);
+
+/* ---- CpxUtil : element-wise CPX vector helpers on DEVICE buffers ---------------------------------------------------------------
+ * Replace pebblelib/cpx.h:161-196, cpx.cpp:35-112 for callers that keep CPX buffers on the device between operator calls
+ * (the fused chain does not need them). copyCPX, scaleCPX, multCPX, addCPX, magCPX / sqrMagCPX (which keep in.re in out.im,
+ * cpx.cpp:82-96), clearCPX, decimateCPX (out[j] = in[j*by]; returns the output count). Results are bit-identical to the
+ * host functions. n counts CPX samples. */
+int pebble_cpx_copy_device(double *d_out, const double *d_in, long long n, void *stream);
+int pebble_cpx_scale_device(double *d_out, const double *d_in, double a, long long n, void *stream);
+int pebble_cpx_mult_device(double *d_out, const double *d_in, const double *d_in2, long long n, void *stream);
+int pebble_cpx_add_device(double *d_out, const double *d_in, const double *d_in2, long long n, void *stream);
+int pebble_cpx_mag_device(double *d_out, const double *d_in, long long n, void *stream);
+int pebble_cpx_sqrmag_device(double *d_out, const double *d_in, long long n, void *stream);
+int pebble_cpx_clear_device(double *d_out, long long n, void *stream);
+int pebble_cpx_decimate_device(double *d_out, const double *d_in, int by, long long n, void *stream);
+
 /* ---- FFT / SignalSpectrum : windowed FFT, unfold, 2-tap averaged amplitude dB -------------------------
  * Replaces pebblelib/fft.h:29-62 (class FFT + FFTfftw, fftw.cpp:17-81) and the FFT use of
  * application/signalspectrum.cpp:54-113.

@@ -42,6 +42,9 @@ def lib():
             "ref_decimator_build_chain": (ctypes.c_float, [_vp, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint]),
             "ref_decimator_dec_by2_stages": (_i, [_vp]), "ref_decimator_process": (_i, [_vp, _i, _vp, _vp]),
             "ref_mixer_set_frequency": (None, [_vp, _d]), "ref_mixer_process": (_i, [_vp, _i, _vp, _vp]),
+            "ref_nco_create": (_vp, [ctypes.c_uint, ctypes.c_uint]), "ref_nco_destroy": (None, [_vp]),
+            "ref_nco_set_frequency": (None, [_vp, _d]), "ref_nco_gen_single": (None, [_vp, _vp, ctypes.c_uint, _d, _i]),
+            "ref_cpx_op": (None, [_i, _vp, _vp, _vp, _d, _i]),
         }
         for k, (r, a) in sig.items():
             f = getattr(L, k)
@@ -199,3 +202,32 @@ def window(wtype, n):
     w = np.empty(n)
     cg = lib().ref_window(wtype, n, w.ctypes.data)
     return w, cg
+
+
+class NCO:
+    """pebblelib/nco.h: setFrequency (Nyquist safety net, nco.cpp:16-45) + genSingle (nco.cpp:65-81)."""
+
+    def __init__(self, fs, n):
+        self.h = lib().ref_nco_create(int(fs), int(n))
+
+    def setFrequency(self, f):
+        lib().ref_nco_set_frequency(self.h, float(f))
+
+    def genSingle(self, io, n, gain, mix):
+        lib().ref_nco_gen_single(self.h, io.ctypes.data, int(n), float(gain), 1 if mix else 0)
+
+    def __del__(self):
+        lib().ref_nco_destroy(self.h)
+
+
+CPX_OPS = {"copy": 0, "scale": 1, "mult": 2, "add": 3, "mag": 4, "sqrmag": 5, "clear": 6, "decimate": 7}
+
+
+def cpx_op(name, a, b=None, s=0.0):
+    """CpxUtil::{copy,scale,mult,add,mag,sqrMag,clear,decimate}CPX (pebblelib/cpx.cpp:35-112)."""
+    a = np.ascontiguousarray(a, dtype=np.complex128)
+    n = len(a)
+    out = np.zeros((n + int(s) - 1) // int(s) if name == "decimate" else n, dtype=np.complex128)
+    b = np.ascontiguousarray(b, dtype=np.complex128) if b is not None else a
+    lib().ref_cpx_op(CPX_OPS[name], out.ctypes.data, a.ctypes.data, b.ctypes.data, float(s), n)
+    return out

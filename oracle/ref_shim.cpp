@@ -36,6 +36,7 @@
 #include "fir.h"
 #include "mixer.h"
 #include "decimator.h"
+#include "nco.h"
 #endif
 #include <cstring>
 
@@ -139,5 +140,26 @@ int ref_decimator_process(void *h, int n, const double *in, double *out) {
     return (int)((Decimator *)h)->process((CPX *)in, (CPX *)out, (quint32)n);
 }
 
+// ---- NCO (pebblelib/nco.h) -------------------------------------------------------------------------
+void *ref_nco_create(unsigned fs, unsigned n) { return new NCO(fs, n); }
+void ref_nco_destroy(void *h) { delete (NCO *)h; }
+void ref_nco_set_frequency(void *h, double f) { ((NCO *)h)->setFrequency(f); }
+void ref_nco_gen_single(void *h, double *io, unsigned n, double gain, int mix) { ((NCO *)h)->genSingle((CPX *)io, n, gain, mix != 0); }
+
+// ---- CpxUtil (pebblelib/cpx.h:161-196, cpx.cpp:35-112) ---------------------------------------------
+// op: 0 copy, 1 scale, 2 mult, 3 add, 4 mag, 5 sqrMag, 6 clear, 7 decimate(by = (int)a)
+void ref_cpx_op(int op, double *out, const double *in, const double *in2, double a, int n) {
+    CPX *o = (CPX *)out; CPX *i1 = (CPX *)in; CPX *i2 = (CPX *)in2;
+    switch (op) {
+        case 0: CpxUtil::copyCPX(o, i1, n); break;
+        case 1: CpxUtil::scaleCPX(o, i1, a, n); break;
+        case 2: CpxUtil::multCPX(o, i1, i2, n); break;
+        case 3: CpxUtil::addCPX(o, i1, i2, n); break;
+        case 4: CpxUtil::magCPX(o, i1, n); break;
+        case 5: CpxUtil::sqrMagCPX(o, i1, n); break;
+        case 6: CpxUtil::clearCPX(o, n); break;
+        default: CpxUtil::decimateCPX(o, i1, (int)a, n); break;
+    }
+}
 #endif  // REF_HAVE_REST
 }  // extern "C"

@@ -74,6 +74,21 @@ SIGNATURES = {
     "pebble_mixer_is_passthrough": (c_int, [c_vp]),
     "pebble_mixer_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "pebble_mixer_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    # NCO + CpxUtil
+    "pebble_nco_create": (c_vp, [ctypes.c_uint, ctypes.c_uint]),
+    "pebble_nco_destroy": (None, [c_vp]),
+    "pebble_nco_set_frequency": (c_dbl, [c_vp, c_dbl]),
+    "pebble_nco_frequency": (c_dbl, [c_vp]),
+    "pebble_nco_gen_single": (c_int, [c_vp, c_vp, c_int, c_dbl, c_int]),
+    "pebble_nco_gen_single_device": (c_int, [c_vp, c_vp, c_int, c_dbl, c_int, c_vp]),
+    "pebble_cpx_copy_device": (c_int, [c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_scale_device": (c_int, [c_vp, c_vp, c_dbl, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_mult_device": (c_int, [c_vp, c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_add_device": (c_int, [c_vp, c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_mag_device": (c_int, [c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_sqrmag_device": (c_int, [c_vp, c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_clear_device": (c_int, [c_vp, ctypes.c_longlong, c_vp]),
+    "pebble_cpx_decimate_device": (c_int, [c_vp, c_vp, c_int, ctypes.c_longlong, c_vp]),
     # FFT / SignalSpectrum
     "pebble_fft_create": (c_vp, []),
     "pebble_fft_destroy": (None, [c_vp]),

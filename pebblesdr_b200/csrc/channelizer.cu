@@ -25,6 +25,20 @@ struct ChanState {      // per-channel demod state
     double am_dc_last;  // Demod_AM::m_amDcLast (demod_am.cpp:52-54)
 };
 
+// sqrt(x), x >= 0, without the library routine's branches: float rsqrt seed (2^-22), two Newton steps on 1/sqrt (2^-85), one
+// correction of x * r: within 1 ulp of the correctly rounded root. Outside the float range (never for IQ envelopes) and for
+// 0 it falls back to sqrt().
+__device__ __forceinline__ double pb_sqrt_newton(double x) {
+    if (!(x > 1e-36 && x < 1e36)) return sqrt(x);
+    double r = (double)rsqrtf((float)x);
+    const double hx = 0.5 * x;
+    r = fma(r, fma(-hx, r * r, 0.5), r);
+    r = fma(r, fma(-hx, r * r, 0.5), r);
+    double s = x * r;
+    s = fma(fma(-s, s, x), 0.5 * r, s);
+    return s;
+}
+
 // one thread per channel: in/out rows of `stride` cpx
 static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__restrict__ out, int n, long long stride, int nch,
                                          const int *__restrict__ modes, const int *__restrict__ order, int slots,
@@ -44,15 +58,18 @@ static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__rest
         st[c].pll = v;
     } else if (mode == CH_AM) {           // Demod_AM::processBlockFiltered, demod_am.cpp:40-59
         double d = st[c].am_dc_last;
-        for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {           // register-blocked like pll_run
-            // the envelopes of a block do not depend on the recurrence: formed first (independent sqrt chains, pipelined), so
-            // the serial part is one multiply-add and one subtract per sample
+        cpx cur[PB_SERIAL_BLK], nxt[PB_SERIAL_BLK];               // register double buffer, as in pll_run
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = j < n ? x[j] : cpx_make(0.0, 0.0);
+        for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {
+#pragma unroll
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) nxt[j] = i0 + PB_SERIAL_BLK + j < n ? x[i0 + PB_SERIAL_BLK + j] : cpx_make(0.0, 0.0);
+            // the envelopes of a block do not depend on the recurrence: formed first (independent, pipelined), so the serial
+            // part is one multiply-add and one subtract per sample. sqrt: branch-free Newton form (the library routine's
+            // special-case branches serialise the 16 evaluations); <= 1 ulp from the correctly rounded value.
             double mg[PB_SERIAL_BLK];
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) {
-                const cpx xs = i0 + j < n ? x[i0 + j] : cpx_make(0.0, 0.0);
-                mg[j] = sqrt(xs.x * xs.x + xs.y * xs.y);                                  // DB::amplitude, db.h:28-30
-            }
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) mg[j] = pb_sqrt_newton(cur[j].x * cur[j].x + cur[j].y * cur[j].y);   // DB::amplitude, db.h:28-30
 #pragma unroll
             for (int j = 0; j < PB_SERIAL_BLK; ++j) {
                 if (i0 + j < n) {
@@ -62,6 +79,8 @@ static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__rest
                     y[i0 + j] = cpx_make(v, v);
                 }
             }
+#pragma unroll
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = nxt[j];
         }
         st[c].am_dc_last = d;
     } else {                              // USB/LSB/...: Demod::processBlock returns `in` (demod.cpp:127-138)

@@ -293,9 +293,28 @@ struct PllState { float phase, freq, dc; };
 #define PB_SERIAL_BLK 16
 #define PB_TWO_PI_HI 6.28125f                  /* 9 trailing zero bits: k * HI is exact for k < 2^15 */
 #define PB_TWO_PI_LO 1.9353071795864769e-3f    /* 2 pi - HI */
+// arg(x) in float, branch-free (atan2f's special-case branches would serialise the block's 16 independent evaluations):
+// odd minimax polynomial for atan on [0, 1] (max abs error 6.4e-8) + octant fix-up; 2-ulp division.
 __device__ __forceinline__ float pll_theta(const cpx xi) {
     const float xr = (float)xi.x, xq = (float)xi.y;
-    return (xr == 0.0f && xq == 0.0f) ? CUDART_NAN_F : atan2f(xq, xr);   // NaN marks "phzerror = 0" (atan2(0, 0))
+    const float ax = fabsf(xr), ay = fabsf(xq);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float a = __fdividef(mn, mx);
+    const float s = a * a;
+    float r = 0.0027856871f;
+    r = fmaf(r, s, -0.0158660002f);
+    r = fmaf(r, s, 0.0424722321f);
+    r = fmaf(r, s, -0.0749753043f);
+    r = fmaf(r, s, 0.106448799f);
+    r = fmaf(r, s, -0.142070308f);
+    r = fmaf(r, s, 0.199934542f);
+    r = fmaf(r, s, -0.333331466f);
+    r = r * s;
+    r = fmaf(r, a, a);
+    r = ay > ax ? 1.57079632679489661923f - r : r;
+    r = xr < 0.0f ? 3.14159265358979323846f - r : r;
+    r = copysignf(r, xq);
+    return mx == 0.0f ? CUDART_NAN_F : r;   // NaN marks "phzerror = 0" (atan2(0, 0) = 0 in the reference)
 }
 __device__ __forceinline__ void pll_step(const float theta, cpx &yo, const PllConst &c, PllState &v) {
     const float k = rintf(v.phase * 0.15915494309189535f);
@@ -323,16 +342,29 @@ __device__ __forceinline__ void pll_run(const cpx *__restrict__ x, cpx *__restri
     for (int f0 = 0; f0 < n; f0 += frame) {
         const int f1 = f0 + frame < n ? f0 + frame : n;
         int i = f0;
+        // register double buffer: block b+1's loads (one row per thread: uncoalesced, L2 / DRAM latency) are in flight while
+        // block b is computed (ncu of the un-prefetched form: 41 % of the stall samples on the first use of the loaded data)
+        cpx cur[PB_SERIAL_BLK], nxt[PB_SERIAL_BLK];
+        if (i + PB_SERIAL_BLK <= f1) {
+#pragma unroll
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = x[i + j];
+        }
         for (; i + PB_SERIAL_BLK <= f1; i += PB_SERIAL_BLK) {
+            if (i + 2 * PB_SERIAL_BLK <= f1) {
+#pragma unroll
+                for (int j = 0; j < PB_SERIAL_BLK; ++j) nxt[j] = x[i + PB_SERIAL_BLK + j];
+            }
             float th[PB_SERIAL_BLK];
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) th[j] = pll_theta(x[i + j]);
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) th[j] = pll_theta(cur[j]);
 #pragma unroll
             for (int j = 0; j < PB_SERIAL_BLK; ++j) {
                 cpx yo;
                 pll_step(th[j], yo, c, v);
                 y[i + j] = yo;
             }
+#pragma unroll
+            for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = nxt[j];
         }
         for (; i < f1; ++i) {
             cpx yo;

@@ -737,3 +737,97 @@ int pebble_mixer_process(pebble_mixer_t *m, int n, const double *in, double *out
 }
 
 }  // extern "C"
+
+// ---- NCO (pebblelib/nco.h:20-60, nco.cpp:5-81): the oscillator primitive with its Nyquist safety net ----------------------
+struct pebble_nco {
+    pebble_downconvert *dc;
+    double frequency;          // m_frequency after the clamp
+    unsigned sample_rate, buffer_size;
+    cpx *d_buf = nullptr; size_t cap = 0;
+};
+
+// out[i] = (mix ? in[i] : 0) + gain * Osc_i, Osc_i = NCO::nextSample (nco.h:29-38) = r_i exp(j (i+1) theta)
+__global__ void __launch_bounds__(256) nco_gen_kernel(const DcChain *__restrict__ ch, const cpx *__restrict__ in, cpx *__restrict__ out,
+                                                      long long n, uint64_t phase_hi, uint64_t phase_lo, long long stream_pos, double gain, int mix) {
+    const long long i0 = (long long)blockIdx.x * 256 * 8 + threadIdx.x;
+    if (i0 >= n) return;
+    const cpx seed = dc_phase_to_osc(dc_phase_at(phase_hi, phase_lo, ch->turn_hi, ch->turn_lo, (uint64_t)(i0 + 1)));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const long long i = i0 + (long long)k * 256;
+        if (i < n) {
+            const long long g = stream_pos + i;
+            const double r = g >= PB_DC_RTAB ? ch->r_inf : ch->rtab[g];
+            const cpx o = cpx_scale(cpx_mul(seed, ch->wtab[k]), r * gain);
+            out[i] = mix ? cpx_add(in[i], o) : o;
+        }
+    }
+}
+
+extern "C" {
+pebble_nco_t *pebble_nco_create(unsigned sample_rate, unsigned buffer_size) {
+    if (sample_rate == 0) return nullptr;
+    pebble_downconvert *dc = pebble_downconvert_create();
+    if (!dc) return nullptr;
+    pebble_nco *h = new pebble_nco();
+    h->dc = dc; h->sample_rate = sample_rate; h->buffer_size = buffer_size;
+    dc->in_rate = (double)sample_rate;
+    dc->lens.clear();
+    pebble_host::dc_fill_chain(dc->chain, dc->lens);
+    pebble_nco_set_frequency(h, 0.0);
+    return h;
+}
+void pebble_nco_destroy(pebble_nco_t *h) {
+    if (!h) return;
+    pebble_downconvert_destroy(h->dc);
+    cudaFree(h->d_buf);
+    delete h;
+}
+// NCO::setFrequency (nco.cpp:16-45): |f| is limited to (sampleRate / 2) - 1 (integer arithmetic) and the oscillator restarts
+double pebble_nco_set_frequency(pebble_nco_t *h, double f) {
+    if (!h) return 0.0;
+    const int nyquist = (int)(h->sample_rate / 2) - 1;
+    if (f < -nyquist) f = -nyquist;
+    else if (f > nyquist) f = nyquist;
+    h->frequency = f;
+    h->dc->nco_freq = f;               // m_oscInc = TWOPI * m_frequency / m_sampleRate: not negated (contrast Mixer, mixer.cpp:31)
+    dc_update_osc(h->dc);
+    h->dc->phase_hi = h->dc->phase_lo = 0;
+    h->dc->stream_pos = 0;
+    return f;
+}
+double pebble_nco_frequency(const pebble_nco_t *h) { return h ? h->frequency : 0.0; }
+// NCO::genSingle (nco.cpp:65-81): n consecutive nextSample() values times `gain`, written to (mix == 0) or added to (mix != 0) io
+int pebble_nco_gen_single_device(pebble_nco_t *h, double *d_io, int n, double gain, int mix, void *stream_v) {
+    if (!h || n < 0 || (n && !d_io)) { pebble::set_error("nco: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream_v;
+    pebble_downconvert *dc = h->dc;
+    if (dc->dirty) {
+        PB_CUDA(cudaMemcpyAsync(dc->d_chain, &dc->chain, sizeof(DcChain), cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
+        dc->dirty = false;
+    }
+    nco_gen_kernel<<<(n + 2047) / 2048, 256, 0, st>>>(dc->d_chain, (const cpx *)d_io, (cpx *)d_io, n, dc->phase_hi, dc->phase_lo, dc->stream_pos,
+                                                     gain, mix);
+    pebble::count_launch();
+    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    pebble_host::phase_advance(dc->phase_hi, dc->phase_lo, dc->chain.turn_hi, dc->chain.turn_lo, (uint64_t)n);
+    dc->stream_pos += n;
+    return n;
+}
+int pebble_nco_gen_single(pebble_nco_t *h, double *io, int n, double gain, int mix) {
+    if (!h || n < 0 || (n && !io)) { pebble::set_error("nco: bad argument"); return PEBBLE_ERR_ARG; }
+    if (n == 0) return 0;
+    if ((size_t)n > h->cap) {
+        cudaFree(h->d_buf); h->d_buf = nullptr; h->cap = 0;
+        PB_CUDA(cudaMalloc(&h->d_buf, sizeof(cpx) * (size_t)n), PEBBLE_ERR_CUDA);
+        h->cap = (size_t)n;
+    }
+    if (mix) PB_CUDA(cudaMemcpyAsync(h->d_buf, io, sizeof(cpx) * (size_t)n, cudaMemcpyHostToDevice, h->dc->stream), PEBBLE_ERR_CUDA);
+    const int r = pebble_nco_gen_single_device(h, (double *)h->d_buf, n, gain, mix, h->dc->stream);
+    if (r < 0) return r;
+    PB_CUDA(cudaMemcpyAsync(io, h->d_buf, sizeof(cpx) * (size_t)n, cudaMemcpyDeviceToHost, h->dc->stream), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamSynchronize(h->dc->stream), PEBBLE_ERR_CUDA);
+    return r;
+}
+}  // extern "C"

@@ -335,6 +335,54 @@ class FFT(_Handle):
         check(lib.pebble_fft_set_state(self._h, buf.ctypes.data, buf.size))
 
 
+class NCO(_Handle):
+    """pebblelib/nco.h: the oscillator primitive. setFrequency clamps to +-((sampleRate / 2) - 1) (nco.cpp:16-45)."""
+    _destroy = staticmethod(lib.pebble_nco_destroy)
+
+    def __init__(self, sampleRate, bufferSize):
+        super().__init__(lib.pebble_nco_create(int(sampleRate), int(bufferSize)), "NCO")
+
+    def setFrequency(self, f):
+        return lib.pebble_nco_set_frequency(self._h, float(f))
+
+    def frequency(self):
+        return lib.pebble_nco_frequency(self._h)
+
+    def genSingle(self, io, numSamples, dbGain, mix):
+        if _is_cuda_tensor(io):
+            return check(lib.pebble_nco_gen_single_device(self._h, _dev_ptr(io, numSamples), numSamples, dbGain, int(bool(mix)),
+                                                          _stream_ptr()), "genSingle")
+        return check(lib.pebble_nco_gen_single(self._h, _host_ptr(io, numSamples, True), numSamples, dbGain, int(bool(mix))), "genSingle")
+
+
+def cpx_util(name, a, b=None, s=0.0):
+    """CpxUtil helpers on CUDA tensors (complex128): copy, scale, mult, add, mag, sqrmag, clear, decimate."""
+    n = a.numel()
+    st = _stream_ptr()
+    if name == "decimate":
+        out = torch.zeros((n + int(s) - 1) // int(s), dtype=torch.complex128, device=a.device)
+        check(lib.pebble_cpx_decimate_device(out.data_ptr(), a.data_ptr(), int(s), n, st), name)
+        return out
+    out = torch.empty_like(a)
+    if name == "copy":
+        check(lib.pebble_cpx_copy_device(out.data_ptr(), a.data_ptr(), n, st), name)
+    elif name == "scale":
+        check(lib.pebble_cpx_scale_device(out.data_ptr(), a.data_ptr(), float(s), n, st), name)
+    elif name == "mult":
+        check(lib.pebble_cpx_mult_device(out.data_ptr(), a.data_ptr(), b.data_ptr(), n, st), name)
+    elif name == "add":
+        check(lib.pebble_cpx_add_device(out.data_ptr(), a.data_ptr(), b.data_ptr(), n, st), name)
+    elif name == "mag":
+        check(lib.pebble_cpx_mag_device(out.data_ptr(), a.data_ptr(), n, st), name)
+    elif name == "sqrmag":
+        check(lib.pebble_cpx_sqrmag_device(out.data_ptr(), a.data_ptr(), n, st), name)
+    elif name == "clear":
+        check(lib.pebble_cpx_clear_device(out.data_ptr(), n, st), name)
+    else:
+        raise PebbleError("unknown CpxUtil op " + name)
+    return out
+
+
 class SignalSpectrum(_Handle):
     """application/signalspectrum.h: `unprocessed` + `zoomed` spectra behind the display-rate gate. now_ms = caller's clock."""
     _destroy = staticmethod(lib.pebble_spectrum_destroy)
