@@ -220,8 +220,10 @@ int pebble_cpx_decimate_device(double *d_out, const double *d_in, int by, long l
 /* ---- FFT / SignalSpectrum : windowed FFT, unfold, 2-tap averaged amplitude dB -------------------------
  * Replaces pebblelib/fft.h:29-62 (class FFT + FFTfftw, fftw.cpp:17-81) and the FFT use of
  * application/signalspectrum.cpp:54-113.
- * pebble_fft_params()    <-> FFT::fftParams       fft.cpp:67-118  (size clamped to [2048,65535] there;
- *                            here: power of two in [2048, 131072], other sizes -> PEBBLE_ERR_ARG)
+ * pebble_fft_params()    <-> FFT::fftParams       fft.cpp:67-118  (the reference clamps the size to [2048, 65535] and accepts
+ *                            any value in between; here sizes below 2048 are raised to 2048 like there, and the supported
+ *                            sizes are 2048, 4096 and 8192 — the transforms that fit one CTA's shared memory; 16384 and
+ *                            32768 and non-powers of two return PEBBLE_ERR_ARG)
  * pebble_fft_forward()   <-> FFTfftw::fftForward  fftw.cpp:31-46  (window applied iff n==samples_per_buffer
  *                            and window!=NONE, fft.cpp:129-157; zero-padded; natural bin order)
  * pebble_fft_inverse()   <-> FFTfftw::fftInverse  fftw.cpp:49-67  (unnormalised)

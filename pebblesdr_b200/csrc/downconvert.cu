@@ -197,7 +197,9 @@ static double dc_set_rate(pebble_downconvert *h, double in_rate, double max_bw, 
             const int c = env_int("PEBBLE_DC_CHUNK", 0);
             if (c == 512 || c == 1024 || c == 2048 || c == 4096) h->chunk = c;
         }
-        // DeleteFilters + new stages: the delay lines restart from zero (downconvert.cpp:150)
+        // DeleteFilters + new stages: the delay lines restart from zero (downconvert.cpp:150). A process call may still be in
+        // flight on a caller's (non-blocking) stream: wait for it, as the reference's m_Mutex does (downconvert.cpp:148,322)
+        cudaDeviceSynchronize();
         const size_t sbytes = sizeof(cpx) * PB_DC_MAX_STAGES * PB_DC_PREFIX;
         cudaMemset(h->d_state[0], 0, sbytes);
         cudaMemset(h->d_state[1], 0, sbytes);

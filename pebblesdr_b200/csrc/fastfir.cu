@@ -262,8 +262,14 @@ __global__ void fastfir_state_kernel(const cpx *__restrict__ state, int s0, cons
     if (i < count) new_state[i] = vs_load(state, s0, in, start + i);
 }
 
+typedef void (*FfKern2048)(const cpx *, int, const cpx *, cpx *, const cpx *, const cpx *, int, int, long long, long long, int, FfCarry,
+                           FfAgg);
 struct pebble_fastfir {
     int N, fir, L;
+    // launch configuration of the fused 2048 kernels, resolved at the handle's first process call on ITS device
+    int cfg_occ2 = 0, cfg_waves = 2;
+    bool cfg_triple = true;
+    FfKern2048 cfg_kern = nullptr;
     // reference members (fastfir.cpp:140-143): "unset" sentinels so the first setup always runs
     double lo, hi, offset, fs;
     cpx *d_tw, *d_hpos, *d_ht, *d_taps, *d_state[2];   // d_ht: H in the fused 2048 kernel's order
@@ -312,10 +318,11 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
     if (grid < 1) grid = 1;
     if (N == 2048 && !getenv("PEBBLE_FF_GENERIC")) {
         const size_t smem2 = sizeof(cpx) * (2048 + 64), smem4 = sizeof(cpx) * PB_FF4_SMEM_CPX;
-        static int occ2 = 0, waves = 2;
-        static bool triple = true;
-        static void (*kern)(const cpx *, int, const cpx *, cpx *, const cpx *, const cpx *, int, int, long long, long long,
-                            int, FfCarry, FfAgg) = nullptr;
+        // per HANDLE, not function-static: the shared-memory opt-in below is a per-device attribute, and a process may hold
+        // handles on several devices (pebble_set_device); a handle is used by one thread at a time
+        int &occ2 = h->cfg_occ2, &waves = h->cfg_waves;
+        bool &triple = h->cfg_triple;
+        FfKern2048 &kern = h->cfg_kern;
         if (!occ2) {
             const char *mb = getenv("PEBBLE_FF_MINB");   // registers per thread: 4 -> 128, 3 -> 168, 2 -> 255
             const int minb = mb ? atoi(mb) : 4;
@@ -343,7 +350,7 @@ static cudaError_t ff_launch_process(pebble_fastfir *h, const cpx *in, cpx *out,
         // dependent chain and every CTA first loads 64 KB of H: take it only when each 256-thread group gets at least
         // `big_min` big blocks, otherwise the call is latency-bound and ONE launch of the 2048 kernel is faster
         // (the receiver tail: 512 reference blocks per step, 29 us as big + rest vs ~10 us).
-        static int big_min = getenv("PEBBLE_FF_BIGMIN") ? atoi(getenv("PEBBLE_FF_BIGMIN")) : 4;
+        const int big_min = getenv("PEBBLE_FF_BIGMIN") ? atoi(getenv("PEBBLE_FF_BIGMIN")) : 4;
         const int ctas_big = streams > 1 ? (pebble::num_sms() + streams - 1) / streams : pebble::num_sms();
         // (the AM aggregate epilogue lives in the 2048 kernel only: such calls are the receiver tail, always latency-bound)
         const int nbig = (triple && !h->agg_map && nblocks / 3 >= 2 * ctas_big * big_min) ? nblocks / 3 : 0;
@@ -463,7 +470,10 @@ int pebble_fastfir_setup(pebble_fastfir_t *h, double lo, double hi, double offse
     h->lo = lo; h->hi = hi; h->offset = offset; h->fs = fs;
     std::vector<double> taps;
     if (!pebble_host::fastfir_design(h->N, h->fir, lo, hi, offset, fs, taps)) return 2;  // fastfir.cpp:208-216
-    // in-order with any process call already queued on the legacy stream
+    // The filter tables are rewritten below. Process calls enqueue on caller streams (non-blocking ones included) without
+    // synchronising, so wait for everything in flight first: the reference serialises the same pair with m_Mutex
+    // (fastfir.cpp:218,290).
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaMemcpy(h->d_taps, taps.data(), sizeof(cpx) * (size_t)h->N, cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
     cudaError_t e = h->lf ? lf_build_filter(h->lf, h->d_taps, h->d_hpos, 0)
                           : FF_DISPATCH(h, ff_launch_filter<2048>(h, 0), ff_launch_filter<4096>(h, 0), ff_launch_filter<8192>(h, 0));

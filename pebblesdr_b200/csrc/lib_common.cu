@@ -20,16 +20,16 @@ bool cuda_ok(cudaError_t e, const char *what) {
 }
 void count_launch(int n) { g_launches += (uint64_t)n; }
 int num_sms() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaDeviceProp p;
-        if (cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&p, dev) == cudaSuccess)
-            sms = p.multiProcessorCount;
-        else
-            sms = 148;
+    // per device ordinal: a process may drive several devices (pebble_set_device)
+    static std::atomic<int> sms[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int v = sms[dev].load(std::memory_order_relaxed);
+    if (!v) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        sms[dev].store(v, std::memory_order_relaxed);
     }
-    return sms;
+    return v;
 }
 bool Staging::reserve(size_t bi, size_t bo) {
     if (bi > cap_in) {
