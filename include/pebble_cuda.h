@@ -366,6 +366,34 @@ int pebble_resampler_set_state(pebble_resampler_t *h, const void *buf, int64_t b
 int pebble_resampler_plan(double float_time, double rate, int n, double *float_time_out);
 int pebble_resampler_plan_times(double float_time, double rate, int n, double *times, int max);
 
+/* ---- CIir, DCRemoval, IQBalance, squelch (the cheap steps either side of the path) --------------------------------
+ * pebble_iir_*  <-> pebblelib/iir.h:17-45 (class CIir): init <-> InitLP / InitHP / InitBP / InitBR (iir.cpp:50-170), process <->
+ *      ProcessFilter(int, TYPECPX*, TYPECPX*) (iir.cpp:191-206; re and im through the same biquad with separate delay values).
+ *      DCRemoval (application/dcremoval.cpp:3-18) is pebble_iir_init(h, PEBBLE_IIR_HP, 10, 0.7071, sampleRate) + process; a
+ *      disabled DCRemoval copies (dcremoval.cpp:11-14). The biquad is a linear recurrence and is evaluated as a three-level
+ *      scan (prefilter.cu); each sample is formed with the reference's own operations, the carried-in state is a re-associated
+ *      sum. For filters with poles ~1e-6 from the unit circle (the DC blocker at MHz rates) the reference's direct form 2 itself
+ *      keeps ~8 digits, and so does the agreement between the two.
+ * pebble_iqbalance_process_device() <-> IQBalance::ProcessBlock (application/iqbalance.cpp:67-88) for n / block_len consecutive
+ *      blocks of numSamples (the correction recurrence restarts in every block there). Bit-identical to the reference.
+ * pebble_sigstrength_fd_estimate_device() <-> SignalStrength::fdEstimate (application/signalstrength.cpp:289-380) for nch
+ *      channels over one spectrum (Receiver: the unprocessed spectrum, receiver.cpp:959-961), without its 100 ms display
+ *      timer; out5[k] = {peakDb, avgDb, snrDb, floorDb, open}, open = avgDb >= squelch_db (receiver.cpp:963-966). */
+enum { PEBBLE_IIR_LP = 0, PEBBLE_IIR_HP = 1, PEBBLE_IIR_BP = 2, PEBBLE_IIR_BR = 3 };
+typedef struct pebble_iir pebble_iir_t;
+pebble_iir_t *pebble_iir_create(void);
+void pebble_iir_destroy(pebble_iir_t *h);
+int pebble_iir_init(pebble_iir_t *h, int kind, double f0, double q, double sample_rate);
+int pebble_iir_get_coefficients(const pebble_iir_t *h, double *a1a2b0b1b2);
+int pebble_iir_process(pebble_iir_t *h, int n, const double *in, double *out);
+int pebble_iir_process_device(pebble_iir_t *h, int n, const double *d_in, double *d_out, void *stream);
+int pebble_iir_get_state(pebble_iir_t *h, double *w4);
+int pebble_iir_set_state(pebble_iir_t *h, const double *w4);
+int pebble_iqbalance_process_device(int n, int block_len, double gain_factor, double phase_factor, const double *d_in, double *d_out,
+                                    void *stream);
+int pebble_sigstrength_fd_estimate_device(const double *d_spectrum, int bins, unsigned spectrum_rate, float bp_lo, float bp_hi,
+                                          const double *mixer_freqs, int nch, double squelch_db, double *out5, void *stream);
+
 /* ---- Receiver chain : the non-WFM branch of Receiver::processIQData ------------------------------------
  * Replaces application/receiver.cpp:903-996: m_downConvert1.ProcessData -> m_sampleBuf re-framing to
  * framesPerBuffer (:922-931) -> scaleCPX gain restore (:935-938) -> m_bpFilter->process (:950) ->

@@ -177,6 +177,17 @@ SIGNATURES = {
     "pebble_resampler_set_state": (c_int, [c_vp, c_vp, c_i64]),
     "pebble_resampler_plan": (c_int, [c_dbl, c_dbl, c_int, c_vp]),
     "pebble_resampler_plan_times": (c_int, [c_dbl, c_dbl, c_int, c_vp, c_int]),
+    # CIir / IQBalance / squelch
+    "pebble_iir_create": (c_vp, []),
+    "pebble_iir_destroy": (None, [c_vp]),
+    "pebble_iir_init": (c_int, [c_vp, c_int, c_dbl, c_dbl, c_dbl]),
+    "pebble_iir_get_coefficients": (c_int, [c_vp, c_vp]),
+    "pebble_iir_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
+    "pebble_iir_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
+    "pebble_iir_get_state": (c_int, [c_vp, c_vp]),
+    "pebble_iir_set_state": (c_int, [c_vp, c_vp]),
+    "pebble_iqbalance_process_device": (c_int, [c_int, c_int, c_dbl, c_dbl, c_vp, c_vp, c_vp]),
+    "pebble_sigstrength_fd_estimate_device": (c_int, [c_vp, c_int, ctypes.c_uint, ctypes.c_float, ctypes.c_float, c_vp, c_int, c_dbl, c_vp, c_vp]),
     # Receiver chain
     "pebble_receiver_create": (c_vp, [c_dbl, c_int]),
     "pebble_receiver_destroy": (None, [c_vp]),

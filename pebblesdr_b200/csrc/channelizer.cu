@@ -154,8 +154,8 @@ struct pebble_channelizer {
     // walk takes the same ~1 us per decimated sample whether 1024 or 128 channels are resident. A call is therefore cut
     // into `parts` runs of whole receiver frames; the demodulator + CFir of part k run on `tail` while the caller's stream
     // already down-converts and filters part k+1 (all operators carry their state, so split == unsplit).
-    cudaStream_t tail = nullptr;
-    cudaEvent_t ev_front = nullptr, ev_tail = nullptr;
+    cudaStream_t tail = nullptr, tail2 = nullptr;   // tail: the serial demodulator walks; tail2: their post filters
+    cudaEvent_t ev_front = nullptr, ev_tail = nullptr, ev_demod = nullptr, ev_cfir = nullptr;
     int parts = 4;
 };
 
@@ -197,6 +197,9 @@ pebble_channelizer_t *pebble_channelizer_create(int nchannels, double in_rate, d
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     if (!pebble::cuda_ok(cudaStreamCreateWithPriority(&h->tail, cudaStreamNonBlocking, prio_hi), "cudaStreamCreate") ||
+        !pebble::cuda_ok(cudaStreamCreateWithPriority(&h->tail2, cudaStreamNonBlocking, prio_hi), "cudaStreamCreate") ||
+        !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_demod, cudaEventDisableTiming), "cudaEventCreate") ||
+        !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_cfir, cudaEventDisableTiming), "cudaEventCreate") ||
         !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming), "cudaEventCreate") ||
         !pebble::cuda_ok(cudaEventCreateWithFlags(&h->ev_tail, cudaEventDisableTiming), "cudaEventCreate")) {
         pebble_channelizer_destroy(h);
@@ -232,6 +235,9 @@ void pebble_channelizer_destroy(pebble_channelizer_t *h) {
     cudaFree(h->d_modes); cudaFree(h->d_order); cudaFree(h->d_state); cudaFree(h->d_taps); cudaFree(h->d_hist[0]); cudaFree(h->d_hist[1]);
     cudaFree(h->d_dec); cudaFree(h->d_bp); cudaFree(h->d_tmp);
     if (h->tail) cudaStreamDestroy(h->tail);
+    if (h->tail2) cudaStreamDestroy(h->tail2);
+    if (h->ev_demod) cudaEventDestroy(h->ev_demod);
+    if (h->ev_cfir) cudaEventDestroy(h->ev_cfir);
     if (h->ev_front) cudaEventDestroy(h->ev_front);
     if (h->ev_tail) cudaEventDestroy(h->ev_tail);
     delete h;
@@ -323,6 +329,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
     // `tail` starts after everything already queued on the caller's stream (mode upload, the consumer of the last output)
     PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamWaitEvent(h->tail2, h->ev_front, 0), PEBBLE_ERR_CUDA);
     int f0 = 0;
     for (int k = 0; k < parts; ++k) {
         const int f1 = (int)((long long)frames * (k + 1) / parts);
@@ -339,19 +346,25 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
         PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
         chan_demod_kernel<<<h->slots / 32, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->d_order,
                                                             h->slots, h->pll, (double)0.9999f, h->d_state, h->fpb);                         // :987
+        // the walks of consecutive parts form the critical chain (32 warps, latency-bound); the post filter of part k runs
+        // beside the walk of part k+1 on its own stream
+        PB_CUDA(cudaEventRecord(h->ev_demod, h->tail), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaStreamWaitEvent(h->tail2, h->ev_demod, 0), PEBBLE_ERR_CUDA);
         int gx = (pd + 255) / 256;
         if (gx > 64) gx = 64;
-        chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, h->tail>>>(h->d_hist[h->hcur], h->d_tmp + pos, row, pd, h->d_taps, h->ntaps_am,
-                                                               h->ntaps_fm, h->d_modes, (cpx *)d_out + pos, out_stride,
-                                                               h->d_hist[h->hcur ^ 1]);
+        chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, h->tail2>>>(h->d_hist[h->hcur], h->d_tmp + pos, row, pd, h->d_taps, h->ntaps_am,
+                                                                h->ntaps_fm, h->d_modes, (cpx *)d_out + pos, out_stride,
+                                                                h->d_hist[h->hcur ^ 1]);
         pebble::count_launch(2);
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
         h->hcur ^= 1;
         f0 = f1;
     }
-    // the call is complete on the caller's stream when the last tail is
+    // the call is complete on the caller's stream when both tails are
     PB_CUDA(cudaEventRecord(h->ev_tail, h->tail), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamWaitEvent(st, h->ev_tail, 0), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaEventRecord(h->ev_cfir, h->tail2), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamWaitEvent(st, h->ev_cfir, 0), PEBBLE_ERR_CUDA);
     return nd;
 }
 

@@ -335,6 +335,79 @@ class FFT(_Handle):
         check(lib.pebble_fft_set_state(self._h, buf.ctypes.data, buf.size))
 
 
+class CIir(_Handle):
+    """pebblelib/iir.h: biquad (InitLP / InitHP / InitBP / InitBR + ProcessFilter on CPX)."""
+    _destroy = staticmethod(lib.pebble_iir_destroy)
+    LP, HP, BP, BR = range(4)
+
+    def __init__(self, kind=None, f0=0.0, q=1.0, fs=1.0):
+        super().__init__(lib.pebble_iir_create(), "CIir")
+        if kind is not None:
+            self.init(kind, f0, q, fs)
+
+    def init(self, kind, f0, q, fs):
+        check(lib.pebble_iir_init(self._h, kind, float(f0), float(q), float(fs)), "CIir.Init")
+
+    def coefficients(self):
+        c = np.zeros(5)
+        check(lib.pebble_iir_get_coefficients(self._h, c.ctypes.data))
+        return c
+
+    def ProcessFilter(self, InLength, InBuf, OutBuf):
+        if _is_cuda_tensor(InBuf):
+            return check(lib.pebble_iir_process_device(self._h, InLength, _dev_ptr(InBuf, InLength), _dev_ptr(OutBuf, InLength),
+                                                       _stream_ptr()), "ProcessFilter")
+        return check(lib.pebble_iir_process(self._h, InLength, _host_ptr(InBuf, InLength), _host_ptr(OutBuf, InLength, True)),
+                     "ProcessFilter")
+
+    def GetState(self):
+        w = np.zeros(4)
+        check(lib.pebble_iir_get_state(self._h, w.ctypes.data))
+        return w
+
+    def SetState(self, w):
+        w = np.ascontiguousarray(w, dtype=np.float64)
+        check(lib.pebble_iir_set_state(self._h, w.ctypes.data))
+
+
+class DCRemoval(CIir):
+    """application/dcremoval.cpp: 10 Hz high-pass biquad, Q = 0.7071; a disabled step copies."""
+
+    def __init__(self, sampleRate, bufferSize=0):
+        super().__init__(CIir.HP, 10, 0.7071, sampleRate)
+        self.enabled = False
+
+    def enableStep(self, on):
+        self.enabled = bool(on)
+
+    def process(self, inb, n, out):
+        if not self.enabled:
+            out[:n] = inb[:n]
+            return out
+        self.ProcessFilter(n, inb, out)
+        return out
+
+
+def iqbalance(d_in, block_len, gainFactor=1.0, phaseFactor=0.0):
+    """IQBalance::ProcessBlock (enabled) over consecutive blocks of block_len samples; CUDA tensor in, CUDA tensor out."""
+    n = d_in.numel()
+    out = torch.empty_like(d_in)
+    check(lib.pebble_iqbalance_process_device(n, int(block_len), float(gainFactor), float(phaseFactor), d_in.data_ptr(), out.data_ptr(),
+                                              _stream_ptr()), "iqbalance")
+    return out
+
+
+def fdEstimate(d_spectrum, spectrumSampleRate, bpLowFreq, bpHighFreq, mixerFreqs, squelchDb=-120.0):
+    """SignalStrength::fdEstimate for one or many channels over one dB spectrum (CUDA float64 tensor).
+    Returns [nch, 5]: peakDb, avgDb, snrDb, floorDb, open."""
+    mix = np.ascontiguousarray(np.atleast_1d(mixerFreqs), dtype=np.float64)
+    out = np.zeros((len(mix), 5))
+    check(lib.pebble_sigstrength_fd_estimate_device(d_spectrum.data_ptr(), d_spectrum.numel(), int(spectrumSampleRate), float(bpLowFreq),
+                                                    float(bpHighFreq), mix.ctypes.data, len(mix), float(squelchDb), out.ctypes.data,
+                                                    _stream_ptr()), "fdEstimate")
+    return out
+
+
 class NCO(_Handle):
     """pebblelib/nco.h: the oscillator primitive. setFrequency clamps to +-((sampleRate / 2) - 1) (nco.cpp:16-45)."""
     _destroy = staticmethod(lib.pebble_nco_destroy)
