@@ -252,6 +252,10 @@ struct pebble_demod {
     PllState *d_pll = nullptr;
     cpx *d_fm_last[2] = {nullptr, nullptr};
     int fm_cur = 0;
+    // SAM (demod_sam.cpp)
+    pebble_cfir sam_bp;
+    SamConst sam;
+    SamState *d_sam = nullptr;
     // scratch (grow-only)
     cpx *d_tmp = nullptr; size_t tmp_cap = 0;
     Aff *d_tiles = nullptr; double *d_carry = nullptr; int tiles_cap = 0;
@@ -330,8 +334,21 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         h->fm_cur ^= 1;
         return n;
     }
-    if (h->mode == 1 || h->mode == 3 || h->mode == 4) {
-        pebble::set_error("demod: SAM / WFM modes are outside this build's hot-path scope (SURVEY 8f rank 4)");
+    if (h->mode == 1) {  // dmSAM -> Demod_SAM::processBlock (demod.cpp:109-111)
+        int r = demod_reserve(h, n);
+        if (r < 0) return r;
+        sam_kernel<<<1, 32, 0, st>>>(d_in, n, h->sam, (double)0.9999f, h->d_sam, h->d_tmp);
+        pebble::count_launch();
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+        r = cfir_run_device(&h->sam_bp, n, h->d_tmp, d_out, st);   // Hilbert pair: I taps on re, Q taps on im (demod_sam.cpp:103)
+        if (r < 0) return r;
+        sam_mix_kernel<<<grid_for(n), 256, 0, st>>>(d_out, n);
+        pebble::count_launch();
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+        return n;
+    }
+    if (h->mode == 3 || h->mode == 4) {
+        pebble::set_error("demod: WFM modes (dmFMM / dmFMS) are not built (SURVEY 8f rank 4)");
         return PEBBLE_ERR_STATE;
     }
     // USB/LSB/DSB/CW/DIG/NONE: Demod::processBlock returns `in` itself (demod.cpp:127-138)
@@ -345,7 +362,9 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
     (void)num_samples;
     pebble_demod *h = new pebble_demod();
     h->rate = input_rate;
-    bool ok = cfir_alloc(&h->am_lp) == 0 && cfir_alloc(&h->nfm_lp) == 0 &&
+    bool ok = cfir_alloc(&h->am_lp) == 0 && cfir_alloc(&h->nfm_lp) == 0 && cfir_alloc(&h->sam_bp) == 0 &&
+              pebble::cuda_ok(cudaMalloc(&h->d_sam, sizeof(SamState)), "cudaMalloc") &&
+              pebble::cuda_ok(cudaMemset(h->d_sam, 0, sizeof(SamState)), "cudaMemset") &&
               pebble::cuda_ok(cudaMalloc(&h->d_pll, sizeof(PllState)), "cudaMalloc") &&
               pebble::cuda_ok(cudaMemset(h->d_pll, 0, sizeof(PllState)), "cudaMemset") &&
               pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -370,12 +389,33 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
     h->pll.dc_alpha = (float)(1.0 - exp(-1.0 / (h->rate * 0.001)));
     h->nfm_lp.ntaps = pebble_host::cfir_design_lp(0, 1.0, 50.0, 3000.0, 1.6 * 3000.0, h->rate, h->nfm_lp.hI);
     memcpy(h->nfm_lp.hQ, h->nfm_lp.hI, sizeof(double) * h->nfm_lp.ntaps);
-    if (cfir_upload(&h->am_lp) < 0 || cfir_upload(&h->nfm_lp) < 0) { pebble_demod_destroy(h); return nullptr; }
+    {
+        // Demod_SAM::Demod_SAM (demod_sam.cpp:5-34): members are float, pllBandwidth / pllLimit are ints, pllZeta a float
+        const float pllZeta = 0.707f;
+        const int pllBandwidth = 100, pllLimit = 1000;
+        const double TWOPI = 6.28318530717958647692528676656;
+        const unsigned sr = (unsigned)h->rate;
+        h->sam.alpha = (float)(2.0 * pllZeta * pllBandwidth * TWOPI / sr);
+        h->sam.beta = (float)(h->sam.alpha * h->sam.alpha / (4.0 * pllZeta * pllZeta));
+        h->sam.lo = (float)(-pllLimit * TWOPI / sr);
+        h->sam.hi = (float)(pllLimit * TWOPI / sr);
+        // m_bpFilter.InitLPFilter(0, 1.0, 40.0, 4500, 5500, sampleRate); GenerateHBFilter(5000.0) (fir.cpp:454-468)
+        double lp[75];
+        const int nt = pebble_host::cfir_design_lp(0, 1.0, 40.0, 4500, 5500, (double)sr, lp);
+        h->sam_bp.ntaps = nt;
+        for (int k = 0; k < nt; ++k) {
+            const double a = (TWOPI * 5000.0 / (double)sr) * ((double)k - ((double)(nt - 1) / 2.0));
+            h->sam_bp.hI[k] = 2.0 * lp[k] * cos(a);
+            h->sam_bp.hQ[k] = 2.0 * lp[k] * sin(a);
+        }
+    }
+    if (cfir_upload(&h->am_lp) < 0 || cfir_upload(&h->nfm_lp) < 0 || cfir_upload(&h->sam_bp) < 0) { pebble_demod_destroy(h); return nullptr; }
     return h;
 }
 void pebble_demod_destroy(pebble_demod_t *h) {
     if (!h) return;
-    cfir_release(&h->am_lp); cfir_release(&h->nfm_lp);
+    cfir_release(&h->am_lp); cfir_release(&h->nfm_lp); cfir_release(&h->sam_bp);
+    cudaFree(h->d_sam);
     cudaFree(h->d_pll); cudaFree(h->d_tmp); cudaFree(h->d_tiles); cudaFree(h->d_carry);
     for (int b = 0; b < 2; ++b) { cudaFree(h->d_am_last[b]); cudaFree(h->d_fm_last[b]); }
     if (h->stream) cudaStreamDestroy(h->stream);

@@ -384,6 +384,67 @@ static __global__ void pll_kernel(const cpx *__restrict__ in, int n, long long s
     st[s] = v;
 }
 
+// ---- Demod_SAM::processBlock, demod_sam.cpp:41-112 (synchronous AM: dttsp PLL + DC block per component) ---------------
+// pll() (:41-79): z = (cos, sin)(phase) [float overloads], pllSample = z * sig (double), difference = |sig| * phaseCpx(pllSample)
+// -> float, frequency += beta * difference (clamped), phase += frequency + alpha * difference, wrapped into [0, 2 pi) every
+// sample. As in the NFM loop, arg(z * sig) = arg(sig) + phase: arg(sig) and |sig| are formed for a register block up front and
+// the serial chain keeps a handful of FP32 operations; the rotated sample (the detector's OUTPUT) is formed off the chain.
+struct SamConst { float alpha, beta, lo, hi; };
+struct SamState { float phase, freq; float pad0, pad1; double dc_re_last, dc_im_last; };
+static __global__ void sam_kernel(const cpx *__restrict__ in, int n, SamConst c, double dc_alpha, SamState *__restrict__ st,
+                                  cpx *__restrict__ out) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    SamState v = *st;
+    cpx cur[PB_SERIAL_BLK], nxt[PB_SERIAL_BLK];
+#pragma unroll
+    for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = j < n ? in[j] : cpx_make(0.0, 0.0);
+    for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) nxt[j] = i0 + PB_SERIAL_BLK + j < n ? in[i0 + PB_SERIAL_BLK + j] : cpx_make(0.0, 0.0);
+        float th[PB_SERIAL_BLK], mg[PB_SERIAL_BLK], ph[PB_SERIAL_BLK];
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+            th[j] = pll_theta(cur[j]);
+            mg[j] = (float)sqrt(cur[j].x * cur[j].x + cur[j].y * cur[j].y);      // magCpx
+        }
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+            ph[j] = v.phase;                                                        // the phase this sample is rotated by
+            float e = th[j] + v.phase;                                              // theta in (-pi, pi], phase in [0, 2 pi)
+            e = e > 3.14159265358979323846f ? e - 6.28318530717958647692f : e;
+            const float diff = th[j] != th[j] ? 0.0f : mg[j] * e;                   // phaseCpx((0,0)) = 0
+            float f = fmaf(c.beta, diff, v.freq);
+            f = f < c.lo ? c.lo : f;                                                // demod_sam.cpp:64-67
+            f = f > c.hi ? c.hi : f;
+            v.freq = f;
+            float p = v.phase + fmaf(c.alpha, diff, f);
+            p = p >= 6.28318530717958647692f ? (float)((double)p - 6.28318530717958647692528676656) : p;   // :72-75
+            p = p < 0.0f ? (float)((double)p + 6.28318530717958647692528676656) : p;
+            v.phase = p;
+        }
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) {
+            if (i0 + j < n) {
+                float sn, cs;
+                sincosf(ph[j], &sn, &cs);
+                const double zr = (double)cs, zi = (double)sn;
+                const double pr = zr * cur[j].x - zi * cur[j].y, pi = zr * cur[j].y + zi * cur[j].x;   // z * sig
+                const double dre = (dc_alpha * v.dc_re_last) + pr, dim = (dc_alpha * v.dc_im_last) + pi;   // :97-98
+                out[i0 + j] = cpx_make(dre - v.dc_re_last, dim - v.dc_im_last);
+                v.dc_re_last = dre; v.dc_im_last = dim;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = nxt[j];
+    }
+    *st = v;
+}
+// out = (re + im, re - im): lower sideband left, upper sideband right (demod_sam.cpp:105-111)
+static __global__ void sam_mix_kernel(cpx *__restrict__ io, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const cpx t = io[i]; io[i] = cpx_make(t.x + t.y, t.x - t.y); }
+}
+
 // ---- AGC::processBlock, agc.cpp:84-207 (modes other than OFF) --------------------------------------------
 #define PB_AGC_BUF 2048  // MAX_DELAY_BUF, agc.h:27
 struct AgcState {

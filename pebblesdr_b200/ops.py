@@ -545,10 +545,12 @@ class AGC(_Handle):
         check(lib.pebble_agc_set_threshold(self._h, g), "setAgcThreshold")
 
     def processBlock(self, pInData, n=None):
+        """Returns the step's OWN output buffer (processstep.h:37-40): valid until the next call, not to be freed."""
         n = self.numSamples if n is None else n
-        out = np.empty(n, dtype=np.complex128)
-        check(lib.pebble_agc_process(self._h, n, _host_ptr(pInData, n), out.ctypes.data), "processBlock")
-        return out
+        if getattr(self, "_out", None) is None or self._out.size < n:
+            self._out = np.empty(n, dtype=np.complex128)
+        check(lib.pebble_agc_process(self._h, n, _host_ptr(pInData, n), self._out.ctypes.data), "processBlock")
+        return self._out[:n]
 
 
 class Demod(_Handle):
@@ -572,9 +574,10 @@ class Demod(_Handle):
         """Like the reference, pass-through modes return the INPUT array itself (demod.cpp:127-138)."""
         if lib.pebble_demod_is_passthrough(self._h) == 1:
             return inb
-        out = np.empty(bufSize, dtype=np.complex128)
-        check(lib.pebble_demod_process(self._h, bufSize, _host_ptr(inb, bufSize), out.ctypes.data), "processBlock")
-        return out
+        if getattr(self, "_out", None) is None or self._out.size < bufSize:
+            self._out = np.empty(bufSize, dtype=np.complex128)   # the step owns `out` (processstep.h:37-40)
+        check(lib.pebble_demod_process(self._h, bufSize, _host_ptr(inb, bufSize), self._out.ctypes.data), "processBlock")
+        return self._out[:bufSize]
 
 
 class CFractResampler(_Handle):

@@ -56,7 +56,7 @@ def test_am_demod_vs_oracle():
     g.setDemodMode(pb.Demod.dmAM)
     g.setBandwidth(10000.0)
     o.setBandwidth(10000.0)
-    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048).copy() for i in range(0, n, 2048)])
     yo = np.concatenate([o.am(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
     assert rel_rms(yg, yo) <= 1e-10
     # one big block == many small ones (scan carries across tiles and calls)
@@ -76,13 +76,13 @@ def test_nbfm_pll_and_fm2_vs_oracle():
     x = _fm_signal(n, RATE)
     g, o = pb.Demod(RATE, 2048), port.Demod(RATE)
     g.setDemodMode(pb.Demod.dmFMN)
-    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048).copy() for i in range(0, n, 2048)])
     yo = np.concatenate([o.nfm_pll(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
     assert np.all(yg.imag == 0.0) or rel_rms(yg.imag, yo.imag) <= 1e-4   # PLL output is real-only before the LP
     assert rel_rms(yg, yo) <= 1e-4                                         # float PLL state (finding F10)
     g.setNfmVariant(1)
     o2 = port.Demod(RATE)
-    yg2 = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
+    yg2 = np.concatenate([g.processBlock(x[i:i + 2048].copy(), 2048).copy() for i in range(0, n, 2048)])
     yo2 = np.concatenate([o2.fm2(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
     assert rel_rms(yg2, yo2) <= 1e-10
 
@@ -109,7 +109,7 @@ def test_agc_vs_oracle(mode, thr):
     g, o = pb.AGC(RATE, 2048), port.AGC(RATE)
     g.setAgcMode(mode, thr)
     o.setAgcMode(mode, thr)
-    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy()) for i in range(0, n, 2048)])
+    yg = np.concatenate([g.processBlock(x[i:i + 2048].copy()).copy() for i in range(0, n, 2048)])
     yo = np.concatenate([o.processBlock(x[i:i + 2048].copy(), 2048) for i in range(0, n, 2048)])
     assert rel_rms(yg, yo) <= 1e-10
 
@@ -152,3 +152,31 @@ def test_receiver_chain_config2(demod, lo, hi):
     k, out = g2.processIQData(torch.from_numpy(x).cuda(), n)
     assert k == len(yo)
     assert rel_rms(out[:k].cpu().numpy(), yo) <= 1e-10
+
+
+def test_sam_demod_vs_compiled_reference():
+    """SURVEY 8f-4: Demod_SAM::processBlock (demod_sam.cpp:41-112) against the class compiled from the reference. The PLL state is
+    float (like Demod_NFM's): relative RMS <= 1e-4 after a lock-time allowance, bounded before it."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    fs, frame, frames = 78125, 2048, 24
+    n = frame * frames
+    t = np.arange(n) / fs
+    rng = np.random.default_rng(12)
+    # AM carrier 180 Hz off tune (inside the +-1 kHz pull-in range), 1 kHz tone, m = 0.6, some noise
+    x = 0.4 * (1 + 0.6 * np.cos(2 * np.pi * 1000.0 * t)) * np.exp(2j * np.pi * 180.0 * t + 0.7j)
+    x = np.ascontiguousarray(x + (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.005)
+    r = ref_app.Demod_SAM(fs, frame)
+    want = np.concatenate([r.processBlock(x[i:i + frame]) for i in range(0, n, frame)])
+    g = pb.Demod(fs, frame)
+    g.setDemodMode(pb.Demod.dmSAM)
+    got = np.concatenate([g.processBlock(np.ascontiguousarray(x[i:i + frame]), frame).copy() for i in range(0, n, frame)])
+    lock = 4 * frame
+    assert rel_rms(got[lock:], want[lock:]) <= 1e-4, rel_rms(got[lock:], want[lock:])
+    assert rel_rms(got[:lock], want[:lock]) <= 0.5
+    assert np.abs(want[lock:]).max() > 0.05
+    # one call over several frames == frame-sized calls (no per-frame state besides what is carried)
+    g2 = pb.Demod(fs, frame)
+    g2.setDemodMode(pb.Demod.dmSAM)
+    got2 = g2.processBlock(x, n).copy()
+    assert rel_rms(got2[lock:], got[lock:]) <= 1e-12

@@ -39,7 +39,7 @@ def test_dc_removal_device_rate_and_the_reference_own_precision():
     from oracle import ref_app
     fs, n = 10000000, 1 << 22
     x = iq_noise_tones(n, 77, fs, [(1.2e6, 0.3)], noise=0.05) + (0.2 - 0.1j)
-    r = ref_app.DCRemoval(fs, 2048)
+    r = ref_app.DCRemoval(fs, 65536)        # the step owns an `out` of bufferSize samples
     r.enableStep(True)
     want = np.concatenate([r.process(x[i:i + 65536]) for i in range(0, n, 65536)])
     g = pb.DCRemoval(fs)
