@@ -106,6 +106,36 @@ __global__ void __launch_bounds__(PB_DEC_THREADS) dec_chain_kernel(const DecPlan
         if (p.front == 1) {
             const int D = p.D[0];
             for (int m = threadIdx.x; m < cnt; m += PB_DEC_THREADS) dst[m] = dec_cic_global(src, a + m, D, vec);
+        } else if (p.front == 2 && p.taps[1] == 11) {
+            // CIC3 + hb11 (the front of every chain planned from a rate >= 16x the protected bandwidth). The 11 CIC3 values
+            // one output needs are built from 12 consecutive raw sample PAIRS, each shared by two of them; all 12 are
+            // requested first, as independent 256-bit loads (12 x 32 B in flight per thread), and only then combined.
+            // Tiles alternate direction: an even tile walks its range upwards, an odd one downwards, so the raw samples two
+            // neighbours both need (the later tile's pre-roll = the end of the earlier tile's range) are asked for by
+            // both at the same end of their walks and the second request is served from L2 instead of DRAM.
+            const int D0 = p.D[0], D1 = p.D[1], bk = p.back[1];
+            const double *h = c_dec_taps + p.off[1];
+            const int iters = (cnt + PB_DEC_THREADS - 1) / PB_DEC_THREADS;
+            const bool down = blockIdx.x & 1;
+            for (int it = 0; it < iters; ++it) {
+                const int m = (down ? iters - 1 - it : it) * PB_DEC_THREADS + threadIdx.x;
+                if (m >= cnt) continue;
+                const long long j0 = (a + m) * D1 - bk;
+                cpx pa[12], pb[12];
+#pragma unroll
+                for (int q = 0; q < 12; ++q) dec_ld_pair(src, (j0 - 1 + q) * D0, vec, pa[q], pb[q]);
+                cpx acc = make_double2(0.0, 0.0);
+#pragma unroll
+                for (int k = 0; k < 11; ++k) {
+                    const double hk = h[k];
+                    if (hk != 0.0) {     // CIC3 value j0+k: (even, odd) = pair k+1, (xEven, xOdd) = pair k
+                        const cpx c = make_double2(dec_cic(pb[k + 1].x, pa[k].x, pb[k].x, pa[k + 1].x),
+                                                   dec_cic(pb[k + 1].y, pa[k].y, pb[k].y, pa[k + 1].y));
+                        dec_mac(acc, c, hk);
+                    }
+                }
+                dst[m] = acc;
+            }
         } else if (p.front == 2) {
             const int D0 = p.D[0], D1 = p.D[1], taps = p.taps[1], bk = p.back[1];
             const double *h = c_dec_taps + p.off[1];

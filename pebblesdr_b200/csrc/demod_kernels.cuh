@@ -385,12 +385,70 @@ static __global__ void pll_kernel(const cpx *__restrict__ in, int n, long long s
 }
 
 // ---- Demod_SAM::processBlock, demod_sam.cpp:41-112 (synchronous AM: dttsp PLL + DC block per component) ---------------
-// pll() (:41-79): z = (cos, sin)(phase) [float overloads], pllSample = z * sig (double), difference = |sig| * phaseCpx(pllSample)
-// -> float, frequency += beta * difference (clamped), phase += frequency + alpha * difference, wrapped into [0, 2 pi) every
-// sample. As in the NFM loop, arg(z * sig) = arg(sig) + phase: arg(sig) and |sig| are formed for a register block up front and
-// the serial chain keeps a handful of FP32 operations; the rotated sample (the detector's OUTPUT) is formed off the chain.
+// pll() (:41-79): z = (cos, sin)(phase) [float], pllSample = z * sig (double), difference = |sig| * phaseCpx(pllSample)
+// -> float, frequency += beta * difference (clamped), phase += frequency + alpha * difference, wrapped into [0, 2 pi).
+//
+// Unlike dttsp's loop, the reference multiplies by z, NOT by conj(z): arg(pllSample) = arg(sig) + phase, and the phase is
+// then pushed FURTHER in the direction of that error. The error therefore runs away from 0 and the loop settles in a
+// chattering regime around +-pi (the atan2 cut), where every sample's sign decision kicks the phase by +-alpha*|sig|*pi.
+// Between kicks the map phase -> phase*(1 + alpha*|sig|) is expanding, so two evaluations that differ in ONE float state
+// bit decorrelate sample by sample within a few thousand samples: the reference's output is only reproducible by
+// reproducing every rounding of the state. Hence no arg(x)+phase shortcut here (the NFM loop, a contracting map, has it):
+// the chain is the reference's, operation by operation —
+//   * cos/sin(float): the host libm's algorithm (glibc >= 2.28 = ARM optimized-routines sinf/cosf: one-step reduction by
+//     pi/2 and two double polynomials, result rounded to float), restated in sam_sincosf below; that restatement was
+//     checked bit for bit against the libm of this image for EVERY float in [0, 2 pi] (1 086 918 620 values, 0 differences);
+//   * z * sig, |sig|, phaseCpx (atan of the quotient + quadrant fix-up, cpx.cpp:5-21) in double with separately rounded
+//     products and sums (no FMA contraction, like the reference's x86-64 build); CUDA's atan is within 2 ulp of the libm's,
+//     which changes the float `difference` about once in 3e8 samples;
+//   * the float updates with their own roundings (a float product, then a float sum), the wraps in double (TWOPI is a double).
+// Cost: ~1 us per sample on one thread (13x real time at 78 125 S/s) — this demodulator is one stream of audio-rate work.
 struct SamConst { float alpha, beta, lo, hi; };
 struct SamState { float phase, freq; float pad0, pad1; double dc_re_last, dc_im_last; };
+__device__ __forceinline__ double sam_sin_poly(double x, double x2) {
+    const double x3 = __dmul_rn(x, x2);
+    const double s1 = __dadd_rn(0x1.1107605230bc4p-7, __dmul_rn(x2, -0x1.994eb3774cf24p-13));
+    const double x7 = __dmul_rn(x3, x2);
+    const double sv = __dadd_rn(x, __dmul_rn(x3, -0x1.555545995a603p-3));
+    return __dadd_rn(sv, __dmul_rn(x7, s1));
+}
+__device__ __forceinline__ double sam_cos_poly(double x2) {
+    const double x4 = __dmul_rn(x2, x2);
+    const double c2 = __dadd_rn(-0x1.6c087e89a359dp-10, __dmul_rn(x2, 0x1.99343027bf8c3p-16));
+    const double c1 = __dadd_rn(1.0, __dmul_rn(x2, -0x1.ffffffd0c621cp-2));
+    const double x6 = __dmul_rn(x4, x2);
+    const double cv = __dadd_rn(c1, __dmul_rn(x4, 0x1.55553e1068f19p-5));
+    return __dadd_rn(cv, __dmul_rn(x6, c2));
+}
+// (float)cos(y), (float)sin(y) for 0 <= y < 120 exactly as the host libm returns them
+__device__ __forceinline__ void sam_sincosf(float y, float &sn, float &cs) {
+    const double x = (double)y;
+    const unsigned top = (__float_as_uint(y) >> 20) & 0x7ff;
+    if (top < 0x3f4) {                      // |y| < pi/4
+        const double x2 = __dmul_rn(x, x);
+        if (top < 0x398) { sn = y; cs = 1.0f; return; }     // |y| < 2^-12
+        sn = (float)sam_sin_poly(x, x2);
+        cs = (float)sam_cos_poly(x2);
+        return;
+    }
+    const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);                    // 2/pi * 2^24
+    const int n = (__double2int_rz(r) + 0x800000) >> 24;
+    const double xr = __dsub_rn(x, __dmul_rn((double)n, 0x1.921FB54442D18p0));
+    const double x2 = __dmul_rn(xr, xr);
+    const double sg = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;           // sign of sine in quadrant n
+    const double sp = sam_sin_poly(__dmul_rn(xr, sg), x2), cp = sam_cos_poly(x2);
+    // sinf: even n -> sine polynomial of (x * sign), odd n -> cosine polynomial, negated in quadrants 2, 3
+    sn = (n & 1) ? (float)((n & 2) ? -cp : cp) : (float)sp;
+    // cosf: odd n -> sine polynomial of (x * sign), even n -> cosine polynomial, negated when (n + 1) & 2
+    cs = (n & 1) ? (float)sp : (float)(((n + 1) & 2) ? -cp : cp);
+}
+// CpxUtil::phaseCpx (cpx.cpp:5-21): atan(im / re) with re == 0 replaced by 1e-200, +-pi in the left half plane
+__device__ __forceinline__ double sam_phase(double re, double im) {
+    double t = atan(__ddiv_rn(im, re == 0.0 ? 1e-200 : re));
+    if (re < 0.0 && im < 0.0) t = __dsub_rn(t, 3.14159265358979323846);
+    else if (re < 0.0 && im >= 0.0) t = __dadd_rn(t, 3.14159265358979323846);
+    return t;
+}
 static __global__ void sam_kernel(const cpx *__restrict__ in, int n, SamConst c, double dc_alpha, SamState *__restrict__ st,
                                   cpx *__restrict__ out) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
@@ -401,36 +459,36 @@ static __global__ void sam_kernel(const cpx *__restrict__ in, int n, SamConst c,
     for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {
 #pragma unroll
         for (int j = 0; j < PB_SERIAL_BLK; ++j) nxt[j] = i0 + PB_SERIAL_BLK + j < n ? in[i0 + PB_SERIAL_BLK + j] : cpx_make(0.0, 0.0);
-        float th[PB_SERIAL_BLK], mg[PB_SERIAL_BLK], ph[PB_SERIAL_BLK];
+        double mg[PB_SERIAL_BLK];
+#pragma unroll
+        for (int j = 0; j < PB_SERIAL_BLK; ++j)      // magCpx (cpx.h:228-238), off the chain
+            mg[j] = sqrt(__dadd_rn(__dmul_rn(cur[j].x, cur[j].x), __dmul_rn(cur[j].y, cur[j].y)));
+        cpx pl[PB_SERIAL_BLK];
 #pragma unroll
         for (int j = 0; j < PB_SERIAL_BLK; ++j) {
-            th[j] = pll_theta(cur[j]);
-            mg[j] = (float)sqrt(cur[j].x * cur[j].x + cur[j].y * cur[j].y);      // magCpx
-        }
-#pragma unroll
-        for (int j = 0; j < PB_SERIAL_BLK; ++j) {
-            ph[j] = v.phase;                                                        // the phase this sample is rotated by
-            float e = th[j] + v.phase;                                              // theta in (-pi, pi], phase in [0, 2 pi)
-            e = e > 3.14159265358979323846f ? e - 6.28318530717958647692f : e;
-            const float diff = th[j] != th[j] ? 0.0f : mg[j] * e;                   // phaseCpx((0,0)) = 0
-            float f = fmaf(c.beta, diff, v.freq);
-            f = f < c.lo ? c.lo : f;                                                // demod_sam.cpp:64-67
+            if (i0 + j >= n) break;
+            float sn, cs;
+            sam_sincosf(v.phase, sn, cs);
+            const double zr = (double)cs, zi = (double)sn;
+            const double pr = __dsub_rn(__dmul_rn(zr, cur[j].x), __dmul_rn(zi, cur[j].y));      // z * sig
+            const double pi = __dadd_rn(__dmul_rn(zr, cur[j].y), __dmul_rn(zi, cur[j].x));
+            pl[j] = cpx_make(pr, pi);
+            const float diff = (float)__dmul_rn(mg[j], sam_phase(pr, pi));                      // :58
+            float f = __fadd_rn(v.freq, __fmul_rn(c.beta, diff));                               // :61
+            f = f < c.lo ? c.lo : f;                                                            // :64-67
             f = f > c.hi ? c.hi : f;
             v.freq = f;
-            float p = v.phase + fmaf(c.alpha, diff, f);
-            p = p >= 6.28318530717958647692f ? (float)((double)p - 6.28318530717958647692528676656) : p;   // :72-75
-            p = p < 0.0f ? (float)((double)p + 6.28318530717958647692528676656) : p;
+            float p = __fadd_rn(v.phase, __fadd_rn(f, __fmul_rn(c.alpha, diff)));               // :69
+            while ((double)p >= 6.28318530717958647692528676656) p = (float)((double)p - 6.28318530717958647692528676656);   // :72-75
+            while ((double)p < 0.0) p = (float)((double)p + 6.28318530717958647692528676656);
             v.phase = p;
         }
 #pragma unroll
         for (int j = 0; j < PB_SERIAL_BLK; ++j) {
             if (i0 + j < n) {
-                float sn, cs;
-                sincosf(ph[j], &sn, &cs);
-                const double zr = (double)cs, zi = (double)sn;
-                const double pr = zr * cur[j].x - zi * cur[j].y, pi = zr * cur[j].y + zi * cur[j].x;   // z * sig
-                const double dre = (dc_alpha * v.dc_re_last) + pr, dim = (dc_alpha * v.dc_im_last) + pi;   // :97-98
-                out[i0 + j] = cpx_make(dre - v.dc_re_last, dim - v.dc_im_last);
+                const double dre = __dadd_rn(__dmul_rn(dc_alpha, v.dc_re_last), pl[j].x);       // :97-98
+                const double dim = __dadd_rn(__dmul_rn(dc_alpha, v.dc_im_last), pl[j].y);
+                out[i0 + j] = cpx_make(__dsub_rn(dre, v.dc_re_last), __dsub_rn(dim, v.dc_im_last));
                 v.dc_re_last = dre; v.dc_im_last = dim;
             }
         }

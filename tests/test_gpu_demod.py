@@ -94,7 +94,7 @@ def test_ssb_passthrough_returns_input():
     for mode in (pb.Demod.dmUSB, pb.Demod.dmLSB, pb.Demod.dmCWU, pb.Demod.dmDIGL, pb.Demod.dmNONE):
         g.setDemodMode(mode)
         assert g.processBlock(x, 2048) is x            # demod.cpp:127-138 returns `in`
-    g.setDemodMode(pb.Demod.dmSAM)
+    g.setDemodMode(pb.Demod.dmFMM)                     # WFM is not built: a loud error, not silence
     with pytest.raises(pb.PebbleError):
         g.processBlock(x, 2048)
 
@@ -155,11 +155,17 @@ def test_receiver_chain_config2(demod, lo, hi):
 
 
 def test_sam_demod_vs_compiled_reference():
-    """SURVEY 8f-4: Demod_SAM::processBlock (demod_sam.cpp:41-112) against the class compiled from the reference. The PLL state is
-    float (like Demod_NFM's): relative RMS <= 1e-4 after a lock-time allowance, bounded before it."""
+    """SURVEY 8f-4: Demod_SAM::processBlock (demod_sam.cpp:41-112) against the class compiled from the reference.
+
+    The reference's loop multiplies by z instead of conj(z) (dttsp has the conjugate), so the phase error is pushed AWAY from 0
+    and the loop chatters around the +-pi cut of the arc tangent; between sign flips the phase map is expanding, i.e. a single
+    differing bit of the float state decorrelates the two outputs within a few thousand samples. Parity is therefore only
+    obtainable by reproducing every rounding (the kernel restates the libm's sinf/cosf, see demod_kernels.cuh) and it is then
+    tight over the WHOLE stream, lock-in included: 1e-9 relative RMS (the band-pass FIR after the loop sums in a different
+    order). A looser agreement is not a thing this loop has."""
     import pebblesdr_b200 as pb
     from oracle import ref_app
-    fs, frame, frames = 78125, 2048, 24
+    fs, frame, frames = 78125, 2048, 48
     n = frame * frames
     t = np.arange(n) / fs
     rng = np.random.default_rng(12)
@@ -172,8 +178,7 @@ def test_sam_demod_vs_compiled_reference():
     g.setDemodMode(pb.Demod.dmSAM)
     got = np.concatenate([g.processBlock(np.ascontiguousarray(x[i:i + frame]), frame).copy() for i in range(0, n, frame)])
     lock = 4 * frame
-    assert rel_rms(got[lock:], want[lock:]) <= 1e-4, rel_rms(got[lock:], want[lock:])
-    assert rel_rms(got[:lock], want[:lock]) <= 0.5
+    assert rel_rms(got, want) <= 1e-9, rel_rms(got, want)
     assert np.abs(want[lock:]).max() > 0.05
     # one call over several frames == frame-sized calls (no per-frame state besides what is carried)
     g2 = pb.Demod(fs, frame)

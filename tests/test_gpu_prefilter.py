@@ -67,7 +67,7 @@ def test_dc_removal_device_rate_and_the_reference_own_precision():
     # and the two double evaluations agree to the precision either of them has
     assert rel_rms(got, want) <= max(100 * ref_err, 1e-9), (rel_rms(got, want), ref_err)
     # the DC offset is gone, the tone is not
-    assert abs(got[n // 2:].mean()) < 1e-3 and np.abs(got[n // 2:]).std() > 0.05
+    assert abs(got[n // 2:].mean()) < 1e-3 and np.abs(got[n // 2:]).mean() > 0.2
     # a disabled step copies (dcremoval.cpp:11-14)
     g2 = pb.DCRemoval(fs)
     o = np.zeros(64, dtype=np.complex128)
