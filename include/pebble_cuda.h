@@ -393,6 +393,19 @@ int pebble_iqbalance_process_device(int n, int block_len, double gain_factor, do
                                     void *stream);
 int pebble_sigstrength_fd_estimate_device(const double *d_spectrum, int bins, unsigned spectrum_rate, float bp_lo, float bp_hi,
                                           const double *mixer_freqs, int nch, double squelch_db, double *out5, void *stream);
+/* pebble_sigstrength_fd_estimate_noalloc_device(): NO counterpart in the reference — added for
+ *      callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same arguments,
+ *      same kernel and same results as pebble_sigstrength_fd_estimate_device(), but it calls no cudaMalloc / cudaFree / allocating
+ *      routine: the scratch the other entry point allocates per call (per-channel bin ranges in, per-channel sums out) lives in
+ *      one file-scope device array of PEBBLE_FD_NOALLOC_MAX_CH entries (48 KiB per GPU that loads the library, held until exit),
+ *      host temporaries are on the stack (52 KiB). nch > PEBBLE_FD_NOALLOC_MAX_CH returns PEBBLE_ERR_ARG with a message naming
+ *      the limit. ALL calls share that array: calls whose GPU work overlaps (other streams / threads) race on it; the call
+ *      synchronises `stream` before returning, so consecutive calls from one thread are safe. Nothing in the array needs
+ *      clearing between calls (every entry read was written by the same call). */
+#define PEBBLE_FD_NOALLOC_MAX_CH 1024
+int pebble_sigstrength_fd_estimate_noalloc_max_channels(void);
+int pebble_sigstrength_fd_estimate_noalloc_device(const double *d_spectrum, int bins, unsigned spectrum_rate, float bp_lo, float bp_hi,
+                                                  const double *mixer_freqs, int nch, double squelch_db, double *out5, void *stream);
 
 /* ---- Receiver chain : the non-WFM branch of Receiver::processIQData ------------------------------------
  * Replaces application/receiver.cpp:903-996: m_downConvert1.ProcessData -> m_sampleBuf re-framing to

@@ -188,6 +188,8 @@ SIGNATURES = {
     "pebble_iir_set_state": (c_int, [c_vp, c_vp]),
     "pebble_iqbalance_process_device": (c_int, [c_int, c_int, c_dbl, c_dbl, c_vp, c_vp, c_vp]),
     "pebble_sigstrength_fd_estimate_device": (c_int, [c_vp, c_int, ctypes.c_uint, ctypes.c_float, ctypes.c_float, c_vp, c_int, c_dbl, c_vp, c_vp]),
+    "pebble_sigstrength_fd_estimate_noalloc_max_channels": (c_int, []),
+    "pebble_sigstrength_fd_estimate_noalloc_device": (c_int, [c_vp, c_int, ctypes.c_uint, ctypes.c_float, ctypes.c_float, c_vp, c_int, c_dbl, c_vp, c_vp]),
     # Receiver chain
     "pebble_receiver_create": (c_vp, [c_dbl, c_int]),
     "pebble_receiver_destroy": (None, [c_vp]),

@@ -19,6 +19,7 @@
 #include <cmath>
 #include <cstring>
 #include <vector>
+#include <mutex>
 
 #define IIR_SEG 16
 #define IIR_T 256
@@ -419,6 +420,93 @@ int pebble_sigstrength_fd_estimate_device(const double *d_spectrum, int bins, un
         o[1] = clip(p2db(bpAvg));
         o[3] = clip(p2db(noiseAvg));
         double snr = (noiseAvg == 0 || res[k].y == 0) ? -120.0 : 10.0 * log10(res[k].y / noiseAvg);   // DB::powerRatioToDb
+        o[2] = snr < 0.0 ? 0.0 : (snr > 120.0 ? 120.0 : snr);
+        o[4] = o[1] < squelch_db ? 0.0 : 1.0;
+    }
+    return nch;
+}
+
+
+// ---- the same estimate for callers that may not allocate -------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it). pebble_sigstrength_fd_estimate_device() above takes its
+// two scratch arrays (the per-channel bin ranges going in, the per-channel sums coming out) from cudaMalloc on every call; this
+// variant keeps them in ONE file-scope device array of PEBBLE_FD_NOALLOC_MAX_CH entries (48 KiB, held by every GPU that loads
+// the library until the process exits) and its host-side temporaries on the stack. It runs the same kernel on the same numbers.
+//   * g_fd_scratch as written in HOST code is a host-side stand-in for the symbol, not a device address; the device address is
+//     asked for once per device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernel is given.
+//   * Every call uses the same array: two calls whose GPU work overlaps (different streams, different host threads) race on
+//     it. Calls on one stream, or separated by a synchronisation, are safe; this entry point synchronises `stream` before
+//     it returns (it has to read the sums back), so back-to-back calls from one thread are.
+//   * The array keeps the previous call's contents. Nothing in it has to start at zero: the nch FdBins entries are copied in
+//     and each of the nch result entries is written in full by its own CTA before any of them is read back; entries past nch
+//     are never read.
+static __device__ __align__(256) unsigned char g_fd_scratch[PEBBLE_FD_NOALLOC_MAX_CH * (sizeof(double4) + sizeof(FdBins))];
+#define PB_FD_MAX_DEVICES 64
+static void *g_fd_scratch_dev[PB_FD_MAX_DEVICES];     // device address of g_fd_scratch per device, filled on first use
+static std::mutex g_fd_mu;
+
+static void *fd_scratch_on_current_device() {
+    int dev = -1;
+    if (!pebble::cuda_ok(cudaGetDevice(&dev), "cudaGetDevice")) return nullptr;
+    if (dev < 0 || dev >= PB_FD_MAX_DEVICES) { pebble::set_error("sigstrength(noalloc): device ordinal %d out of range", dev); return nullptr; }
+    std::lock_guard<std::mutex> lk(g_fd_mu);
+    if (!g_fd_scratch_dev[dev]) {
+        void *p = nullptr;
+        if (!pebble::cuda_ok(cudaGetSymbolAddress(&p, g_fd_scratch), "cudaGetSymbolAddress(g_fd_scratch)") || !p) return nullptr;
+        g_fd_scratch_dev[dev] = p;
+    }
+    return g_fd_scratch_dev[dev];
+}
+
+int pebble_sigstrength_fd_estimate_noalloc_max_channels(void) { return PEBBLE_FD_NOALLOC_MAX_CH; }
+
+int pebble_sigstrength_fd_estimate_noalloc_device(const double *d_spectrum, int bins, unsigned spectrum_rate, float bp_lo, float bp_hi,
+                                                  const double *mixer_freqs, int nch, double squelch_db, double *out5, void *stream_v) {
+    if (!d_spectrum || bins <= 0 || !mixer_freqs || nch <= 0 || !out5) { pebble::set_error("sigstrength(noalloc): bad argument"); return PEBBLE_ERR_ARG; }
+    if (nch > PEBBLE_FD_NOALLOC_MAX_CH) {
+        pebble::set_error("sigstrength(noalloc): %d channels exceed the static scratch array's %d (PEBBLE_FD_NOALLOC_MAX_CH); split the call or "
+                          "use pebble_sigstrength_fd_estimate_device", nch, PEBBLE_FD_NOALLOC_MAX_CH);
+        return PEBBLE_ERR_ARG;
+    }
+    unsigned char *scratch = (unsigned char *)fd_scratch_on_current_device();
+    if (!scratch) return PEBBLE_ERR_CUDA;
+    double4 *d_res = (double4 *)scratch;
+    FdBins *d_fb = (FdBins *)(scratch + sizeof(double4) * PEBBLE_FD_NOALLOC_MAX_CH);
+    cudaStream_t st = (cudaStream_t)stream_v;
+    FdBins fb[PEBBLE_FD_NOALLOC_MAX_CH];          // 16 KiB + 4 KiB + 32 KiB of stack: no heap either
+    int bpbins[PEBBLE_FD_NOALLOC_MAX_CH];
+    double4 res[PEBBLE_FD_NOALLOC_MAX_CH];
+    const double binWidth = (double)(spectrum_rate / (unsigned)bins);    // signalstrength.cpp:311, integer division
+    const int centerBin = bins / 2;
+    for (int k = 0; k < nch; ++k) {                                       // :324-345, as in the allocating entry point
+        int mixerBin = (int)(centerBin + (mixer_freqs[k] / binWidth));
+        mixerBin = mixerBin < 0 ? 0 : (mixerBin > bins ? bins : mixerBin);
+        int lo = (int)(mixerBin + ((double)bp_lo / binWidth)); lo = lo < 0 ? 0 : (lo > bins ? bins : lo);
+        int hi = (int)(mixerBin + ((double)bp_hi / binWidth)); hi = hi < 0 ? 0 : (hi > bins ? bins : hi);
+        const int bpBins = hi - lo;
+        int nlo = lo - bpBins, nhi = hi + bpBins;
+        nlo = nlo < 0 ? 0 : (nlo > bins ? bins : nlo);
+        nhi = nhi < 0 ? 0 : (nhi > bins ? bins : nhi);
+        fb[k].bp_lo = lo; fb[k].bp_hi = hi; fb[k].noise_lo = nlo; fb[k].noise_hi = nhi;
+        bpbins[k] = bpBins;
+    }
+    PB_CUDA(cudaMemcpyAsync(d_fb, fb, sizeof(FdBins) * nch, cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
+    fd_estimate_kernel<<<nch, 256, 0, st>>>(d_spectrum, bins, d_fb, d_res);
+    pebble::count_launch();
+    PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpyAsync(res, d_res, sizeof(double4) * nch, cudaMemcpyDeviceToHost, st), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaStreamSynchronize(st), PEBBLE_ERR_CUDA);
+    for (int k = 0; k < nch; ++k) {
+        const double bpAvg = res[k].x / bpbins[k], noiseAvg = res[k].z / res[k].w;     // :352-353
+        double *o = out5 + 5 * k;
+        const double pk = res[k].y == 0 ? -120.0 : 10 * log10(res[k].y);
+        const double av = bpAvg == 0 ? -120.0 : 10 * log10(bpAvg);
+        const double fl = noiseAvg == 0 ? -120.0 : 10 * log10(noiseAvg);
+        o[0] = pk < -120.0 ? -120.0 : (pk > 0.0 ? 0.0 : pk);
+        o[1] = av < -120.0 ? -120.0 : (av > 0.0 ? 0.0 : av);
+        o[3] = fl < -120.0 ? -120.0 : (fl > 0.0 ? 0.0 : fl);
+        const double snr = (noiseAvg == 0 || res[k].y == 0) ? -120.0 : 10.0 * log10(res[k].y / noiseAvg);
         o[2] = snr < 0.0 ? 0.0 : (snr > 120.0 ? 120.0 : snr);
         o[4] = o[1] < squelch_db ? 0.0 : 1.0;
     }
