@@ -8,11 +8,12 @@
 //   1. dc_cic_kernel, batched: blockIdx.x = segment*nch + channel (downconvert.cu). Every channel mixes the full-rate
 //      stream (the reference algorithm, kept for parity): FP64-bound, the input is shared through L2.
 //   2. fastfir_kernel, blockIdx.y = channel, the two scalar gains fused (fastfir.cu).
-//   3. chan_demod_kernel: one thread per channel (the PLL and the DC-block IIR are serial recurrences, finding F10).
+//   3. chan_demod_kernel: four channels per warp, eight lanes each (the PLL and the DC-block IIR are serial recurrences, F10).
 //   4. chan_cfir_kernel: the demod post filter, blockIdx.y = channel, per-mode tap set.
 #include "lib_common.h"
 #include "demod_kernels.cuh"
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -39,95 +40,220 @@ __device__ __forceinline__ double pb_sqrt_newton(double x) {
     return s;
 }
 
-// one thread per channel: in/out rows of `stride` cpx
-static __global__ void chan_demod_kernel(const cpx *__restrict__ in, cpx *__restrict__ out, int n, long long stride, int nch,
-                                         const int *__restrict__ modes, const int *__restrict__ order, int slots,
+// chan_demod_kernel: in/out rows of `stride` cpx. The demodulators are serial recurrences (PLL feedback, DC-block IIR), so a
+// channel's speed is the latency of ONE sample's dependent chain and nothing else; what the kernel can choose is how many
+// issue slots it spends around that chain, because the walks run BESIDE the next part's front end (other streams):
+//   * one thread per channel (first version, 32 warps): that thread also issued everything that is NOT on the chain — the
+//     uncoalesced row loads, the double->float conversions, the 20-instruction arg(x) polynomial, the stores: 265 cycles per
+//     sample for a chain of ~14 FP32 operations;
+//   * one warp per channel (1024 warps, every lane repeating the chain on shuffled inputs): 99 cycles per sample alone
+//     (207 us per 4096-sample part) but 1024 x 30 instructions per sample step — a third of the GPU's issue slots while it
+//     runs; beside the front end both slowed down 1.5-2.8x (event timeline, tools/trace_chz.py);
+//   * this form: a warp carries PB_CHZ_C = 8 channels, PB_CHZ_L = 4 lanes each. A block is 32 consecutive samples of each
+//     channel: lane s of a channel's group loads samples s, s + 4, ... (64-byte runs), forms the loop-independent part of ITS
+//     samples (arg(x) / |x|), then all lanes run the same 32 chain steps on the group's state, picking step j's input out of
+//     its owner lane with a width-4 shuffle (issued ahead of the chain: it does not depend on the state). One warp
+//     instruction advances 8 recurrences, so the walk costs 1/8 of the issue slots of the warp-per-channel form at the same
+//     latency; one warp per CTA, 128 CTAs for 1024 channels.
+#define PB_CHZ_L 4                     // lanes per channel
+#define PB_CHZ_C (32 / PB_CHZ_L)       // channels per warp
+#define PB_CHZ_R (32 / PB_CHZ_L)       // samples per lane in a 32-sample block
+// One PLL step (demod_nfm.cpp:225-257) on the chain. th = arg(x) (NaN for an exactly-zero sample: phzerror = 0 there),
+// th_turns = th / 2 pi. arg(x e^{j phase}) = th + phase reduced to [-pi, pi]: the reduction (Cody-Waite, k by the 1.5 * 2^23
+// trick) is applied to the SUM, so no separate wrap — and no predicate-producing instruction — sits on the chain.
+__device__ __forceinline__ float pll_chain(const float th, const float th_turns, const bool th_nan, const PllConst &c, PllState &v) {
+    const float q = fmaf(v.phase, 0.15915494309189535f, th_turns);
+    const float k = (q + 12582912.0f) - 12582912.0f;
+    float r = fmaf(k, -PB_TWO_PI_HI, v.phase);
+    r = fmaf(k, -PB_TWO_PI_LO, r);
+    const float e = th + r;
+    const float phzerror = th_nan ? 0.0f : -e;
+    float f = fmaf(c.beta, phzerror, v.freq);
+    f = fminf(fmaxf(f, c.lo), c.hi);
+    v.freq = f;
+    v.phase = v.phase + fmaf(c.alpha, phzerror, f);
+    v.dc = fmaf(c.dc_alpha, f, (1.0f - c.dc_alpha) * v.dc);   // its own, shorter chain
+    return (f - v.dc) * c.out_gain;
+}
+static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__restrict__ in, cpx *__restrict__ out_rows, int n, long long stride,
+                                         int nch, const int *__restrict__ modes, const int *__restrict__ order, int slots,
                                          PllConst pc, double am_alpha, ChanState *__restrict__ st, int frame) {
-    // order[]: channels grouped by demodulator and padded to whole warps (-1), so a warp runs ONE of the recurrences
-    // below; with channels in natural order (NBFM and AM alternating in config 4) every warp ran both, one after the other.
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= slots) return;
-    const int c = order[slot];
-    if (c < 0 || c >= nch) return;
-    const cpx *x = in + (long long)c * stride;
-    cpx *y = out + (long long)c * stride;
-    const int mode = modes[c];
+    // order[]: channels grouped by demodulator, each group padded (-1) to whole warps: a warp runs ONE kind of recurrence
+    const int lane = threadIdx.x;
+    const int s = lane % PB_CHZ_L;                           // this lane's position inside its channel's group
+    const int slot0 = blockIdx.x * PB_CHZ_C;
+    if (slot0 >= slots) return;
+    const int slot = slot0 + lane / PB_CHZ_L;
+    const int c = slot < slots ? order[slot] : -1;
+    const bool valid = c >= 0 && c < nch;
+    const int c0 = order[slot0];                             // never a pad: groups are padded at their END
+    const int mode = modes[c0];
+    const cpx *x = in + (long long)(valid ? c : c0) * stride;
+    // Both detectors produce a REAL stream (NBFM: (o, 0), AM: (v, v)); the row written here holds those reals, and the post
+    // filter, which duplicates / zero-extends them, reads 8 instead of 16 bytes per sample. Same row pitch as the input.
+    double *y = (double *)(out_rows + (long long)(valid ? c : c0) * stride);
+    // a block = 32 consecutive samples of every channel of the warp; lane s of a group holds samples s, s + L, s + 2L, ...
+    // The next block's loads are issued before the current block's 32 chain steps (~2000 cycles: well past the L2 latency).
     if (mode == CH_FMN) {                 // Demod_NFM::processBlockNCO, demod_nfm.cpp:225-257
-        PllState v = st[c].pll;
-        pll_run(x, y, n, pc, v, frame);
-        st[c].pll = v;
+        PllState v = st[valid ? c : c0].pll;
+        if (frame <= 0) frame = n;
+        for (int f0 = 0; f0 < n; f0 += frame) {             // the reference wraps the phase once per receiver frame (:252)
+            const int f1 = f0 + frame < n ? f0 + frame : n;
+            cpx cur[PB_CHZ_R], nxt[PB_CHZ_R];
+#pragma unroll
+            for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = f0 + m * PB_CHZ_L + s < f1 ? x[f0 + m * PB_CHZ_L + s] : cpx_make(1.0, 0.0);
+            for (int i = f0; i < f1; i += 32) {
+#pragma unroll
+                for (int m = 0; m < PB_CHZ_R; ++m) cur[m] = nxt[m];
+                if (i + 32 < f1) {
+#pragma unroll
+                    for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = i + 32 + m * PB_CHZ_L + s < f1 ? x[i + 32 + m * PB_CHZ_L + s] : cpx_make(1.0, 0.0);
+                }
+                float th[PB_CHZ_R], tt[PB_CHZ_R], mine[PB_CHZ_R];
+#pragma unroll
+                for (int m = 0; m < PB_CHZ_R; ++m) { th[m] = pll_theta(cur[m]); tt[m] = th[m] * 0.15915494309189535f; mine[m] = 0.0f; }
+                const int cnt = f1 - i < 32 ? f1 - i : 32;
+                if (cnt == 32) {
+                    // no per-step branch here: a branch between steps pins every shuffle right in front of its use and puts
+                    // its ~25-cycle latency on the chain (measured: 164 instead of ~100 cycles per step)
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                        const float ttj = __shfl_sync(0xffffffffu, tt[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                        const float o = pll_chain(tj, ttj, tj != tj, pc, v);
+                        mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (j < cnt) {                       // uniform
+                            const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                            const float ttj = __shfl_sync(0xffffffffu, tt[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                            const float o = pll_chain(tj, ttj, tj != tj, pc, v);
+                            mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
+                        }
+                    }
+                }
+#pragma unroll
+                for (int m = 0; m < PB_CHZ_R; ++m)
+                    if (valid && m * PB_CHZ_L + s < cnt) y[i + m * PB_CHZ_L + s] = (double)mine[m];   // CPX = float there; imaginary part 0
+            }
+            v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
+        }
+        if (valid && s == 0) st[c].pll = v;
     } else if (mode == CH_AM) {           // Demod_AM::processBlockFiltered, demod_am.cpp:40-59
-        double d = st[c].am_dc_last;
-        cpx cur[PB_SERIAL_BLK], nxt[PB_SERIAL_BLK];               // register double buffer, as in pll_run
+        double d = st[valid ? c : c0].am_dc_last;
+        cpx cur[PB_CHZ_R], nxt[PB_CHZ_R];
 #pragma unroll
-        for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = j < n ? x[j] : cpx_make(0.0, 0.0);
-        for (int i0 = 0; i0 < n; i0 += PB_SERIAL_BLK) {
+        for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = m * PB_CHZ_L + s < n ? x[m * PB_CHZ_L + s] : cpx_make(0.0, 0.0);
+        for (int i = 0; i < n; i += 32) {
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) nxt[j] = i0 + PB_SERIAL_BLK + j < n ? x[i0 + PB_SERIAL_BLK + j] : cpx_make(0.0, 0.0);
-            // the envelopes of a block do not depend on the recurrence: formed first (independent, pipelined), so the serial
-            // part is one multiply-add and one subtract per sample. sqrt: branch-free Newton form (the library routine's
-            // special-case branches serialise the 16 evaluations); <= 1 ulp from the correctly rounded value.
-            double mg[PB_SERIAL_BLK];
+            for (int m = 0; m < PB_CHZ_R; ++m) cur[m] = nxt[m];
+            if (i + 32 < n) {
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) mg[j] = pb_sqrt_newton(cur[j].x * cur[j].x + cur[j].y * cur[j].y);   // DB::amplitude, db.h:28-30
+                for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = i + 32 + m * PB_CHZ_L + s < n ? x[i + 32 + m * PB_CHZ_L + s] : cpx_make(0.0, 0.0);
+            }
+            // sqrt: branch-free Newton form, <= 1 ulp from the correctly rounded value (DB::amplitude, db.h:28-30)
+            double mg[PB_CHZ_R], mine[PB_CHZ_R];
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) {
-                if (i0 + j < n) {
-                    const double dn = (am_alpha * d) + mg[j];                             // demod_am.cpp:52
-                    const double v = dn - d;                                              // demod_am.cpp:53
+            for (int m = 0; m < PB_CHZ_R; ++m) { mg[m] = pb_sqrt_newton(cur[m].x * cur[m].x + cur[m].y * cur[m].y); mine[m] = 0.0; }
+            const int cnt = n - i < 32 ? n - i : 32;
+            if (cnt == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const double mj = __shfl_sync(0xffffffffu, mg[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                    const double dn = (am_alpha * d) + mj;                                // demod_am.cpp:52
+                    const double w = dn - d;                                              // demod_am.cpp:53
                     d = dn;
-                    y[i0 + j] = cpx_make(v, v);
+                    mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? w : mine[j / PB_CHZ_L];
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    if (j < cnt) {
+                        const double mj = __shfl_sync(0xffffffffu, mg[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                        const double dn = (am_alpha * d) + mj;
+                        const double w = dn - d;
+                        d = dn;
+                        mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? w : mine[j / PB_CHZ_L];
+                    }
                 }
             }
 #pragma unroll
-            for (int j = 0; j < PB_SERIAL_BLK; ++j) cur[j] = nxt[j];
+            for (int m = 0; m < PB_CHZ_R; ++m)
+                if (valid && m * PB_CHZ_L + s < cnt) y[i + m * PB_CHZ_L + s] = mine[m];             // (v, v) in the reference
         }
-        st[c].am_dc_last = d;
-    } else {                              // USB/LSB/...: Demod::processBlock returns `in` (demod.cpp:127-138)
-        for (int i = 0; i < n; ++i) y[i] = x[i];
+        if (valid && s == 0) st[c].am_dc_last = d;
     }
+    // USB/LSB/...: Demod::processBlock returns `in` (demod.cpp:127-138): nothing to walk, chan_cfir_kernel copies the row
 }
 
-// CFir::ProcessFilter over every channel (fir.cpp:106-132): virtual stream = hist ++ in, per-mode taps.
-// taps: [2][PB_FIR_MAX] (row 0 AM low-pass, row 1 NFM low-pass); ntaps[2]. Pass-through channels are copied.
-static __global__ void chan_cfir_kernel(const cpx *__restrict__ hist, const cpx *__restrict__ in, long long in_stride, int n,
-                                        const double *__restrict__ taps, int ntaps_am, int ntaps_fm,
-                                        const int *__restrict__ modes, cpx *__restrict__ out, long long out_stride,
-                                        cpx *__restrict__ new_hist) {
-    __shared__ double sh[PB_FIR_MAX];
+// CFir::ProcessFilter over every channel (fir.cpp:106-132): virtual stream = hist ++ in, per-mode taps, blockIdx.y = channel,
+// blockIdx.x = tile of PB_FIR_TILE outputs. The detectors' outputs are real streams whose I and Q tap sets are equal
+// (Init*Filter designs, fir.cpp:298-302), so ONE real convolution per channel gives both components: AM writes (r, r), NBFM
+// (r, +0) — what the complex filter returns for (v, v) and (o, 0) inputs, bit for bit (same tap order, same FMAs; the
+// imaginary sum of +-0 products is +0). Register-blocked like cfir_dup_kernel (demod_kernels.cuh): each thread makes
+// PB_FIR_R consecutive outputs from a sliding register window, one shared load per tap.
+// taps: [2][PB_FIR_MAX] (row 0 AM low-pass, row 1 NFM low-pass). hist rows: PB_FIR_MAX reals, the last ntaps-1 are used.
+// Pass-through channels are copied from the band-pass output `bp`.
+static __global__ void __launch_bounds__(PB_FIR_THREADS)
+chan_cfir_kernel(const double *__restrict__ hist, const cpx *__restrict__ in_rows, long long in_stride, const cpx *__restrict__ bp,
+                 int n, const double *__restrict__ taps, int ntaps_am, int ntaps_fm, const int *__restrict__ modes,
+                 cpx *__restrict__ out, long long out_stride, double *__restrict__ new_hist) {
+    __shared__ double win[PB_FIR_TILE + PB_FIR_MAX + (PB_FIR_TILE + PB_FIR_MAX) / 8 + 1];
+    __shared__ double sh_t[PB_FIR_MAX];
     const int c = blockIdx.y;
     const int mode = modes[c];
-    const cpx *x = in + c * in_stride;
     cpx *y = out + c * out_stride;
+    const int t0 = blockIdx.x * PB_FIR_TILE;
+    const int valid = min(PB_FIR_TILE, n - t0);
     if (mode != CH_AM && mode != CH_FMN) {
-        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) y[i] = x[i];
+        const cpx *xb = bp + c * in_stride;
+        for (int i = threadIdx.x; i < valid; i += PB_FIR_THREADS) y[t0 + i] = xb[t0 + i];
         return;
     }
+    const double *x = (const double *)(in_rows + c * in_stride);
     const int ntaps = mode == CH_AM ? ntaps_am : ntaps_fm;
-    const double *h = taps + (mode == CH_AM ? 0 : PB_FIR_MAX);
-    for (int k = threadIdx.x; k < ntaps; k += blockDim.x) sh[k] = h[k];
-    __syncthreads();
-    const int hl = PB_FIR_MAX;   // history rows are PB_FIR_MAX long; the last ntaps-1 entries are used
-    const cpx *hc = hist + (long long)c * hl + (hl - (ntaps - 1));
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        double re = 0.0, im = 0.0;
-        for (int k = 0; k < ntaps; ++k) {
-            const int v = i + (ntaps - 1) - k;
-            const cpx s = v < ntaps - 1 ? hc[v] : x[v - (ntaps - 1)];
-            re += sh[k] * s.x;     // I and Q tap sets are equal for Init*Filter designs (fir.cpp:298-302)
-            im += sh[k] * s.y;
-        }
-        y[i] = cpx_make(re, im);
+    const double *tp = taps + (mode == CH_AM ? 0 : PB_FIR_MAX);
+    const int hl = PB_FIR_MAX, h = ntaps - 1;
+    const double *ho = hist + (long long)c * hl;
+    for (int k = threadIdx.x; k < ntaps; k += PB_FIR_THREADS) sh_t[k] = tp[k];
+    for (int p = threadIdx.x; p < valid + h; p += PB_FIR_THREADS) {
+        const int idx = t0 + p - h;                        // index into `in`; negative: history
+        win[fir_slot(p)] = idx < 0 ? ho[hl + idx] : x[idx];
     }
-    // the last PB_FIR_MAX samples of hist ++ in become the next history (block 0 of each channel writes them)
+    // the last PB_FIR_MAX samples of hist ++ in become the next history (tile 0 of each channel writes them)
     if (blockIdx.x == 0) {
-        cpx *nh = new_hist + (long long)c * hl;
-        const cpx *ho = hist + (long long)c * hl;
-        for (int i = threadIdx.x; i < hl; i += blockDim.x) {
-            const long long v = (long long)n + i;      // index into (hist ++ in)
+        double *nh = new_hist + (long long)c * hl;
+        for (int i = threadIdx.x; i < hl; i += PB_FIR_THREADS) {
+            const long long v = (long long)n + i;          // index into (hist ++ in)
             nh[i] = v < hl ? ho[v] : x[v - hl];
         }
     }
+    __syncthreads();
+    const int i0 = threadIdx.x * PB_FIR_R;
+    if (i0 >= valid) return;
+    double re[PB_FIR_R], w[PB_FIR_R];
+#pragma unroll
+    for (int j = 0; j < PB_FIR_R; ++j) { re[j] = 0.0; w[j] = win[fir_slot(i0 + h + j)]; }
+    for (int k0 = 0; k0 < ntaps; k0 += PB_FIR_R) {
+#pragma unroll
+        for (int kk = 0; kk < PB_FIR_R; ++kk) {
+            const int k = k0 + kk;
+            if (k < ntaps) {
+                const double cI = sh_t[k];
+#pragma unroll
+                for (int j = 0; j < PB_FIR_R; ++j) re[j] += cI * w[j];
+#pragma unroll
+                for (int j = PB_FIR_R - 1; j > 0; --j) w[j] = w[j - 1];
+                if (k + 1 < ntaps) w[0] = win[fir_slot(i0 + h - k - 1)];
+            }
+        }
+    }
+    const bool dup = mode == CH_AM;
+#pragma unroll
+    for (int j = 0; j < PB_FIR_R; ++j)
+        if (i0 + j < valid) y[t0 + i0 + j] = cpx_make(re[j], dup ? re[j] : 0.0);
 }
 
 struct pebble_channelizer {
@@ -137,7 +263,7 @@ struct pebble_channelizer {
     pebble_fastfir_t *bp = nullptr;
     std::vector<int> modes;
     int *d_modes = nullptr, *d_order = nullptr;
-    int slots = 0;                     // entries of d_order (multiple of 32)
+    int slots = 0;                     // entries of d_order
     bool modes_dirty = true;
     PllConst pll;
     ChanState *d_state = nullptr;
@@ -182,6 +308,36 @@ static int chz_reserve(pebble_channelizer *h, size_t row) {
     h->row_cap = row;
     return 0;
 }
+
+// PEBBLE_CHZ_TRACE=1: time-stamp every stage of every part with events on its own stream and print the timeline (us from the
+// call's first event) to stderr after the call — the only way to see how far the three streams really overlap without nsys.
+namespace {
+struct ChzTrace {
+    struct Mark { const char *what; int part; cudaEvent_t a, b; };
+    std::vector<Mark> marks;
+    bool on = false;
+    void begin(const char *what, int part, cudaStream_t s) {
+        if (!on) return;
+        Mark m{what, part, nullptr, nullptr};
+        cudaEventCreate(&m.a); cudaEventCreate(&m.b);
+        cudaEventRecord(m.a, s);
+        marks.push_back(m);
+    }
+    void end(cudaStream_t s) { if (on) cudaEventRecord(marks.back().b, s); }
+    void report() {
+        if (!on || marks.empty()) return;
+        cudaDeviceSynchronize();
+        for (const Mark &m : marks) {
+            float t0 = 0, t1 = 0;
+            const cudaError_t e0 = cudaEventElapsedTime(&t0, marks[0].a, m.a), e1 = cudaEventElapsedTime(&t1, marks[0].a, m.b);
+            if (e0 != cudaSuccess || e1 != cudaSuccess) fprintf(stderr, "chz-trace: %s / %s\n", cudaGetErrorString(e0), cudaGetErrorString(e1));
+            fprintf(stderr, "chz-trace part %d %-8s %9.1f -> %9.1f us (%7.1f)\n", m.part, m.what, t0 * 1e3, t1 * 1e3, (t1 - t0) * 1e3);
+        }
+        for (const Mark &m : marks) { cudaEventDestroy(m.a); cudaEventDestroy(m.b); }
+        marks.clear();
+    }
+};
+}  // namespace
 
 extern "C" {
 
@@ -306,14 +462,15 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
     if (r < 0) return r;
     if (h->modes_dirty) {
         PB_CUDA(cudaMemcpyAsync(h->d_modes, h->modes.data(), sizeof(int) * h->nch, cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
-        // thread slots of chan_demod_kernel: NBFM channels, then AM, then pass-through, each group padded to a whole warp
+        // channel slots of chan_demod_kernel: NBFM channels (the longest walks) first, then AM, then pass-through; a warp takes
+        // PB_CHZ_C consecutive slots, so every group is padded to a multiple of that
         std::vector<int> order;
         for (int grp = 0; grp < 3; ++grp) {
             for (int c = 0; c < h->nch; ++c) {
                 const int g = h->modes[c] == CH_FMN ? 0 : h->modes[c] == CH_AM ? 1 : 2;
                 if (g == grp) order.push_back(c);
             }
-            while (order.size() % 32) order.push_back(-1);
+            while (order.size() % PB_CHZ_C) order.push_back(-1);
         }
         h->slots = (int)order.size();
         PB_CUDA(cudaMemcpy(h->d_order, order.data(), sizeof(int) * order.size(), cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
@@ -330,31 +487,39 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
     PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamWaitEvent(h->tail2, h->ev_front, 0), PEBBLE_ERR_CUDA);
+    ChzTrace tr;
+    tr.on = getenv("PEBBLE_CHZ_TRACE") != nullptr;
     int f0 = 0;
     for (int k = 0; k < parts; ++k) {
         const int f1 = (int)((long long)frames * (k + 1) / parts);
         const int pd = (f1 - f0) * h->fpb;             // decimated samples of this part
         const long long pos = (long long)f0 * h->fpb;  // its column in the work rows and in the output rows
         const long long pn = (long long)pd << h->S;
+        tr.begin("front", k, st);
         r = pebble_downconvert_process_channels_device(h->dc, (int)pn, (const char *)d_in + bps * (size_t)(pos << h->S),
                                                        (double *)(h->d_dec + pos), row, st);   // receiver.cpp:908
+        tr.end(st);
         if (r < 0) return r;
+        tr.begin("fastfir", k, st);
         r = pebble_fastfir_process_batch_device(h->bp, pd, (const double *)(h->d_dec + pos), row, (double *)(h->d_bp + pos), row, st);   // :950
+        tr.end(st);
         if (r < 0) return r;
         if (r != pd) { pebble::set_error("channelizer: FastFIR returned %d of %d", r, pd); return PEBBLE_ERR_STATE; }
         PB_CUDA(cudaEventRecord(h->ev_front, st), PEBBLE_ERR_CUDA);
         PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
-        chan_demod_kernel<<<h->slots / 32, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->d_order,
+        tr.begin("demod", k, h->tail);
+        chan_demod_kernel<<<(h->slots + PB_CHZ_C - 1) / PB_CHZ_C, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->d_order,
                                                             h->slots, h->pll, (double)0.9999f, h->d_state, h->fpb);                         // :987
         // the walks of consecutive parts form the critical chain (32 warps, latency-bound); the post filter of part k runs
         // beside the walk of part k+1 on its own stream
+        tr.end(h->tail);
         PB_CUDA(cudaEventRecord(h->ev_demod, h->tail), PEBBLE_ERR_CUDA);
         PB_CUDA(cudaStreamWaitEvent(h->tail2, h->ev_demod, 0), PEBBLE_ERR_CUDA);
-        int gx = (pd + 255) / 256;
-        if (gx > 64) gx = 64;
-        chan_cfir_kernel<<<dim3(gx, h->nch), 256, 0, h->tail2>>>(h->d_hist[h->hcur], h->d_tmp + pos, row, pd, h->d_taps, h->ntaps_am,
-                                                                h->ntaps_fm, h->d_modes, (cpx *)d_out + pos, out_stride,
-                                                                h->d_hist[h->hcur ^ 1]);
+        tr.begin("cfir", k, h->tail2);
+        chan_cfir_kernel<<<dim3((pd + PB_FIR_TILE - 1) / PB_FIR_TILE, h->nch), PB_FIR_THREADS, 0, h->tail2>>>(
+            (const double *)h->d_hist[h->hcur], h->d_tmp + pos, row, h->d_bp + pos, pd, h->d_taps, h->ntaps_am, h->ntaps_fm, h->d_modes,
+            (cpx *)d_out + pos, out_stride, (double *)h->d_hist[h->hcur ^ 1]);
+        tr.end(h->tail2);
         pebble::count_launch(2);
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
         h->hcur ^= 1;
@@ -365,6 +530,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
     PB_CUDA(cudaStreamWaitEvent(st, h->ev_tail, 0), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaEventRecord(h->ev_cfir, h->tail2), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaStreamWaitEvent(st, h->ev_cfir, 0), PEBBLE_ERR_CUDA);
+    tr.report();
     return nd;
 }
 

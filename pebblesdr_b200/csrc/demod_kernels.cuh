@@ -317,7 +317,8 @@ __device__ __forceinline__ float pll_theta(const cpx xi) {
     return mx == 0.0f ? CUDART_NAN_F : r;   // NaN marks "phzerror = 0" (atan2(0, 0) = 0 in the reference)
 }
 __device__ __forceinline__ void pll_step(const float theta, cpx &yo, const PllConst &c, PllState &v) {
-    const float k = rintf(v.phase * 0.15915494309189535f);
+    // k = nearest integer to phase / 2 pi by the 1.5 * 2^23 trick (|k| < 2^22): two FP32-pipe operations instead of FMUL + FRND
+    const float k = fmaf(v.phase, 0.15915494309189535f, 12582912.0f) - 12582912.0f;
     float r = fmaf(k, -PB_TWO_PI_HI, v.phase);
     r = fmaf(k, -PB_TWO_PI_LO, r);
     float e = theta + r;                                   // arg(x e^{j phase}) in (-2 pi, 2 pi)
