@@ -85,12 +85,28 @@ __global__ void __launch_bounds__(128, 2) poly_fir_kernel(const PolyArgs a) {
     const int total = nt + Q - 1;
     cpx osc = cpx_make(0.0, 0.0);
     const double inv_r = a.chain->inv_r_inf;
+    // The rows of a branch are D samples apart, so every row is a fresh DRAM line and a load issued where it is used costs the
+    // warp the full memory latency per row (ncu of that form: 1070 cycles per row, FP64 pipe 19.5 % busy with 8 warps per SM;
+    // the compiler may not hoist the load over the store to `v`). PF rows are kept in flight in a register ring instead: row
+    // k + PF is requested before row k is mixed and filtered (~2 x 110 pipe cycles per row and warp: PF = 5 rows cover ~1100).
+    constexpr int PF = (Q % 5 == 0) ? 5 : 4;
+    static_assert(Q % PF == 0, "the ring index must be static under the Q-fold unroll");
+    cpx ring[PF];
+#pragma unroll
+    for (int f = 0; f < PF; ++f) {
+        const long long jf = j + (long long)f * D;
+        ring[f] = poly_load<FMT>(a.hist, a.in, jf < jmax ? jf : jmax, a.hist_len);
+    }
     for (int kb = 0; kb < total; kb += Q) {
 #pragma unroll
         for (int r = 0; r < Q; ++r) {
             const int k = kb + r;
             const long long jj = j < jmax ? j : jmax;          // rows past the tile end are computed but never stored
-            cpx x = poly_load<FMT>(a.hist, a.in, jj, a.hist_len);
+            const cpx x = ring[r % PF];
+            {
+                const long long jn = j + (long long)PF * D;
+                ring[r % PF] = poly_load<FMT>(a.hist, a.in, jn < jmax ? jn : jmax, a.hist_len);
+            }
             if ((k & 31) == 0)
                 osc = cpx_scale(dc_phase_to_osc(dc_phase_at(a.ph_hi, a.ph_lo, a.turn_hi, a.turn_lo, (uint64_t)(jj + 1))), a.seed_amp);
             else
