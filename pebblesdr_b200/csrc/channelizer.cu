@@ -26,20 +26,6 @@ struct ChanState {      // per-channel demod state
     double am_dc_last;  // Demod_AM::m_amDcLast (demod_am.cpp:52-54)
 };
 
-// sqrt(x), x >= 0, without the library routine's branches: float rsqrt seed (2^-22), two Newton steps on 1/sqrt (2^-85), one
-// correction of x * r: within 1 ulp of the correctly rounded root. Outside the float range (never for IQ envelopes) and for
-// 0 it falls back to sqrt().
-__device__ __forceinline__ double pb_sqrt_newton(double x) {
-    if (!(x > 1e-36 && x < 1e36)) return sqrt(x);
-    double r = (double)rsqrtf((float)x);
-    const double hx = 0.5 * x;
-    r = fma(r, fma(-hx, r * r, 0.5), r);
-    r = fma(r, fma(-hx, r * r, 0.5), r);
-    double s = x * r;
-    s = fma(fma(-s, s, x), 0.5 * r, s);
-    return s;
-}
-
 // chan_demod_kernel: in/out rows of `stride` cpx. The demodulators are serial recurrences (PLL feedback, DC-block IIR), so a
 // channel's speed is the latency of ONE sample's dependent chain and nothing else; what the kernel can choose is how many
 // issue slots it spends around that chain, because the walks run BESIDE the next part's front end (other streams):

@@ -1,6 +1,6 @@
 // common.cuh — shared types and helpers for the pebblesdr_b200 kernels.
-// The core math lives in PB_HD functions so the same source compiles (a) as sm_100a device code and
-// (b) with plain g++ for the thread-by-thread host emulation in tests/host_emul/ (no GPU in CI).
+// The core math lives in PB_HD functions: the same source compiles as sm_100a device code and, in the host-only
+// translation units (host_design.cpp), with plain g++.
 #pragma once
 #include <stdint.h>
 #include <math.h>
@@ -30,3 +30,19 @@ template <bool INV> PB_HD cpx cpx_mulj(cpx a) {
     return INV ? make_double2(-a.y, a.x) : make_double2(a.y, -a.x);
 }
 static_assert(sizeof(cpx) == 16 && alignof(cpx) == 16, "cpx must match CUDA double2 in host-only translation units");
+
+#if defined(__CUDACC__)
+// sqrt(x), x >= 0, without the library routine's branches: float rsqrt seed (2^-22), two Newton steps on 1/sqrt (2^-85), one
+// correction of x * r: within 1 ulp of the correctly rounded root. Outside the float range (never for IQ envelopes) and for
+// 0 it falls back to sqrt().
+__device__ __forceinline__ double pb_sqrt_newton(double x) {
+    if (!(x > 1e-36 && x < 1e36)) return sqrt(x);
+    double r = (double)rsqrtf((float)x);
+    const double hx = 0.5 * x;
+    r = fma(r, fma(-hx, r * r, 0.5), r);
+    r = fma(r, fma(-hx, r * r, 0.5), r);
+    double s = x * r;
+    s = fma(fma(-s, s, x), 0.5 * r, s);
+    return s;
+}
+#endif

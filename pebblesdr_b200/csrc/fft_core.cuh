@@ -159,6 +159,7 @@ template <int N> struct FftPlan;
 
 template <> struct FftPlan<1024> {   // 16 x 8 x 8 (the polyphase channelizer's branch DFT, chz_poly.cu)
     static constexpr int NP = 3, SH = 3 + 100 * 6, THREADS = 128;
+    static constexpr int R0 = 16;   // radix of pass 0 (sub-transform length N)
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<1024, 16, 1024, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<1024, 8, 64, INV, SH>(a, tw, tid, nt);
@@ -170,6 +171,7 @@ template <> struct FftPlan<1024> {   // 16 x 8 x 8 (the polyphase channelizer's 
 
 template <> struct FftPlan<2048> {
     static constexpr int NP = 3, SH = 3 + 100 * 7, THREADS = 128;
+    static constexpr int R0 = 16;   // radix of pass 0 (sub-transform length N)
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<2048, 16, 2048, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<2048, 16, 128, INV, SH>(a, tw, tid, nt);
@@ -181,6 +183,7 @@ template <> struct FftPlan<2048> {
 
 template <> struct FftPlan<4096> {
     static constexpr int NP = 3, SH = 4 + 100 * 8, THREADS = 256;
+    static constexpr int R0 = 16;   // radix of pass 0 (sub-transform length N)
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<4096, 16, 4096, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<4096, 16, 256, INV, SH>(a, tw, tid, nt);
@@ -192,6 +195,7 @@ template <> struct FftPlan<4096> {
 
 template <> struct FftPlan<8192> {
     static constexpr int NP = 4, SH = 4 + 100 * 10, THREADS = 512;
+    static constexpr int R0 = 8;   // radix of pass 0 (sub-transform length N)
     template <int P, bool INV> static PB_HD void pass(cpx *a, const cpx *tw, int tid, int nt) {
         if (P == 0) fft_pass<8192, 8, 8192, INV, SH>(a, tw, tid, nt);
         if (P == 1) fft_pass<8192, 8, 1024, INV, SH>(a, tw, tid, nt);

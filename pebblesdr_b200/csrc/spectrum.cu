@@ -8,6 +8,7 @@
 #include "lib_common.h"
 #include "fft_kernels.cuh"
 #include "host_design.h"
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -38,7 +39,8 @@ template <int N> __device__ __forceinline__ double spec_asd(const cpx *a, int j,
     // DB::amplitude / coherentGain (fft.cpp:350) / maxBinPower (fft.cpp:358). cg and maxbin arrive as RECIPROCALS: two
     // FP64 divisions per bin were ~60 instructions of the ~300 per sample; the products differ from the quotients by
     // <= 1 ulp each (1e-15 dB), far inside the 1e-6 dB tolerance; 1/maxbin is exact for power-of-two buffer sizes.
-    return sqrt(X.x * X.x + X.y * X.y) * inv_cg * inv_maxbin;
+    // sqrt: the branch-free Newton form (common.cuh), within 1 ulp of the correctly rounded root: ~2e-15 dB
+    return pb_sqrt_newton(X.x * X.x + X.y * X.y) * inv_cg * inv_maxbin;
 }
 
 // DB::amplitudeTodB (db.h:44-48) + DB::clip (db.h:24-26): 20 log10(bin) clipped to [-120, 0]. The library log10 was 31 % of
@@ -128,6 +130,123 @@ spectrum_kernel(const cpx *__restrict__ in, int frames, int n, const double *__r
     }
 }
 
+// ---- full frames (n == N): the frame never sits in shared memory as raw input ------------------------------------------
+// spectrum_kernel stages a frame (global -> window -> shared), then pass 0 reads it back: one shared-memory round trip, one
+// barrier, and the whole DRAM latency of the frame exposed once per frame (one CTA per SM at N = 8192: nothing else runs
+// meanwhile; ncu r1: DRAM 17.8 % busy, LSU data pipe 63 %). Pass 0's butterfly bf takes the points bf + k N / R0 — consecutive
+// bf are consecutive samples, so the butterfly can take its inputs straight from global memory, coalesced, window and overload
+// test applied in registers. The loads of frame f+1 are issued BEFORE the epilogue of frame f (sqrt, dB, stores: thousands of
+// cycles) and consumed after it, so they are in flight under work that needs no shared memory bandwidth.
+template <int N> struct SpecFetch {
+    static constexpr int T = FftPlan<N>::THREADS, R0 = FftPlan<N>::R0, S0 = N / R0, NB = S0 / T;   // butterflies per thread in pass 0
+    cpx x[NB][R0];
+    __device__ __forceinline__ void fetch(const cpx *__restrict__ in) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b)
+#pragma unroll
+            for (int k = 0; k < R0; ++k) x[b][k] = __ldg(in + threadIdx.x + b * T + k * S0);
+    }
+    // window + overload test + pass 0 (forward: DFT, then twiddle), written to the swizzled slots of a[]
+    __device__ __forceinline__ int pass0(cpx *a, const cpx *__restrict__ tw, const double *__restrict__ win, bool windowed, double over_limit) {
+        constexpr int SH = FftPlan<N>::SH;
+        int over = 0;
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            const int i = threadIdx.x + b * T;
+            cpx v[R0];
+            cpx w[16];
+#pragma unroll
+            for (int k = 0; k < R0; ++k) {
+                v[k] = x[b][k];
+                if (windowed) {   // fft.cpp:136-142: overload test on the raw sample, then in[i] * windowCpx[i]
+                    if (fabs(v[k].x) > over_limit || fabs(v[k].y) > over_limit) over = 1;
+                    v[k] = cpx_scale(v[k], __ldg(win + i + k * S0));
+                }
+            }
+            fft_twiddle_powers<R0>(tw, i, N - 1, w);
+            DftR<R0, false>::run(v);
+#pragma unroll
+            for (int q = 1; q < R0; ++q) v[q] = cpx_mul(v[q], w[q]);
+#pragma unroll
+            for (int k = 0; k < R0; ++k) a[fft_swz<SH>(i + k * S0)] = v[k];
+        }
+        return over;
+    }
+};
+template <int N, int P> struct FftRunFrom1 {   // passes 1 .. P, a barrier after each
+    static PB_D void fwd(cpx *a, const cpx *tw) {
+        FftRunFrom1<N, P - 1>::fwd(a, tw);
+        FftPlan<N>::template pass<P, false>(a, tw, threadIdx.x, blockDim.x);
+        __syncthreads();
+    }
+};
+template <int N> struct FftRunFrom1<N, 0> { static PB_D void fwd(cpx *, const cpx *) {} };
+
+template <int N>
+__global__ void __launch_bounds__(FftPlan<N>::THREADS)
+spectrum_full_kernel(const cpx *__restrict__ in, int frames, const double *__restrict__ win, int windowed,
+                     double cg, double maxbin /* both reciprocals, see spec_asd */, double over_limit, const double *__restrict__ prev_in,
+                     double *__restrict__ prev_out, const int *__restrict__ flag_in, int *__restrict__ flag_out,
+                     double *__restrict__ out_db, int *__restrict__ out_flags, int run, const cpx *__restrict__ tw) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cpx *a = reinterpret_cast<cpx *>(smem_raw);
+    constexpr int T = FftPlan<N>::THREADS;
+    constexpr int PER = N / T;
+    __shared__ double db_tab[64];
+    if (threadIdx.x < 32) {
+        const double c = 1.0 + (threadIdx.x + 0.5) / 32.0;
+        db_tab[threadIdx.x] = 1.0 / c;
+        db_tab[32 + threadIdx.x] = 20 * log10(c);
+    }
+    // the previous frame's unaveraged amplitudes sit behind the frame in shared memory (8 N bytes): in registers they and the
+    // prefetched frame (64 + 32 registers at N = 8192, 512 threads = 128 registers each) spilled
+    double *prev = reinterpret_cast<double *>(a + N) + threadIdx.x;   // element k of this thread: prev[k * T]
+    const int f0 = blockIdx.x * run;
+    int f1 = f0 + run;
+    if (f1 > frames) f1 = frames;
+    if (f0 >= f1) return;
+    const int carried_flag = *flag_in;
+    SpecFetch<N> sf;
+    if (f0 == 0) {
+#pragma unroll
+        for (int k = 0; k < PER; ++k) prev[k * T] = prev_in[threadIdx.x + k * T];
+    } else {
+        // pre-roll: unaveraged amplitudes of frame f0-1
+        sf.fetch(in + (long long)(f0 - 1) * N);
+        sf.pass0(a, tw, win, windowed != 0, over_limit);
+        __syncthreads();
+        FftRunFrom1<N, FftPlan<N>::NP - 1>::fwd(a, tw);
+#pragma unroll
+        for (int k = 0; k < PER; ++k) prev[k * T] = spec_asd<N>(a, threadIdx.x + k * T, cg, maxbin);
+        __syncthreads();
+    }
+    sf.fetch(in + (long long)f0 * N);
+    for (int f = f0; f < f1; ++f) {
+        const bool over = __syncthreads_or(sf.pass0(a, tw, win, windowed != 0, over_limit)) != 0;   // also the barrier after pass 0
+        FftRunFrom1<N, FftPlan<N>::NP - 1>::fwd(a, tw);
+        if (f + 1 < f1) sf.fetch(in + (long long)(f + 1) * N);      // in flight during the epilogue below
+        double *o = out_db + (long long)f * N;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const int j = threadIdx.x + k * T;
+            const double asd = spec_asd<N>(a, j, cg, maxbin);
+            const double bin = (asd + prev[k * T]) / 2;   // fft.cpp:380 (m_isAveraged is always true, fft.cpp:103)
+            prev[k * T] = asd;                            // fft.cpp:388: keep the UNAVERAGED value
+            __stcs(o + j, spec_db(bin, db_tab));      // DB::amplitudeTodB + DB::clip; streaming store: never re-read here
+        }
+        if (threadIdx.x == 0) {
+            const int fl = windowed ? (over ? 1 : 0) : carried_flag;
+            if (out_flags) out_flags[f] = fl;
+            if (f == frames - 1) *flag_out = fl;
+        }
+        __syncthreads();
+    }
+    if (f1 == frames) {
+#pragma unroll
+        for (int k = 0; k < PER; ++k) prev_out[threadIdx.x + k * T] = prev[k * T];
+    }
+}
+
 // plain transforms with natural (FFTW) bin order at the interface
 template <int N, bool INV>
 __global__ void __launch_bounds__(FftPlan<N>::THREADS)
@@ -190,6 +309,18 @@ template <int N> static cudaError_t spec_launch(pebble_fft *h, int frames, int n
     if (run > frames) run = frames;
     const int grid = (frames + run - 1) / run;
     const bool windowed = h->wtype != PEBBLE_WINDOW_NONE && n == h->spb;
+    if constexpr (N == 8192) {   // one CTA per SM either way at this size; the smaller sizes keep their higher occupancy
+      if (n == N && !getenv("PEBBLE_SPEC_STAGED")) {     // full frames: pass 0 fed from global memory (spectrum_full_kernel)
+        const size_t smem2 = smem + sizeof(double) * N;
+        e = cudaFuncSetAttribute(spectrum_full_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+        if (e != cudaSuccess) return e;
+        spectrum_full_kernel<N><<<grid, FftPlan<N>::THREADS, smem2, st>>>(in, frames, h->d_win, windowed ? 1 : 0, 1.0 / h->cg, 1.0 / h->maxbin, 0.9,
+                                                                        h->d_prev[h->cur], h->d_prev[h->cur ^ 1], h->d_flag[h->cur],
+                                                                        h->d_flag[h->cur ^ 1], out, flags, run, h->d_tw);
+        pebble::count_launch();
+        return cudaGetLastError();
+      }
+    }
     spectrum_kernel<N><<<grid, FftPlan<N>::THREADS, smem, st>>>(in, frames, n, h->d_win, windowed ? 1 : 0, 1.0 / h->cg, 1.0 / h->maxbin, 0.9,
                                                                h->d_prev[h->cur], h->d_prev[h->cur ^ 1], h->d_flag[h->cur],
                                                                h->d_flag[h->cur ^ 1], out, flags, run, h->d_tw);
