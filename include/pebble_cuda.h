@@ -324,13 +324,18 @@ int pebble_agc_process_device(pebble_agc_t *h, int n, const double *d_in, double
  * Replaces application/demod.h Demod::processBlock (demod.cpp:100-141). mode = DeviceInterface::DemodMode
  * (device_interfaces.h:124-137): 0 dmAM (Demod_AM::processBlockFiltered, demod_am.cpp:40-64), 2 dmFMN
  * (Demod_NFM::processBlockNCO, demod_nfm.cpp:225-257; variant 1 = processBlockFM2, :124-140),
+ * 1 dmSAM (Demod_SAM::processBlock, demod/demod_sam.cpp:41-112), 3 dmFMM (Demod::fmMono -> Demod_WFM::processDataMono,
+ * demod.cpp:168-175, demod/demod_wfm.cpp:207-231: 75 kHz IIR low-pass at >= 150 kS/s, discriminator, 15 kHz CFir, 75 us
+ * de-emphasis, 19 kHz notch; pebble_demod_set_wfm_sample_rate() = the second rate of Demod(sampleRate, wfmSampleRate, n),
+ * demod.cpp:50-66, default = input_rate),
  * 5..12 DSB/LSB/USB/CW/DIG/NONE = pass-through (the reference returns `in`; here out is a copy and
- * pebble_demod_is_passthrough() reports it). 1 dmSAM, 3 dmFMM, 4 dmFMS: PEBBLE_ERR_STATE (out of scope). */
+ * pebble_demod_is_passthrough() reports it). 4 dmFMS (stereo + RDS): PEBBLE_ERR_STATE (not built). */
 typedef struct pebble_demod pebble_demod_t;
 pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples);
 void pebble_demod_destroy(pebble_demod_t *h);
 int pebble_demod_set_mode(pebble_demod_t *h, int mode);
 int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant);
+int pebble_demod_set_wfm_sample_rate(pebble_demod_t *h, double rate);
 int pebble_demod_set_bandwidth(pebble_demod_t *h, double bandwidth);
 int pebble_demod_is_passthrough(const pebble_demod_t *h);
 int pebble_demod_process(pebble_demod_t *h, int n, const double *in, double *out);
@@ -385,6 +390,7 @@ pebble_iir_t *pebble_iir_create(void);
 void pebble_iir_destroy(pebble_iir_t *h);
 int pebble_iir_init(pebble_iir_t *h, int kind, double f0, double q, double sample_rate);
 int pebble_iir_get_coefficients(const pebble_iir_t *h, double *a1a2b0b1b2);
+int pebble_iir_set_coefficients(pebble_iir_t *h, const double *a1a2b0b1b2);   /* raw biquad (m_A1.. are public members of CIir, iir.h) */
 int pebble_iir_process(pebble_iir_t *h, int n, const double *in, double *out);
 int pebble_iir_process_device(pebble_iir_t *h, int n, const double *d_in, double *d_out, void *stream);
 int pebble_iir_get_state(pebble_iir_t *h, double *w4);

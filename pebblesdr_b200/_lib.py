@@ -138,6 +138,7 @@ SIGNATURES = {
     "pebble_demod_destroy": (None, [c_vp]),
     "pebble_demod_set_mode": (c_int, [c_vp, c_int]),
     "pebble_demod_set_nfm_variant": (c_int, [c_vp, c_int]),
+    "pebble_demod_set_wfm_sample_rate": (c_int, [c_vp, c_dbl]),
     "pebble_demod_set_bandwidth": (c_int, [c_vp, c_dbl]),
     "pebble_demod_is_passthrough": (c_int, [c_vp]),
     "pebble_demod_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
@@ -182,6 +183,7 @@ SIGNATURES = {
     "pebble_iir_destroy": (None, [c_vp]),
     "pebble_iir_init": (c_int, [c_vp, c_int, c_dbl, c_dbl, c_dbl]),
     "pebble_iir_get_coefficients": (c_int, [c_vp, c_vp]),
+    "pebble_iir_set_coefficients": (c_int, [c_vp, c_vp]),
     "pebble_iir_process": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "pebble_iir_process_device": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp]),
     "pebble_iir_get_state": (c_int, [c_vp, c_vp]),

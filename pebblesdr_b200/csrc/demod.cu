@@ -256,12 +256,50 @@ struct pebble_demod {
     pebble_cfir sam_bp;
     SamConst sam;
     SamState *d_sam = nullptr;
+    // WFM mono (demod_wfm.cpp:207-231): input LP (>= 150 kS/s only), discriminator, audio LP, de-emphasis, pilot notch
+    double wfm_rate = 0;
+    pebble_iir_t *wfm_in_lp = nullptr, *wfm_deemph = nullptr, *wfm_notch = nullptr;
+    pebble_cfir wfm_lp;
+    cpx *d_wfm_last[2] = {nullptr, nullptr};
+    int wfm_cur = 0;
     // scratch (grow-only)
     cpx *d_tmp = nullptr; size_t tmp_cap = 0;
     Aff *d_tiles = nullptr; double *d_carry = nullptr; int tiles_cap = 0;
     cudaStream_t stream = nullptr;
     pebble::Staging stg;
 };
+// Demod_WFM::processDataMono's discriminator (demod_wfm.cpp:214-220): FMDEMOD_GAIN * atan2(D1.re D0.im - D0.re D1.im,
+// D1.re D0.re + D1.im D0.im), D1 = the previous sample (carried over calls); products and sums separately rounded like the
+// reference's build. Output (v, v).
+static __global__ void wfm_disc_kernel(const cpx *__restrict__ in, int n, const cpx *__restrict__ last_in, cpx *__restrict__ out,
+                                       cpx *__restrict__ last_out) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const cpx d0 = in[i];
+        const cpx d1 = i ? in[i - 1] : *last_in;
+        const double im = __dsub_rn(__dmul_rn(d1.x, d0.y), __dmul_rn(d0.x, d1.y));
+        const double re = __dadd_rn(__dmul_rn(d1.x, d0.x), __dmul_rn(d1.y, d0.y));
+        const double v = __dmul_rn(0.25, atan2(im, re));
+        out[i] = cpx_make(v, v);
+        if (i == n - 1) *last_out = d0;
+    }
+}
+// Demod_WFM::setSampleRate (demod_wfm.cpp:155-196) for the mono path; out rate = sample rate (the constructor's init, :110-114)
+static int wfm_setup(pebble_demod *h, double rate) {
+    h->wfm_rate = rate;
+    if (pebble_iir_init(h->wfm_in_lp, PEBBLE_IIR_LP, 75000.0, 1.0, rate) < 0) return PEBBLE_ERR_CUDA;      // m_MonoLPFilter.InitLP(75000, 1.0, rate)
+    if (pebble_iir_init(h->wfm_notch, PEBBLE_IIR_BR, 19000.0, 5.0, rate) < 0) return PEBBLE_ERR_CUDA;     // m_NotchFilter.InitBR(19000, 5, rate)
+    // de-emphasis, US version 75 us (:183, :452-470): Ave = (1 - a) Ave + a x, out = 2 Ave — a one-pole section written as the
+    // biquad w0 = x + (1 - a) w1, y = 2 a w0 (same transfer function; the two orders differ by roundings, ~1e-16)
+    const double a = 1.0 - exp(-1.0 / (rate * 75E-6));
+    const double co[5] = {-(1.0 - a), 0.0, 2.0 * a, 0.0, 0.0};
+    if (pebble_iir_set_coefficients(h->wfm_deemph, co) < 0) return PEBBLE_ERR_CUDA;
+    h->wfm_lp.ntaps = pebble_host::cfir_design_lp(0, 1.0, 60.0, 15000.0, 1.4 * 15000.0, rate, h->wfm_lp.hI);   // m_LPFilter, :176
+    memcpy(h->wfm_lp.hQ, h->wfm_lp.hI, sizeof(double) * h->wfm_lp.ntaps);
+    if (cfir_upload(&h->wfm_lp) < 0) return PEBBLE_ERR_CUDA;
+    for (int b = 0; b < 2; ++b) PB_CUDA(cudaMemset(h->d_wfm_last[b], 0, sizeof(cpx)), PEBBLE_ERR_CUDA);
+    return 0;
+}
+
 static int demod_reserve(pebble_demod *h, int n) {
     if ((size_t)n > h->tmp_cap) {
         cudaFree(h->d_tmp);
@@ -347,8 +385,27 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
         return n;
     }
-    if (h->mode == 3 || h->mode == 4) {
-        pebble::set_error("demod: WFM modes (dmFMM / dmFMS) are not built (SURVEY 8f rank 4)");
+    if (h->mode == 3) {  // dmFMM -> Demod::fmMono -> Demod_WFM::processDataMono (demod.cpp:168-175, demod_wfm.cpp:207-231)
+        int r = demod_reserve(h, n);
+        if (r < 0) return r;
+        const cpx *x = d_in;
+        if (h->wfm_rate >= 150000.0) {   // the 75 kHz IIR needs >= 150 kS/s to be stable (:209-211)
+            r = pebble_iir_process_device(h->wfm_in_lp, n, (const double *)d_in, (double *)d_out, st);
+            if (r < 0) return r;
+            x = d_out;
+        }
+        wfm_disc_kernel<<<grid_for(n), 256, 0, st>>>(x, n, h->d_wfm_last[h->wfm_cur], h->d_tmp, h->d_wfm_last[h->wfm_cur ^ 1]);
+        pebble::count_launch();
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+        h->wfm_cur ^= 1;
+        r = cfir_run_device(&h->wfm_lp, n, h->d_tmp, d_out, st, true);                                   // roll off above 15 kHz; input is (v, v)
+        if (r < 0) return r;
+        r = pebble_iir_process_device(h->wfm_deemph, n, (const double *)d_out, (double *)h->d_tmp, st);  // 75 us de-emphasis
+        if (r < 0) return r;
+        return pebble_iir_process_device(h->wfm_notch, n, (const double *)h->d_tmp, (double *)d_out, st);   // 19 kHz pilot notch
+    }
+    if (h->mode == 4) {
+        pebble::set_error("demod: WFM stereo / RDS (dmFMS) is not built (SURVEY 8f rank 4); dmFMM (mono) is");
         return PEBBLE_ERR_STATE;
     }
     // USB/LSB/DSB/CW/DIG/NONE: Demod::processBlock returns `in` itself (demod.cpp:127-138)
@@ -362,7 +419,9 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
     (void)num_samples;
     pebble_demod *h = new pebble_demod();
     h->rate = input_rate;
-    bool ok = cfir_alloc(&h->am_lp) == 0 && cfir_alloc(&h->nfm_lp) == 0 && cfir_alloc(&h->sam_bp) == 0 &&
+    h->wfm_in_lp = pebble_iir_create(); h->wfm_deemph = pebble_iir_create(); h->wfm_notch = pebble_iir_create();
+    bool ok = h->wfm_in_lp && h->wfm_deemph && h->wfm_notch && cfir_alloc(&h->wfm_lp) == 0 &&
+              cfir_alloc(&h->am_lp) == 0 && cfir_alloc(&h->nfm_lp) == 0 && cfir_alloc(&h->sam_bp) == 0 &&
               pebble::cuda_ok(cudaMalloc(&h->d_sam, sizeof(SamState)), "cudaMalloc") &&
               pebble::cuda_ok(cudaMemset(h->d_sam, 0, sizeof(SamState)), "cudaMemset") &&
               pebble::cuda_ok(cudaMalloc(&h->d_pll, sizeof(PllState)), "cudaMalloc") &&
@@ -372,7 +431,8 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
         ok = pebble::cuda_ok(cudaMalloc(&h->d_am_last[b], sizeof(double)), "cudaMalloc") &&
              pebble::cuda_ok(cudaMemset(h->d_am_last[b], 0, sizeof(double)), "cudaMemset") &&
              pebble::cuda_ok(cudaMalloc(&h->d_fm_last[b], sizeof(cpx)), "cudaMalloc") &&
-             pebble::cuda_ok(cudaMemset(h->d_fm_last[b], 0, sizeof(cpx)), "cudaMemset");
+             pebble::cuda_ok(cudaMemset(h->d_fm_last[b], 0, sizeof(cpx)), "cudaMemset") &&
+             pebble::cuda_ok(cudaMalloc(&h->d_wfm_last[b], sizeof(cpx)), "cudaMalloc");
     }
     if (!ok) { pebble_demod_destroy(h); return nullptr; }
     // Demod_AM ctor: setBandwidth(16000) (demod_am.cpp:9)
@@ -409,12 +469,18 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
             h->sam_bp.hQ[k] = 2.0 * lp[k] * sin(a);
         }
     }
-    if (cfir_upload(&h->am_lp) < 0 || cfir_upload(&h->nfm_lp) < 0 || cfir_upload(&h->sam_bp) < 0) { pebble_demod_destroy(h); return nullptr; }
+    if (cfir_upload(&h->am_lp) < 0 || cfir_upload(&h->nfm_lp) < 0 || cfir_upload(&h->sam_bp) < 0 ||
+        wfm_setup(h, h->rate) < 0) {   // Demod_WFM(_inputRate, n): init(_inputRate, _inputRate) (demod_wfm.cpp:105-111)
+        pebble_demod_destroy(h);
+        return nullptr;
+    }
     return h;
 }
 void pebble_demod_destroy(pebble_demod_t *h) {
     if (!h) return;
-    cfir_release(&h->am_lp); cfir_release(&h->nfm_lp); cfir_release(&h->sam_bp);
+    cfir_release(&h->am_lp); cfir_release(&h->nfm_lp); cfir_release(&h->sam_bp); cfir_release(&h->wfm_lp);
+    pebble_iir_destroy(h->wfm_in_lp); pebble_iir_destroy(h->wfm_deemph); pebble_iir_destroy(h->wfm_notch);
+    cudaFree(h->d_wfm_last[0]); cudaFree(h->d_wfm_last[1]);
     cudaFree(h->d_sam);
     cudaFree(h->d_pll); cudaFree(h->d_tmp); cudaFree(h->d_tiles); cudaFree(h->d_carry);
     for (int b = 0; b < 2; ++b) { cudaFree(h->d_am_last[b]); cudaFree(h->d_fm_last[b]); }
@@ -426,6 +492,12 @@ int pebble_demod_set_mode(pebble_demod_t *h, int mode) {  // Demod::setDemodMode
     if (!h || mode < 0 || mode > 12) return PEBBLE_ERR_ARG;
     h->mode = mode;
     return 0;
+}
+// Demod(sampleRate, wfmSampleRate, bufferSize) (demod.cpp:50-66): the WFM object runs at its own input rate
+int pebble_demod_set_wfm_sample_rate(pebble_demod_t *h, double rate) {
+    if (!h || !(rate > 0)) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    return wfm_setup(h, rate);
 }
 int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant) {
     if (!h || variant < 0 || variant > 1) return PEBBLE_ERR_ARG;

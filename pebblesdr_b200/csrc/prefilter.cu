@@ -325,6 +325,15 @@ int pebble_iir_init(pebble_iir_t *h, int kind, double f0, double q, double fs) {
     h->tb_G = -1;
     return 0;
 }
+// Raw biquad (iir.h keeps m_A1, m_A2, m_B0, m_B1, m_B2 public): w0 = x - A1 w1 - A2 w2, y = B0 w0 + B1 w1 + B2 w2. State restarts at 0.
+int pebble_iir_set_coefficients(pebble_iir_t *h, const double *a1a2b0b1b2) {
+    if (!h || !a1a2b0b1b2) return PEBBLE_ERR_ARG;
+    h->c.a1 = a1a2b0b1b2[0]; h->c.a2 = a1a2b0b1b2[1]; h->c.b0 = a1a2b0b1b2[2]; h->c.b1 = a1a2b0b1b2[3]; h->c.b2 = a1a2b0b1b2[4];
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    for (int b = 0; b < 2; ++b) PB_CUDA(cudaMemset(h->d_state[b], 0, sizeof(double4)), PEBBLE_ERR_CUDA);
+    h->tb_G = -1;
+    return 0;
+}
 int pebble_iir_get_coefficients(const pebble_iir_t *h, double *a1a2b0b1b2) {
     if (!h || !a1a2b0b1b2) return PEBBLE_ERR_ARG;
     a1a2b0b1b2[0] = h->c.a1; a1a2b0b1b2[1] = h->c.a2; a1a2b0b1b2[2] = h->c.b0; a1a2b0b1b2[3] = h->c.b1; a1a2b0b1b2[4] = h->c.b2;

@@ -567,6 +567,10 @@ class Demod(_Handle):
     def setNfmVariant(self, variant):
         check(lib.pebble_demod_set_nfm_variant(self._h, variant))
 
+    def setWfmSampleRate(self, rate):
+        """The second rate of Demod(sampleRate, wfmSampleRate, bufferSize) (demod.cpp:50-66)."""
+        check(lib.pebble_demod_set_wfm_sample_rate(self._h, float(rate)), "setWfmSampleRate")
+
     def setBandwidth(self, bandwidth):
         check(lib.pebble_demod_set_bandwidth(self._h, bandwidth), "setBandwidth")
 

@@ -94,7 +94,7 @@ def test_ssb_passthrough_returns_input():
     for mode in (pb.Demod.dmUSB, pb.Demod.dmLSB, pb.Demod.dmCWU, pb.Demod.dmDIGL, pb.Demod.dmNONE):
         g.setDemodMode(mode)
         assert g.processBlock(x, 2048) is x            # demod.cpp:127-138 returns `in`
-    g.setDemodMode(pb.Demod.dmFMM)                     # WFM is not built: a loud error, not silence
+    g.setDemodMode(pb.Demod.dmFMS)                     # WFM stereo / RDS is not built: a loud error, not silence
     with pytest.raises(pb.PebbleError):
         g.processBlock(x, 2048)
 
@@ -185,3 +185,37 @@ def test_sam_demod_vs_compiled_reference():
     g2.setDemodMode(pb.Demod.dmSAM)
     got2 = g2.processBlock(x, n).copy()
     assert rel_rms(got2[lock:], got[lock:]) <= 1e-12
+
+
+@pytest.mark.parametrize("rate", [312500, 125000])
+def test_wfm_mono_vs_compiled_reference(rate):
+    """SURVEY 8f-4: Demod::fmMono -> Demod_WFM::processDataMono (demod_wfm.cpp:207-231) against the class compiled from the
+    reference: 75 kHz IIR low-pass (only at >= 150 kS/s: the 125 kS/s case skips it, :209-211), discriminator, 15 kHz CFir,
+    75 us de-emphasis, 19 kHz notch. Every stage is linear or pointwise: 1e-10 relative RMS from sample 0, frame-sized calls and
+    one call over the whole stream alike."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    frame, frames = 2048, 24
+    n = frame * frames
+    t = np.arange(n) / rate
+    rng = np.random.default_rng(31)
+    # 75 kHz deviation by a 1 kHz + 5 kHz programme, a 19 kHz pilot at 10 %, carrier 3 kHz off tune, some noise
+    m = 0.6 * np.sin(2 * np.pi * 1000.0 * t) + 0.3 * np.sin(2 * np.pi * 5000.0 * t) + 0.1 * np.sin(2 * np.pi * 19000.0 * t)
+    ph = 2 * np.pi * np.cumsum(60000.0 * m) / rate + 2 * np.pi * 3000.0 * t
+    x = np.ascontiguousarray(0.4 * np.exp(1j * ph) + (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.002)
+    r = ref_app.Demod_WFM(rate, frame)
+    want = np.concatenate([r.processDataMono(x[i:i + frame].copy()) for i in range(0, n, frame)])   # the reference overwrites its input
+    g = pb.Demod(rate, frame)
+    g.setDemodMode(pb.Demod.dmFMM)
+    got = np.concatenate([g.processBlock(np.ascontiguousarray(x[i:i + frame]), frame).copy() for i in range(0, n, frame)])
+    assert np.abs(want).max() > 0.01 and np.array_equal(want.real, want.imag)
+    assert rel_rms(got, want) <= 1e-10, rel_rms(got, want)
+    g2 = pb.Demod(78125, frame)                            # the two-rate constructor shape: Demod(sampleRate, wfmSampleRate, n)
+    g2.setWfmSampleRate(rate)
+    g2.setDemodMode(pb.Demod.dmFMM)
+    got2 = g2.processBlock(x, n).copy()
+    assert rel_rms(got2, want) <= 1e-10
+    # the pilot is notched out and the programme survives: 19 kHz at least 20 dB below 1 kHz in the audio
+    sp = np.abs(np.fft.rfft(got.real[n // 2:] * np.hanning(n - n // 2)))
+    f = np.fft.rfftfreq(n - n // 2, 1.0 / rate)
+    assert sp[np.argmin(np.abs(f - 19000.0))] < 0.1 * sp[np.argmin(np.abs(f - 1000.0))]

@@ -26,9 +26,11 @@ def stats(f, calls=CALLS):
 
 f = pb.FFT(); f.fftParams(N, 0, 20e6, N, 12)
 db = np.zeros(N)
-res = {"bins": N, "fftSpectrum_host_call": stats(lambda i: f.fftSpectrum(x, db, N))}
-ss = pb.SignalSpectrum(20000000, 20000000, N, N, 2048, 30)
+res = {"fftSpectrum_host_call_8192_bins": stats(lambda i: f.fftSpectrum(x, db, N))}
+# the reference's display shape: framesPerBuffer = 2048 samples zero-padded into 4096 bins (signalspectrum.cpp:21-52)
+ss = pb.SignalSpectrum(2000000, 62500, 2048, 4096, 2048, 30)
+x2 = np.ascontiguousarray(x[:2048])
 # every call 40 ms of caller clock after the last one: the 30 frames/s gate lets each through
-res["SignalSpectrum_unprocessed_host_call"] = stats(lambda i: ss.unprocessed(x, N, 40 * (i + 1)))
+res["SignalSpectrum_unprocessed_host_call_2048_into_4096_bins"] = stats(lambda i: ss.unprocessed(x2, 2048, 40 * (i + 1)))
 res["frame_period_ms_at_10_to_30_fps"] = [100.0, 33.3]
 print(json.dumps(res))
