@@ -479,6 +479,13 @@ int pebble_channelizer_set_demod_mode(pebble_channelizer_t *h, int ch, int mode)
 int pebble_channelizer_set_am_bandwidth(pebble_channelizer_t *h, double bandwidth);
 int pebble_channelizer_set_agc_threshold(pebble_channelizer_t *h, int threshold);
 int pebble_channelizer_out_count(const pebble_channelizer_t *h, int n);
+/* Squelch per channel (receiver.cpp:955-965: a frame whose band average is below the squelch level returns before AGC and
+ * demodulator). open[ch] == 0: channel ch yields zeros and its demodulator / post-filter state does not advance; NULL: all open.
+ * _from_spectrum: SignalStrength::fdEstimate (signalstrength.cpp:289-380) for every channel over ONE wideband dB spectrum on the
+ * device, with the channelizer's band-pass edges and channel centres; open = avgDb >= squelch_db; returns the open count. */
+int pebble_channelizer_set_squelch(pebble_channelizer_t *h, const unsigned char *open, int nch);
+int pebble_channelizer_squelch_from_spectrum(pebble_channelizer_t *h, const double *d_spectrum, int bins, unsigned spectrum_rate,
+                                             double squelch_db, void *stream);
 int pebble_channelizer_set_input_format(pebble_channelizer_t *h, int fmt, int order, double user_gain, double norm_gain);
 /* Front end of the last call: 1 = polyphase-DFT (all channel centres on the grid in_rate / 2^S: ONE mix, a 2^S-branch
  * polyphase FIR with the cascade's composite response and a 2^S-point DFT per output sample serve every channel; the

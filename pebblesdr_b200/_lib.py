@@ -161,6 +161,8 @@ SIGNATURES = {
     "pebble_channelizer_set_am_bandwidth": (c_int, [c_vp, c_dbl]),
     "pebble_channelizer_set_agc_threshold": (c_int, [c_vp, c_int]),
     "pebble_channelizer_out_count": (c_int, [c_vp, c_int]),
+    "pebble_channelizer_set_squelch": (c_int, [c_vp, c_vp, c_int]),
+    "pebble_channelizer_squelch_from_spectrum": (c_int, [c_vp, c_vp, c_int, ctypes.c_uint, c_dbl, c_vp]),
     "pebble_channelizer_set_input_format": (c_int, [c_vp, c_int, c_int, c_dbl, c_dbl]),
     "pebble_channelizer_front_path": (c_int, [c_vp]),
     "pebble_channelizer_downconvert_device": (c_int, [c_vp, c_int, c_vp, c_vp, ctypes.c_longlong, c_vp]),

@@ -63,7 +63,8 @@ __device__ __forceinline__ float pll_chain(const float th, const float th_turns,
 }
 static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__restrict__ in, cpx *__restrict__ out_rows, int n, long long stride,
                                          int nch, const int *__restrict__ modes, const int *__restrict__ order, int slots,
-                                         PllConst pc, double am_alpha, ChanState *__restrict__ st, int frame) {
+                                         PllConst pc, double am_alpha, ChanState *__restrict__ st, int frame,
+                                         const unsigned char *__restrict__ open) {
     // order[]: channels grouped by demodulator, each group padded (-1) to whole warps: a warp runs ONE kind of recurrence
     const int lane = threadIdx.x;
     const int s = lane % PB_CHZ_L;                           // this lane's position inside its channel's group
@@ -71,7 +72,9 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
     if (slot0 >= slots) return;
     const int slot = slot0 + lane / PB_CHZ_L;
     const int c = slot < slots ? order[slot] : -1;
-    const bool valid = c >= 0 && c < nch;
+    // a squelched channel (receiver.cpp:955-965 returns before AGC and demodulator: their state does not advance) rides along
+    // in its warp like a pad slot: nothing is stored for it
+    const bool valid = c >= 0 && c < nch && (open == nullptr || open[c] != 0);
     const int c0 = order[slot0];                             // never a pad: groups are padded at their END
     const int mode = modes[c0];
     const cpx *x = in + (long long)(valid ? c : c0) * stride;
@@ -185,7 +188,7 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
 static __global__ void __launch_bounds__(PB_FIR_THREADS)
 chan_cfir_kernel(const double *__restrict__ hist, const cpx *__restrict__ in_rows, long long in_stride, const cpx *__restrict__ bp,
                  int n, const double *__restrict__ taps, int ntaps_am, int ntaps_fm, const int *__restrict__ modes,
-                 cpx *__restrict__ out, long long out_stride, double *__restrict__ new_hist) {
+                 cpx *__restrict__ out, long long out_stride, double *__restrict__ new_hist, const unsigned char *__restrict__ open) {
     __shared__ double win[PB_FIR_TILE + PB_FIR_MAX + (PB_FIR_TILE + PB_FIR_MAX) / 8 + 1];
     __shared__ double sh_t[PB_FIR_MAX];
     const int c = blockIdx.y;
@@ -193,6 +196,12 @@ chan_cfir_kernel(const double *__restrict__ hist, const cpx *__restrict__ in_row
     cpx *y = out + c * out_stride;
     const int t0 = blockIdx.x * PB_FIR_TILE;
     const int valid = min(PB_FIR_TILE, n - t0);
+    if (open != nullptr && open[c] == 0) {   // squelched: no audio for this call (zeros), the filter's delay line is kept
+        for (int i = threadIdx.x; i < valid; i += PB_FIR_THREADS) y[t0 + i] = cpx_make(0.0, 0.0);
+        if (blockIdx.x == 0)
+            for (int i = threadIdx.x; i < PB_FIR_MAX; i += PB_FIR_THREADS) new_hist[(long long)c * PB_FIR_MAX + i] = hist[(long long)c * PB_FIR_MAX + i];
+        return;
+    }
     if (mode != CH_AM && mode != CH_FMN) {
         const cpx *xb = bp + c * in_stride;
         for (int i = threadIdx.x; i < valid; i += PB_FIR_THREADS) y[t0 + i] = xb[t0 + i];
@@ -249,6 +258,11 @@ struct pebble_channelizer {
     pebble_fastfir_t *bp = nullptr;
     std::vector<int> modes;
     int *d_modes = nullptr, *d_order = nullptr;
+    std::vector<double> freqs;         // channel centres (for the squelch estimate)
+    double bp_lo = 0, bp_hi = 0;       // band-pass edges
+    std::vector<unsigned char> open;   // per-channel squelch decision; empty = every channel open
+    unsigned char *d_open = nullptr;
+    bool open_dirty = false;
     int slots = 0;                     // entries of d_order
     bool modes_dirty = true;
     PllConst pll;
@@ -353,12 +367,14 @@ pebble_channelizer_t *pebble_channelizer_create(int nchannels, double in_rate, d
     const size_t hb = sizeof(cpx) * PB_FIR_MAX * (size_t)nchannels;
     ok = ok && pebble::cuda_ok(cudaMalloc(&h->d_modes, sizeof(int) * nchannels), "cudaMalloc") &&
          pebble::cuda_ok(cudaMalloc(&h->d_order, sizeof(int) * ((size_t)nchannels + 3 * 32)), "cudaMalloc") &&
+         pebble::cuda_ok(cudaMalloc(&h->d_open, (size_t)nchannels), "cudaMalloc") &&
          pebble::cuda_ok(cudaMalloc(&h->d_state, sizeof(ChanState) * nchannels), "cudaMalloc") &&
          pebble::cuda_ok(cudaMemset(h->d_state, 0, sizeof(ChanState) * nchannels), "cudaMemset") &&
          pebble::cuda_ok(cudaMalloc(&h->d_taps, sizeof(h->taps)), "cudaMalloc") &&
          pebble::cuda_ok(cudaMalloc(&h->d_hist[0], hb), "cudaMalloc") && pebble::cuda_ok(cudaMalloc(&h->d_hist[1], hb), "cudaMalloc");
     if (!ok) { pebble_channelizer_destroy(h); return nullptr; }
     h->modes.assign(nchannels, CH_AM);   // Demod starts in dmAM
+    h->freqs.assign(nchannels, 0.0);
     // Demod_NFM::init (demod_nfm.cpp:44-66); members are float
     const double norm = 6.28318530717958647692528676656 / (double)(unsigned)h->out_rate;
     h->pll.lo = (float)(-15000.0 * norm);
@@ -374,7 +390,7 @@ void pebble_channelizer_destroy(pebble_channelizer_t *h) {
     if (!h) return;
     if (h->dc) pebble_downconvert_destroy(h->dc);
     if (h->bp) pebble_fastfir_destroy(h->bp);
-    cudaFree(h->d_modes); cudaFree(h->d_order); cudaFree(h->d_state); cudaFree(h->d_taps); cudaFree(h->d_hist[0]); cudaFree(h->d_hist[1]);
+    cudaFree(h->d_modes); cudaFree(h->d_order); cudaFree(h->d_open); cudaFree(h->d_state); cudaFree(h->d_taps); cudaFree(h->d_hist[0]); cudaFree(h->d_hist[1]);
     cudaFree(h->d_dec); cudaFree(h->d_bp); cudaFree(h->d_tmp);
     if (h->tail) cudaStreamDestroy(h->tail);
     if (h->tail2) cudaStreamDestroy(h->tail2);
@@ -389,11 +405,38 @@ int pebble_channelizer_num_stages(const pebble_channelizer_t *h) { return h ? h-
 int pebble_channelizer_num_channels(const pebble_channelizer_t *h) { return h ? h->nch : PEBBLE_ERR_ARG; }
 int pebble_channelizer_set_frequency(pebble_channelizer_t *h, int ch, double f) {   // Receiver::mixerChanged per channel
     if (!h) return PEBBLE_ERR_ARG;
+    if (ch >= 0 && ch < h->nch) h->freqs[ch] = f;
     return pebble_downconvert_set_channel_frequency(h->dc, ch, f);
 }
 int pebble_channelizer_set_filter(pebble_channelizer_t *h, double lo, double hi) {   // BandPassFilter::setBandPass, all channels
     if (!h) return PEBBLE_ERR_ARG;
+    h->bp_lo = lo; h->bp_hi = hi;
     return pebble_fastfir_setup(h->bp, lo, hi, 0, h->out_rate);
+}
+// Squelch (receiver.cpp:955-965): a frame whose band average is below the squelch level returns before AGC and demodulator.
+// open[ch] != 0: channel ch is demodulated; 0: its calls produce zeros and its demodulator / post-filter state does not
+// advance (the down-converter and the band-pass keep running, as in the reference). open == NULL: every channel open.
+int pebble_channelizer_set_squelch(pebble_channelizer_t *h, const unsigned char *open, int nch) {
+    if (!h || (open && nch != h->nch)) return PEBBLE_ERR_ARG;
+    if (open) h->open.assign(open, open + nch); else h->open.clear();
+    h->open_dirty = true;
+    return 0;
+}
+// The decision itself, for every channel at once, from ONE wideband dB spectrum on the device (SignalSpectrum's unprocessed
+// output of the capture): SignalStrength::fdEstimate per channel with the channelizer's own band-pass edges and channel
+// centres, open = avgDb >= squelch_db. Returns the number of open channels.
+int pebble_channelizer_squelch_from_spectrum(pebble_channelizer_t *h, const double *d_spectrum, int bins, unsigned spectrum_rate,
+                                             double squelch_db, void *stream) {
+    if (!h || !d_spectrum || bins <= 0) return PEBBLE_ERR_ARG;
+    std::vector<double> out5((size_t)h->nch * 5);
+    const int r = pebble_sigstrength_fd_estimate_device(d_spectrum, bins, spectrum_rate, (float)h->bp_lo, (float)h->bp_hi, h->freqs.data(),
+                                                        h->nch, squelch_db, out5.data(), stream);
+    if (r < 0) return r;
+    h->open.resize(h->nch);
+    int nopen = 0;
+    for (int c = 0; c < h->nch; ++c) { h->open[c] = out5[(size_t)c * 5 + 4] != 0.0; nopen += h->open[c]; }
+    h->open_dirty = true;
+    return nopen;
 }
 int pebble_channelizer_set_demod_mode(pebble_channelizer_t *h, int ch, int mode) {
     if (!h || ch < 0 || ch >= h->nch || mode < 0 || mode > 12) return PEBBLE_ERR_ARG;
@@ -462,6 +505,11 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
         PB_CUDA(cudaMemcpy(h->d_order, order.data(), sizeof(int) * order.size(), cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
         h->modes_dirty = false;
     }
+    if (h->open_dirty) {
+        if (!h->open.empty()) PB_CUDA(cudaMemcpyAsync(h->d_open, h->open.data(), (size_t)h->nch, cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
+        h->open_dirty = false;
+    }
+    const unsigned char *d_open = h->open.empty() ? nullptr : h->d_open;
     const long long row = (long long)h->row_cap;
     const double gain = pow(10, (h->S * 2) / 20.0);                                                  // receiver.cpp:935-938
     const double agc_gain = pow(10, (h->agc_threshold / 5) / 20.0);                                  // agc.cpp:86-94 (integer division)
@@ -495,7 +543,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
         PB_CUDA(cudaStreamWaitEvent(h->tail, h->ev_front, 0), PEBBLE_ERR_CUDA);
         tr.begin("demod", k, h->tail);
         chan_demod_kernel<<<(h->slots + PB_CHZ_C - 1) / PB_CHZ_C, 32, 0, h->tail>>>(h->d_bp + pos, h->d_tmp + pos, pd, row, h->nch, h->d_modes, h->d_order,
-                                                            h->slots, h->pll, (double)0.9999f, h->d_state, h->fpb);                         // :987
+                                                            h->slots, h->pll, (double)0.9999f, h->d_state, h->fpb, d_open);                         // :987
         // the walks of consecutive parts form the critical chain (32 warps, latency-bound); the post filter of part k runs
         // beside the walk of part k+1 on its own stream
         tr.end(h->tail);
@@ -504,7 +552,7 @@ int pebble_channelizer_process_device(pebble_channelizer_t *h, int n, const void
         tr.begin("cfir", k, h->tail2);
         chan_cfir_kernel<<<dim3((pd + PB_FIR_TILE - 1) / PB_FIR_TILE, h->nch), PB_FIR_THREADS, 0, h->tail2>>>(
             (const double *)h->d_hist[h->hcur], h->d_tmp + pos, row, h->d_bp + pos, pd, h->d_taps, h->ntaps_am, h->ntaps_fm, h->d_modes,
-            (cpx *)d_out + pos, out_stride, (double *)h->d_hist[h->hcur ^ 1]);
+            (cpx *)d_out + pos, out_stride, (double *)h->d_hist[h->hcur ^ 1], d_open);
         tr.end(h->tail2);
         pebble::count_launch(2);
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);

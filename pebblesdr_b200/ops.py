@@ -756,6 +756,19 @@ class Channelizer(_Handle):
     def outCount(self, n):
         return check(lib.pebble_channelizer_out_count(self._h, n))
 
+    def setSquelch(self, open_mask=None):
+        """Per-channel squelch decision (receiver.cpp:955-965): 0 = the channel yields zeros and its demodulator state does not
+        advance. None: every channel open."""
+        if open_mask is None:
+            return check(lib.pebble_channelizer_set_squelch(self._h, None, 0), "setSquelch")
+        m = np.ascontiguousarray(open_mask, dtype=np.uint8)
+        return check(lib.pebble_channelizer_set_squelch(self._h, m.ctypes.data, int(m.size)), "setSquelch")
+
+    def squelchFromSpectrum(self, d_spectrum, spectrumSampleRate, squelchDb):
+        """fdEstimate for every channel over one wideband dB spectrum (CUDA float64 tensor); returns the number of open channels."""
+        return check(lib.pebble_channelizer_squelch_from_spectrum(self._h, d_spectrum.data_ptr(), d_spectrum.numel(), int(spectrumSampleRate),
+                                                                  float(squelchDb), _stream_ptr()), "squelchFromSpectrum")
+
     def downConvert(self, d_in, n, d_out):
         """d_out: [nchannels, >= n >> S] complex128 CUDA tensor (rows contiguous)."""
         assert d_out.dim() == 2 and d_out.shape[0] == self.nchannels and d_out.stride(1) == 1

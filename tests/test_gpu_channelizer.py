@@ -240,3 +240,84 @@ def test_channelizer_1024_channels_bench_shape_vs_oracle():
             assert rel_rms(got[k][:1024], want[:1024]) <= 0.5, (k, rel_rms(got[k][:1024], want[:1024]))
         else:
             assert rel_rms(got[k], want) <= 1e-10, (k, rel_rms(got[k], want))
+
+
+def test_squelch_is_a_per_channel_enable_and_keeps_demodulator_state():
+    """receiver.cpp:955-965: below the squelch level a frame returns BEFORE the AGC and the demodulator — their state does not
+    advance, the down-converter and band-pass keep running. Three one-frame calls A, B, C with channels 0 (NBFM) and 1 (AM)
+    squelched during B only:
+      * open channels are bit-identical to an unsquelched channelizer in all three calls;
+      * squelched channels give zeros in B;
+      * in C they give what the single-stream Demod operator (pinned to the compiled reference in test_gpu_demod.py) gives
+        when it sees the band-pass output of A and then of C — taken from a third channelizer whose channels 0, 1 are
+        pass-through (USB), i.e. its rows ARE the band-pass output."""
+    import torch
+    import pebblesdr_b200 as pb
+    nch, frame = 6, 2048
+    n1 = frame << 10
+    freqs = [-30.69e6 + 60e3 * (k * 170 + 3) for k in range(nch)]
+    modes = [2, 0, 2, 0, 7, 0]
+    x = torch.from_numpy(_capture(3 * n1, freqs, seed=99)).cuda()
+
+    def make(ms):
+        cz = pb.Channelizer(nch, FS, BW)
+        cz.setFilter(-7500.0, 7500.0)
+        for k in range(nch):
+            cz.setFrequency(k, freqs[k]); cz.setDemodMode(k, ms[k])
+        return cz
+
+    def run(cz, masks):
+        outs = []
+        for i, m in enumerate(masks):
+            cz.setSquelch(m)
+            o = torch.full((nch, frame), 7.0 + 7.0j, dtype=torch.complex128, device="cuda")
+            assert cz.process(x[i * n1:(i + 1) * n1], n1, o) == frame
+            outs.append(o.cpu().numpy())
+        return outs
+
+    closed = np.array([0, 0, 1, 1, 1, 1], dtype=np.uint8)
+    g0 = run(make(modes), [None, None, None])
+    g1 = run(make(modes), [None, closed, np.ones(nch, dtype=np.uint8)])
+    bp = run(make([7, 7] + modes[2:]), [None, None, None])
+    for i in range(3):
+        assert np.array_equal(g1[i][2:], g0[i][2:])                   # open channels: untouched
+    assert np.array_equal(g1[0][:2], g0[0][:2])
+    assert np.all(g1[1][:2] == 0)
+    assert not np.array_equal(g1[2][:2], g0[2][:2])                   # the gap changed the carried state
+    for ch, mode, tol in ((0, pb.Demod.dmFMN, 1e-4), (1, pb.Demod.dmAM, 1e-10)):
+        d = pb.Demod(60000, frame)
+        d.setDemodMode(mode)
+        if mode == pb.Demod.dmAM:
+            d.setBandwidth(16000.0)
+        a = d.processBlock(np.ascontiguousarray(bp[0][ch]), frame).copy()
+        c = d.processBlock(np.ascontiguousarray(bp[2][ch]), frame).copy()
+        assert rel_rms(g1[0][ch], a) <= tol, (ch, rel_rms(g1[0][ch], a))
+        assert rel_rms(g1[2][ch], c) <= tol, (ch, rel_rms(g1[2][ch], c))
+
+
+def test_squelch_decision_from_one_wideband_spectrum():
+    """pebble_channelizer_squelch_from_spectrum == fdEstimate per channel (pinned to the compiled reference in
+    test_gpu_prefilter.py) with the channelizer's own band-pass edges and channel centres; closed channels then give zeros."""
+    import torch
+    import pebblesdr_b200 as pb
+    nch, frame, bins = 8, 2048, 8192
+    n1 = frame << 10
+    freqs = [-30.69e6 + 60e3 * (k * 120 + 5) for k in range(nch)]
+    rng = np.random.default_rng(5)
+    db = -110.0 + 3.0 * rng.standard_normal(bins)
+    for k in (1, 4, 6):                                               # carriers on three of the channels
+        b = int(bins / 2 + freqs[k] / (int(FS) // bins))
+        db[b - 1:b + 2] = -40.0
+    d_db = torch.from_numpy(np.clip(db, -120.0, 0.0)).cuda()
+    cz = pb.Channelizer(nch, FS, BW)
+    cz.setFilter(-7500.0, 7500.0)
+    for k in range(nch):
+        cz.setFrequency(k, freqs[k]); cz.setDemodMode(k, 0)
+    want = pb.fdEstimate(d_db, FS, -7500.0, 7500.0, freqs, squelchDb=-80.0)[:, 4]
+    assert want.sum() == 3 and cz.squelchFromSpectrum(d_db, FS, -80.0) == 3
+    x = torch.from_numpy(_capture(n1, freqs, seed=7)).cuda()
+    o = torch.full((nch, frame), 7.0 + 7.0j, dtype=torch.complex128, device="cuda")
+    assert cz.process(x, n1, o) == frame
+    o = o.cpu().numpy()
+    for k in range(nch):
+        assert (np.abs(o[k]).max() > 0) == bool(want[k]), k
