@@ -413,6 +413,22 @@ int pebble_sigstrength_fd_estimate_noalloc_max_channels(void);
 int pebble_sigstrength_fd_estimate_noalloc_device(const double *d_spectrum, int bins, unsigned spectrum_rate, float bp_lo, float bp_hi,
                                                   const double *mixer_freqs, int nch, double squelch_db, double *out5, void *stream);
 
+/* ---- NoiseBlanker ----------------------------------------------------------------------------------------------
+ * Replaces application/noiseblanker.h: ProcessBlock (NB1: a sample above 3.3 x the running magnitude average starts 7 zeroed
+ * outputs, otherwise the input delayed by two samples; noiseblanker.cpp:47-77) and ProcessBlock2 (NB2: the running complex
+ * average where the sample exceeds 3.3 x the average, else the input; :80-98), called back to back at the device rate
+ * (receiver.cpp:820-822). which = 1 / 2 selects the block. The running average is a float updated in double arithmetic, so the
+ * walk is serial and bit-faithful (decisions identical to the reference's). Disabled (the reference's default): the reference
+ * returns `in` itself; here out is a copy. In-place calls are refused. */
+typedef struct pebble_noiseblanker pebble_noiseblanker_t;
+pebble_noiseblanker_t *pebble_noiseblanker_create(unsigned sample_rate, unsigned buffer_size);
+void pebble_noiseblanker_destroy(pebble_noiseblanker_t *h);
+int pebble_noiseblanker_set_nb_enabled(pebble_noiseblanker_t *h, int on);    /* setNbEnabled, noiseblanker.cpp:21-29 */
+int pebble_noiseblanker_set_nb2_enabled(pebble_noiseblanker_t *h, int on);   /* setNb2Enabled, :30-37 */
+int pebble_noiseblanker_enabled(const pebble_noiseblanker_t *h, int which);
+int pebble_noiseblanker_process(pebble_noiseblanker_t *h, int which, int n, const double *in, double *out);
+int pebble_noiseblanker_process_device(pebble_noiseblanker_t *h, int which, int n, const double *d_in, double *d_out, void *stream);
+
 /* ---- Receiver chain : the non-WFM branch of Receiver::processIQData ------------------------------------
  * Replaces application/receiver.cpp:903-996: m_downConvert1.ProcessData -> m_sampleBuf re-framing to
  * framesPerBuffer (:922-931) -> scaleCPX gain restore (:935-938) -> m_bpFilter->process (:950) ->

@@ -194,6 +194,14 @@ SIGNATURES = {
     "pebble_sigstrength_fd_estimate_device": (c_int, [c_vp, c_int, ctypes.c_uint, ctypes.c_float, ctypes.c_float, c_vp, c_int, c_dbl, c_vp, c_vp]),
     "pebble_sigstrength_fd_estimate_noalloc_max_channels": (c_int, []),
     "pebble_sigstrength_fd_estimate_noalloc_device": (c_int, [c_vp, c_int, ctypes.c_uint, ctypes.c_float, ctypes.c_float, c_vp, c_int, c_dbl, c_vp, c_vp]),
+    # NoiseBlanker
+    "pebble_noiseblanker_create": (c_vp, [ctypes.c_uint, ctypes.c_uint]),
+    "pebble_noiseblanker_destroy": (None, [c_vp]),
+    "pebble_noiseblanker_set_nb_enabled": (c_int, [c_vp, c_int]),
+    "pebble_noiseblanker_set_nb2_enabled": (c_int, [c_vp, c_int]),
+    "pebble_noiseblanker_enabled": (c_int, [c_vp, c_int]),
+    "pebble_noiseblanker_process": (c_int, [c_vp, c_int, c_int, c_vp, c_vp]),
+    "pebble_noiseblanker_process_device": (c_int, [c_vp, c_int, c_int, c_vp, c_vp, c_vp]),
     # Receiver chain
     "pebble_receiver_create": (c_vp, [c_dbl, c_int]),
     "pebble_receiver_destroy": (None, [c_vp]),

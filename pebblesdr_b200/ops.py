@@ -408,6 +408,35 @@ def fdEstimate(d_spectrum, spectrumSampleRate, bpLowFreq, bpHighFreq, mixerFreqs
     return out
 
 
+class NoiseBlanker(_Handle):
+    """application/noiseblanker.h: ProcessBlock (NB1) / ProcessBlock2 (NB2); both disabled at construction like the reference."""
+    _destroy = staticmethod(lib.pebble_noiseblanker_destroy)
+
+    def __init__(self, sampleRate, bufferSize):
+        super().__init__(lib.pebble_noiseblanker_create(int(sampleRate), int(bufferSize)), "NoiseBlanker")
+        self.numSamples = int(bufferSize)
+
+    def setNbEnabled(self, b):
+        check(lib.pebble_noiseblanker_set_nb_enabled(self._h, int(bool(b))), "setNbEnabled")
+
+    def setNb2Enabled(self, b):
+        check(lib.pebble_noiseblanker_set_nb2_enabled(self._h, int(bool(b))), "setNb2Enabled")
+
+    def _run(self, which, inb):
+        if lib.pebble_noiseblanker_enabled(self._h, which) != 1:
+            return inb                                     # the reference returns `in` itself when the blanker is off
+        n = len(inb)
+        out = np.empty(n, dtype=np.complex128)
+        check(lib.pebble_noiseblanker_process(self._h, which, n, _host_ptr(inb, n), out.ctypes.data), "NoiseBlanker")
+        return out
+
+    def ProcessBlock(self, inb):
+        return self._run(1, inb)
+
+    def ProcessBlock2(self, inb):
+        return self._run(2, inb)
+
+
 class NCO(_Handle):
     """pebblelib/nco.h: the oscillator primitive. setFrequency clamps to +-((sampleRate / 2) - 1) (nco.cpp:16-45)."""
     _destroy = staticmethod(lib.pebble_nco_destroy)

@@ -118,3 +118,44 @@ def test_fd_estimate_squelch_vs_compiled_reference():
                     assert abs(got[k, j] - v[j]) <= 1e-9, (lo, hi, mf, j, got[k], v)
             assert got[k, 4] == (0.0 if v[1] < -60.0 else 1.0)
     assert got[:, 4].min() == 0.0 and pb.fdEstimate(torch.from_numpy(db).cuda(), fs, -5000.0, 5000.0, mixers[:3], -60.0)[0, 4] == 1.0
+
+
+def _impulsive(n, seed):
+    """Noise with lightning-like spikes (what NB1 blanks) and bursts (what NB2 replaces), plus a carrier."""
+    rng = np.random.default_rng(seed)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.05 + 0.1 * np.exp(2j * np.pi * 0.0123 * np.arange(n))
+    for p in rng.integers(100, n - 100, size=n // 700):
+        x[p:p + int(rng.integers(1, 4))] *= 12.0
+    return np.ascontiguousarray(x)
+
+
+def test_noise_blankers_bit_identical_to_compiled_reference():
+    """SURVEY 8f-3: NoiseBlanker::ProcessBlock / ProcessBlock2 (noiseblanker.cpp:47-98) against the class compiled from the reference,
+    block after block (the average, the spike run and the two-sample delay line cross block boundaries). Outputs are copies of
+    inputs, zeros or the running average, and every decision is taken on the reference's own float arithmetic: np.array_equal."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    fs, frame, frames = 2000000, 2048, 40
+    x = _impulsive(frame * frames, 3)
+    r, g = ref_app.NoiseBlanker(fs, frame), pb.NoiseBlanker(fs, frame)
+    # disabled (the default): both return the input
+    b = x[:frame]
+    assert g.ProcessBlock(b) is b and g.ProcessBlock2(b) is b and np.array_equal(r.ProcessBlock(b)[0], b)
+    r.enable(True, True); g.setNbEnabled(True); g.setNb2Enabled(True)
+    blanked = replaced = 0
+    for i in range(0, len(x), frame):
+        b = np.ascontiguousarray(x[i:i + frame])
+        w1, g1 = r.ProcessBlock(b)[0], g.ProcessBlock(b)
+        assert np.array_equal(g1, w1), (i, int(np.sum(g1 != w1)))
+        w2, g2 = r.ProcessBlock2(w1)[0], g.ProcessBlock2(g1)         # chained as receiver.cpp:821-822 does
+        assert np.array_equal(g2, w2), (i, int(np.sum(g2 != w2)))
+        blanked += int(np.sum(w1 == 0)); replaced += int(np.sum(w2 != w1))
+    assert blanked > 100 and replaced > 100                        # both blankers actually fired
+    # re-enabling restarts the averages (setNbEnabled / setNb2Enabled), ragged block sizes
+    r.enable(True, True); g.setNbEnabled(True); g.setNb2Enabled(True)
+    r2 = ref_app.NoiseBlanker(fs, 777); r2.enable(True, True)
+    g3 = pb.NoiseBlanker(fs, 777); g3.setNbEnabled(True); g3.setNb2Enabled(True)
+    for i in range(0, 777 * 5, 777):
+        b = np.ascontiguousarray(x[i:i + 777])
+        assert np.array_equal(g3.ProcessBlock(b), r2.ProcessBlock(b)[0])
+        assert np.array_equal(g3.ProcessBlock2(b), r2.ProcessBlock2(b)[0])
