@@ -44,20 +44,21 @@ struct ChanState {      // per-channel demod state
 #define PB_CHZ_L 4                     // lanes per channel
 #define PB_CHZ_C (32 / PB_CHZ_L)       // channels per warp
 #define PB_CHZ_R (32 / PB_CHZ_L)       // samples per lane in a 32-sample block
-// One PLL step (demod_nfm.cpp:225-257) on the chain. th = arg(x) (NaN for an exactly-zero sample: phzerror = 0 there),
-// th_turns = th / 2 pi. arg(x e^{j phase}) = th + phase reduced to [-pi, pi]: the reduction (Cody-Waite, k by the 1.5 * 2^23
-// trick) is applied to the SUM, so no separate wrap — and no predicate-producing instruction — sits on the chain.
-__device__ __forceinline__ float pll_chain(const float th, const float th_turns, const bool th_nan, const PllConst &c, PllState &v) {
+// One PLL step (demod_nfm.cpp:225-257) on the chain. th = arg(x) (0 for an exactly-zero sample), th_turns = th / 2 pi,
+// nb / na = -beta / -alpha (0 for an exactly-zero sample: phzerror = 0 there, atan2(0, 0) = 0 in the reference).
+// arg(x e^{j phase}) = th + phase reduced to [-pi, pi]: the reduction (Cody-Waite, k by the 1.5 * 2^23 trick) is applied to the
+// SUM, so no separate wrap sits on the chain, and the zero-sample case rides on the two gains instead of a select: the chain
+// is 11 plain FP32 operations, none of which produces or consumes a predicate.
+__device__ __forceinline__ float pll_chain(const float th, const float th_turns, const float nb, const float na, const PllConst &c, PllState &v) {
     const float q = fmaf(v.phase, 0.15915494309189535f, th_turns);
     const float k = (q + 12582912.0f) - 12582912.0f;
     float r = fmaf(k, -PB_TWO_PI_HI, v.phase);
     r = fmaf(k, -PB_TWO_PI_LO, r);
-    const float e = th + r;
-    const float phzerror = th_nan ? 0.0f : -e;
-    float f = fmaf(c.beta, phzerror, v.freq);
+    const float e = th + r;                                   // phzerror = -e
+    float f = fmaf(nb, e, v.freq);
     f = fminf(fmaxf(f, c.lo), c.hi);
     v.freq = f;
-    v.phase = v.phase + fmaf(c.alpha, phzerror, f);
+    v.phase = v.phase + fmaf(na, e, f);
     v.dc = fmaf(c.dc_alpha, f, (1.0f - c.dc_alpha) * v.dc);   // its own, shorter chain
     return (f - v.dc) * c.out_gain;
 }
@@ -98,9 +99,14 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
 #pragma unroll
                     for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = i + 32 + m * PB_CHZ_L + s < f1 ? x[i + 32 + m * PB_CHZ_L + s] : cpx_make(1.0, 0.0);
                 }
-                float th[PB_CHZ_R], tt[PB_CHZ_R], mine[PB_CHZ_R];
+                float th[PB_CHZ_R], nbv[PB_CHZ_R], mine[PB_CHZ_R];
 #pragma unroll
-                for (int m = 0; m < PB_CHZ_R; ++m) { th[m] = pll_theta(cur[m]); tt[m] = th[m] * 0.15915494309189535f; mine[m] = 0.0f; }
+                for (int m = 0; m < PB_CHZ_R; ++m) {
+                    const float t = pll_theta(cur[m]);                  // NaN marks an exactly-zero sample
+                    th[m] = t != t ? 0.0f : t;
+                    nbv[m] = t != t ? 0.0f : -pc.beta;
+                    mine[m] = 0.0f;
+                }
                 const int cnt = f1 - i < 32 ? f1 - i : 32;
                 if (cnt == 32) {
                     // no per-step branch here: a branch between steps pins every shuffle right in front of its use and puts
@@ -108,8 +114,8 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                        const float ttj = __shfl_sync(0xffffffffu, tt[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                        const float o = pll_chain(tj, ttj, tj != tj, pc, v);
+                        const float nbj = __shfl_sync(0xffffffffu, nbv[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                        const float o = pll_chain(tj, tj * 0.15915494309189535f, nbj, nbj == 0.0f ? 0.0f : -pc.alpha, pc, v);
                         mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
                     }
                 } else {
@@ -117,8 +123,8 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
                     for (int j = 0; j < 32; ++j) {
                         if (j < cnt) {                       // uniform
                             const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                            const float ttj = __shfl_sync(0xffffffffu, tt[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                            const float o = pll_chain(tj, ttj, tj != tj, pc, v);
+                            const float nbj = __shfl_sync(0xffffffffu, nbv[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                            const float o = pll_chain(tj, tj * 0.15915494309189535f, nbj, nbj == 0.0f ? 0.0f : -pc.alpha, pc, v);
                             mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
                         }
                     }
