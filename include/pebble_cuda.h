@@ -329,13 +329,17 @@ int pebble_agc_process_device(pebble_agc_t *h, int n, const double *d_in, double
  * de-emphasis, 19 kHz notch; pebble_demod_set_wfm_sample_rate() = the second rate of Demod(sampleRate, wfmSampleRate, n),
  * demod.cpp:50-66, default = input_rate),
  * 5..12 DSB/LSB/USB/CW/DIG/NONE = pass-through (the reference returns `in`; here out is a copy and
- * pebble_demod_is_passthrough() reports it). 4 dmFMS (stereo + RDS): PEBBLE_ERR_STATE (not built). */
+ * pebble_demod_is_passthrough() reports it). 4 dmFMS (Demod::fmStereo -> Demod_WFM::processDataStereo, demod_wfm.cpp:258-366):
+ * the AUDIO path — discriminator, Hilbert pair, 19 kHz pilot band-pass, pilot PLL (with the reference's own arctan2), stereo
+ * demux when locked, 15 kHz CFir, de-emphasis, notch; pebble_demod_get_stereo_lock() = getStereoLock. The RDS branch
+ * (:298-357: 57 kHz down-conversion, RDS PLL, matched filter, bit decoder) is NOT built: no RDS groups are produced. */
 typedef struct pebble_demod pebble_demod_t;
 pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples);
 void pebble_demod_destroy(pebble_demod_t *h);
 int pebble_demod_set_mode(pebble_demod_t *h, int mode);
 int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant);
 int pebble_demod_set_wfm_sample_rate(pebble_demod_t *h, double rate);
+int pebble_demod_get_stereo_lock(pebble_demod_t *h);
 int pebble_demod_set_bandwidth(pebble_demod_t *h, double bandwidth);
 int pebble_demod_is_passthrough(const pebble_demod_t *h);
 int pebble_demod_process(pebble_demod_t *h, int n, const double *in, double *out);

@@ -139,6 +139,7 @@ SIGNATURES = {
     "pebble_demod_set_mode": (c_int, [c_vp, c_int]),
     "pebble_demod_set_nfm_variant": (c_int, [c_vp, c_int]),
     "pebble_demod_set_wfm_sample_rate": (c_int, [c_vp, c_dbl]),
+    "pebble_demod_get_stereo_lock": (c_int, [c_vp]),
     "pebble_demod_set_bandwidth": (c_int, [c_vp, c_dbl]),
     "pebble_demod_is_passthrough": (c_int, [c_vp]),
     "pebble_demod_process": (c_int, [c_vp, c_int, c_vp, c_vp]),

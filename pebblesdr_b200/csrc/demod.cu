@@ -8,6 +8,7 @@
 #include "lib_common.h"
 #include "common.cuh"
 #include "host_design.h"
+#include "wfm_coefs.h"
 #include <cmath>
 #include <cstring>
 #include <vector>
@@ -237,6 +238,9 @@ int pebble_agc_process(pebble_agc_t *h, int n, const double *in, double *out) {
 }  // extern "C"
 
 // ---- Demod handle (application/demod.cpp:100-141 dispatch + demod_am.cpp + demod_nfm.cpp) --------------------
+// WFM stereo pilot PLL (demod_wfm.cpp:369-430): constants of initPilotPll and the carried state (double, as there)
+struct WfmPllConst { double alpha, beta, lo, hi, err_alpha, phase_adjust; };
+struct WfmPllState { double phase, freq, err_ave; int locked; int pad; };
 struct pebble_demod {
     double rate = 0;
     int mode = 0;                 // DeviceInterface::DemodMode numbering (device_interfaces.h:124-137); dmAM at create
@@ -262,6 +266,13 @@ struct pebble_demod {
     pebble_cfir wfm_lp;
     cpx *d_wfm_last[2] = {nullptr, nullptr};
     int wfm_cur = 0;
+    // WFM stereo audio (demod_wfm.cpp:258-366 without the RDS branch): Hilbert pair, pilot band-pass, pilot PLL, demux
+    pebble_cfir wfm_hilb;
+    pebble_iir_t *wfm_pilot_bp = nullptr;
+    WfmPllConst wfm_pll;
+    WfmPllState *d_wfm_pll = nullptr;          // [2]: ping-pong; .locked of the current one = m_PilotLocked
+    int wfm_pll_cur = 0;
+    cpx *d_w1 = nullptr, *d_w2 = nullptr; double *d_wphase = nullptr; size_t w_cap = 0;
     // scratch (grow-only)
     cpx *d_tmp = nullptr; size_t tmp_cap = 0;
     Aff *d_tiles = nullptr; double *d_carry = nullptr; int tiles_cap = 0;
@@ -283,6 +294,72 @@ static __global__ void wfm_disc_kernel(const cpx *__restrict__ in, int n, const 
         if (i == n - 1) *last_out = d0;
     }
 }
+// ---- WFM stereo: pilot PLL (demod_wfm.cpp:388-430) and demux (:272-296) ---------------------------------------------------------
+// Demod_WFM::arctan2 (:792-818), the reference's own approximation ("|error| < 0.005"; its |z| >= 1 branch returns angles near
+// 2 pi — kept as written: the loop's behaviour far from lock depends on it)
+__device__ __forceinline__ double wfm_arctan2(double y, double x) {
+    const double TWOPI = 6.28318530717958647692528676656, PI = 3.14159265358979323846264338328;
+    if (x == 0.0) return y > 0.0 ? TWOPI : (y == 0.0 ? 0.0 : -TWOPI);
+    const double z = __ddiv_rn(y, x);
+    double angle;
+    if (fabs(z) < 1.0) {
+        angle = __ddiv_rn(z, __dadd_rn(1.0, __dmul_rn(__dmul_rn(0.2854, z), z)));
+        if (x < 0.0) return y < 0.0 ? __dsub_rn(angle, PI) : __dadd_rn(angle, PI);
+    } else {
+        angle = __dsub_rn(TWOPI, __ddiv_rn(z, __dadd_rn(__dmul_rn(z, z), 0.2854)));
+        if (y < 0.0) return __dsub_rn(angle, PI);
+    }
+    return angle;
+}
+// One warp; the loop is a serial recurrence in double (sin/cos of the NCO phase, rotate, arctan2, loop filter), the lanes only
+// fetch the samples of a 32-sample block. The reference takes sin/cos from x87 fsincos (:398); the double results agree to ~1 ulp
+// and the loop is a contracting map, so the audio agrees to ~1e-12.
+static __global__ void __launch_bounds__(32) wfm_pilot_pll_kernel(const cpx *__restrict__ in, int n, WfmPllConst c, const WfmPllState *__restrict__ st_in,
+                                                                  WfmPllState *__restrict__ st_out, double *__restrict__ pilot_phase) {
+    const int lane = threadIdx.x;
+    WfmPllState v = *st_in;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int idx = i0 + lane;
+        const cpx x = idx < n ? in[idx] : cpx_make(0.0, 0.0);
+        const int cnt = n - i0 < 32 ? n - i0 : 32;
+        double mine = 0.0;
+        for (int j = 0; j < cnt; ++j) {
+            const double xr = __shfl_sync(0xffffffffu, x.x, j), xi = __shfl_sync(0xffffffffu, x.y, j);
+            double sn, cs;
+            sincos(v.phase, &sn, &cs);
+            const double tr = __dsub_rn(__dmul_rn(cs, xr), __dmul_rn(sn, xi));                    // :406-407
+            const double ti = __dadd_rn(__dmul_rn(cs, xi), __dmul_rn(sn, xr));
+            const double phzerror = -wfm_arctan2(ti, tr);                                         // :409
+            v.freq = __dadd_rn(v.freq, __dmul_rn(c.beta, phzerror));                              // :412
+            if (v.freq > c.hi) v.freq = c.hi; else if (v.freq < c.lo) v.freq = c.lo;              // :414-417
+            v.phase = __dadd_rn(v.phase, __dadd_rn(v.freq, __dmul_rn(c.alpha, phzerror)));        // :419
+            const double pp = __dadd_rn(v.phase, c.phase_adjust);                                 // :420
+            v.err_ave = __dadd_rn(__dmul_rn(1.0 - c.err_alpha, v.err_ave), __dmul_rn(__dmul_rn(c.err_alpha, phzerror), phzerror));   // :422
+            mine = lane == j ? pp : mine;
+        }
+        if (idx < n) pilot_phase[idx] = mine;
+    }
+    if (lane == 0) {
+        v.phase = fmod(v.phase, 6.28318530717958647692528676656);                                 // :424
+        v.locked = v.err_ave < 0.05 ? 1 : 0;                                                      // LOCK_MAG_THRESHOLD, :426-429
+        *st_out = v;
+    }
+}
+// raw = the discriminator output (v, v); locked: L-R = 2 v sin(2 pilotPhase), out = (v + L-R, v - L-R); else (v, v)   (:272-296)
+static __global__ void wfm_demux_kernel(const cpx *__restrict__ raw, const double *__restrict__ pilot_phase, const WfmPllState *__restrict__ st, int n,
+                                        cpx *__restrict__ out) {
+    const bool locked = st->locked != 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double v = raw[i].x;
+        if (locked) {
+            const double lmr = __dmul_rn(__dmul_rn(2.0, v), sin(__dmul_rn(pilot_phase[i], 2.0)));
+            out[i] = cpx_make(__dadd_rn(v, lmr), __dsub_rn(v, lmr));
+        } else {
+            out[i] = cpx_make(v, v);
+        }
+    }
+}
+
 // Demod_WFM::setSampleRate (demod_wfm.cpp:155-196) for the mono path; out rate = sample rate (the constructor's init, :110-114)
 static int wfm_setup(pebble_demod *h, double rate) {
     h->wfm_rate = rate;
@@ -297,6 +374,30 @@ static int wfm_setup(pebble_demod *h, double rate) {
     memcpy(h->wfm_lp.hQ, h->wfm_lp.hI, sizeof(double) * h->wfm_lp.ntaps);
     if (cfir_upload(&h->wfm_lp) < 0) return PEBBLE_ERR_CUDA;
     for (int b = 0; b < 2; ++b) PB_CUDA(cudaMemset(h->d_wfm_last[b], 0, sizeof(cpx)), PEBBLE_ERR_CUDA);
+    // stereo: m_HilbertFilter.InitConstFir(61, HILBLP_H, rate); GenerateHBFilter(42000) (:166-168, fir.cpp:454-468)
+    {
+        const double TWOPI = 6.28318530717958647692528676656;
+        const int nt = pebble_wfm::kHilbLen;
+        h->wfm_hilb.ntaps = nt;
+        for (int k = 0; k < nt; ++k) {
+            const double a = (TWOPI * 42000.0 / rate) * ((double)k - ((double)(nt - 1) / 2.0));
+            h->wfm_hilb.hI[k] = 2.0 * pebble_wfm::kHilbLp[k] * cos(a);
+            h->wfm_hilb.hQ[k] = 2.0 * pebble_wfm::kHilbLp[k] * sin(a);
+        }
+        if (cfir_upload(&h->wfm_hilb) < 0) return PEBBLE_ERR_CUDA;
+        if (pebble_iir_init(h->wfm_pilot_bp, PEBBLE_IIR_BP, 19000.0, 500.0, rate) < 0) return PEBBLE_ERR_CUDA;   // m_PilotBPFilter.InitBP(19000, 500, rate)
+        // initPilotPll (:369-384)
+        const double norm = TWOPI / rate, f0 = -19000.0;
+        h->wfm_pll.lo = (f0 - 20.0) * norm;
+        h->wfm_pll.hi = (f0 + 20.0) * norm;
+        h->wfm_pll.alpha = 2.0 * .707 * 10.0 * norm;
+        h->wfm_pll.beta = (h->wfm_pll.alpha * h->wfm_pll.alpha) / (4.0 * .707 * .707);
+        h->wfm_pll.err_alpha = (1.0 - exp(-1.0 / (rate * .5)));
+        h->wfm_pll.phase_adjust = -7.267e-6 * rate + 3.677;                                                     // :163
+        WfmPllState s0; memset(&s0, 0, sizeof(s0)); s0.freq = f0;                                               // m_PilotNcoFreq = -PILOTPLL_FREQ (Hz, as written)
+        for (int b = 0; b < 2; ++b) PB_CUDA(cudaMemcpy(h->d_wfm_pll + b, &s0, sizeof(s0), cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
+        h->wfm_pll_cur = 0;
+    }
     return 0;
 }
 
@@ -404,9 +505,35 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         if (r < 0) return r;
         return pebble_iir_process_device(h->wfm_notch, n, (const double *)h->d_tmp, (double *)d_out, st);   // 19 kHz pilot notch
     }
-    if (h->mode == 4) {
-        pebble::set_error("demod: WFM stereo / RDS (dmFMS) is not built (SURVEY 8f rank 4); dmFMM (mono) is");
-        return PEBBLE_ERR_STATE;
+    if (h->mode == 4) {  // dmFMS -> Demod::fmStereo -> Demod_WFM::processDataStereo (demod_wfm.cpp:258-366), audio path; RDS is not decoded
+        int r = demod_reserve(h, n);
+        if (r < 0) return r;
+        if ((size_t)n > h->w_cap) {
+            cudaFree(h->d_w1); cudaFree(h->d_w2); cudaFree(h->d_wphase);
+            h->d_w1 = h->d_w2 = nullptr; h->d_wphase = nullptr; h->w_cap = 0;
+            PB_CUDA(cudaMalloc(&h->d_w1, sizeof(cpx) * (size_t)n), PEBBLE_ERR_CUDA);
+            PB_CUDA(cudaMalloc(&h->d_w2, sizeof(cpx) * (size_t)n), PEBBLE_ERR_CUDA);
+            PB_CUDA(cudaMalloc(&h->d_wphase, sizeof(double) * (size_t)n), PEBBLE_ERR_CUDA);
+            h->w_cap = (size_t)n;
+        }
+        wfm_disc_kernel<<<grid_for(n), 256, 0, st>>>(d_in, n, h->d_wfm_last[h->wfm_cur], h->d_tmp, h->d_wfm_last[h->wfm_cur ^ 1]);   // m_RawFm as (v, v)
+        pebble::count_launch();
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+        h->wfm_cur ^= 1;
+        r = cfir_run_device(&h->wfm_hilb, n, h->d_tmp, h->d_w1, st);                                      // real -> complex: I taps on v, Q taps on v (:266)
+        if (r < 0) return r;
+        r = pebble_iir_process_device(h->wfm_pilot_bp, n, (const double *)h->d_w1, (double *)h->d_w2, st);   // :269
+        if (r < 0) return r;
+        wfm_pilot_pll_kernel<<<1, 32, 0, st>>>(h->d_w2, n, h->wfm_pll, h->d_wfm_pll + h->wfm_pll_cur, h->d_wfm_pll + (h->wfm_pll_cur ^ 1), h->d_wphase);
+        h->wfm_pll_cur ^= 1;
+        wfm_demux_kernel<<<grid_for(n), 256, 0, st>>>(h->d_tmp, h->d_wphase, h->d_wfm_pll + h->wfm_pll_cur, n, h->d_w1);
+        pebble::count_launch(2);
+        PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
+        r = cfir_run_device(&h->wfm_lp, n, h->d_w1, d_out, st);                                           // :361 (complex: left / right)
+        if (r < 0) return r;
+        r = pebble_iir_process_device(h->wfm_deemph, n, (const double *)d_out, (double *)h->d_w1, st);    // :362
+        if (r < 0) return r;
+        return pebble_iir_process_device(h->wfm_notch, n, (const double *)h->d_w1, (double *)d_out, st);  // :363
     }
     // USB/LSB/DSB/CW/DIG/NONE: Demod::processBlock returns `in` itself (demod.cpp:127-138)
     if (passthrough) *passthrough = 1;
@@ -419,8 +546,9 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
     (void)num_samples;
     pebble_demod *h = new pebble_demod();
     h->rate = input_rate;
-    h->wfm_in_lp = pebble_iir_create(); h->wfm_deemph = pebble_iir_create(); h->wfm_notch = pebble_iir_create();
-    bool ok = h->wfm_in_lp && h->wfm_deemph && h->wfm_notch && cfir_alloc(&h->wfm_lp) == 0 &&
+    h->wfm_in_lp = pebble_iir_create(); h->wfm_deemph = pebble_iir_create(); h->wfm_notch = pebble_iir_create(); h->wfm_pilot_bp = pebble_iir_create();
+    bool ok = h->wfm_in_lp && h->wfm_deemph && h->wfm_notch && h->wfm_pilot_bp && cfir_alloc(&h->wfm_lp) == 0 && cfir_alloc(&h->wfm_hilb) == 0 &&
+              pebble::cuda_ok(cudaMalloc(&h->d_wfm_pll, 2 * sizeof(WfmPllState)), "cudaMalloc") &&
               cfir_alloc(&h->am_lp) == 0 && cfir_alloc(&h->nfm_lp) == 0 && cfir_alloc(&h->sam_bp) == 0 &&
               pebble::cuda_ok(cudaMalloc(&h->d_sam, sizeof(SamState)), "cudaMalloc") &&
               pebble::cuda_ok(cudaMemset(h->d_sam, 0, sizeof(SamState)), "cudaMemset") &&
@@ -479,7 +607,8 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
 void pebble_demod_destroy(pebble_demod_t *h) {
     if (!h) return;
     cfir_release(&h->am_lp); cfir_release(&h->nfm_lp); cfir_release(&h->sam_bp); cfir_release(&h->wfm_lp);
-    pebble_iir_destroy(h->wfm_in_lp); pebble_iir_destroy(h->wfm_deemph); pebble_iir_destroy(h->wfm_notch);
+    pebble_iir_destroy(h->wfm_in_lp); pebble_iir_destroy(h->wfm_deemph); pebble_iir_destroy(h->wfm_notch); pebble_iir_destroy(h->wfm_pilot_bp);
+    cfir_release(&h->wfm_hilb); cudaFree(h->d_wfm_pll); cudaFree(h->d_w1); cudaFree(h->d_w2); cudaFree(h->d_wphase);
     cudaFree(h->d_wfm_last[0]); cudaFree(h->d_wfm_last[1]);
     cudaFree(h->d_sam);
     cudaFree(h->d_pll); cudaFree(h->d_tmp); cudaFree(h->d_tiles); cudaFree(h->d_carry);
@@ -498,6 +627,14 @@ int pebble_demod_set_wfm_sample_rate(pebble_demod_t *h, double rate) {
     if (!h || !(rate > 0)) return PEBBLE_ERR_ARG;
     PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
     return wfm_setup(h, rate);
+}
+// Demod_WFM::getStereoLock (demod_wfm.cpp:436-448): the pilot lock decision of the last dmFMS call
+int pebble_demod_get_stereo_lock(pebble_demod_t *h) {
+    if (!h) return PEBBLE_ERR_ARG;
+    WfmPllState s;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    PB_CUDA(cudaMemcpy(&s, h->d_wfm_pll + h->wfm_pll_cur, sizeof(s), cudaMemcpyDeviceToHost), PEBBLE_ERR_CUDA);
+    return s.locked;
 }
 int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant) {
     if (!h || variant < 0 || variant > 1) return PEBBLE_ERR_ARG;

@@ -603,6 +603,10 @@ class Demod(_Handle):
     def setBandwidth(self, bandwidth):
         check(lib.pebble_demod_set_bandwidth(self._h, bandwidth), "setBandwidth")
 
+    def getStereoLock(self):
+        """Demod_WFM::getStereoLock: the pilot lock decision of the last dmFMS block."""
+        return bool(check(lib.pebble_demod_get_stereo_lock(self._h), "getStereoLock"))
+
     def processBlock(self, inb, bufSize):
         """Like the reference, pass-through modes return the INPUT array itself (demod.cpp:127-138)."""
         if lib.pebble_demod_is_passthrough(self._h) == 1:

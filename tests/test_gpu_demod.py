@@ -94,9 +94,8 @@ def test_ssb_passthrough_returns_input():
     for mode in (pb.Demod.dmUSB, pb.Demod.dmLSB, pb.Demod.dmCWU, pb.Demod.dmDIGL, pb.Demod.dmNONE):
         g.setDemodMode(mode)
         assert g.processBlock(x, 2048) is x            # demod.cpp:127-138 returns `in`
-    g.setDemodMode(pb.Demod.dmFMS)                     # WFM stereo / RDS is not built: a loud error, not silence
-    with pytest.raises(pb.PebbleError):
-        g.processBlock(x, 2048)
+    with pytest.raises(pb.PebbleError):                # a mode outside DeviceInterface::DemodMode: a loud error, not silence
+        g.setDemodMode(13)
 
 
 @pytest.mark.parametrize("mode,thr", [(0, 20), (0, 37), (1, 20), (3, 40)])
@@ -219,3 +218,45 @@ def test_wfm_mono_vs_compiled_reference(rate):
     sp = np.abs(np.fft.rfft(got.real[n // 2:] * np.hanning(n - n // 2)))
     f = np.fft.rfftfreq(n - n // 2, 1.0 / rate)
     assert sp[np.argmin(np.abs(f - 19000.0))] < 0.1 * sp[np.argmin(np.abs(f - 1000.0))]
+
+
+@pytest.mark.parametrize("pilot_hz,pilot_phase,frames", [(19010.0, 0.0, 40), (19010.0, 3.0, 150), (19000.0, 0.0, 40)])
+def test_wfm_stereo_audio_vs_compiled_reference(pilot_hz, pilot_phase, frames):
+    """SURVEY 8f-4: Demod::fmStereo -> Demod_WFM::processDataStereo (demod_wfm.cpp:258-366), the AUDIO path, against the class
+    compiled from the reference: discriminator, Hilbert pair, pilot band-pass, pilot PLL, demux, 15 kHz CFir, de-emphasis, notch.
+
+    The reference's arctan2 (:792-818) returns angles near 2 pi when |y/x| >= 1 (cuteSDR's K_PI2 = pi/2 became TWOPI), so its
+    pilot loop only locks when it starts close: with the pilot at 19010 Hz and a favourable phase it is locked from the first
+    frame (stereo separation visible), from phase 3.0 it unlocks and re-locks, at 19000 Hz it never locks within the test and
+    the output is mono. All three must match — lock decisions per frame exactly, audio to 1e-9 relative RMS over the whole
+    stream. The RDS branch (:298-357) is not built and does not touch the audio."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    rate, frame = 312500, 2048
+    n = frame * frames
+    t = np.arange(n) / rate
+    left, right = 0.8 * np.sin(2 * np.pi * 1000.0 * t), 0.5 * np.sin(2 * np.pi * 2500.0 * t)
+    pil = 2 * np.pi * pilot_hz * t + pilot_phase
+    m = 0.45 * (left + right) + 0.1 * np.sin(pil) + 0.45 * (left - right) * np.sin(2 * pil)
+    ph = 2 * np.pi * np.cumsum(75000.0 * m) / rate
+    rng = np.random.default_rng(1)
+    x = np.ascontiguousarray(0.4 * np.exp(1j * ph) + (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.001)
+    r = ref_app.Demod_WFM(rate, frame)
+    g = pb.Demod(rate, frame)
+    g.setDemodMode(pb.Demod.dmFMS)
+    want, got, lw, lg = [], [], [], []
+    for i in range(0, n, frame):
+        want.append(r.processDataStereo(x[i:i + frame].copy())); lw.append(r.getStereoLock()[1])      # the reference overwrites its input
+        got.append(g.processBlock(np.ascontiguousarray(x[i:i + frame]), frame).copy()); lg.append(int(g.getStereoLock()))
+    want, got = np.concatenate(want), np.concatenate(got)
+    assert lg == lw, (sum(lg), sum(lw))
+    assert rel_rms(got, want) <= 1e-9, rel_rms(got, want)
+    if pilot_hz == 19010.0 and pilot_phase == 0.0:
+        assert all(lw)
+        tone = lambda v, f: abs(np.sum(v * np.exp(-2j * np.pi * f * np.arange(len(v)) / rate))) / len(v)
+        seg = got[n // 2:]
+        assert tone(seg.real, 1000.0) > 3 * tone(seg.imag, 1000.0) and tone(seg.imag, 2500.0) > 3 * tone(seg.real, 2500.0)   # separation
+    if pilot_hz == 19000.0:
+        assert not any(lw[2:]) and np.array_equal(want.real[frame * 2:], want.imag[frame * 2:])                          # mono fallback
+    if pilot_phase == 3.0:
+        assert 0 < sum(lw) < frames
