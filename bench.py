@@ -70,6 +70,7 @@ def parse():
     ap.add_argument("--channels", type=int, default=1024, help="channelizer workload: total channels")
     ap.add_argument("--mode", default="am", choices=sorted(MODES))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--wav", default=None, help="chain workload: an IQ .wav capture (PebbleSDR layout, pebblesdr_b200/wavfile.py) instead of the synthetic stream")
     ap.add_argument("--no-sharded", action="store_true", help="skip the config-4 / config-5 `sharded` block")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work per baseline leg")
     a = ap.parse_args()
@@ -384,6 +385,18 @@ def main_ours(args):
     K, W = args.steps, args.warmup
     np_par = min(n, 1 << PARITY_LOG2)
     x = synth_torch(n, dev, seed=2345 + rank)
+    data_desc = "synthetic"
+    if args.wav:
+        # a recorded capture in PebbleSDR's IQ .wav layout (pebblesdr_b200/wavfile.py) replaces the synthetic samples; it is tiled
+        # to the step length and treated as the workload's 10 MSPS stream (the chain, not the file's own rate, is the workload)
+        from pebblesdr_b200 import wavfile
+        w = wavfile.read_iq_wav(args.wav)
+        raw = torch.from_numpy(w["raw"].astype("float64") / (32767.0 if w["fmt_tag"] == wavfile.PCM_FORMAT else 1.0)).to(dev)
+        cap = torch.view_as_complex(raw.view(-1, 2).contiguous())
+        reps = (n + cap.numel() - 1) // cap.numel()
+        x = cap.repeat(reps)[:n].contiguous()
+        data_desc = "wav:%s (%d samples at %d S/s, LO %d Hz, tiled to the step length; treated as the workload's 10 MSPS stream)" % (
+            os.path.basename(args.wav), cap.numel(), w["sample_rate"], w["lo_freq"])
 
     def barrier():
         if world > 1:
@@ -465,7 +478,7 @@ def main_ours(args):
         line = {
             "metric": METRIC, "value": world * n * K / (ms_total * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "vs_baseline": None, "dtype": "f64", "data": data_desc,
             "config": workload_config(args),
             "e2e": {"value": world * n * K / (ms_e2e * 1e-3) / 1e6, "unit": UNIT,
                     "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": 16 * nout, "ms_per_step": ms_e2e / K,
