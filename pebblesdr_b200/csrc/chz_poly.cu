@@ -50,23 +50,103 @@ struct PolyArgs {
     long long stream_v0;     // stream index of virtual sample 0 (negative while the history predates the stream)
 };
 
-template <int FMT> __device__ __forceinline__ cpx poly_load(const void *hist, const void *in, long long j, long long hl) {
-    const void *base = j < hl ? hist : in;
-    const long long i = j < hl ? j : j - hl;
-    if (FMT == PB_IQ_CPX) return __ldg((const cpx *)base + i);
-    if (FMT == PB_IQ_CS16) {
-        const unsigned w = __ldg((const unsigned *)base + i) ^ 0x80008000u;
-        return cpx_make(iq_code_to_double(w & 0xffffu, PB_IQ_MAGIC16), iq_code_to_double(w >> 16, PB_IQ_MAGIC16));
+// One raw sample as it sits in memory (16 / 4 / 8 / 2 bytes) and its conversion. The load is a volatile asm statement: a plain
+// __ldg may be SUNK by the compiler to just before the first use of its result (fewer live registers), which put the DRAM
+// latency of every row back on the critical path (ncu: the three DMULs that first touch a loaded sample held 20 % of all stall
+// samples although the loads were written PF rows earlier). The conversion to double happens where the sample is consumed.
+template <int FMT> struct PolyRaw;
+template <> struct PolyRaw<PB_IQ_CPX> {
+    double x, y;
+    __device__ __forceinline__ void load(const void *base, long long i) {
+        asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(x), "=d"(y) : "l"((const cpx *)base + i));
     }
-    if (FMT == PB_IQ_CF32) { const float2 f = __ldg((const float2 *)base + i); return cpx_make((double)f.x, (double)f.y); }
-    unsigned w = __ldg((const unsigned short *)base + i);
-    if (FMT == PB_IQ_CS8) w ^= 0x8080u;
-    return cpx_make(iq_code_to_double(w & 0xffu, PB_IQ_MAGIC8), iq_code_to_double(w >> 8, PB_IQ_MAGIC8));
+    __device__ __forceinline__ cpx get() const { return cpx_make(x, y); }
+};
+template <> struct PolyRaw<PB_IQ_CS16> {
+    unsigned w;
+    __device__ __forceinline__ void load(const void *base, long long i) { asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(w) : "l"((const unsigned *)base + i)); }
+    __device__ __forceinline__ cpx get() const {
+        const unsigned u = w ^ 0x80008000u;
+        return cpx_make(iq_code_to_double(u & 0xffffu, PB_IQ_MAGIC16), iq_code_to_double(u >> 16, PB_IQ_MAGIC16));
+    }
+};
+template <> struct PolyRaw<PB_IQ_CF32> {
+    float x, y;
+    __device__ __forceinline__ void load(const void *base, long long i) {
+        asm volatile("ld.global.nc.v2.f32 {%0,%1}, [%2];" : "=f"(x), "=f"(y) : "l"((const float2 *)base + i));
+    }
+    __device__ __forceinline__ cpx get() const { return cpx_make((double)x, (double)y); }
+};
+template <int FMT> struct PolyRaw8 {
+    unsigned short w;
+    __device__ __forceinline__ void load(const void *base, long long i) { asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(w) : "l"((const unsigned short *)base + i)); }
+    __device__ __forceinline__ cpx get() const {
+        unsigned u = w;
+        if (FMT == PB_IQ_CS8) u ^= 0x8080u;
+        return cpx_make(iq_code_to_double(u & 0xffu, PB_IQ_MAGIC8), iq_code_to_double(u >> 8, PB_IQ_MAGIC8));
+    }
+};
+template <> struct PolyRaw<PB_IQ_CU8> : PolyRaw8<PB_IQ_CU8> {};
+template <> struct PolyRaw<PB_IQ_CS8> : PolyRaw8<PB_IQ_CS8> {};
+template <int FMT> __device__ __forceinline__ void poly_fetch(PolyRaw<FMT> &r, const void *hist, const void *in, long long j, long long hl) {
+    r.load(j < hl ? hist : in, j < hl ? j : j - hl);
 }
 
 // Mix + polyphase FIR. Thread = branch p; it walks the rows m = n0-(Q-1) .. of its branch (samples D apart) with a register
 // window of the last Q mixed samples and its own Q taps in registers: 2Q DFMA per row against one 16-byte (or 2..8-byte)
 // coalesced load. blockIdx.x = group of 128 branches, blockIdx.y = tile of `nt` outputs.
+//   * PF rows are kept in flight in a register ring of RAW samples: row k + PF is requested before row k is mixed and filtered
+//     (rows are D samples apart: every row is a fresh DRAM line; the first version, load at use, spent 1070 cycles per row with the
+//     FP64 pipe 19.5 % busy).
+//   * The window has STATIC register indices: PF rows are unrolled over Q + PF - 1 entries which are then shifted down by PF
+//     (~10 moves per row). Unrolling Q-fold instead (indices (r - q) mod Q, no moves) made 64 KB of code: a quarter of the stall
+//     samples were instruction fetches.
+//   * No divergent branch in the row loop: the oscillator is re-seeded exactly once per RS rows at the top of an iteration
+//     (uniform), and the amplitude transient r_i of the first PB_DC_RTAB stream samples — a per-thread test with a table load
+//     behind it — is compiled into a separate instance of the loop that only tiles at the very start of a stream enter.
+template <int FMT, int Q, int PF, bool TRANSIENT>
+__device__ __forceinline__ void poly_rows(const PolyArgs &a, const int p, const int n0, const int total, const double (&h)[Q], cpx (&w)[Q + PF - 1],
+                                          PolyRaw<FMT> (&ring)[PF], cpx &osc, long long &j, int kb0, int kb1) {
+    constexpr int RS = 6 * PF;               // rows between exact re-seeds of the oscillator recurrence
+    const int D = a.D;
+    const long long jmax = a.hist_len + a.n - 1;
+    const double inv_r = a.chain->inv_r_inf;
+    for (int kb = kb0; kb < kb1; kb += PF) {
+        const bool reseed = (kb % RS) == 0;
+#pragma unroll
+        for (int r = 0; r < PF; ++r) {
+            const int k = kb + r;
+            const long long jj = j < jmax ? j : jmax;          // rows past the tile end are computed but never stored
+            const cpx x = ring[r].get();
+            {
+                const long long jn = j + (long long)PF * D;
+                poly_fetch<FMT>(ring[r], a.hist, a.in, jn < jmax ? jn : jmax, a.hist_len);
+            }
+            if (r == 0 && reseed)
+                osc = cpx_scale(dc_phase_to_osc(dc_phase_at(a.ph_hi, a.ph_lo, a.turn_hi, a.turn_lo, (uint64_t)(jj + 1))), a.seed_amp);
+            else
+                osc = cpx_mul(osc, a.wD);
+            cpx o = osc;
+            if (TRANSIENT) {
+                const long long g = a.stream_v0 + jj;           // stream index: the first PB_DC_RTAB samples carry the transient r_i
+                if (g < PB_DC_RTAB) o = cpx_scale(osc, g >= 0 ? a.chain->rtab[g] * inv_r : 0.0);
+            }
+            w[Q - 1 + r] = cpx_mul(x, o);                       // newest sample of row k; tap q multiplies the sample q rows back
+            double ar0 = 0.0, ai0 = 0.0, ar1 = 0.0, ai1 = 0.0;   // two partial sums per component: shorter DFMA chains
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                const cpx s = w[Q - 1 + r - q];
+                if (q & 1) { ar1 = fma(h[q], s.x, ar1); ai1 = fma(h[q], s.y, ai1); }
+                else { ar0 = fma(h[q], s.x, ar0); ai0 = fma(h[q], s.y, ai0); }
+            }
+            if (k >= Q - 1 && k < total) a.v[(long long)(n0 + k - (Q - 1)) * D + p] = cpx_make(ar0 + ar1, ai0 + ai1);
+            j += D;
+        }
+#pragma unroll
+        for (int q = 0; q < Q - 1; ++q) w[q] = w[q + PF];
+    }
+}
+
 template <int FMT, int Q>
 __global__ void __launch_bounds__(128, 2) poly_fir_kernel(const PolyArgs a) {
     const int D = a.D;
@@ -76,56 +156,31 @@ __global__ void __launch_bounds__(128, 2) poly_fir_kernel(const PolyArgs a) {
     double h[Q];
 #pragma unroll
     for (int q = 0; q < Q; ++q) h[q] = __ldg(a.taps + (long long)q * D + p);
-    cpx w[Q];
+    constexpr int PF = (Q % 5 == 0) ? 5 : 4;
+    cpx w[Q + PF - 1];
 #pragma unroll
-    for (int q = 0; q < Q; ++q) w[q] = cpx_make(0.0, 0.0);
+    for (int q = 0; q < Q + PF - 1; ++q) w[q] = cpx_make(0.0, 0.0);
     const long long jmax = a.hist_len + a.n - 1;
     // row k of this tile: m = n0 - (Q-1) + k, virtual index j = D (m + Q) + c - p
     long long j = (long long)D * (n0 + 1) + a.c - p;
     const int total = nt + Q - 1;
     cpx osc = cpx_make(0.0, 0.0);
-    const double inv_r = a.chain->inv_r_inf;
-    // The rows of a branch are D samples apart, so every row is a fresh DRAM line and a load issued where it is used costs the
-    // warp the full memory latency per row (ncu of that form: 1070 cycles per row, FP64 pipe 19.5 % busy with 8 warps per SM;
-    // the compiler may not hoist the load over the store to `v`). PF rows are kept in flight in a register ring instead: row
-    // k + PF is requested before row k is mixed and filtered (~2 x 110 pipe cycles per row and warp: PF = 5 rows cover ~1100).
-    constexpr int PF = (Q % 5 == 0) ? 5 : 4;
-    static_assert(Q % PF == 0, "the ring index must be static under the Q-fold unroll");
-    cpx ring[PF];
+    PolyRaw<FMT> ring[PF];
 #pragma unroll
     for (int f = 0; f < PF; ++f) {
         const long long jf = j + (long long)f * D;
-        ring[f] = poly_load<FMT>(a.hist, a.in, jf < jmax ? jf : jmax, a.hist_len);
+        poly_fetch<FMT>(ring[f], a.hist, a.in, jf < jmax ? jf : jmax, a.hist_len);
     }
-    for (int kb = 0; kb < total; kb += Q) {
-#pragma unroll
-        for (int r = 0; r < Q; ++r) {
-            const int k = kb + r;
-            const long long jj = j < jmax ? j : jmax;          // rows past the tile end are computed but never stored
-            const cpx x = ring[r % PF];
-            {
-                const long long jn = j + (long long)PF * D;
-                ring[r % PF] = poly_load<FMT>(a.hist, a.in, jn < jmax ? jn : jmax, a.hist_len);
-            }
-            if ((k & 31) == 0)
-                osc = cpx_scale(dc_phase_to_osc(dc_phase_at(a.ph_hi, a.ph_lo, a.turn_hi, a.turn_lo, (uint64_t)(jj + 1))), a.seed_amp);
-            else
-                osc = cpx_mul(osc, a.wD);
-            cpx o = osc;
-            const long long g = a.stream_v0 + jj;               // stream index: the first PB_DC_RTAB samples carry the transient r_i
-            if (g < PB_DC_RTAB) o = cpx_scale(osc, g >= 0 ? a.chain->rtab[g] * inv_r : 0.0);
-            w[r] = cpx_mul(x, o);
-            double ar0 = 0.0, ai0 = 0.0, ar1 = 0.0, ai1 = 0.0;   // two partial sums per component: shorter DFMA chains
-#pragma unroll
-            for (int q = 0; q < Q; ++q) {
-                const cpx s = w[(r - q + Q) % Q];
-                if (q & 1) { ar1 = fma(h[q], s.x, ar1); ai1 = fma(h[q], s.y, ai1); }
-                else { ar0 = fma(h[q], s.x, ar0); ai0 = fma(h[q], s.y, ai0); }
-            }
-            if (k >= Q - 1 && k < total) a.v[(long long)(n0 + k - (Q - 1)) * D + p] = cpx_make(ar0 + ar1, ai0 + ai1);
-            j += D;
-        }
-    }
+    // rows whose smallest stream index in this CTA (largest p) is still inside the transient table take the TRANSIENT instance
+    const long long j_lo = (long long)D * (n0 + 1) + a.c - (blockIdx.x * 128 + 127);
+    long long kt = (PB_DC_RTAB - a.stream_v0 - j_lo + D - 1) / D;    // first row with stream index >= PB_DC_RTAB for every thread
+    if (kt < 0) kt = 0;
+    const int total_pf = (total + PF - 1) / PF * PF;
+    constexpr int RS = 6 * PF;
+    int ksplit = kt >= total_pf ? total_pf : (int)((kt + RS - 1) / RS * RS);   // on a re-seed boundary, so both instances re-seed alike
+    if (ksplit > total_pf) ksplit = total_pf;
+    poly_rows<FMT, Q, PF, true>(a, p, n0, total, h, w, ring, osc, j, 0, ksplit);
+    poly_rows<FMT, Q, PF, false>(a, p, n0, total, h, w, ring, osc, j, ksplit, total_pf);
 }
 
 // D-point DFT over the branches of NB consecutive output samples + per-channel rotation, written channel-major.
@@ -140,12 +195,26 @@ __global__ void __launch_bounds__(256) poly_dft_kernel(const cpx *__restrict__ v
     const int tid = threadIdx.x;
     const int n0 = blockIdx.x * NB;
     const int nb = min(NB, nout - n0);
-    for (int i = tid; i < nb * N; i += 256) {
-        const int t = i >> 10, p = i & (N - 1);
-        a[t * N + fft_swz<SH>(p)] = __ldg(v + (long long)(n0 + t) * N + p);
+    // Pass 0 (radix 16, points b + 64 k) takes its inputs straight from global memory: consecutive b are consecutive branches,
+    // so the 16 loads of a thread are coalesced across the warp and all in flight at once; staging the rows in shared memory
+    // first cost one more shared-memory store and load per point in a kernel whose busiest unit is the shared-memory pipe
+    // (ncu: LSU data pipe 69 %, FP64 18 %).
+    static_assert(NB * 64 == 256, "one pass-0 butterfly per thread");
+    {
+        const int t = tid >> 6, b = tid & 63;
+        if (t < nb) {
+            const cpx *src = v + (long long)(n0 + t) * N + b;
+            cpx x[16], w[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) x[k] = __ldg(src + k * 64);
+            fft_twiddle_powers<16>(tw, b, N - 1, w);
+            DftR<16, false>::run(x);
+#pragma unroll
+            for (int q = 1; q < 16; ++q) x[q] = cpx_mul(x[q], w[q]);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) a[t * N + fft_swz<SH>(b + k * 64)] = x[k];
+        }
     }
-    __syncthreads();
-    for (int b = tid; b < nb * 64; b += 256) fft_butterfly<N, 16, 1024, false, SH>(a + (b >> 6) * N, tw, b & 63);
     __syncthreads();
     for (int b = tid; b < nb * 128; b += 256) fft_butterfly<N, 8, 64, false, SH>(a + (b >> 7) * N, tw, b & 127);
     __syncthreads();
