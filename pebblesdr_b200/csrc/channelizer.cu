@@ -87,53 +87,64 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
     if (mode == CH_FMN) {                 // Demod_NFM::processBlockNCO, demod_nfm.cpp:225-257
         PllState v = st[valid ? c : c0].pll;
         if (frame <= 0) frame = n;
-        for (int f0 = 0; f0 < n; f0 += frame) {             // the reference wraps the phase once per receiver frame (:252)
-            const int f1 = f0 + frame < n ? f0 + frame : n;
-            cpx cur[PB_CHZ_R], nxt[PB_CHZ_R];
+        // Three blocks are in flight per channel: block b is walked (th / nbv), block b+1's samples (raw) are turned into
+        // arg(x) INSIDE block b's 32 chain steps — one sample every fourth step, straight-line code the scheduler drops into
+        // the chain's 4-cycle dependent-issue gaps — and block b+2's loads (nxt) are outstanding. Doing arg(x), the
+        // conversions and the stores between two blocks instead cost ~1000 cycles per block on top of the chain's ~1700
+        // (tools/lat_probe.cu: the chain with its shuffles, DC tracker and selects alone takes 53 cycles per step; the kernel
+        // took 85).
+        auto sample = [&](int i) -> cpx { return i < n ? x[i] : cpx_make(1.0, 0.0); };
+        cpx raw[PB_CHZ_R], nxt[PB_CHZ_R];
+        float th[PB_CHZ_R], nbv[PB_CHZ_R];
 #pragma unroll
-            for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = f0 + m * PB_CHZ_L + s < f1 ? x[f0 + m * PB_CHZ_L + s] : cpx_make(1.0, 0.0);
-            for (int i = f0; i < f1; i += 32) {
+        for (int m = 0; m < PB_CHZ_R; ++m) {
+            const float t = pll_theta(sample(m * PB_CHZ_L + s));            // NaN marks an exactly-zero sample
+            th[m] = t != t ? 0.0f : t;
+            nbv[m] = t != t ? 0.0f : -pc.beta;
+            raw[m] = sample(32 + m * PB_CHZ_L + s);
+        }
+        for (int i = 0; i < n; i += 32) {
 #pragma unroll
-                for (int m = 0; m < PB_CHZ_R; ++m) cur[m] = nxt[m];
-                if (i + 32 < f1) {
+            for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = sample(i + 64 + m * PB_CHZ_L + s);
+            const int cnt = n - i < 32 ? n - i : 32;
+            float thn[PB_CHZ_R], nbn[PB_CHZ_R], mine[PB_CHZ_R];
 #pragma unroll
-                    for (int m = 0; m < PB_CHZ_R; ++m) nxt[m] = i + 32 + m * PB_CHZ_L + s < f1 ? x[i + 32 + m * PB_CHZ_L + s] : cpx_make(1.0, 0.0);
+            for (int m = 0; m < PB_CHZ_R; ++m) mine[m] = 0.0f;
+            if (cnt == 32) {
+                // no per-step branch here: a branch between steps pins every shuffle right in front of its use and puts
+                // its ~25-cycle latency on the chain (measured: 164 instead of ~100 cycles per step)
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                    const float nbj = __shfl_sync(0xffffffffu, nbv[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+                    const float o = pll_chain(tj, tj * 0.15915494309189535f, nbj, nbj == 0.0f ? 0.0f : -pc.alpha, pc, v);
+                    mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
+                    if (j % PB_CHZ_L == 1) {                                // next block's sample j / L: off the chain
+                        const float t = pll_theta(raw[j / PB_CHZ_L]);
+                        thn[j / PB_CHZ_L] = t != t ? 0.0f : t;
+                        nbn[j / PB_CHZ_L] = t != t ? 0.0f : -pc.beta;
+                    }
                 }
-                float th[PB_CHZ_R], nbv[PB_CHZ_R], mine[PB_CHZ_R];
+            } else {
 #pragma unroll
-                for (int m = 0; m < PB_CHZ_R; ++m) {
-                    const float t = pll_theta(cur[m]);                  // NaN marks an exactly-zero sample
-                    th[m] = t != t ? 0.0f : t;
-                    nbv[m] = t != t ? 0.0f : -pc.beta;
-                    mine[m] = 0.0f;
-                }
-                const int cnt = f1 - i < 32 ? f1 - i : 32;
-                if (cnt == 32) {
-                    // no per-step branch here: a branch between steps pins every shuffle right in front of its use and puts
-                    // its ~25-cycle latency on the chain (measured: 164 instead of ~100 cycles per step)
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
+                for (int j = 0; j < 32; ++j) {
+                    if (j < cnt) {                           // uniform
                         const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
                         const float nbj = __shfl_sync(0xffffffffu, nbv[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
                         const float o = pll_chain(tj, tj * 0.15915494309189535f, nbj, nbj == 0.0f ? 0.0f : -pc.alpha, pc, v);
                         mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
                     }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        if (j < cnt) {                       // uniform
-                            const float tj = __shfl_sync(0xffffffffu, th[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                            const float nbj = __shfl_sync(0xffffffffu, nbv[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                            const float o = pll_chain(tj, tj * 0.15915494309189535f, nbj, nbj == 0.0f ? 0.0f : -pc.alpha, pc, v);
-                            mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? o : mine[j / PB_CHZ_L];
-                        }
-                    }
                 }
 #pragma unroll
-                for (int m = 0; m < PB_CHZ_R; ++m)
-                    if (valid && m * PB_CHZ_L + s < cnt) y[i + m * PB_CHZ_L + s] = (double)mine[m];   // CPX = float there; imaginary part 0
+                for (int m = 0; m < PB_CHZ_R; ++m) { thn[m] = 0.0f; nbn[m] = 0.0f; }
             }
-            v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
+#pragma unroll
+            for (int m = 0; m < PB_CHZ_R; ++m)
+                if (valid && m * PB_CHZ_L + s < cnt) y[i + m * PB_CHZ_L + s] = (double)mine[m];   // CPX = float there; imaginary part 0
+#pragma unroll
+            for (int m = 0; m < PB_CHZ_R; ++m) { th[m] = thn[m]; nbv[m] = nbn[m]; raw[m] = nxt[m]; }
+            // the reference wraps the phase once per receiver frame (:252) and at the end of the call
+            if ((i + 32) % frame == 0 || i + 32 >= n) v.phase = (float)fmod((double)v.phase, 6.28318530717958647692528676656);
         }
         if (valid && s == 0) st[c].pll = v;
     } else if (mode == CH_AM) {           // Demod_AM::processBlockFiltered, demod_am.cpp:40-59
@@ -153,25 +164,19 @@ static __global__ void __launch_bounds__(32) chan_demod_kernel(const cpx *__rest
 #pragma unroll
             for (int m = 0; m < PB_CHZ_R; ++m) { mg[m] = pb_sqrt_newton(cur[m].x * cur[m].x + cur[m].y * cur[m].y); mine[m] = 0.0; }
             const int cnt = n - i < 32 ? n - i : 32;
-            if (cnt == 32) {
+            // all 32 magnitudes of the block into registers first (64 shuffles issued back to back, pipelined), then a recurrence
+            // that touches registers only: with the shuffle inside the step the 64-bit shuffle's latency sat on every step
+            // (tools/lat_probe.cu: 46.6 cycles per step for a chain of one 8-cycle DFMA)
+            double mall[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const double mj = __shfl_sync(0xffffffffu, mg[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                    const double dn = (am_alpha * d) + mj;                                // demod_am.cpp:52
-                    const double w = dn - d;                                              // demod_am.cpp:53
+            for (int j = 0; j < 32; ++j) mall[j] = __shfl_sync(0xffffffffu, mg[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < cnt) {                                                        // uniform; cnt == 32 except in a ragged tail
+                    const double dn = (am_alpha * d) + mall[j];                       // demod_am.cpp:52
+                    const double w = dn - d;                                          // demod_am.cpp:53
                     d = dn;
                     mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? w : mine[j / PB_CHZ_L];
-                }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    if (j < cnt) {
-                        const double mj = __shfl_sync(0xffffffffu, mg[j / PB_CHZ_L], j % PB_CHZ_L, PB_CHZ_L);
-                        const double dn = (am_alpha * d) + mj;
-                        const double w = dn - d;
-                        d = dn;
-                        mine[j / PB_CHZ_L] = s == j % PB_CHZ_L ? w : mine[j / PB_CHZ_L];
-                    }
                 }
             }
 #pragma unroll

@@ -13,7 +13,7 @@ cz = pb.Channelizer(1024, 61.44e6, 15000.0)
 cz.setFilter(-7500.0, 7500.0)
 for k in range(1024):
     cz.setFrequency(k, -30.69e6 + 60e3 * k)
-    cz.setDemodMode(k, [2, 0][k & 1])
+    cz.setDemodMode(k, {"am": 0, "nbfm": 2, "usb": 7}.get(os.environ.get("PEBBLE_TRACE_MODES", ""), [2, 0][k & 1]))
 out = torch.zeros(1024, n >> 10, dtype=torch.complex128, device="cuda")
 for _ in range(3):
     cz.process(x, n, out)
