@@ -31,6 +31,11 @@ struct pebble_receiver {
     int fill = 0;                                      // m_sampleBufLen
     cpx *d_bp = nullptr, *d_agc = nullptr; size_t work_cap = 0;
     void *d_pin_in = nullptr, *d_pin_out = nullptr; size_t pin_in_cap = 0, pin_out_cap = 0;
+    // pinned path: chunked, double-buffered upload on its own stream (the chain of chunk c runs under the copy of chunk c+1)
+    void *d_pin_chunk[2] = {nullptr, nullptr}; size_t pin_chunk_cap = 0;
+    cudaStream_t copy_st = nullptr;
+    cudaEvent_t ev_up[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
+    bool pin_used[2] = {false, false};
     cudaStream_t stream = nullptr;
     pebble::Staging stg;
     // optional per-step device timing (bench.py's roofline leg): 5 events per process call, recorded on the
@@ -98,6 +103,9 @@ void pebble_receiver_destroy(pebble_receiver_t *h) {
     if (h->agc) pebble_agc_destroy(h->agc);
     if (h->demod) pebble_demod_destroy(h->demod);
     cudaFree(h->d_frames); cudaFree(h->d_bp); cudaFree(h->d_agc); cudaFree(h->d_pin_in); cudaFree(h->d_pin_out); cudaFree(h->d_demod);
+    cudaFree(h->d_pin_chunk[0]); cudaFree(h->d_pin_chunk[1]);
+    if (h->copy_st) cudaStreamDestroy(h->copy_st);
+    for (int b = 0; b < 2; ++b) { if (h->ev_up[b]) cudaEventDestroy(h->ev_up[b]); if (h->ev_free[b]) cudaEventDestroy(h->ev_free[b]); }
     if (h->rs) pebble_resampler_destroy(h->rs);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
@@ -285,16 +293,33 @@ int pebble_receiver_process(pebble_receiver_t *h, int n, const void *in, double 
     return r;
 }
 // Pinned-buffer form for end-to-end timing: `in`/`out` must be page-locked host memory (no extra memcpy).
+// The input is uploaded in chunks of PB_PIN_CHUNK samples on a copy stream into two alternating device buffers, and the chain of
+// chunk c runs on `stream` while chunk c+1 is still crossing PCIe (the chain carries its state, so chunked == unchunked); across
+// consecutive calls the first upload of call k+1 overlaps the last chain run and the download of call k. Everything is enqueued
+// without synchronising; `out` is complete when `stream` is.
+#define PB_PIN_CHUNK (1 << 24)
 int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const void *in, double *out, void *stream_v) {
     if (!h || n <= 0 || !in) { pebble::set_error("receiver: bad argument"); return PEBBLE_ERR_ARG; }
     cudaStream_t st = (cudaStream_t)stream_v;
     const int k = pebble_receiver_out_count(h, n);
-    const size_t bi = (size_t)pebble_downconvert_input_bytes_per_sample(h->dc) * (size_t)n, bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
-    if (bi > h->pin_in_cap) {
+    const size_t bps = (size_t)pebble_downconvert_input_bytes_per_sample(h->dc);
+    const size_t bo = sizeof(cpx) * (size_t)(k > 0 ? k : 1);
+    if (!h->copy_st) {
+        PB_CUDA(cudaStreamCreateWithFlags(&h->copy_st, cudaStreamNonBlocking), PEBBLE_ERR_CUDA);
+        for (int b = 0; b < 2; ++b) {
+            PB_CUDA(cudaEventCreateWithFlags(&h->ev_up[b], cudaEventDisableTiming), PEBBLE_ERR_CUDA);
+            PB_CUDA(cudaEventCreateWithFlags(&h->ev_free[b], cudaEventDisableTiming), PEBBLE_ERR_CUDA);
+        }
+    }
+    const size_t chunk = (size_t)n < (size_t)PB_PIN_CHUNK ? (size_t)n : (size_t)PB_PIN_CHUNK;
+    if (chunk * bps > h->pin_chunk_cap) {
         PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
-        cudaFree(h->d_pin_in); h->d_pin_in = nullptr; h->pin_in_cap = 0;
-        PB_CUDA(cudaMalloc(&h->d_pin_in, bi), PEBBLE_ERR_CUDA);
-        h->pin_in_cap = bi;
+        for (int b = 0; b < 2; ++b) {
+            cudaFree(h->d_pin_chunk[b]); h->d_pin_chunk[b] = nullptr;
+            PB_CUDA(cudaMalloc(&h->d_pin_chunk[b], chunk * bps), PEBBLE_ERR_CUDA);
+            h->pin_used[b] = false;
+        }
+        h->pin_chunk_cap = chunk * bps;
     }
     if (bo > h->pin_out_cap) {
         PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
@@ -302,11 +327,22 @@ int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const void *in, 
         PB_CUDA(cudaMalloc(&h->d_pin_out, bo), PEBBLE_ERR_CUDA);
         h->pin_out_cap = bo;
     }
-    PB_CUDA(cudaMemcpyAsync(h->d_pin_in, in, bi, cudaMemcpyHostToDevice, st), PEBBLE_ERR_CUDA);
-    int r = pebble_receiver_process_device(h, n, (const double *)h->d_pin_in, (double *)h->d_pin_out, st);
-    if (r < 0) return r;
-    if (r > 0 && out) PB_CUDA(cudaMemcpyAsync(out, h->d_pin_out, sizeof(cpx) * (size_t)r, cudaMemcpyDeviceToHost, st), PEBBLE_ERR_CUDA);
-    return r;
+    int produced = 0, c = 0;
+    for (size_t pos = 0; pos < (size_t)n; pos += chunk, ++c) {
+        const int nc = (int)((size_t)n - pos < chunk ? (size_t)n - pos : chunk);
+        const int b = c & 1;
+        if (h->pin_used[b]) PB_CUDA(cudaStreamWaitEvent(h->copy_st, h->ev_free[b], 0), PEBBLE_ERR_CUDA);   // its last reader has finished
+        PB_CUDA(cudaMemcpyAsync(h->d_pin_chunk[b], (const char *)in + pos * bps, (size_t)nc * bps, cudaMemcpyHostToDevice, h->copy_st), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaEventRecord(h->ev_up[b], h->copy_st), PEBBLE_ERR_CUDA);
+        PB_CUDA(cudaStreamWaitEvent(st, h->ev_up[b], 0), PEBBLE_ERR_CUDA);
+        const int r = pebble_receiver_process_device(h, nc, (const double *)h->d_pin_chunk[b], (double *)h->d_pin_out + 2 * (size_t)produced, st);
+        PB_CUDA(cudaEventRecord(h->ev_free[b], st), PEBBLE_ERR_CUDA);
+        h->pin_used[b] = true;
+        if (r < 0) return r;
+        produced += r;
+    }
+    if (produced > 0 && out) PB_CUDA(cudaMemcpyAsync(out, h->d_pin_out, sizeof(cpx) * (size_t)produced, cudaMemcpyDeviceToHost, st), PEBBLE_ERR_CUDA);
+    return produced;
 }
 
 }  // extern "C"
