@@ -463,7 +463,10 @@ int pebble_receiver_set_profiling(pebble_receiver_t *h, int on);
 int pebble_receiver_get_profile(pebble_receiver_t *h, double *ms4, int64_t *calls);
 int pebble_receiver_process(pebble_receiver_t *h, int n, const void *in, double *out);
 int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in, double *d_out, void *stream);
-/* in/out are page-locked HOST buffers; copies and kernels are enqueued on `stream` without synchronising */
+/* in/out are page-locked HOST buffers; copies and kernels are enqueued without synchronising and `out` is complete when `stream`
+ * is. The upload runs in 2^24-sample chunks on an internal copy stream into two alternating device buffers; the chain of chunk c
+ * runs on `stream` under the copy of chunk c+1 (the chain carries its state: chunked == one call up to the roundings of the
+ * down-converter's per-call oscillator seeds, 1e-16). `in` must stay untouched until `stream` has passed this call. */
 int pebble_receiver_process_pinned(pebble_receiver_t *h, int n, const void *in, double *out, void *stream);
 
 /* ---- Batched forms (library extensions for BASELINE config 4; no single reference counterpart) -------------------------
