@@ -23,7 +23,9 @@ __device__ __forceinline__ cpx dc_shfl_up1(cpx v) {
 
 // Oscillator + mix + CIC3 for one thread's NS samples. Returns the K outputs in y[]; m_last0/1 = the thread's last
 // mixed pair (the stage-0 state a following call needs).
-template <int K, bool FULL>
+// PERM: the warp's 32 sample groups are dealt to its lanes as group = 4*(lane & 7) + (lane >> 3) (dc_pipe_kernel, K == 2),
+// so the previous group lives 8 lanes down, or 23 lanes up for the first quarter.
+template <int K, bool FULL, bool PERM = false>
 __device__ __forceinline__ void dc_mix_cic(const cpx (&x0)[K], const cpx (&x1)[K], cpx xh0, cpx xh1, cpx seed, cpx w1, cpx w2,
                                            const DcChain *__restrict__ ch, long long g0 /* stream index of x0[0] */,
                                            bool halo_from_state, cpx b_state, cpx (&y)[K], cpx &m_last0, cpx &m_last1) {
@@ -60,7 +62,13 @@ __device__ __forceinline__ void dc_mix_cic(const cpx (&x0)[K], const cpx (&x1)[K
         b = bn;
         if (q == K - 1) { m_last0 = m0; m_last1 = m1; }
     }
-    const cpx bup = dc_shfl_up1(b);                 // lane-1's last pair
+    cpx bup;                                        // the previous group's last pair
+    if (PERM) {
+        const int lane = threadIdx.x & 31, src = lane >= 8 ? lane - 8 : lane + 23;
+        bup = cpx_make(__shfl_sync(0xffffffffu, b.x, src), __shfl_sync(0xffffffffu, b.y, src));
+    } else {
+        bup = dc_shfl_up1(b);
+    }
     y[0] = cpx_add(y[0], (threadIdx.x & 31) ? bup : bprev);
 }
 

@@ -115,6 +115,11 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx *smem = reinterpret_cast<cpx *>(smem_raw);
     const int tid = threadIdx.x;
+    // Which NS input samples a thread mixes. With K == 2 a thread stores ONE slot per array, and lanes storing consecutive
+    // slots span 10 padded slots per quarter-warp (two wavefronts per STS.128). Dealing the warp's 32 groups out as
+    // 4*(lane & 7) + (lane >> 3) gives every quarter-warp the stride-5 pattern the tile reads already use: one wavefront.
+    constexpr bool PERM = K == 2;
+    const int mtid = PERM ? (tid & ~31) | (4 * (tid & 7) + ((tid & 31) >> 3)) : tid;
 
     // single channel only (the batched form of the 10-stage channelizer chain stays on dc_cic_kernel)
     __shared__ DcSeg seg_info;
@@ -167,15 +172,15 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
             }
             seg_info.b_state = b_state;
         }
-        in_t = reinterpret_cast<const char *>(call.in) + (start + NS * tid) * SB;
+        in_t = reinterpret_cast<const char *>(call.in) + (start + NS * mtid) * SB;
         const int len0 = (int)(total < C ? total : C);
         raw.zero();
-        if (NS * tid < len0) raw.load(in_t);
-        if (halo_lane && tid > 0 && NS * tid < len0) rawh.load(in_t - 2 * SB);
+        if (NS * mtid < len0) raw.load(in_t);
+        if (halo_lane && tid > 0 && NS * mtid < len0) rawh.load(in_t - 2 * SB);
     }
     int sl[K];   // slot of this thread's q-th CIC3 output inside half 0 of stage 1's arrays (even q -> even array)
 #pragma unroll
-    for (int q = 0; q < K; ++q) sl[q] = G::base(1) + (q & 1) * A1 + dc_slot(HH1 + ((K * tid + q) >> 1));
+    for (int q = 0; q < K; ++q) sl[q] = G::base(1) + (q & 1) * A1 + dc_slot(HH1 + ((K * mtid + q) >> 1));
     __syncthreads();
 
     cpx seed = cpx_make(0.0, 0.0);
@@ -190,7 +195,7 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
             cpx y[K], ml0, ml1;
             if ((ci & 31) == 0) {
                 seed = cpx_scale(dc_phase_to_osc(dc_phase_at(call.phase_hi, call.phase_lo, call.turn_hi, call.turn_lo,
-                                                             (uint64_t)(si->start + (long long)ci * C + NS * tid + 1))), call.r_inf);
+                                                             (uint64_t)(si->start + (long long)ci * C + NS * mtid + 1))), call.r_inf);
             } else {
                 seed = cpx_mul(seed, call.wchunk);
             }
@@ -200,26 +205,26 @@ __global__ void __launch_bounds__(T, MINB) dc_pipe_kernel(const DcChain *__restr
             for (int k = 0; k < K; ++k) raw.get(k, nx0[k], nx1[k]);
             rawh.get(nxh0, nxh1);
             if (full) {
-                dc_mix_cic<K, true>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, 0, false, cpx_make(0.0, 0.0), y, ml0, ml1);
+                dc_mix_cic<K, true, PERM>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, 0, false, cpx_make(0.0, 0.0), y, ml0, ml1);
             } else {
                 const cpx b_state = cpx_make(si->b_state.x, si->b_state.y);
-                dc_mix_cic<K, false>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, call.stream_pos + si->start + (long long)ci * C + NS * tid,
+                dc_mix_cic<K, false, PERM>(nx0, nx1, nxh0, nxh1, seed, w1, w2, ch, call.stream_pos + si->start + (long long)ci * C + NS * mtid,
                                      ci == 0 && tid == 0, b_state, y, ml0, ml1);
             }
             // the samples of chunk p+1 are loaded INTO THE SAME REGISTERS as soon as the mix has consumed chunk p's: they
             // are in flight during the stage tiles and the barrier below (no second register set, no copies)
             in_t += C * SB;
-            if (ci + 2 < N || (ci + 1 < N && NS * tid < len_last)) {
+            if (ci + 2 < N || (ci + 1 < N && NS * mtid < len_last)) {
                 raw.load(in_t);
                 if (halo_lane) rawh.load(in_t - 2 * SB);
             }
             if (full) {
 #pragma unroll
                 for (int q = 0; q < K; ++q) smem[sl[q] + hoff] = y[q];
-            } else if (NS * tid < len) {
+            } else if (NS * mtid < len) {
 #pragma unroll
                 for (int q = 0; q < K; ++q) smem[sl[q] + hoff] = y[q];
-                if (si->last_seg && ci == N - 1 && NS * tid + NS == len) {   // CIC3 delay line for the next call
+                if (si->last_seg && ci == N - 1 && NS * mtid + NS == len) {   // CIC3 delay line for the next call
                     call.state_out[0] = ml0;
                     call.state_out[1] = ml1;
                 }
