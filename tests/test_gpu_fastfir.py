@@ -153,10 +153,15 @@ def _long_oracle(N):
 
 
 @pytest.mark.parametrize("N,calls", [(32768, [16384 * 5]), (32768, [7, 16377, 40000, 9152]),
-                                     (131072, [65536 * 3]), (131072, [65536, 5000, 2 * 65536 - 5000, 4096, 61440])])
-def test_long_filter_vs_reference(N, calls):
+                                     (131072, [65536 * 3]), (131072, [65536, 5000, 2 * 65536 - 5000, 4096, 61440]),
+                                     # >= 7 blocks in a call: super-blocks (4N-point transforms, 7 blocks each) + the remainder
+                                     (32768, [16384 * 17]), (32768, [16384 * 7 + 100, 16384 * 9 - 95, 16384 * 14]),
+                                     (131072, [65536 * 9]), (131072, [65536 * 7 + 123, 65536 * 8])])
+def test_long_filter_vs_reference(N, calls, monkeypatch):
     import pebblesdr_b200 as pb
     L, n = N // 2, sum(calls)
+    if n >= 14 * L:
+        monkeypatch.setenv("PEBBLE_LF_PIPE_MIN", "1")              # the longest cases also run the persistent pipeline kernel
     x = iq_noise_tones(n, 5000, 100e6, [(7e6, 0.4), (31e6, 0.5)], 0.1)
     g, r = pb.CFastFIR(N, L + 1), _long_oracle(N)
     assert g.SetupParameters(-20e6, 20e6, 0.0, 100e6) == 0
@@ -235,6 +240,56 @@ def test_long_filter_streams_batch_equals_single_streams_and_split():
     o = np.zeros(n + N, complex)
     f.ProcessData(n, np.ascontiguousarray(0.5 * xs[0] - 2.0 * xs[1]), o)
     assert rel_rms(o[:n], mix) <= 1e-12
+
+
+@pytest.mark.parametrize("N", [32768, 131072])
+def test_long_filter_super_blocks_equal_block_by_block(N):
+    """A call of 16 blocks (two 4N-point super-blocks of 7 + two N-point blocks) against the same stream fed one block per
+    call (N-point plan only), three batched streams, device-resident; and against a handle created with the super-block plan
+    disabled. Same linear convolution: FP64 rounding apart (1e-13)."""
+    import os
+    import torch
+    import pebblesdr_b200 as pb
+    from pebblesdr_b200._lib import lib, check
+    L, S, nb = N // 2, 3, 16
+    n = L * nb
+    xs = np.stack([iq_noise_tones(n, 5200 + s, 100e6, [((s - 1) * 9e6, 0.4)], 0.1) for s in range(S)])
+    dx = torch.from_numpy(xs).cuda()
+
+    def run(step_blocks, **env):
+        os.environ.update(env)                                  # read when the handle is created
+        try:
+            f = pb.CFastFIR(N, L + 1)
+        finally:
+            for k in env:
+                os.environ.pop(k, None)
+        f.SetupParameters(-20e6, 20e6, 0.0, 100e6)
+        check(lib.pebble_fastfir_set_streams(f._h, S))
+        dy = torch.zeros((S, n), dtype=torch.complex128, device="cuda")
+        done = 0
+        while done < n:
+            c = min(step_blocks * L, n - done)
+            d = dx[:, done:done + c].contiguous()
+            k = check(lib.pebble_fastfir_process_batch_device(f._h, c, d.data_ptr(), c, dy.data_ptr() + 16 * done, n, None))
+            assert k == c
+            done += c
+        torch.cuda.synchronize()
+        return dy.cpu().numpy()
+
+    whole, single, off = run(nb), run(1), run(nb, PEBBLE_LF_NOSUPER="1")
+    # the persistent pipeline kernel (lf_pipe_kernel) forced on at this small size, with the smallest and the default ring,
+    # and forced off: the same tile functions in a different launch structure (inlined twice, so FMA contraction may differ)
+    piped = run(nb, PEBBLE_LF_PIPE_MIN="1")
+    piped_small_ring = run(nb, PEBBLE_LF_PIPE_MIN="1", PEBBLE_LF_RING="4" if N == 131072 else "6")
+    triples = whole                                            # the default: launch triples
+    piped_single = run(1, PEBBLE_LF_PIPE_MIN="1")
+    for s in range(S):
+        assert rel_rms(whole[s], single[s]) <= 1e-13, s
+        assert rel_rms(whole[s], off[s]) <= 1e-13, s
+        assert rel_rms(single[s], off[s]) <= 1e-13, s
+        assert rel_rms(piped[s], triples[s]) <= 1e-14, s
+        assert rel_rms(piped_small_ring[s], piped[s]) <= 1e-14, s
+        assert rel_rms(piped_single[s], single[s]) <= 1e-13, s
 
 
 def test_long_filter_small_calls_and_state_round_trip():
