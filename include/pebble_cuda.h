@@ -331,8 +331,15 @@ int pebble_agc_process_device(pebble_agc_t *h, int n, const double *d_in, double
  * 5..12 DSB/LSB/USB/CW/DIG/NONE = pass-through (the reference returns `in`; here out is a copy and
  * pebble_demod_is_passthrough() reports it). 4 dmFMS (Demod::fmStereo -> Demod_WFM::processDataStereo, demod_wfm.cpp:258-366):
  * the AUDIO path — discriminator, Hilbert pair, 19 kHz pilot band-pass, pilot PLL (with the reference's own arctan2), stereo
- * demux when locked, 15 kHz CFir, de-emphasis, notch; pebble_demod_get_stereo_lock() = getStereoLock. The RDS branch
- * (:298-357: 57 kHz down-conversion, RDS PLL, matched filter, bit decoder) is NOT built: no RDS groups are produced. */
+ * demux when locked, 15 kHz CFir, de-emphasis, notch; pebble_demod_get_stereo_lock() = getStereoLock — and the RDS branch
+ * (:298-357: CDownConvert by -57 kHz to ~8-20 kS/s, 2400 Hz complex low-pass, RDS PLL, bi-phase matched filter, bit-rate
+ * resonator, bit slicer on the GPU; differential decode, (26,16) syndrome check with burst correction and the block / group
+ * state machine of processNewRdsBit / checkBlock :584-758 on the host, fed through a page-locked ring so that the audio
+ * path never waits for it). pebble_demod_get_next_rds_group() = Demod_WFM::getNextRdsGroupData (:764-788): pops one group,
+ * returns 1 when it differs from the last one returned. With RDS on (default, as in the reference) a dmFMS call must be a
+ * multiple of the RDS down-converter's decimation (rate / pebble_demod_get_rds_rate()); pebble_demod_set_rds(h, 0) runs the
+ * audio path alone. pebble_demod_get_rds_tap() (tests): the last call's m_RdsRaw as the reference leaves it (:336-352),
+ * pairs (value at the sampling instant or 0, matched-filter output). rdsdecode.cpp (groups -> text) is not part of the path. */
 typedef struct pebble_demod pebble_demod_t;
 pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples);
 void pebble_demod_destroy(pebble_demod_t *h);
@@ -340,6 +347,19 @@ int pebble_demod_set_mode(pebble_demod_t *h, int mode);
 int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant);
 int pebble_demod_set_wfm_sample_rate(pebble_demod_t *h, double rate);
 int pebble_demod_get_stereo_lock(pebble_demod_t *h);
+int pebble_demod_set_rds(pebble_demod_t *h, int on);
+double pebble_demod_get_rds_rate(const pebble_demod_t *h);
+int pebble_demod_get_next_rds_group(pebble_demod_t *h, unsigned short *blocks4);
+int pebble_demod_get_rds_tap(pebble_demod_t *h, double *out, int max_samples);
+/* The block / group synchroniser of the RDS branch by itself (Demod_WFM::processNewRdsBit + checkBlock, demod_wfm.cpp:584-758):
+ * pure host logic, fed with DATA bits (after the differential decode); pebble_rds_sync_next_group as
+ * pebble_demod_get_next_rds_group. The demodulator owns one of these; this handle exists for callers that get their bits
+ * elsewhere and for the CPU tests. */
+typedef struct pebble_rds_sync pebble_rds_sync_t;
+pebble_rds_sync_t *pebble_rds_sync_create(void);
+void pebble_rds_sync_destroy(pebble_rds_sync_t *h);
+int pebble_rds_sync_push_bits(pebble_rds_sync_t *h, const unsigned char *bits, int n);
+int pebble_rds_sync_next_group(pebble_rds_sync_t *h, unsigned short *blocks4);
 int pebble_demod_set_bandwidth(pebble_demod_t *h, double bandwidth);
 int pebble_demod_is_passthrough(const pebble_demod_t *h);
 int pebble_demod_process(pebble_demod_t *h, int n, const double *in, double *out);

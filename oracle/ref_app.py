@@ -50,6 +50,8 @@ def lib():
             "ref_demod_wfm_set_sample_rate": (_d, [_vp, _d, _d, _i]),
             "ref_demod_wfm_process_mono": (_i, [_vp, _i, _vp, _vp]), "ref_demod_wfm_process_stereo": (_i, [_vp, _i, _vp, _vp]),
             "ref_demod_wfm_stereo_lock": (_i, [_vp, _vp]), "ref_demod_wfm_next_rds_group": (_i, [_vp, _vp]),
+            "ref_demod_wfm_rds_tap": (_i, [_vp, _i, _vp]), "ref_demod_wfm_rds_rate": (_d, [_vp]),
+            "ref_demod_wfm_push_bits": (None, [_vp, _vp, _i]),
             "ref_spectrum_create": (_vp, [_u, _u, _u, _i, _i, _i]), "ref_spectrum_destroy": (None, [_vp]),
             "ref_spectrum_set_hires": (None, [_vp, _i]), "ref_spectrum_set_updates_per_sec": (None, [_vp, _i]),
             "ref_spectrum_set_sample_rate": (None, [_vp, _u, _u]),
@@ -208,6 +210,20 @@ class Demod_WFM(_H):
         if lib().ref_demod_wfm_next_rds_group(self.h, b):
             return tuple(b)
         return None
+
+    def pushRdsBits(self, bits):
+        """Demod_WFM::processNewRdsBit for every element of `bits` (data bits, after the differential decode)."""
+        b = np.ascontiguousarray(bits, dtype=np.uint8)
+        lib().ref_demod_wfm_push_bits(self.h, b.ctypes.data, len(b))
+
+    def rdsRate(self):
+        return lib().ref_demod_wfm_rds_rate(self.h)
+
+    def rdsTap(self, length):
+        """m_RdsRaw after the last processDataStereo call (the debug pairs the reference leaves there, demod_wfm.cpp:336-352)."""
+        out = np.empty(int(length), dtype=np.complex128)
+        lib().ref_demod_wfm_rds_tap(self.h, int(length), out.ctypes.data)
+        return out
 
 
 class SignalSpectrum(_H):

@@ -15,7 +15,9 @@
 #include "demod/demod_am.h"
 #include "demod/demod_nfm.h"
 #include "demod/demod_sam.h"
+#define private public   // ONLY for the RDS test tap below (reads m_RdsRaw / m_RdsOutputRate); layout and code are untouched
 #include "demod/demod_wfm.h"
+#undef private
 #include "signalstrength.h"
 #include "signalspectrum.h"
 #include "dcremoval.h"
@@ -120,6 +122,18 @@ int ref_demod_wfm_next_rds_group(void *h, unsigned short *blocks4) {
     if (!((Demod_WFM *)h)->getNextRdsGroupData(&g)) return 0;
     blocks4[0] = g.BlockA; blocks4[1] = g.BlockB; blocks4[2] = g.BlockC; blocks4[3] = g.BlockD;
     return 1;
+}
+
+// test tap: what processDataStereo itself leaves in m_RdsRaw (demod_wfm.cpp:336-352): per RDS-rate sample the pair
+// (matched-filter value at a sampling instant or 0, matched-filter output). len = InLength / the RDS decimation.
+int ref_demod_wfm_rds_tap(void *h, int len, double *out) {
+    memcpy(out, ((Demod_WFM *)h)->m_RdsRaw, sizeof(double) * 2 * (size_t)len);
+    return len;
+}
+double ref_demod_wfm_rds_rate(void *h) { return ((Demod_WFM *)h)->m_RdsOutputRate; }
+// the block / group synchroniser alone: Demod_WFM::processNewRdsBit (demod_wfm.cpp:584) fed with data bits
+void ref_demod_wfm_push_bits(void *h, const unsigned char *bits, int n) {
+    for (int i = 0; i < n; ++i) ((Demod_WFM *)h)->processNewRdsBit(bits[i] & 1);
 }
 
 // ---- SignalSpectrum (application/signalspectrum.h) ---------------------------------------------------------------

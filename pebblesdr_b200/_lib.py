@@ -140,6 +140,14 @@ SIGNATURES = {
     "pebble_demod_set_nfm_variant": (c_int, [c_vp, c_int]),
     "pebble_demod_set_wfm_sample_rate": (c_int, [c_vp, c_dbl]),
     "pebble_demod_get_stereo_lock": (c_int, [c_vp]),
+    "pebble_demod_set_rds": (c_int, [c_vp, c_int]),
+    "pebble_demod_get_rds_rate": (c_dbl, [c_vp]),
+    "pebble_demod_get_next_rds_group": (c_int, [c_vp, c_vp]),
+    "pebble_demod_get_rds_tap": (c_int, [c_vp, c_vp, c_int]),
+    "pebble_rds_sync_create": (c_vp, []),
+    "pebble_rds_sync_destroy": (None, [c_vp]),
+    "pebble_rds_sync_push_bits": (c_int, [c_vp, c_vp, c_int]),
+    "pebble_rds_sync_next_group": (c_int, [c_vp, c_vp]),
     "pebble_demod_set_bandwidth": (c_int, [c_vp, c_dbl]),
     "pebble_demod_is_passthrough": (c_int, [c_vp]),
     "pebble_demod_process": (c_int, [c_vp, c_int, c_vp, c_vp]),

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpebblecuda.so")
-CU_SRCS = ["lib_common.cu", "downconvert.cu", "decimator.cu", "fastfir.cu", "fastfir_long.cu", "spectrum.cu", "demod.cu", "receiver.cu", "channelizer.cu", "chz_poly.cu", "resampler.cu", "cpxutil.cu", "prefilter.cu", "noiseblanker.cu"]
+CU_SRCS = ["lib_common.cu", "downconvert.cu", "decimator.cu", "fastfir.cu", "fastfir_long.cu", "spectrum.cu", "demod.cu", "receiver.cu", "channelizer.cu", "chz_poly.cu", "resampler.cu", "cpxutil.cu", "prefilter.cu", "noiseblanker.cu", "rds.cu"]
 CPP_SRCS = ["host_design.cpp", "host_window.cpp", "host_demod.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]

@@ -266,7 +266,9 @@ struct pebble_demod {
     pebble_cfir wfm_lp;
     cpx *d_wfm_last[2] = {nullptr, nullptr};
     int wfm_cur = 0;
-    // WFM stereo audio (demod_wfm.cpp:258-366 without the RDS branch): Hilbert pair, pilot band-pass, pilot PLL, demux
+    // WFM stereo (demod_wfm.cpp:258-366): Hilbert pair, pilot band-pass, pilot PLL, demux; the RDS branch lives in rds.cu
+    RdsBranch *rds = nullptr;
+    bool rds_on = true, rds_ok = false;   // rds_ok: the RDS chain could be designed for the current WFM rate
     pebble_cfir wfm_hilb;
     pebble_iir_t *wfm_pilot_bp = nullptr;
     WfmPllConst wfm_pll;
@@ -295,22 +297,6 @@ static __global__ void wfm_disc_kernel(const cpx *__restrict__ in, int n, const 
     }
 }
 // ---- WFM stereo: pilot PLL (demod_wfm.cpp:388-430) and demux (:272-296) ---------------------------------------------------------
-// Demod_WFM::arctan2 (:792-818), the reference's own approximation ("|error| < 0.005"; its |z| >= 1 branch returns angles near
-// 2 pi — kept as written: the loop's behaviour far from lock depends on it)
-__device__ __forceinline__ double wfm_arctan2(double y, double x) {
-    const double TWOPI = 6.28318530717958647692528676656, PI = 3.14159265358979323846264338328;
-    if (x == 0.0) return y > 0.0 ? TWOPI : (y == 0.0 ? 0.0 : -TWOPI);
-    const double z = __ddiv_rn(y, x);
-    double angle;
-    if (fabs(z) < 1.0) {
-        angle = __ddiv_rn(z, __dadd_rn(1.0, __dmul_rn(__dmul_rn(0.2854, z), z)));
-        if (x < 0.0) return y < 0.0 ? __dsub_rn(angle, PI) : __dadd_rn(angle, PI);
-    } else {
-        angle = __dsub_rn(TWOPI, __ddiv_rn(z, __dadd_rn(__dmul_rn(z, z), 0.2854)));
-        if (y < 0.0) return __dsub_rn(angle, PI);
-    }
-    return angle;
-}
 // One warp; the loop is a serial recurrence in double (sin/cos of the NCO phase, rotate, arctan2, loop filter), the lanes only
 // fetch the samples of a 32-sample block. The reference takes sin/cos from x87 fsincos (:398); the double results agree to ~1 ulp
 // and the loop is a contracting map, so the audio agrees to ~1e-12.
@@ -398,6 +384,9 @@ static int wfm_setup(pebble_demod *h, double rate) {
         for (int b = 0; b < 2; ++b) PB_CUDA(cudaMemcpy(h->d_wfm_pll + b, &s0, sizeof(s0), cudaMemcpyHostToDevice), PEBBLE_ERR_CUDA);
         h->wfm_pll_cur = 0;
     }
+    // m_RdsDownConvert.SetDataRate(rate, 8000), SetFrequency(-57 kHz), initRds (:190-193). A rate the RDS chain cannot be
+    // designed for (matched filter longer than CFir's 75 taps) leaves the audio path working and RDS off.
+    h->rds_ok = rds_setup(h->rds, rate) == 0;
     return 0;
 }
 
@@ -505,7 +494,7 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         if (r < 0) return r;
         return pebble_iir_process_device(h->wfm_notch, n, (const double *)h->d_tmp, (double *)d_out, st);   // 19 kHz pilot notch
     }
-    if (h->mode == 4) {  // dmFMS -> Demod::fmStereo -> Demod_WFM::processDataStereo (demod_wfm.cpp:258-366), audio path; RDS is not decoded
+    if (h->mode == 4) {  // dmFMS -> Demod::fmStereo -> Demod_WFM::processDataStereo (demod_wfm.cpp:258-366)
         int r = demod_reserve(h, n);
         if (r < 0) return r;
         if ((size_t)n > h->w_cap) {
@@ -526,6 +515,10 @@ int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaSt
         if (r < 0) return r;
         wfm_pilot_pll_kernel<<<1, 32, 0, st>>>(h->d_w2, n, h->wfm_pll, h->d_wfm_pll + h->wfm_pll_cur, h->d_wfm_pll + (h->wfm_pll_cur ^ 1), h->d_wphase);
         h->wfm_pll_cur ^= 1;
+        if (h->rds_on && h->rds_ok) {   // :298-357, from m_CpxRawFm (d_w1) before the demux below reuses the buffer
+            r = rds_process(h->rds, n, h->d_w1, st);
+            if (r < 0) return r;
+        }
         wfm_demux_kernel<<<grid_for(n), 256, 0, st>>>(h->d_tmp, h->d_wphase, h->d_wfm_pll + h->wfm_pll_cur, n, h->d_w1);
         pebble::count_launch(2);
         PB_CUDA(cudaGetLastError(), PEBBLE_ERR_CUDA);
@@ -547,7 +540,8 @@ pebble_demod_t *pebble_demod_create(unsigned input_rate, unsigned num_samples) {
     pebble_demod *h = new pebble_demod();
     h->rate = input_rate;
     h->wfm_in_lp = pebble_iir_create(); h->wfm_deemph = pebble_iir_create(); h->wfm_notch = pebble_iir_create(); h->wfm_pilot_bp = pebble_iir_create();
-    bool ok = h->wfm_in_lp && h->wfm_deemph && h->wfm_notch && h->wfm_pilot_bp && cfir_alloc(&h->wfm_lp) == 0 && cfir_alloc(&h->wfm_hilb) == 0 &&
+    h->rds = rds_create();
+    bool ok = h->rds && h->wfm_in_lp && h->wfm_deemph && h->wfm_notch && h->wfm_pilot_bp && cfir_alloc(&h->wfm_lp) == 0 && cfir_alloc(&h->wfm_hilb) == 0 &&
               pebble::cuda_ok(cudaMalloc(&h->d_wfm_pll, 2 * sizeof(WfmPllState)), "cudaMalloc") &&
               cfir_alloc(&h->am_lp) == 0 && cfir_alloc(&h->nfm_lp) == 0 && cfir_alloc(&h->sam_bp) == 0 &&
               pebble::cuda_ok(cudaMalloc(&h->d_sam, sizeof(SamState)), "cudaMalloc") &&
@@ -608,6 +602,7 @@ void pebble_demod_destroy(pebble_demod_t *h) {
     if (!h) return;
     cfir_release(&h->am_lp); cfir_release(&h->nfm_lp); cfir_release(&h->sam_bp); cfir_release(&h->wfm_lp);
     pebble_iir_destroy(h->wfm_in_lp); pebble_iir_destroy(h->wfm_deemph); pebble_iir_destroy(h->wfm_notch); pebble_iir_destroy(h->wfm_pilot_bp);
+    rds_destroy(h->rds);
     cfir_release(&h->wfm_hilb); cudaFree(h->d_wfm_pll); cudaFree(h->d_w1); cudaFree(h->d_w2); cudaFree(h->d_wphase);
     cudaFree(h->d_wfm_last[0]); cudaFree(h->d_wfm_last[1]);
     cudaFree(h->d_sam);
@@ -635,6 +630,23 @@ int pebble_demod_get_stereo_lock(pebble_demod_t *h) {
     PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
     PB_CUDA(cudaMemcpy(&s, h->d_wfm_pll + h->wfm_pll_cur, sizeof(s), cudaMemcpyDeviceToHost), PEBBLE_ERR_CUDA);
     return s.locked;
+}
+// The RDS branch of dmFMS (demod_wfm.cpp:298-357) is on by default, as in the reference; off = audio path alone.
+int pebble_demod_set_rds(pebble_demod_t *h, int on) {
+    if (!h) return PEBBLE_ERR_ARG;
+    h->rds_on = on != 0;
+    return 0;
+}
+double pebble_demod_get_rds_rate(const pebble_demod_t *h) { return h && h->rds_ok ? rds_rate(h->rds) : 0.0; }
+// Demod_WFM::getNextRdsGroupData (demod_wfm.cpp:764-788)
+int pebble_demod_get_next_rds_group(pebble_demod_t *h, unsigned short *blocks4) {
+    if (!h || !blocks4) return 0;
+    return rds_next_group(h->rds, blocks4);
+}
+int pebble_demod_get_rds_tap(pebble_demod_t *h, double *out, int max_samples) {
+    if (!h || !out || max_samples < 0) return PEBBLE_ERR_ARG;
+    PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+    return rds_tap(h->rds, out, max_samples);
 }
 int pebble_demod_set_nfm_variant(pebble_demod_t *h, int variant) {
     if (!h || variant < 0 || variant > 1) return PEBBLE_ERR_ARG;

@@ -34,3 +34,13 @@ int fastfir_am_aggregate_next(pebble_fastfir *h, void *tile_map, double alpha, i
 void demod_am_cancel_tiles(pebble_demod *h);
 double agc_manual_gain(const pebble_agc *h);
 int agc_is_off(const pebble_agc *h);
+
+// rds.cu: the RDS branch of Demod_WFM::processDataStereo (demod_wfm.cpp:298-357) and its block / group synchroniser
+struct RdsBranch;
+RdsBranch *rds_create();
+void rds_destroy(RdsBranch *r);
+int rds_setup(RdsBranch *r, double wfm_rate);                                       // setSampleRate's RDS part + initRds
+double rds_rate(const RdsBranch *r);
+int rds_process(RdsBranch *r, int n, const cpx *d_cpx_raw_fm, cudaStream_t st);     // returns the RDS-rate sample count
+int rds_next_group(RdsBranch *r, unsigned short *blocks4);                          // getNextRdsGroupData
+int rds_tap(RdsBranch *r, double *out, int max_samples);

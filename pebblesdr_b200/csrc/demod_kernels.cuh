@@ -567,3 +567,20 @@ static __global__ void agc_kernel(const cpx *__restrict__ in, int n, long long s
     st[s] = v;
 }
 
+// ---- WFM (demod_wfm.cpp), shared by demod.cu (pilot PLL) and rds.cu (RDS PLL) -----------------------------------------
+// Demod_WFM::arctan2 (:792-818), the reference's own approximation ("|error| < 0.005"; its |z| >= 1 branch returns angles near
+// 2 pi — kept as written: the loop's behaviour far from lock depends on it)
+__device__ __forceinline__ double wfm_arctan2(double y, double x) {
+    const double TWOPI = 6.28318530717958647692528676656, PI = 3.14159265358979323846264338328;
+    if (x == 0.0) return y > 0.0 ? TWOPI : (y == 0.0 ? 0.0 : -TWOPI);
+    const double z = __ddiv_rn(y, x);
+    double angle;
+    if (fabs(z) < 1.0) {
+        angle = __ddiv_rn(z, __dadd_rn(1.0, __dmul_rn(__dmul_rn(0.2854, z), z)));
+        if (x < 0.0) return y < 0.0 ? __dsub_rn(angle, PI) : __dadd_rn(angle, PI);
+    } else {
+        angle = __dsub_rn(TWOPI, __ddiv_rn(z, __dadd_rn(__dmul_rn(z, z), 0.2854)));
+        if (y < 0.0) return __dsub_rn(angle, PI);
+    }
+    return angle;
+}

@@ -437,6 +437,23 @@ class NoiseBlanker(_Handle):
         return self._run(2, inb)
 
 
+class RdsSync(_Handle):
+    """The RDS block / group synchroniser alone (Demod_WFM::processNewRdsBit + checkBlock + getNextRdsGroupData,
+    demod_wfm.cpp:584-788): host logic, fed with data bits."""
+    _destroy = staticmethod(lib.pebble_rds_sync_destroy)
+
+    def __init__(self):
+        super().__init__(lib.pebble_rds_sync_create(), "RdsSync")
+
+    def pushBits(self, bits):
+        b = np.ascontiguousarray(bits, dtype=np.uint8)
+        check(lib.pebble_rds_sync_push_bits(self._h, b.ctypes.data, len(b)), "pushBits")
+
+    def getNextRdsGroupData(self):
+        b = (ctypes.c_ushort * 4)()
+        return tuple(b) if lib.pebble_rds_sync_next_group(self._h, b) == 1 else None
+
+
 class NCO(_Handle):
     """pebblelib/nco.h: the oscillator primitive. setFrequency clamps to +-((sampleRate / 2) - 1) (nco.cpp:16-45)."""
     _destroy = staticmethod(lib.pebble_nco_destroy)
@@ -606,6 +623,26 @@ class Demod(_Handle):
     def getStereoLock(self):
         """Demod_WFM::getStereoLock: the pilot lock decision of the last dmFMS block."""
         return bool(check(lib.pebble_demod_get_stereo_lock(self._h), "getStereoLock"))
+
+    def setRds(self, on):
+        """dmFMS: the RDS branch (demod_wfm.cpp:298-357) on (default, as in the reference) or off (audio path alone)."""
+        check(lib.pebble_demod_set_rds(self._h, 1 if on else 0), "setRds")
+
+    def getRdsRate(self):
+        """m_RdsOutputRate: the sample rate of the RDS branch after its down-converter."""
+        return float(lib.pebble_demod_get_rds_rate(self._h))
+
+    def getNextRdsGroupData(self):
+        """Demod_WFM::getNextRdsGroupData (demod_wfm.cpp:764-788): pops one queued group; the four 16-bit blocks when it
+        differs from the last group returned, else None (queue empty or an unchanged group)."""
+        b = (ctypes.c_ushort * 4)()
+        return tuple(b) if lib.pebble_demod_get_next_rds_group(self._h, b) == 1 else None
+
+    def getRdsTap(self, max_samples):
+        """Test tap: the last dmFMS call's m_RdsRaw as the reference leaves it (:336-352)."""
+        out = np.empty(max_samples, dtype=np.complex128)
+        k = check(lib.pebble_demod_get_rds_tap(self._h, out.ctypes.data, max_samples), "getRdsTap")
+        return out[:k].copy()
 
     def processBlock(self, inb, bufSize):
         """Like the reference, pass-through modes return the INPUT array itself (demod.cpp:127-138)."""

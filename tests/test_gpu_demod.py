@@ -229,7 +229,8 @@ def test_wfm_stereo_audio_vs_compiled_reference(pilot_hz, pilot_phase, frames):
     pilot loop only locks when it starts close: with the pilot at 19010 Hz and a favourable phase it is locked from the first
     frame (stereo separation visible), from phase 3.0 it unlocks and re-locks, at 19000 Hz it never locks within the test and
     the output is mono. All three must match — lock decisions per frame exactly, audio to 1e-9 relative RMS over the whole
-    stream. The RDS branch (:298-357) is not built and does not touch the audio."""
+    stream. The RDS branch (:298-357) runs too (it is on by default, as in the reference) and does not touch the audio; it has its
+    own test below."""
     import pebblesdr_b200 as pb
     from oracle import ref_app
     rate, frame = 312500, 2048
@@ -260,3 +261,74 @@ def test_wfm_stereo_audio_vs_compiled_reference(pilot_hz, pilot_phase, frames):
         assert not any(lw[2:]) and np.array_equal(want.real[frame * 2:], want.imag[frame * 2:])                          # mono fallback
     if pilot_phase == 3.0:
         assert 0 < sum(lw) < frames
+
+
+@pytest.mark.parametrize("rds_off,errors", [(0.0, False), (-3.0, True), (2.0, False)])
+def test_wfm_stereo_rds_branch_vs_compiled_reference(rds_off, errors):
+    """SURVEY 8f-4, the RDS branch of Demod_WFM::processDataStereo (demod_wfm.cpp:298-357, 489-573) and the group queue behind it
+    (:584-788), against the class compiled from the reference, on a synthetic broadcast: standard RDS shaping on a 57 kHz
+    subcarrier inside an FM stereo multiplex (tests/rds_signal.py), 2048-sample calls, groups polled after every call.
+
+    Compared per call: the groups handed out (exactly), and m_RdsRaw as the reference leaves it — matched-filter output and the
+    value picked at each sampling instant, so also WHERE the bit slicer sampled. Subcarrier exactly at 57 kHz or 3 Hz low: the
+    reference's RDS PLL de-rotates it and every transmitted group comes out (with error bursts inside blocks: corrected by the
+    (26,16) code). 2 Hz high: its arctan2 (:792-818) keeps that loop from locking, ~3 % of the bits are wrong and no group
+    passes — the same on both sides."""
+    import pebblesdr_b200 as pb
+    from oracle import ref_app
+    from rds_signal import GROUPS, stream_bits, fm_broadcast, BITRATE
+    rate, frame, frames = 247000, 2048, 330                       # 247000 = 208 samples per bit; 2.7 s
+    n = frame * frames
+    bits = stream_bits(GROUPS, int(n / rate * BITRATE) + 208).copy()
+    if errors:
+        for grp in range(8, 30, 2):                               # bursts of 1..4 wrong bits inside single blocks
+            p = 104 * grp + 26 * (grp % 4) + 3
+            bits[p:p + 1 + grp % 4] ^= 1
+    x = fm_broadcast(bits, rate, n, rds_off=rds_off)
+    r = ref_app.Demod_WFM(rate, frame)
+    g = pb.Demod(rate, frame)
+    g.setDemodMode(pb.Demod.dmFMS)
+    assert g.getRdsRate() == r.rdsRate() == 30875.0
+    per = frame // 8
+    want_groups, got_groups, want_tap, got_tap, want_audio, got_audio = [], [], [], [], [], []
+    for i in range(0, n, frame):
+        want_audio.append(r.processDataStereo(x[i:i + frame].copy()))
+        got_audio.append(g.processBlock(np.ascontiguousarray(x[i:i + frame]), frame).copy())
+        want_tap.append(r.rdsTap(per)); got_tap.append(g.getRdsTap(per))
+        for obj, dst in ((r, want_groups), (g, got_groups)):
+            while True:
+                grp = obj.getNextRdsGroupData()
+                if grp is None:
+                    break
+                dst.append((i // frame, grp))
+    want_tap, got_tap = np.concatenate(want_tap), np.concatenate(got_tap)
+    assert len(got_tap) == len(want_tap) == per * frames
+    assert rel_rms(np.concatenate(got_audio), np.concatenate(want_audio)) <= 1e-9
+    err = rel_rms(got_tap.imag, want_tap.imag)
+    print("rds matched-filter output rel-RMS vs reference: %.3e; groups %d" % (err, len(want_groups)))
+    assert err <= 1e-6, err
+    assert np.array_equal(got_tap.real != 0, want_tap.real != 0)          # the same sampling instants
+    assert rel_rms(got_tap.real, want_tap.real) <= 1e-6
+    assert got_groups == want_groups
+    if rds_off <= 0.0:
+        assert len(want_groups) >= 20
+        sent = [GROUPS[k % 4] for k in range(40)]
+        first = sent.index(want_groups[0][1])
+        assert [grp for _, grp in want_groups] == sent[first:first + len(want_groups)]   # and they are the groups that were sent
+    else:
+        assert want_groups == []
+
+
+def test_wfm_stereo_rds_off_and_call_size_rule():
+    """RDS on: a dmFMS call must be a multiple of the RDS down-converter's decimation (the reference's CDownConvert has the same
+    rule, downconvert.cpp:257-334); pebble_demod_set_rds(h, 0) runs the audio path alone for any size."""
+    import pebblesdr_b200 as pb
+    rate = 247000
+    x = iq_noise_tones(2052, 77, rate, [(20e3, 0.4)], 0.01)
+    g = pb.Demod(rate, 4096)
+    g.setDemodMode(pb.Demod.dmFMS)
+    with pytest.raises(pb.PebbleError, match="multiple"):
+        g.processBlock(np.ascontiguousarray(x[:2052]), 2052)
+    g.setRds(False)
+    y = g.processBlock(np.ascontiguousarray(x[:2052]), 2052)
+    assert len(y) == 2052 and g.getNextRdsGroupData() is None
