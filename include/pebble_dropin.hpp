@@ -323,17 +323,35 @@ private:
 struct DeviceInterface {   // the one enum of pebblelib/device_interfaces.h:124-137 the demodulator needs
     enum DemodMode { dmAM, dmSAM, dmFMN, dmFMM, dmFMS, dmDSB, dmLSB, dmUSB, dmCWL, dmCWU, dmDIGL, dmDIGU, dmNONE };
 };
+struct tRDS_GROUPS { quint16 BlockA, BlockB, BlockC, BlockD; };   // application/demod/rbdsconstants.h:100-106
 class Demod : public ProcessStep {
 public:
     Demod(quint32 _sampleRate, quint32 _bufferSize)
         : ProcessStep(_sampleRate, _bufferSize), h(pebble_demod_create(_sampleRate, _bufferSize)), m_mode(DeviceInterface::dmAM) {}
-    Demod(quint32 _sampleRate, quint32 /*_wfmSampleRate*/, quint32 _bufferSize)
-        : ProcessStep(_sampleRate, _bufferSize), h(pebble_demod_create(_sampleRate, _bufferSize)), m_mode(DeviceInterface::dmAM) {}
+    // demod.cpp:50-66: the WFM demodulator runs at its own (wider) input rate
+    Demod(quint32 _sampleRate, quint32 _wfmSampleRate, quint32 _bufferSize)
+        : ProcessStep(_sampleRate, _bufferSize), h(pebble_demod_create(_sampleRate, _bufferSize)), m_mode(DeviceInterface::dmAM) {
+        pebble_demod_set_wfm_sample_rate(h, (double)_wfmSampleRate);
+    }
     ~Demod() { pebble_demod_destroy(h); }
     void setDemodMode(DeviceInterface::DemodMode _mode, int /*_sourceSampleRate*/, int /*_audioSampleRate*/) {
         if (pebble_demod_set_mode(h, (int)_mode) == 0) m_mode = _mode;
     }
     DeviceInterface::DemodMode demodMode() const { return m_mode; }
+    // what Demod::fmStereo reads from its Demod_WFM after every block (demod.cpp:196-219, demod_wfm.cpp:436-448, 764-788)
+    int getStereoLock(int *pPilotLock) {
+        const int now = pebble_demod_get_stereo_lock(h);
+        const int changed = now != m_lastLock;
+        m_lastLock = now;
+        if (pPilotLock) *pPilotLock = now > 0;
+        return changed;
+    }
+    int getNextRdsGroupData(tRDS_GROUPS *pGroupData) {
+        unsigned short b[4];
+        if (!pGroupData || pebble_demod_get_next_rds_group(h, b) != 1) return 0;
+        pGroupData->BlockA = b[0]; pGroupData->BlockB = b[1]; pGroupData->BlockC = b[2]; pGroupData->BlockD = b[3];
+        return 1;
+    }
     void setBandwidth(double bandwidth) { if (m_mode == DeviceInterface::dmAM) pebble_demod_set_bandwidth(h, bandwidth); }   // demod.cpp:230-240
     CPX *processBlock(CPX *in, int bufSize) {
         if (pebble_demod_is_passthrough(h) == 1) return in;                // USB/LSB/DSB/CW/DIG: `return in` (demod.cpp:127-138)
@@ -343,6 +361,7 @@ public:
 private:
     pebble_demod_t *h;
     DeviceInterface::DemodMode m_mode;
+    int m_lastLock = -1;
 };
 
 // ---- CFractResampler — pebblelib/fractresampler.h:20-40 ------------------------------------------------------------------------------
