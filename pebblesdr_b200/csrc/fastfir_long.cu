@@ -28,6 +28,9 @@
 namespace {
 constexpr int LF_N2 = 2048;
 // columns per CTA of the column kernels: 16 x 16 B = 256 B contiguous per row (8 for the radix-16 plan: 32 KB of shared memory)
+#ifndef LF_DISCARD
+#define LF_DISCARD 1
+#endif
 template <int R> struct LfTc { static constexpr int v = R == 16 ? 8 : 16; };
 
 __device__ __forceinline__ cpx lf_ld_stream(const cpx *p) {
@@ -115,6 +118,13 @@ __device__ __forceinline__ void lf_cols_tile(cpx *a, const cpx *w, const cpx *__
 #pragma unroll
         for (int q = 0; q < R; ++q) a[(R * i + q) * LF_TC + c] = v[q];
         __syncthreads();
+        // The scratch of this tile has been read for the last time (every thread's loads were consumed above): tell L2 the
+        // lines are dead, so that they are dropped instead of written back to DRAM when the output stream pushes them out.
+        // One 128-byte line = 8 columns of one row; the next forward pass rewrites whole lines before anything reads them.
+        if (LF_DISCARD && (c & 7) == 0) {
+#pragma unroll
+            for (int k = 0; k < R; ++k) asm volatile("discard.global.L2 [%0], 128;" ::"l"(sc + (size_t)(i + R * k) * LF_N2) : "memory");
+        }
 #pragma unroll
         for (int q = 0; q < R; ++q) {
             v[q] = a[(i + R * q) * LF_TC + c];
