@@ -453,12 +453,19 @@ int pebble_noiseblanker_enabled(const pebble_noiseblanker_t *h, int which);
 int pebble_noiseblanker_process(pebble_noiseblanker_t *h, int which, int n, const double *in, double *out);
 int pebble_noiseblanker_process_device(pebble_noiseblanker_t *h, int which, int n, const double *d_in, double *d_out, void *stream);
 
-/* ---- Receiver chain : the non-WFM branch of Receiver::processIQData ------------------------------------
- * Replaces application/receiver.cpp:903-996: m_downConvert1.ProcessData -> m_sampleBuf re-framing to
+/* ---- Receiver chain : Receiver::processIQData, both branches ---------------------------------------------
+ * Non-WFM (application/receiver.cpp:903-996): m_downConvert1.ProcessData -> m_sampleBuf re-framing to
  * framesPerBuffer (:922-931) -> scaleCPX gain restore (:935-938) -> m_bpFilter->process (:950) ->
  * m_agc->processBlock (:983) -> m_demod->processBlock (:987). Returns the number of demodulated samples
  * written (a multiple of framesPerBuffer; 0 while a frame is still filling). SignalSpectrum, squelch,
- * noise filter, modem plugins and the audio resampler are not part of this entry point. */
+ * noise filter and modem plugins are separate entry points.
+ * WFM (demod mode dmFMM / dmFMS, receiver.cpp:854-901): m_downConvertWfm1 (SetDataRateSimple(sampleRate, 200000), :217:
+ * 51-tap stages until the rate is below 400 kS/s; pebble_receiver_get_wfm_rate) -> re-framing -> m_demod->processBlock
+ * (Demod::fmMono / fmStereo at the WFM rate, one call per frame) — no band-pass, gain restore or AGC on this branch —
+ * and, with pebble_receiver_set_audio, the resampler at wfmRate / audioRate (:901). Switching between the branches drops the
+ * partial frame (they decimate to different rates). pebble_receiver_demod() is the receiver's own demodulator, for
+ * pebble_demod_get_stereo_lock / pebble_demod_get_next_rds_group after a call (demod.cpp:196-219); it stays owned by the receiver
+ * and is replaced by pebble_receiver_set_data_rate. */
 typedef struct pebble_receiver pebble_receiver_t;
 pebble_receiver_t *pebble_receiver_create(double sample_rate, int frames_per_buffer);
 void pebble_receiver_destroy(pebble_receiver_t *h);
@@ -475,6 +482,8 @@ int pebble_receiver_set_input_format(pebble_receiver_t *h, int fmt, int order, d
  * with clip != 0, the audio sink's +-0.9999 clip (AudioQT::SendToOutput, pebblelib/audioqt.cpp:190-201). The process calls
  * then return AUDIO samples (a data-independent count, pebble_receiver_out_count). audio_rate <= 0 switches it off. */
 int pebble_receiver_set_audio(pebble_receiver_t *h, int audio_rate, int clip);
+double pebble_receiver_get_wfm_rate(const pebble_receiver_t *h);
+pebble_demod_t *pebble_receiver_demod(pebble_receiver_t *h);
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n);
 /* Library extension (the reference's Perform timer call sites, receiver.cpp:788,805,827, are commented out):
  * per-step DEVICE time via CUDA events recorded on the caller's stream. get_profile sums the calls made since

@@ -223,6 +223,8 @@ SIGNATURES = {
     "pebble_receiver_set_gain_stages": (c_int, [c_vp, c_int]),
     "pebble_receiver_out_count": (c_int, [c_vp, c_int]),
     "pebble_receiver_set_audio": (c_int, [c_vp, c_int, c_int]),
+    "pebble_receiver_get_wfm_rate": (c_dbl, [c_vp]),
+    "pebble_receiver_demod": (c_vp, [c_vp]),
     "pebble_receiver_set_profiling": (c_int, [c_vp, c_int]),
     "pebble_receiver_get_profile": (c_int, [c_vp, c_vp, c_vp]),
     "pebble_receiver_process": (c_int, [c_vp, c_int, c_vp, c_vp]),

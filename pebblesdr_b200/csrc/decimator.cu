@@ -388,7 +388,7 @@ int pebble_decimator_process_device(pebble_decimator_t *h, int n, const double *
     if (dec_make_plan(h, n) != 0) return PEBBLE_ERR_STATE;
     const DecPlan &p = h->plan;
     if (h->smem > 48 * 1024)
-        PB_CUDA(cudaFuncSetAttribute(dec_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem), PEBBLE_ERR_CUDA);
+        PB_CUDA(pebble::ensure_dynamic_smem((const void *)dec_chain_kernel, h->smem), PEBBLE_ERR_CUDA);
     const int tiles = (n_out + p.To - 1) / p.To;
     const int vec = (((uintptr_t)d_in) & 31) == 0;
     dec_chain_kernel<<<tiles, PB_DEC_THREADS, h->smem, stream>>>(p, (const cpx *)d_in, h->d_hist[h->cur], (cpx *)d_out, n_out, vec);

@@ -419,6 +419,7 @@ void *demod_am_expect_tiles(pebble_demod *h, int n, double *alpha) {
 }
 
 void demod_am_cancel_tiles(pebble_demod *h) { h->am_pre_tiles = false; }
+int demod_mode(const pebble_demod *h) { return h->mode; }
 
 int demod_run_device(pebble_demod *h, int n, const cpx *d_in, cpx *d_out, cudaStream_t st, int *passthrough, int frame) {
     if (passthrough) *passthrough = 0;

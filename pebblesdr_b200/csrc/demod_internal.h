@@ -32,6 +32,7 @@ void *demod_am_expect_tiles(pebble_demod *h, int n, double *alpha);
 struct pebble_fastfir;
 int fastfir_am_aggregate_next(pebble_fastfir *h, void *tile_map, double alpha, int n);
 void demod_am_cancel_tiles(pebble_demod *h);
+int demod_mode(const pebble_demod *h);
 double agc_manual_gain(const pebble_agc *h);
 int agc_is_off(const pebble_agc *h);
 

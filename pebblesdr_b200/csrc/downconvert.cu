@@ -466,7 +466,7 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const void
         int threads = PB_DC_THREADS;
         if (const void *pf = dc_pick_pipe(C, h->chain, &smem_pipe, &threads, fused_fmt)) { fn = pf; smem = smem_pipe; }
         if (smem > h->smem_set || fn != h->fn_set) {
-            PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
+            PB_CUDA(pebble::ensure_dynamic_smem(fn, smem), PEBBLE_ERR_CUDA);
             h->smem_set = smem;
             h->fn_set = fn;
         }
@@ -645,7 +645,7 @@ int pebble_downconvert_process_channels_device(pebble_downconvert_t *h, int n, c
     call.w1 = call.wchunk = cpx_make(0.0, 0.0); call.r_inf = 0.0; call.turn_hi = call.turn_lo = 0;   // per channel: DcChan
     const size_t smem = (size_t)(dc_smem_cpx(h->chain, C, front, call.group) - 2 * dc_stage_arr(h->chain.st[0], C)) * sizeof(cpx);
     if (smem > h->smem_set || fn != h->fn_set) {
-        PB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), PEBBLE_ERR_CUDA);
+        PB_CUDA(pebble::ensure_dynamic_smem(fn, smem), PEBBLE_ERR_CUDA);
         h->smem_set = smem;
         h->fn_set = fn;
     }

@@ -1,5 +1,8 @@
 #include "lib_common.h"
 #include <atomic>
+#include <map>
+#include <mutex>
+#include <utility>
 #include <cstdarg>
 #include <cstdio>
 
@@ -30,6 +33,19 @@ int num_sms() {
         sms[dev].store(v, std::memory_order_relaxed);
     }
     return v;
+}
+cudaError_t ensure_dynamic_smem(const void *fn, size_t bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void *>, size_t> limit;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(mu);
+    size_t &cur = limit[std::make_pair(dev, fn)];
+    if (bytes <= cur) return cudaSuccess;
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) cur = bytes;
+    return e;
 }
 bool Staging::reserve(size_t bi, size_t bo) {
     if (bi > cap_in) {

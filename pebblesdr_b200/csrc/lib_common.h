@@ -12,6 +12,9 @@ void set_error(const char *fmt, ...);
 bool cuda_ok(cudaError_t e, const char *what);   // records the error text when e != cudaSuccess
 void count_launch(int n = 1);
 int num_sms();
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the FUNCTION (per device), not to a handle: two handles that launch
+// the same kernel with different sizes must never lower each other's limit. Raises it to at least `bytes`, never lowers.
+cudaError_t ensure_dynamic_smem(const void *fn, size_t bytes);
 
 // Grow-only pinned host + device scratch used by the host-pointer (compat) entry points.
 struct Staging {

@@ -18,6 +18,12 @@ struct pebble_receiver {
     double sample_rate = 0, demod_rate = 0;
     int fpb = 2048;                // framesPerBuffer (settings.cpp:57)
     pebble_downconvert_t *dc = nullptr;
+    // the WFM branch of processIQData (receiver.cpp:854-901): its own down-converter to < 400 kS/s (SetDataRateSimple, :217),
+    // then straight to the demodulator — no band-pass, no gain restore, no AGC — and the resampler at wfmRate / audioRate
+    pebble_downconvert_t *dc_wfm = nullptr;
+    double wfm_rate = 0;
+    int audio_rate = 0;
+    bool was_wfm = false;
     pebble_fastfir_t *bp = nullptr;
     pebble_agc *agc = nullptr;
     pebble_demod *demod = nullptr;
@@ -88,8 +94,9 @@ pebble_receiver_t *pebble_receiver_create(double sample_rate, int frames_per_buf
     pebble_receiver *h = new pebble_receiver();
     h->sample_rate = sample_rate; h->fpb = frames_per_buffer;
     h->dc = pebble_downconvert_create();
+    h->dc_wfm = pebble_downconvert_create();
     h->bp = pebble_fastfir_create();
-    if (!h->dc || !h->bp || !pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) {
+    if (!h->dc || !h->dc_wfm || !h->bp || !pebble::cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) {
         pebble_receiver_destroy(h);
         return nullptr;
     }
@@ -99,6 +106,7 @@ pebble_receiver_t *pebble_receiver_create(double sample_rate, int frames_per_buf
 void pebble_receiver_destroy(pebble_receiver_t *h) {
     if (!h) return;
     if (h->dc) pebble_downconvert_destroy(h->dc);
+    if (h->dc_wfm) pebble_downconvert_destroy(h->dc_wfm);
     if (h->bp) pebble_fastfir_destroy(h->bp);
     if (h->agc) pebble_agc_destroy(h->agc);
     if (h->demod) pebble_demod_destroy(h->demod);
@@ -121,9 +129,20 @@ double pebble_receiver_set_data_rate(pebble_receiver_t *h, double max_bw) {
     h->agc = pebble_agc_create((unsigned)h->demod_rate, (unsigned)h->fpb);
     h->demod = pebble_demod_create((unsigned)h->demod_rate, (unsigned)h->fpb);
     h->fill = 0;
+    // receiver.cpp:217,228: m_demodWfmSampleRate = m_downConvertWfm1.SetDataRateSimple(sampleRate, 200000) (an int there);
+    // Demod(demodSampleRate, demodWfmSampleRate, framesPerBuffer)
+    h->wfm_rate = (double)(int)pebble_downconvert_set_data_rate_simple(h->dc_wfm, h->sample_rate, 200000.0);
+    if (h->demod && h->wfm_rate > 0) pebble_demod_set_wfm_sample_rate(h->demod, h->wfm_rate);
+    if (h->audio_rate > 0) pebble_receiver_set_audio(h, h->audio_rate, h->audio_clip);
     return (h->agc && h->demod) ? h->demod_rate : 0.0;
 }
-void pebble_receiver_set_mixer(pebble_receiver_t *h, double freq) { if (h) pebble_downconvert_set_frequency(h->dc, freq); }
+double pebble_receiver_get_wfm_rate(const pebble_receiver_t *h) { return h ? h->wfm_rate : 0.0; }
+pebble_demod_t *pebble_receiver_demod(pebble_receiver_t *h) { return h ? h->demod : nullptr; }
+void pebble_receiver_set_mixer(pebble_receiver_t *h, double freq) {   // receiver.cpp:716-719: both down-converters follow the mixer
+    if (!h) return;
+    pebble_downconvert_set_frequency(h->dc, freq);
+    pebble_downconvert_set_frequency(h->dc_wfm, freq);
+}
 int pebble_receiver_set_filter(pebble_receiver_t *h, double lo, double hi) {  // BandPassFilter::setBandPass, bandpassfilter.cpp:35-45
     if (!h) return PEBBLE_ERR_ARG;
     return pebble_fastfir_setup(h->bp, lo, hi, 0, h->demod_rate);
@@ -144,7 +163,8 @@ int pebble_receiver_set_agc(pebble_receiver_t *h, int mode, int threshold) {
 // conversion runs inside the down-converter's load stage, so `in` of the process calls holds raw device samples.
 int pebble_receiver_set_input_format(pebble_receiver_t *h, int fmt, int order, double user_gain, double norm_gain) {
     if (!h) return PEBBLE_ERR_ARG;
-    return pebble_downconvert_set_input_format(h->dc, fmt, order, user_gain, norm_gain);
+    const int r = pebble_downconvert_set_input_format(h->dc, fmt, order, user_gain, norm_gain);
+    return r < 0 ? r : pebble_downconvert_set_input_format(h->dc_wfm, fmt, order, user_gain, norm_gain);
 }
 int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages) {
     if (!h) return PEBBLE_ERR_ARG;
@@ -158,9 +178,10 @@ int pebble_receiver_set_gain_stages(pebble_receiver_t *h, int stages) {
 // m_demodSampleRate.
 int pebble_receiver_set_audio(pebble_receiver_t *h, int audio_rate, int clip) {
     if (!h) return PEBBLE_ERR_ARG;
-    if (audio_rate <= 0) { h->audio_on = false; return 0; }
+    if (audio_rate <= 0) { h->audio_on = false; h->audio_rate = 0; return 0; }
     if (!h->rs) h->rs = pebble_resampler_create(h->fpb);
     if (!h->rs) return PEBBLE_ERR_CUDA;
+    h->audio_rate = audio_rate;
     h->resamp_rate = ((int)h->demod_rate * 1.0) / (audio_rate * 1.0);
     h->audio_on = true;
     h->audio_clip = clip != 0;
@@ -189,12 +210,62 @@ int pebble_receiver_get_profile(pebble_receiver_t *h, double *ms, int64_t *calls
     h->ev_used = 0;
     return 0;
 }
+static bool rx_wfm(const pebble_receiver *h) {   // receiver.cpp:854
+    const int m = h->demod ? demod_mode(h->demod) : -1;
+    return m == 3 || m == 4;
+}
+static double rx_resamp_rate(const pebble_receiver *h, bool wfm) {   // receiver.cpp:901 / :994
+    return wfm ? ((int)h->wfm_rate * 1.0) / (h->audio_rate * 1.0) : h->resamp_rate;
+}
 int pebble_receiver_out_count(const pebble_receiver_t *h, int n) {
     if (!h || n < 0) return PEBBLE_ERR_ARG;
-    const int S = pebble_downconvert_num_stages(h->dc);
-    const int nproc = (int)((((long long)h->fill + (n >> S)) / h->fpb) * h->fpb);
-    if (h->audio_on && h->resamp_rate != 1.0 && nproc > 0) return (int)resampler_peek_count(h->rs, nproc, h->fpb, h->resamp_rate);
+    const bool wfm = rx_wfm(h);
+    const int S = pebble_downconvert_num_stages(wfm ? h->dc_wfm : h->dc);
+    const int fill = wfm == h->was_wfm ? h->fill : 0;
+    const int nproc = (int)((((long long)fill + (n >> S)) / h->fpb) * h->fpb);
+    const double rr = rx_resamp_rate(h, wfm);
+    if (h->audio_on && rr != 1.0 && nproc > 0) return (int)resampler_peek_count(h->rs, nproc, h->fpb, rr);
     return nproc;
+}
+
+// The WFM branch (receiver.cpp:854-901 + the common tail :994-1007): m_downConvertWfm1 -> full frames -> Demod (fmMono /
+// fmStereo, one call per frame: the pilot lock decision and the loops' phase wrap are per call) -> resampler.
+static int rx_process_wfm(pebble_receiver *h, int n, const void *d_in, double *d_out, cudaStream_t st) {
+    const int S = pebble_downconvert_num_stages(h->dc_wfm);
+    const int ndec = n >> S;
+    int r = rx_reserve(h, (size_t)h->fill + (size_t)ndec);
+    if (r < 0) return r;
+    r = pebble_downconvert_process_device(h->dc_wfm, n, d_in, (double *)(h->d_frames + h->fill), st);
+    if (r < 0) return r;
+    const int total = h->fill + ndec, nframes = total / h->fpb, nproc = nframes * h->fpb;
+    if (nframes == 0) { h->fill = total; return 0; }
+    if (!d_out) { pebble::set_error("receiver: NULL output"); return PEBBLE_ERR_ARG; }
+    const double rr = rx_resamp_rate(h, true);
+    const bool resample = h->audio_on && rr != 1.0;
+    cpx *demod_out = (cpx *)d_out;
+    if (resample) {
+        if ((size_t)nproc > h->demod_cap) {
+            PB_CUDA(cudaDeviceSynchronize(), PEBBLE_ERR_CUDA);
+            cudaFree(h->d_demod); h->d_demod = nullptr; h->demod_cap = 0;
+            PB_CUDA(cudaMalloc(&h->d_demod, sizeof(cpx) * (size_t)nproc), PEBBLE_ERR_CUDA);
+            h->demod_cap = (size_t)nproc;
+        }
+        demod_out = h->d_demod;
+    }
+    for (int f = 0; f < nframes; ++f) {
+        r = demod_run_device(h->demod, h->fpb, h->d_frames + (size_t)f * h->fpb, demod_out + (size_t)f * h->fpb, st, nullptr, 0);
+        if (r < 0) return r;
+    }
+    int produced = nproc;
+    if (resample) {
+        produced = resampler_run_device(h->rs, nproc, h->fpb, rr, h->d_demod, (cpx *)d_out, h->audio_clip, st);
+        if (produced < 0) return produced;
+    }
+    const int rem = total - nproc;
+    if (rem > 0)
+        PB_CUDA(cudaMemcpyAsync(h->d_frames, h->d_frames + nproc, sizeof(cpx) * (size_t)rem, cudaMemcpyDeviceToDevice, st), PEBBLE_ERR_CUDA);
+    h->fill = rem;
+    return produced;
 }
 
 int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in, double *d_out, void *stream_v) {
@@ -202,6 +273,9 @@ int pebble_receiver_process_device(pebble_receiver_t *h, int n, const void *d_in
     if (!h->agc || !h->demod) { pebble::set_error("receiver: set_data_rate not called"); return PEBBLE_ERR_STATE; }
     if (n == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream_v;
+    const bool wfm = rx_wfm(h);
+    if (wfm != h->was_wfm) { h->fill = 0; h->was_wfm = wfm; }   // the two branches decimate to different rates: the partial frame is dropped
+    if (wfm) return rx_process_wfm(h, n, d_in, d_out, st);
     const int S = pebble_downconvert_num_stages(h->dc);
     const int ndec = n >> S;
     int r = rx_reserve(h, (size_t)h->fill + (size_t)ndec);

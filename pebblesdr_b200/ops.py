@@ -757,6 +757,18 @@ class Receiver(_Handle):
     def outCount(self, n):
         return check(lib.pebble_receiver_out_count(self._h, n))
 
+    def wfmRate(self):
+        """m_demodWfmSampleRate (receiver.cpp:217): the rate the WFM branch demodulates at."""
+        return float(lib.pebble_receiver_get_wfm_rate(self._h))
+
+    def getStereoLock(self):
+        """What Demod::fmStereo reads after every block (demod.cpp:201-205)."""
+        return bool(check(lib.pebble_demod_get_stereo_lock(lib.pebble_receiver_demod(self._h)), "getStereoLock"))
+
+    def getNextRdsGroupData(self):
+        b = (ctypes.c_ushort * 4)()
+        return tuple(b) if lib.pebble_demod_get_next_rds_group(lib.pebble_receiver_demod(self._h), b) == 1 else None
+
     def setProfiling(self, on):
         check(lib.pebble_receiver_set_profiling(self._h, int(bool(on))))
 

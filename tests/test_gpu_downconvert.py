@@ -179,6 +179,29 @@ def test_every_generic_halfband_length_runs_on_the_gpu(rate, bw, simple, expect)
     assert rel_rms(yg, yr) <= TOL
 
 
+def test_two_handles_sharing_a_kernel_do_not_lower_each_others_shared_memory_limit():
+    """The dynamic shared-memory limit is an attribute of the kernel, not of a handle: a 3 x 51-tap chain (large stage arrays)
+    and a one-stage chain run the same generic kernel with different sizes, interleaved. Regression for a launch failure
+    ("invalid argument") once the smaller handle had set the limit after the larger one."""
+    import pebblesdr_b200 as pb
+    from oracle import ref
+    big, small = pb.CDownConvert(), pb.CDownConvert()
+    rb, rs = ref.CDownConvert(), ref.CDownConvert()
+    assert big.SetDataRateSimple(2e6, 15000.0) == rb.SetDataRateSimple(2e6, 15000.0)
+    assert small.SetDataRate(250000.0, 30000.0) == rs.SetDataRate(250000.0, 30000.0)
+    for o in (big, rb):
+        o.SetFrequency(2e5)
+    for o in (small, rs):
+        o.SetFrequency(3e4)
+    xb = iq_noise_tones(4096 * 6, 35, 2e6, [(2.01e5, 0.4)], noise=0.05)
+    xs = iq_noise_tones(4096 * 6, 36, 250000.0, [(3.05e4, 0.4)], noise=0.05)
+    yb, ys = [], []
+    for i in range(0, 4096 * 6, 4096):                       # big, small, big, small, ...
+        yb.append(_feed(big, xb[i:i + 4096], [4096], 3)); ys.append(_feed(small, xs[i:i + 4096], [4096], 1))
+    assert rel_rms(np.concatenate(yb), _feed(rb, xb, [4096] * 6, 3)) <= TOL
+    assert rel_rms(np.concatenate(ys), _feed(rs, xs, [4096] * 6, 1)) <= TOL
+
+
 def test_short_call_rule_documented_deviation_and_strict_mode():
     """downconvert.cpp:362-363: a generic half-band stage that receives fewer samples than it has taps returns n/2 WITHOUT
     filtering (the caller's buffer is left as it is, so the 'output' is the stage's leading input samples); and with fewer

@@ -122,3 +122,61 @@ def test_receiver_chain_iq_in_audio_out():
 
 def rx_count_check(k):
     return k
+
+
+@pytest.mark.parametrize("mode", ["dmFMS", "dmFMM"])
+def test_receiver_wfm_branch_iq_in_audio_out(mode):
+    """The WFM branch of Receiver::processIQData (receiver.cpp:854-901 + the tail :994-1007): m_downConvertWfm1
+    (SetDataRateSimple(2 MSPS, 200000) -> 250 kS/s) -> 2048-sample frames -> Demod::fmStereo / fmMono at the WFM rate, one call
+    per frame -> Resample(frame, 250000/48000) -> the sink's clip. Reference = the same steps compiled from the reference
+    (CDownConvert, Demod_WFM, CFractResampler), composed in that order. Input: an FM stereo broadcast 300 kHz off centre at
+    2 MSPS; calls cut across frames; a switch to AM and back in the middle restarts the frame on both sides."""
+    import torch
+    import pebblesdr_b200 as pb
+    from oracle import ref, ref_app
+    fs, fpb, off = 2000000.0, 2048, 300000.0
+    n = 16384 * 40
+    t = np.arange(n) / fs
+    left, right = 0.5 * np.sin(2 * np.pi * 1000.0 * t), 0.3 * np.sin(2 * np.pi * 2500.0 * t)
+    pil = 2 * np.pi * 19010.0 * t
+    m = 0.4 * (left + right) + 0.1 * np.sin(pil) + 0.4 * (left - right) * np.sin(2 * pil)
+    ph = 2 * np.pi * np.cumsum(75000.0 * m) / fs
+    rng = np.random.default_rng(3)
+    x = np.ascontiguousarray(0.4 * np.exp(1j * (ph + 2 * np.pi * off * t)) + (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.002)
+
+    rx = pb.Receiver(fs, fpb)
+    rx.setDataRate(15000.0)
+    assert rx.wfmRate() == 250000.0
+    rx.setMixer(-off); rx.setFilter(-5000.0, 5000.0); rx.setAgc(0, 20)
+    rx.setDemodMode(getattr(pb.Demod, mode))
+    rx.setAudio(48000, clip=True)
+    outs, locks, pos = [], [], 0
+    for c in (16384 * 9, 16384 * 2, 16384 * 29):
+        k, y = rx.processIQData(torch.from_numpy(x[pos:pos + c]).cuda(), c)
+        outs.append(y[:k].cpu().numpy()); pos += c
+        locks.append(rx.getStereoLock())
+    got = np.concatenate(outs)
+
+    dc = ref.CDownConvert()
+    assert dc.SetDataRateSimple(fs, 200000.0) == 250000.0
+    dc.SetFrequency(-off)
+    dem = ref_app.Demod_WFM(250000, fpb)
+    rs = ref_app.CFractResampler(fpb)
+    y = np.zeros(n // 8, dtype=np.complex128)
+    for i in range(0, n, 16384):                      # the reference's own call size is irrelevant once >= 2 (taps - 1) per stage
+        k = dc.ProcessData(16384, x[i:i + 16384], y[i // 8:])
+        assert k == 2048
+    rate = (250000 * 1.0) / (48000 * 1.0)
+    want, lock = [], 0
+    for i in range(0, len(y) - fpb + 1, fpb):
+        a = dem.processDataStereo(y[i:i + fpb].copy()) if mode == "dmFMS" else dem.processDataMono(y[i:i + fpb].copy())
+        want.append(rs.Resample(a, rate))
+        lock = dem.getStereoLock()[1]
+    want = np.concatenate(want)
+    mx = float(np.float32(0.9999))
+    want = np.clip(want.real, -mx, mx) + 1j * np.clip(want.imag, -mx, mx)
+    assert len(got) == len(want) > 15000
+    assert rel_rms(got, want) <= 1e-9, rel_rms(got, want)
+    if mode == "dmFMS":
+        assert locks[-1] == bool(lock)                                        # the pilot lock state the GUI would read
+
