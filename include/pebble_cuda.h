@@ -81,6 +81,7 @@ pebble_fastfir_t *pebble_fastfir_create_sized(int fft_size, int fir_size);
 void pebble_fastfir_destroy(pebble_fastfir_t *h);
 int pebble_fastfir_setup(pebble_fastfir_t *h, double f_lo, double f_hi, double offset, double sample_rate);
 int pebble_fastfir_process(pebble_fastfir_t *h, int n, const double *in, double *out);
+/* d_in and d_out must not overlap (PEBBLE_ERR_ARG): blocks are filtered concurrently. The host-pointer call may be in place. */
 int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in, double *d_out, void *stream);
 /* Output count a process call with n inputs WOULD return, without running it. */
 int pebble_fastfir_out_count(const pebble_fastfir_t *h, int n);
@@ -137,6 +138,7 @@ int pebble_downconvert_stage_lengths(const pebble_downconvert_t *h, int *lens, i
 int pebble_downconvert_set_input_format(pebble_downconvert_t *h, int fmt, int order, double user_gain, double norm_gain);
 int pebble_downconvert_input_bytes_per_sample(const pebble_downconvert_t *h);
 int pebble_downconvert_process(pebble_downconvert_t *h, int n, const void *in, double *out);
+/* d_in and d_out must not overlap (PEBBLE_ERR_ARG; the same holds for pebble_decimator_process_device). */
 int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const void *d_in, double *d_out,
                                       void *stream);
 int64_t pebble_downconvert_state_size(const pebble_downconvert_t *h);

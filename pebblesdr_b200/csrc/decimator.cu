@@ -377,6 +377,10 @@ int pebble_decimator_process_device(pebble_decimator_t *h, int n, const double *
         return n;
     }
     const int n_out = pebble_decimator_out_count(h, n);
+    if (n_out > 0 && pebble::ranges_overlap(d_in, sizeof(cpx) * (size_t)n, d_out, sizeof(cpx) * (size_t)n_out)) {
+        pebble::set_error("decimator: d_in and d_out overlap (in-place device calls are not supported)");
+        return PEBBLE_ERR_ARG;
+    }
     if (n_out < 0) {
         // The reference degrades here: a stage that sees fewer samples than taps plain-decimates and refills its delay
         // line from beyond the valid input (decimator.cpp:605-626), and a call that is not a multiple of the total

@@ -383,6 +383,12 @@ int pebble_downconvert_process_device(pebble_downconvert_t *h, int n, const void
     if (n == 0) return 0;
     cudaStream_t stream = (cudaStream_t)stream_v;
     const int S = h->chain.nstages;
+    // the reference decimates in place (downconvert.cpp:309-325); a grid cannot: segments are read while others are written
+    if (pebble::ranges_overlap(d_in_v, (size_t)pebble_downconvert_input_bytes_per_sample(h) * (size_t)n, d_out,
+                               sizeof(cpx) * (size_t)((n >> S) > 0 ? (n >> S) : 1))) {
+        pebble::set_error("downconvert: d_in and d_out overlap (in-place device calls are not supported)");
+        return PEBBLE_ERR_ARG;
+    }
     if (h->strict_lengths) {
         // the reference's per-stage preconditions: a generic half-band filters only for InLength >= taps (downconvert.cpp:
         // 362-363) and, run in place as CDownConvert runs it (:325), keeps a correct history only for InLength >= 2*(taps-1)

@@ -507,6 +507,9 @@ int pebble_fastfir_set_streams(pebble_fastfir_t *h, int streams) {
     return 0;
 }
 
+// The kernels read a block's input (and its L-sample overlap) while other CTAs / lanes write other blocks' outputs: the
+// input and output of a device call must not overlap (the reference's caller, BandPassFilter::process, never aliases them
+// either: bandpassfilter.cpp:47-53 writes ProcessStep::out). Refused with a clear error instead of racing.
 int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double *d_in, long long in_stride,
                                         double *d_out, long long out_stride, void *stream_v) {
     if (!h || n < 0 || (n && !d_in)) { pebble::set_error("fastfir: bad argument"); return PEBBLE_ERR_ARG; }
@@ -521,6 +524,11 @@ int pebble_fastfir_process_batch_device(pebble_fastfir_t *h, int n, const double
     const FfCarry carry = {h->d_state[h->cur ^ 1], vlen - count, count};
     if (nblocks > 0) {
         if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
+        if (pebble::ranges_overlap(d_in, sizeof(cpx) * ((size_t)(h->streams - 1) * (size_t)in_stride + (size_t)n), d_out,
+                              sizeof(cpx) * ((size_t)(h->streams - 1) * (size_t)out_stride + (size_t)nblocks * h->L))) {
+            pebble::set_error("fastfir: d_in and d_out overlap (in-place device calls are not supported)");
+            return PEBBLE_ERR_ARG;
+        }
         cudaError_t e = h->lf ? ff_launch_long(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, in_stride, out_stride) : FF_DISPATCH(h,
             ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride),
             ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, h->streams, in_stride, out_stride),
@@ -552,6 +560,10 @@ int pebble_fastfir_process_device(pebble_fastfir_t *h, int n, const double *d_in
     const FfCarry carry = {h->d_state[h->cur ^ 1], vlen - count, count};
     if (nblocks > 0) {
         if (!d_out) { pebble::set_error("fastfir: NULL output"); return PEBBLE_ERR_ARG; }
+        if (pebble::ranges_overlap(d_in, sizeof(cpx) * (size_t)n, d_out, sizeof(cpx) * (size_t)nblocks * h->L)) {
+            pebble::set_error("fastfir: d_in and d_out overlap (in-place device calls are not supported)");
+            return PEBBLE_ERR_ARG;
+        }
         cudaError_t e = h->lf ? ff_launch_long(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry, 0, 0) :
                         FF_DISPATCH(h, ff_launch_process<2048>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),
                                     ff_launch_process<4096>(h, (const cpx *)d_in, (cpx *)d_out, nblocks, st, carry),

@@ -2,6 +2,7 @@
 // accounting, pinned staging. No CPU compute fallback exists anywhere in this library: if CUDA is not
 // usable every entry point fails with PEBBLE_ERR_CUDA.
 #pragma once
+#include <cstdint>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
@@ -15,6 +16,11 @@ int num_sms();
 // cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the FUNCTION (per device), not to a handle: two handles that launch
 // the same kernel with different sizes must never lower each other's limit. Raises it to at least `bytes`, never lowers.
 cudaError_t ensure_dynamic_smem(const void *fn, size_t bytes);
+// Device entry points whose grids read the input while other CTAs already write the output refuse overlapping buffers.
+inline bool ranges_overlap(const void *a, size_t abytes, const void *b, size_t bbytes) {
+    const uintptr_t a0 = (uintptr_t)a, b0 = (uintptr_t)b;
+    return a0 < b0 + bbytes && b0 < a0 + abytes;
+}
 
 // Grow-only pinned host + device scratch used by the host-pointer (compat) entry points.
 struct Staging {

@@ -263,8 +263,8 @@ def test_wfm_stereo_audio_vs_compiled_reference(pilot_hz, pilot_phase, frames):
         assert 0 < sum(lw) < frames
 
 
-@pytest.mark.parametrize("rds_off,errors", [(0.0, False), (-3.0, True), (2.0, False)])
-def test_wfm_stereo_rds_branch_vs_compiled_reference(rds_off, errors):
+@pytest.mark.parametrize("rate,rds_off,errors", [(247000, 0.0, False), (247000, -3.0, True), (247000, 2.0, False), (313500, 0.0, True)])
+def test_wfm_stereo_rds_branch_vs_compiled_reference(rate, rds_off, errors):
     """SURVEY 8f-4, the RDS branch of Demod_WFM::processDataStereo (demod_wfm.cpp:298-357, 489-573) and the group queue behind it
     (:584-788), against the class compiled from the reference, on a synthetic broadcast: standard RDS shaping on a 57 kHz
     subcarrier inside an FM stereo multiplex (tests/rds_signal.py), 2048-sample calls, groups polled after every call.
@@ -277,7 +277,8 @@ def test_wfm_stereo_rds_branch_vs_compiled_reference(rds_off, errors):
     import pebblesdr_b200 as pb
     from oracle import ref_app
     from rds_signal import GROUPS, stream_bits, fm_broadcast, BITRATE
-    rate, frame, frames = 247000, 2048, 330                       # 247000 = 208 samples per bit; 2.7 s
+    frame = 2048                                                  # rates with a whole number of samples per half bit
+    frames = int(2.7 * rate) // frame
     n = frame * frames
     bits = stream_bits(GROUPS, int(n / rate * BITRATE) + 208).copy()
     if errors:
@@ -288,7 +289,7 @@ def test_wfm_stereo_rds_branch_vs_compiled_reference(rds_off, errors):
     r = ref_app.Demod_WFM(rate, frame)
     g = pb.Demod(rate, frame)
     g.setDemodMode(pb.Demod.dmFMS)
-    assert g.getRdsRate() == r.rdsRate() == 30875.0
+    assert g.getRdsRate() == r.rdsRate() == rate / 8.0            # SetDataRate(rate, 8000): three stages at both rates
     per = frame // 8
     want_groups, got_groups, want_tap, got_tap, want_audio, got_audio = [], [], [], [], [], []
     for i in range(0, n, frame):
@@ -310,6 +311,8 @@ def test_wfm_stereo_rds_branch_vs_compiled_reference(rds_off, errors):
     assert np.array_equal(got_tap.real != 0, want_tap.real != 0)          # the same sampling instants
     assert rel_rms(got_tap.real, want_tap.real) <= 1e-6
     assert got_groups == want_groups
+    if rate == 313500:
+        return        # at this rate the reference's own chain recovers nothing from this signal; the parity above is the test
     if rds_off <= 0.0:
         assert len(want_groups) >= 20
         sent = [GROUPS[k % 4] for k in range(40)]

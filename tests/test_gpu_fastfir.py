@@ -93,6 +93,25 @@ def test_empty_and_param_error():
     assert rel_rms(yg, yr) <= TOL
 
 
+def test_in_place_device_call_is_refused_host_call_is_not():
+    import torch
+    import pebblesdr_b200 as pb
+    from pebblesdr_b200._lib import lib
+    x = iq_noise_tones(4096, 12, 2e6, [(3e3, 0.4)], 0.05)
+    f = pb.CFastFIR()
+    f.SetupParameters(-5000.0, 5000.0, 0.0, 2e6)
+    d = torch.from_numpy(x).cuda()
+    assert lib.pebble_fastfir_process_device(f._h, 4096, d.data_ptr(), d.data_ptr(), None) < 0
+    assert b"overlap" in lib.pebble_last_error()
+    assert lib.pebble_fastfir_process_device(f._h, 4096, d.data_ptr(), d.data_ptr() + 16 * 1000, None) < 0
+    g, r = pb.CFastFIR(), pb.CFastFIR()
+    for o in (g, r):
+        o.SetupParameters(-5000.0, 5000.0, 0.0, 2e6)
+    buf, out = x.copy(), np.zeros(4096, complex)
+    assert g.ProcessData(4096, buf, buf) == r.ProcessData(4096, x, out) == 4096      # in place through the host call
+    assert np.array_equal(buf, out)
+
+
 def test_state_roundtrip():
     g, _ = _pair()
     x = iq_noise_tones(5000, 3, 2e6, [(1e3, 0.5)])
