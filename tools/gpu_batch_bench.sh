@@ -8,7 +8,8 @@ for w in fastfir spectrum decimator channelizer longfir; do
 done
 python tools/trace_chz.py 2>&1 | grep chz-trace > $O/r2_channelizer_timeline.txt
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"poly_|fastfir|chan_|ff_" -c 120 --csv --log-file $O/r2_launches_channelizer.csv python bench.py --workload channelizer --steps 2 --warmup 1 --no-cpu-baseline --no-sharded > /dev/null 2>&1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/r2_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-sharded > /dev/null 2>&1
+# the chain's own kernels only (the synthetic-input torch kernels would use up the launch budget)
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"dc_|fastfir|ff_|am_|cfir|agc|iq_|scale_" -c 200 --csv --log-file $O/r2_launches.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-sharded > /dev/null 2>&1
 python -m pytest tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -2; cp gpurun_out/dropin_latency_*.json $O/ 2>/dev/null
 python - <<'PY'
 import json, glob
